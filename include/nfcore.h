@@ -1,0 +1,103 @@
+/* libnfcore -- C ABI of the B200 (sm_100a) planar-flow free-energy hot path.
+ *
+ * The reference (benlevyx/vi-normflows) is pure Python and has no FFI of its own;
+ * these entry points are what a binding for its hot path would call.  Each one
+ * names the reference code it replaces (paths relative to the reference checkout).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every `*_f32`/`*_f64` pair differs only in the
+ *     element type.  f32 is the throughput mode, f64 the reference-precision mode.
+ *   - unless the name says `host`, pointers are DEVICE pointers owned by the caller;
+ *     the call enqueues work on `stream` (a cudaStream_t passed as void*) and returns
+ *     without synchronising.
+ *   - return value: NF_OK (0) or a negative nf_status; nf_status_string() explains it,
+ *     nf_last_cuda_error() returns the CUDA error string behind NF_ERR_CUDA.
+ *   - reductions over samples are returned as SUMS (not means) so that sample-sharded
+ *     callers need one all-reduce followed by a scale by 1/N_global.
+ *   - matrices are row-major: eps[N][D], w[K][D], s[K][D].
+ */
+#ifndef NFCORE_H_
+#define NFCORE_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    NF_OK = 0,
+    NF_ERR_INVALID = -1,      /* bad argument (null pointer, N<0, K<1, D<1, ...) */
+    NF_ERR_UNSUPPORTED = -2,  /* shape/target combination this build does not implement */
+    NF_ERR_WORKSPACE = -3,    /* workspace_bytes smaller than nf_planar_elbo_workspace_bytes() */
+    NF_ERR_CUDA = -4,         /* a CUDA runtime call failed; see nf_last_cuda_error() */
+    NF_ERR_NO_DEVICE = -5     /* no CUDA device / not an sm_100 device */
+} nf_status;
+
+/* Target densities exp(-U(z)) the free energy is taken against.  The objective
+ * always forms log(eps + target(z_K)) as get_data.py:112 does.
+ *   U1..U4, TRIAL1 : get_data.py:28-59, 20-26 (p1..p4, trial1); D must be 2; no params.
+ *   MIXDIAG        : distributions.py:60-69 prob_gm with diagonal covariances, and
+ *                    get_data.py:61-66 / experimentation.py:18-23 gmm (D=1, var=sigma^2).
+ *                    params = [pi_0..pi_{G-1} | mu (G*D) | var (G*D)], G = n/(1+2D);
+ *                    pi_{G-1} is passed explicitly (= 1 - sum of the others).
+ *   GAUSSDIAG      : exp(distributions.py:35-54 log_mvn); params = [mu (D) | log_sigma_diag (D)];
+ *                    for D == 1 the inverse variance is exp(1 - log_sigma) as at :46-47.
+ */
+typedef enum {
+    NF_TARGET_U1 = 0,
+    NF_TARGET_U2 = 1,
+    NF_TARGET_U3 = 2,
+    NF_TARGET_U4 = 3,
+    NF_TARGET_TRIAL1 = 4,
+    NF_TARGET_MIXDIAG = 5,
+    NF_TARGET_GAUSSDIAG = 6
+} nf_target;
+
+const char* nf_status_string(int status);
+const char* nf_last_cuda_error(void);
+/* Library version, and the compute capability it was built for (100 = sm_100a). */
+int nf_version(void);
+int nf_built_for_sm(void);
+/* NF_OK when the current device can run the kernels (compute capability 10.x). */
+int nf_check_device(void);
+
+/* ---------------------------------------------------------------------------
+ * Shared-parameter Monte-Carlo free energy, forward + backward in one launch.
+ * Replaces get_data.py:97-113 `variational_objective` (= experimentation.py:54-70)
+ * and the autograd tape replay `grad(variational_objective)` at get_data.py:115.
+ *
+ * Per layer k the caller supplies the direction w_k, the step vector s_k, the
+ * offset b_k and the log-det coefficient c_k; per sample the kernel evaluates
+ *     a = w_k.z + b_k ; t = tanh(a) ; ld += log(eps + |1 + (1 - t^2) c_k|) ; z += s_k t
+ * which is get_data.py:106-109 with s_k = u_hat (:106) and c_k = w_k.u_k (:107-108).
+ * Outputs (all sums over the N samples given):
+ *     out_F[0] = sum_n (log q_K - log p)      (get_data.py:113 before the mean)
+ *     out_F[1] = sum_n log q_K                (get_data.py:94, `other_metrics`)
+ *     out_F[2] = sum_n log(eps + target(z_K)) (get_data.py:95)
+ *     g_w[K][D], g_s[K][D], g_b[K], g_c[K] = d out_F[0] / d (w, s, b, c)
+ * g_* may all be NULL: then only out_F is produced (forward only; what the
+ * reference's callbacks use, get_data.py:128-138).
+ * `workspace` holds per-block partial sums; its contents on entry are ignored.
+ * ------------------------------------------------------------------------- */
+size_t nf_planar_elbo_workspace_bytes(int K, int D, int elem_size);
+
+int nf_planar_elbo_fwd_bwd_f32(const float* eps, int64_t N, int D, int K,
+                               const float* w, const float* s, const float* b, const float* c,
+                               int target_id, const float* target_params, int n_target_params,
+                               float log_eps,
+                               float* out_F, float* g_w, float* g_s, float* g_b, float* g_c,
+                               void* workspace, size_t workspace_bytes, void* stream);
+
+int nf_planar_elbo_fwd_bwd_f64(const double* eps, int64_t N, int D, int K,
+                               const double* w, const double* s, const double* b, const double* c,
+                               int target_id, const double* target_params, int n_target_params,
+                               double log_eps,
+                               double* out_F, double* g_w, double* g_s, double* g_b, double* g_c,
+                               void* workspace, size_t workspace_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NFCORE_H_ */

@@ -1,0 +1,175 @@
+"""GPU parity: libnfcore (through the C ABI) against the committed golden vectors and the
+oracle, for the shared-parameter free energy forward + backward (get_data.py:97-115).
+
+Tolerances (north_star): float32 1e-4 relative, float64 1e-10 relative.  "Relative" for a
+gradient vector means max|g - g_ref| <= tol * max|g_ref|; for F, |F - F_ref| <= tol * max(1, |F_ref|).
+The "wide" parameter sets sit next to the log|1 + h'c| singularity, where
+float32 can only hold a looser bound -- stated per case below.
+"""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN, golden_script_cases
+
+pytestmark = pytest.mark.gpu
+
+F32_TOL, F64_TOL = 1e-4, 1e-10
+F32_TOL_WIDE = 2e-3
+
+
+def _target_arg(g):
+    name, tp, D = str(g['target']), g['target_params'], int(g['D'])
+    if name in ('p1', 'p2', 'p3', 'p4', 'trial1'):
+        return name
+    if name == 'gmm1d':
+        return 'gmm'
+    if name == 'mix':
+        G = tp.size // (1 + 2 * D)
+        return ('mixdiag', tp[:G], tp[G:G + G * D].reshape(G, D), tp[G + G * D:].reshape(G, D))
+    return ('gaussdiag', tp[:D], tp[D:])
+
+
+def _relerr(a, ref):
+    return float(np.abs(np.asarray(a) - ref).max() / max(np.abs(ref).max(), 1e-300))
+
+
+@pytest.mark.parametrize('dtype', ['float64', 'float32'])
+@pytest.mark.parametrize('case', golden_script_cases())
+def test_free_energy_and_gradient_match_golden(case, dtype):
+    from nfcore.objective import SharedFlowObjective
+    g = np.load(os.path.join(GOLDEN, case + '.npz'))
+    K, D = int(g['K']), int(g['D'])
+    obj = SharedFlowObjective(_target_arg(g), K, D, log_eps=float(g['eps']), dtype=dtype)
+    F, grad = obj.value_and_grad(g['params'], g['z0'])
+    tol = F64_TOL if dtype == 'float64' else (F32_TOL_WIDE if 'wide' in case else F32_TOL)
+    F_ref = float(g['F_ref'])
+    assert abs(F - F_ref) <= tol * max(1.0, abs(F_ref)), (F, F_ref)
+    assert _relerr(grad, g['g_torch']) <= tol, _relerr(grad, g['g_torch'])
+    # forward-only launch and the other_metrics split (get_data.py:80-95)
+    assert abs(obj.value(g['params'], g['z0']) - F_ref) <= tol * max(1.0, abs(F_ref))
+    mq, mp = obj.metrics(g['params'], g['z0'])
+    assert abs(mq - float(g['mean_log_q'])) <= tol * max(1.0, abs(float(g['mean_log_q'])))
+    assert abs(mp - float(g['mean_log_p'])) <= tol * max(1.0, abs(float(g['mean_log_p'])))
+
+
+@pytest.mark.parametrize('N', [1, 31, 100, 257, 1000, 2049])
+def test_ragged_sample_counts_match_oracle(N):
+    """Tail tiles (N not a multiple of the 256-sample tile), down to a single sample."""
+    from nfcore.objective import SharedFlowObjective
+    from oracle import planar_torch as pt
+    rs = np.random.RandomState(N)
+    K, D = 8, 2
+    z0 = rs.randn(N, D)
+    params = np.concatenate([0.1 + 0.05 * rs.randn(2 * K * D), 0.1 * np.ones(K)])
+    F_ref, g_ref = pt.script_value_and_grad(params, z0, pt.p1, 1e-7, K)
+    obj = SharedFlowObjective('p1', K, D, dtype='float64')
+    F, grad = obj.value_and_grad(params, z0)
+    assert abs(F - F_ref) <= F64_TOL * max(1.0, abs(F_ref))
+    assert _relerr(grad, g_ref) <= F64_TOL
+
+
+@pytest.mark.parametrize('D', [1, 2, 3, 4])
+def test_small_dims_gauss_and_mixture(D):
+    from nfcore.objective import SharedFlowObjective
+    from oracle import planar_torch as pt
+    rs = np.random.RandomState(40 + D)
+    K, N = 6, 777
+    z0 = rs.randn(N, D)
+    params = np.concatenate([0.4 * rs.randn(2 * K * D), 0.3 * rs.randn(K)])
+    mu, ls = 0.5 * rs.randn(D), 0.4 * rs.randn(D)
+    tgt = lambda z: torch.exp(pt.log_mvn(z, mu, ls))
+    F_ref, g_ref = pt.script_value_and_grad(params, z0, tgt, 1e-7, K)
+    for dtype, tol in (('float64', F64_TOL), ('float32', F32_TOL_WIDE)):
+        obj = SharedFlowObjective(('gaussdiag', mu, ls), K, D, dtype=dtype)
+        F, grad = obj.value_and_grad(params, z0)
+        assert abs(F - F_ref) <= tol * max(1.0, abs(F_ref))
+        assert _relerr(grad, g_ref) <= tol
+    G = 3
+    pi = np.array([0.2, 0.5]); mmu = rs.randn(G, D); var = 0.5 + rs.rand(G, D)
+    sig = torch.tensor(np.array([np.diag(v) for v in var])) if D > 1 else torch.tensor(var)
+    tgt = lambda z: pt.prob_gm(z, torch.tensor(mmu), sig, torch.tensor(pi))
+    F_ref, g_ref = pt.script_value_and_grad(params, z0, tgt, 1e-7, K)
+    obj = SharedFlowObjective(('mixdiag', pi, mmu, var), K, D, dtype='float64')
+    F, grad = obj.value_and_grad(params, z0)
+    assert abs(F - F_ref) <= F64_TOL * max(1.0, abs(F_ref))
+    assert _relerr(grad, g_ref) <= F64_TOL
+
+
+def test_large_K_uses_single_sample_tiles():
+    from nfcore.objective import SharedFlowObjective
+    from oracle import planar_torch as pt
+    rs = np.random.RandomState(9)
+    K, D, N = 160, 2, 600
+    z0 = rs.randn(N, D)
+    params = np.concatenate([0.1 + 0.02 * rs.randn(2 * K * D), 0.1 * np.ones(K)])
+    F_ref, g_ref = pt.script_value_and_grad(params, z0, pt.p4, 1e-7, K)
+    obj = SharedFlowObjective('p4', K, D, dtype='float64')
+    F, grad = obj.value_and_grad(params, z0)
+    assert abs(F - F_ref) <= F64_TOL * max(1.0, abs(F_ref))
+    assert _relerr(grad, g_ref) <= 1e-9
+
+
+def test_full_size_properties():
+    """BASELINE size (K=32, D=2, N=2^20): run-to-run bitwise determinism, additivity over a
+    split of the sample set, and float32 vs float64 agreement."""
+    from nfcore import ops, semantics as sem
+    torch.manual_seed(1234)
+    K, D, N = 32, 2, 1 << 20
+    dev = torch.device('cuda:0')
+    eps64 = torch.randn(N, D, dtype=torch.float64, device=dev)
+    rs = np.random.RandomState(7)
+    W = 0.1 + 0.01 * rs.randn(K, D); U = 0.1 + 0.01 * rs.randn(K, D); B = 0.1 * np.ones(K)
+    S, c = sem.forward(W, U)
+    res = {}
+    for dt in (torch.float64, torch.float32):
+        a = [torch.as_tensor(x).to(dev, dt).contiguous() for x in (W, S, B, c)]
+        e = eps64.to(dt)
+        out1 = ops.planar_elbo(e, *a, 'p1')
+        out2 = ops.planar_elbo(e, *a, 'p1')
+        torch.cuda.synchronize()
+        for x, y in zip(out1, out2):
+            assert torch.equal(x, y), 'not bitwise reproducible'
+        h = N // 2 + 128          # uneven split
+        oa = ops.planar_elbo(e[:h].contiguous(), *a, 'p1')
+        ob = ops.planar_elbo(e[h:].contiguous(), *a, 'p1')
+        tol = 1e-11 if dt == torch.float64 else 2e-5
+        for x, ya, yb in zip(out1, oa, ob):
+            ref = x.double().cpu().numpy()
+            got = (ya.double() + yb.double()).cpu().numpy()
+            assert np.abs(got - ref).max() <= tol * max(np.abs(ref).max(), 1.0)
+        res[dt] = [x.double().cpu().numpy() for x in out1]
+    for x32, x64 in zip(res[torch.float32], res[torch.float64]):
+        assert np.abs(x32 - x64).max() <= F32_TOL * max(np.abs(x64).max(), 1.0)
+
+
+def test_abi_error_codes():
+    import nfcore
+    from nfcore import ops, _lib
+    lib = nfcore.load()
+    dev = torch.device('cuda:0')
+    K, D, N = 4, 2, 64
+    eps = torch.randn(N, D, device=dev)
+    w = torch.randn(K, D, device=dev); s = torch.randn(K, D, device=dev)
+    b = torch.randn(K, device=dev); c = torch.randn(K, device=dev)
+    # 2-D potential with D=3 -> invalid
+    with pytest.raises(nfcore.NFError):
+        ops.planar_elbo(torch.randn(N, 3, device=dev), torch.randn(K, 3, device=dev), torch.randn(K, 3, device=dev), b, c, 'p1')
+    # D beyond this build
+    with pytest.raises(nfcore.NFError):
+        ops.planar_elbo(torch.randn(N, 5, device=dev), torch.randn(K, 5, device=dev), torch.randn(K, 5, device=dev),
+                        b, c, 'gaussdiag', torch.zeros(10, device=dev))
+    # workspace too small
+    out = torch.empty(3, device=dev)
+    ws = torch.empty(16, dtype=torch.uint8, device=dev)
+    p = lambda t: ctypes.c_void_p(t.data_ptr())
+    rc = lib.nf_planar_elbo_fwd_bwd_f32(p(eps), N, D, K, p(w), p(s), p(b), p(c), 0, None, 0, ctypes.c_float(1e-7),
+                                        p(out), None, None, None, None, p(ws), 16, None)
+    assert rc == -3 and b'workspace' in lib.nf_status_string(rc)
+    # empty sample set is legal: sums are zero
+    oF, gw, gs, gb, gc = ops.planar_elbo(torch.empty(0, D, device=dev), w, s, b, c, 'p1')
+    torch.cuda.synchronize()
+    assert float(oF.abs().max()) == 0.0 and float(gw.abs().max()) == 0.0

@@ -1,0 +1,215 @@
+// Target densities for the free energy: value log(eps + target(z)) and, when BWD,
+// gz[d] = -d/dz_d log(eps + target(z))  (the seed of the reverse sweep).
+// Reference: get_data.py:15-66 (potentials), distributions.py:10-69 (mvn / prob_gm / log_mvn).
+#pragma once
+#include "nf_common.cuh"
+
+namespace nf {
+
+// number of preprocessed target parameters held in shared memory
+__host__ __device__ inline int target_smem_count(int tgt, int D, int ntp) {
+    if (tgt == NF_TARGET_MIXDIAG) return ntp;          // coef(G) | mu(G*D) | inv_var(G*D)
+    if (tgt == NF_TARGET_GAUSSDIAG) return 1 + 2 * D;  // const | mu(D) | inv_var(D)
+    return 0;
+}
+
+// One block-wide pass that turns the caller's raw target parameters into the
+// form the per-sample code wants.  Call before __syncthreads().
+template <typename T>
+__device__ inline void target_prepare(int tgt, int D, const T* __restrict__ raw, int ntp, T* tp) {
+    const double LOG2PI = 1.8378770664093453;
+    if (tgt == NF_TARGET_MIXDIAG) {
+        const int G = ntp / (1 + 2 * D);
+        for (int i = threadIdx.x; i < G * D; i += blockDim.x) {
+            tp[G + i] = raw[G + i];                                    // mu
+            tp[G + G * D + i] = (T)(1.0 / (double)raw[G + G * D + i]);  // 1/var
+        }
+        for (int g = threadIdx.x; g < G; g += blockDim.x) {
+            double logdet = 0.0;
+            for (int d = 0; d < D; ++d) logdet += ::log((double)raw[G + G * D + g * D + d]);
+            // pi_g (2 pi)^{-D/2} det^{-1/2}   -- distributions.py:29
+            tp[g] = (T)((double)raw[g] * ::exp(-0.5 * D * LOG2PI - 0.5 * logdet));
+        }
+    } else if (tgt == NF_TARGET_GAUSSDIAG) {
+        for (int d = threadIdx.x; d < D; d += blockDim.x) {
+            tp[1 + d] = raw[d];
+            // distributions.py:46-49: exp(1 - logsig) when len == 1, else inv(diag(exp(logsig)))
+            tp[1 + D + d] = (T)(D == 1 ? ::exp(1.0 - (double)raw[D + d]) : ::exp(-(double)raw[D + d]));
+        }
+        if (threadIdx.x == 0) {
+            double s = 0.0;
+            for (int d = 0; d < D; ++d) s += (double)raw[D + d];
+            tp[0] = (T)(-0.5 * D * LOG2PI - 0.5 * s);                  // distributions.py:50
+        }
+    }
+}
+
+// ring-shaped potentials p1 (get_data.py:28-35) and trial1 (:20-26)
+template <typename T, bool BWD>
+__device__ __forceinline__ void target_ring(const T* z, T R, T inv_sr, T inv_sx, T eps, T& lp, T* gz) {
+    using M = Mth<T>;
+    const T z1 = z[0], z2 = z[1];
+    const T n = M::sqrt(z1 * z1 + z2 * z2);
+    const T f = (n - R) * inv_sr;
+    const T q1 = (z1 - (T)2) * inv_sx, q2 = (z1 + (T)2) * inv_sx;
+    const T a1 = (T)-0.5 * q1 * q1, a2 = (T)-0.5 * q2 * q2;
+    // log(exp(a1) + exp(a2)) in max + log1p form (same value, no underflow to log(0))
+    const T mx = M::fmax(a1, a2);
+    const T ed = M::exp(-M::fabs(a1 - a2));
+    const T lse = mx + M::log1p(ed);
+    const T u = (T)0.5 * f * f - lse;
+    const T dens = M::exp(-u);
+    const T den = eps + dens;
+    lp = M::logp(den);
+    if (BWD) {
+        const T rho = M::div(dens, den);
+        const T wbig = M::div((T)1, (T)1 + ed);
+        const T pw1 = (a1 >= a2) ? wbig : (T)1 - wbig;       // e^{a1}/(e^{a1}+e^{a2})
+        const T dlse = -(pw1 * q1 + ((T)1 - pw1) * q2) * inv_sx;
+        const T fr = M::div(f * inv_sr, n);
+        gz[0] = rho * (fr * z1 - dlse);
+        gz[1] = rho * (fr * z2);
+    }
+}
+
+template <typename T, int D, int TGT, bool BWD>
+struct Target {
+    static __device__ __forceinline__ void eval(const T* z, const T* tp, int ntp, T eps, T& lp, T* gz);
+};
+
+template <typename T, bool BWD> struct Target<T, 2, NF_TARGET_U1, BWD> {
+    static __device__ __forceinline__ void eval(const T* z, const T*, int, T eps, T& lp, T* gz) {
+        target_ring<T, BWD>(z, (T)2, (T)2.5, (T)(1.0 / 0.6), eps, lp, gz);
+    }
+};
+template <typename T, bool BWD> struct Target<T, 2, NF_TARGET_TRIAL1, BWD> {
+    static __device__ __forceinline__ void eval(const T* z, const T*, int, T eps, T& lp, T* gz) {
+        target_ring<T, BWD>(z, (T)4, (T)2.5, (T)1.25, eps, lp, gz);
+    }
+};
+
+// p2 -- get_data.py:37-43
+template <typename T, bool BWD> struct Target<T, 2, NF_TARGET_U2, BWD> {
+    static __device__ __forceinline__ void eval(const T* z, const T*, int, T eps, T& lp, T* gz) {
+        using M = Mth<T>;
+        const T HPI = (T)1.5707963267948966;
+        const T z1 = z[0], z2 = z[1];
+        const T w1 = M::sin(HPI * z1);
+        const T q = (z2 - w1) * (T)2.5;
+        const bool inside = M::fabs(z1) <= (T)4;
+        const T dens = inside ? M::exp((T)-0.5 * q * q) : (T)0;   // exp(-1e7) == 0
+        const T den = eps + dens;
+        lp = M::logp(den);
+        if (BWD) {
+            const T rho = M::div(dens, den);
+            const T du2 = q * (T)2.5;
+            gz[0] = -rho * du2 * (M::cos(HPI * z1) * HPI);
+            gz[1] = rho * du2;
+        }
+    }
+};
+
+// p3 / p4 -- get_data.py:45-59: two ridges, second one displaced by w2 (p3) or w3 (p4)
+template <typename T, bool BWD, bool IS_P4>
+__device__ __forceinline__ void target_ridges(const T* z, T eps, T& lp, T* gz) {
+    using M = Mth<T>;
+    const T HPI = (T)1.5707963267948966;
+    const T z1 = z[0], z2 = z[1];
+    const T w1 = M::sin(HPI * z1);
+    T wb, dwb;
+    if (IS_P4) {                                  // w3 = 3 sigmoid((z1-1)/0.3)      get_data.py:18
+        const T sg = M::div((T)1, (T)1 + M::exp(-(z1 - (T)1) * (T)(1.0 / 0.3)));
+        wb = (T)3 * sg;
+        dwb = (T)3 * sg * ((T)1 - sg) * (T)(1.0 / 0.3);
+    } else {                                      // w2 = 3 exp(-.5((z1-1)/0.6)^2)   get_data.py:17
+        const T g = (z1 - (T)1) * (T)(1.0 / 0.6);
+        wb = (T)3 * M::exp((T)-0.5 * g * g);
+        dwb = -wb * g * (T)(1.0 / 0.6);
+    }
+    const T i1 = IS_P4 ? (T)2.5 : (T)(1.0 / 0.35);
+    const T i2 = (T)(1.0 / 0.35);
+    const T r1 = (z2 - w1) * i1;
+    const T r2 = (z2 - w1 + wb) * i2;
+    const T e1 = M::exp((T)-0.5 * r1 * r1);
+    const T e2 = M::exp((T)-0.5 * r2 * r2);
+    const T dens = e1 + e2;
+    const T den = eps + dens;
+    lp = M::logp(den);
+    if (BWD) {
+        const T dw1 = M::cos(HPI * z1) * HPI;
+        const T k1 = e1 * r1 * i1, k2 = e2 * r2 * i2;       // -d dens/d z2 = k1 + k2
+        const T inv = M::div((T)1, den);
+        gz[1] = (k1 + k2) * inv;
+        gz[0] = (k1 * (-dw1) + k2 * (dwb - dw1)) * inv;
+    }
+}
+template <typename T, bool BWD> struct Target<T, 2, NF_TARGET_U3, BWD> {
+    static __device__ __forceinline__ void eval(const T* z, const T*, int, T eps, T& lp, T* gz) {
+        target_ridges<T, BWD, false>(z, eps, lp, gz);
+    }
+};
+template <typename T, bool BWD> struct Target<T, 2, NF_TARGET_U4, BWD> {
+    static __device__ __forceinline__ void eval(const T* z, const T*, int, T eps, T& lp, T* gz) {
+        target_ridges<T, BWD, true>(z, eps, lp, gz);
+    }
+};
+
+// mixture of diagonal Gaussians -- distributions.py:60-69 (prob_gm) over :10-32 (mvn)
+template <typename T, int D, bool BWD> struct Target<T, D, NF_TARGET_MIXDIAG, BWD> {
+    static __device__ __forceinline__ void eval(const T* z, const T* tp, int ntp, T eps, T& lp, T* gz) {
+        using M = Mth<T>;
+        const int G = ntp / (1 + 2 * D);
+        T dens = (T)0;
+        T dd[D];
+#pragma unroll
+        for (int d = 0; d < D; ++d) dd[d] = (T)0;
+        for (int g = 0; g < G; ++g) {
+            T q = (T)0;
+            T sc[D];
+#pragma unroll
+            for (int d = 0; d < D; ++d) {
+                const T df = z[d] - tp[G + g * D + d];
+                sc[d] = df * tp[G + G * D + g * D + d];
+                q = M::fma(df, sc[d], q);
+            }
+            const T e = tp[g] * M::exp((T)-0.5 * q);
+            dens += e;
+            if (BWD) {
+#pragma unroll
+                for (int d = 0; d < D; ++d) dd[d] = M::fma(e, sc[d], dd[d]);   // -d dens/d z_d
+            }
+        }
+        const T den = eps + dens;
+        lp = M::logp(den);
+        if (BWD) {
+            const T inv = M::div((T)1, den);
+#pragma unroll
+            for (int d = 0; d < D; ++d) gz[d] = dd[d] * inv;
+        }
+    }
+};
+
+// exp(log_mvn) -- distributions.py:35-54
+template <typename T, int D, bool BWD> struct Target<T, D, NF_TARGET_GAUSSDIAG, BWD> {
+    static __device__ __forceinline__ void eval(const T* z, const T* tp, int, T eps, T& lp, T* gz) {
+        using M = Mth<T>;
+        T q = (T)0;
+        T sc[D];
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            const T df = z[d] - tp[1 + d];
+            sc[d] = df * tp[1 + D + d];
+            q = M::fma(df, sc[d], q);
+        }
+        const T dens = M::exp(tp[0] - (T)0.5 * q);
+        const T den = eps + dens;
+        lp = M::logp(den);
+        if (BWD) {
+            const T rho = M::div(dens, den);
+#pragma unroll
+            for (int d = 0; d < D; ++d) gz[d] = rho * sc[d];
+        }
+    }
+};
+
+}  // namespace nf

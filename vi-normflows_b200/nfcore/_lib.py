@@ -1,0 +1,70 @@
+"""ctypes loader for libnfcore.so -- the only way Python reaches the CUDA kernels.
+
+There is no CPU fallback: if the library is missing, or no sm_100 device is
+current when a kernel is requested, an exception is raised.
+"""
+import ctypes
+import os
+import re
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(HERE), 'lib', 'libnfcore.so')
+HEADER = os.path.join(os.path.dirname(os.path.dirname(HERE)), 'include', 'nfcore.h')
+
+
+class NFError(RuntimeError):
+    pass
+
+
+_lib = None
+
+c_void_p, c_int, c_int64, c_size_t = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_size_t
+c_float, c_double, c_char_p = ctypes.c_float, ctypes.c_double, ctypes.c_char_p
+
+
+def _elbo_args(real):
+    return [c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int,
+            real, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]
+
+
+PROTOTYPES = {
+    'nf_status_string': (c_char_p, [c_int]),
+    'nf_last_cuda_error': (c_char_p, []),
+    'nf_version': (c_int, []),
+    'nf_built_for_sm': (c_int, []),
+    'nf_check_device': (c_int, []),
+    'nf_planar_elbo_workspace_bytes': (c_size_t, [c_int, c_int, c_int]),
+    'nf_planar_elbo_fwd_bwd_f32': (c_int, _elbo_args(c_float)),
+    'nf_planar_elbo_fwd_bwd_f64': (c_int, _elbo_args(c_double)),
+}
+
+
+def declared_symbols():
+    """Every function the public header declares (used by the CPU export test)."""
+    text = open(HEADER).read()
+    text = re.sub(r'/\*.*?\*/', '', text, flags=re.S)
+    return sorted(set(re.findall(r'\b(nf_[a-z0-9_]+)\s*\(', text)))
+
+
+def load():
+    global _lib
+    if _lib is None:
+        if not os.path.isfile(LIB_PATH):
+            raise NFError('libnfcore.so not found at %s -- run `python __graft_entry__.py build` '
+                          '(there is no CPU fallback)' % LIB_PATH)
+        lib = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in PROTOTYPES.items():
+            fn = getattr(lib, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib
+
+
+def check(status):
+    if status != 0:
+        lib = load()
+        msg = lib.nf_status_string(status).decode()
+        if status == -4:
+            msg += ': ' + lib.nf_last_cuda_error().decode()
+        raise NFError('libnfcore: %s (status %d)' % (msg, status))

@@ -1,0 +1,188 @@
+"""Host-side driver of the shared-parameter free energy (the object behind
+``gradient_create`` of get_data.py:72-117).
+
+NumPy in / NumPy out, exactly like the reference's ``objective(params, t)`` and
+``gradient(params, t)``; the arithmetic over the samples happens in libnfcore on
+the GPU.  No CPU fallback: constructing the object without a CUDA device raises.
+"""
+import numpy as np
+import torch
+
+from . import ops, semantics as sem
+from ._lib import NFError
+
+_NP2T = {np.dtype('float32'): torch.float32, np.dtype('float64'): torch.float64}
+
+
+def resolve_target(target, D):
+    """Map what the reference's callers pass as ``target`` to (kernel id name, raw params).
+
+    Accepted: the names 'p1'..'p4', 'trial1', 'gmm' (get_data.py:61-66 constants),
+    'gmm_exp' (experimentation.py:18-23 constants); a callable whose __name__ is one of
+    those (the reference's own functions are recognised by name); or a tuple
+    ('mixdiag', pi[G], mu[G,D], var[G,D]) / ('gaussdiag', mu[D], log_sigma_diag[D]).
+    Arbitrary Python callables cannot be fused into the kernel and are rejected.
+    """
+    if callable(target) and not isinstance(target, (str, tuple)):
+        name = getattr(target, '__name__', None)
+        if name not in ('p1', 'p2', 'p3', 'p4', 'trial1', 'gmm'):
+            raise NFError('target callable %r is not one of the reference potentials; pass a name or a '
+                          "('mixdiag'|'gaussdiag', ...) tuple (arbitrary callables cannot be fused)" % (name,))
+        target = name
+    if isinstance(target, str):
+        if target in ('p1', 'p2', 'p3', 'p4', 'trial1', 'U1', 'U2', 'U3', 'U4'):
+            if D != 2:
+                raise NFError('%s is a 2-D potential (get_data.py:29), dim_z=%d' % (target, D))
+            return target, None
+        if target in ('gmm', 'gmm_exp'):
+            if D != 1:
+                raise NFError('gmm is the 1-D mixture of get_data.py:61-66, dim_z=%d' % D)
+            if target == 'gmm':
+                pi, mu, sg = [0.3, 0.7], [-1.0, 3.0], [1.0, 1.0]
+            else:
+                pi, mu, sg = [0.5, 0.5], [-1.0, 1.0], [0.5, 0.5]
+            return 'mixdiag', np.concatenate([pi, mu, np.square(sg)]).astype(np.float64)
+        raise NFError('unknown target %r' % target)
+    kind = target[0]
+    if kind == 'mixdiag':
+        pi, mu, var = (np.asarray(a, dtype=np.float64) for a in target[1:])
+        mu = mu.reshape(-1, D)
+        var = var.reshape(-1, D)
+        G = mu.shape[0]
+        if pi.shape[0] == G - 1:            # distributions.py:63-66: last weight is 1 - sum(pi)
+            pi = np.concatenate([pi, [1 - pi.sum()]])
+        if pi.shape[0] != G or var.shape[0] != G:
+            raise NFError('mixdiag: inconsistent component count')
+        return 'mixdiag', np.concatenate([pi, mu.ravel(), var.ravel()])
+    if kind == 'gaussdiag':
+        mu, ls = (np.asarray(a, dtype=np.float64).reshape(-1) for a in target[1:])
+        if mu.shape[0] != D or ls.shape[0] != D:
+            raise NFError('gaussdiag: mu/log_sigma_diag must have dim_z entries')
+        return 'gaussdiag', np.concatenate([mu, ls])
+    raise NFError('unknown target %r' % (target,))
+
+
+class SharedFlowObjective:
+    """Free energy of K shared-parameter planar layers and its gradient on the GPU.
+
+    value_and_grad(params, z0) returns what get_data.py:113/115 return on the same z0:
+    (mean_n(log q_K - log p), d/dparams of it), params laid out [W(K*D) | U(K*D) | B(K)].
+    """
+
+    def __init__(self, target, K, D, log_eps=1e-7, dtype='float32', semantics='script', device=None,
+                 process_group=None):
+        ops.require_cuda()
+        self.K, self.D = int(K), int(D)
+        self.log_eps = float(log_eps)
+        self.np_dtype = np.dtype(dtype)
+        self.dtype = _NP2T[self.np_dtype]
+        self.semantics = semantics
+        self.device = torch.device('cuda', torch.cuda.current_device()) if device is None else torch.device(device)
+        self.target_name, tparams = resolve_target(target, self.D)
+        self.tparams = None
+        if tparams is not None:
+            self.tparams = torch.as_tensor(tparams.astype(self.np_dtype)).to(self.device)
+        K_, D_ = self.K, self.D
+        self.n_lc = 2 * K_ * D_ + 2 * K_
+        # one device buffer for the per-layer constants, one for every result: one H2D, one D2H per call
+        self._lc_host = torch.empty(self.n_lc, dtype=self.dtype).pin_memory()
+        self._lc = torch.empty(self.n_lc, dtype=self.dtype, device=self.device)
+        self._res = torch.empty(3 + self.n_lc, dtype=self.dtype, device=self.device)
+        self._res_host = torch.empty(3 + self.n_lc, dtype=self.dtype).pin_memory()
+        self._eps_dev = None
+        self._eps_pinned = None
+        self.group = process_group
+        self.launches = 0
+
+    # -- sample staging ------------------------------------------------------------------
+    def stage_samples(self, z0):
+        """Copy host samples (N,D) into device memory (pinned staging buffer, async H2D)."""
+        if isinstance(z0, torch.Tensor) and z0.is_cuda:
+            if z0.dtype != self.dtype:
+                z0 = z0.to(self.dtype)
+            return z0.contiguous()
+        if isinstance(z0, torch.Tensor):
+            if z0.dtype == self.dtype and z0.is_pinned() and z0.is_contiguous():
+                # caller-owned pinned buffer: straight async H2D, no staging copy
+                if z0.ndim != 2 or z0.shape[1] != self.D:
+                    raise NFError('z0 must have shape (N, %d), got %r' % (self.D, tuple(z0.shape)))
+                n = z0.numel()
+                if self._eps_dev is None or self._eps_dev.numel() < n:
+                    self._eps_dev = torch.empty(max(n, 1), dtype=self.dtype, device=self.device)
+                dev = self._eps_dev[:n]
+                dev.copy_(z0.view(-1), non_blocking=True)
+                return dev.view(z0.shape[0], self.D)
+            z0 = z0.numpy()
+        z0 = np.ascontiguousarray(z0, dtype=self.np_dtype)
+        if z0.ndim != 2 or z0.shape[1] != self.D:
+            raise NFError('z0 must have shape (N, %d), got %r' % (self.D, z0.shape))
+        n = z0.shape[0] * self.D
+        if self._eps_pinned is None or self._eps_pinned.numel() < n:
+            self._eps_pinned = torch.empty(max(n, 1), dtype=self.dtype).pin_memory()
+        if self._eps_dev is None or self._eps_dev.numel() < n:
+            self._eps_dev = torch.empty(max(n, 1), dtype=self.dtype, device=self.device)
+        self._eps_pinned[:n].numpy()[:] = z0.reshape(-1)
+        dev = self._eps_dev[:n]
+        dev.copy_(self._eps_pinned[:n], non_blocking=True)
+        return dev.view(z0.shape[0], self.D)
+
+    # -- evaluation ----------------------------------------------------------------------
+    def _launch(self, params, eps_dev, backward):
+        K, D = self.K, self.D
+        W, U, B = sem.unpack(np.asarray(params, dtype=np.float64), K, D)
+        S, c = sem.forward(W, U, self.semantics)
+        host = self._lc_host.numpy()
+        host[:K * D] = W.ravel()
+        host[K * D:2 * K * D] = S.ravel()
+        host[2 * K * D:2 * K * D + K] = B
+        host[2 * K * D + K:] = c
+        self._lc.copy_(self._lc_host, non_blocking=True)
+        lc = self._lc
+        w = lc[:K * D].view(K, D)
+        s = lc[K * D:2 * K * D].view(K, D)
+        b = lc[2 * K * D:2 * K * D + K]
+        cc = lc[2 * K * D + K:]
+        r = self._res
+        out = (r[:3], r[3:3 + K * D].view(K, D), r[3 + K * D:3 + 2 * K * D].view(K, D),
+               r[3 + 2 * K * D:3 + 2 * K * D + K], r[3 + 2 * K * D + K:]) if backward else (r[:3], None, None, None, None)
+        ops.planar_elbo(eps_dev, w, s, b, cc, self.target_name, self.tparams, self.log_eps, backward, out)
+        self.launches += 2
+        return W, U
+
+    def _fetch(self, n_local):
+        """all-reduce (when sharded) + D2H of [F parts | grads]; returns float64 array and global N."""
+        n_global = n_local
+        if self.group is not None:
+            import torch.distributed as dist
+            cnt = torch.tensor([float(n_local)], dtype=torch.float64, device=self.device)
+            dist.all_reduce(self._res, group=self.group)
+            dist.all_reduce(cnt, group=self.group)
+            n_global = int(cnt.item())
+        self._res_host.copy_(self._res, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        return self._res_host.numpy().astype(np.float64), n_global
+
+    def value_and_grad(self, params, z0):
+        eps_dev = self.stage_samples(z0)
+        W, U = self._launch(params, eps_dev, True)
+        res, n = self._fetch(eps_dev.shape[0])
+        K, D = self.K, self.D
+        g_w = res[3:3 + K * D].reshape(K, D)
+        g_s = res[3 + K * D:3 + 2 * K * D].reshape(K, D)
+        g_b = res[3 + 2 * K * D:3 + 2 * K * D + K]
+        g_c = res[3 + 2 * K * D + K:]
+        dW, dU, dB = sem.backward(W, U, g_w, g_s, g_b, g_c, self.semantics)
+        return res[0] / n, sem.pack(dW, dU, dB) / n
+
+    def value(self, params, z0):
+        eps_dev = self.stage_samples(z0)
+        self._launch(params, eps_dev, False)
+        res, n = self._fetch(eps_dev.shape[0])
+        return res[0] / n
+
+    def metrics(self, params, z0):
+        """(mean log q_K, mean log p) -- get_data.py:80-95 ``other_metrics``."""
+        eps_dev = self.stage_samples(z0)
+        self._launch(params, eps_dev, False)
+        res, n = self._fetch(eps_dev.shape[0])
+        return res[1] / n, res[2] / n
