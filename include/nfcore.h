@@ -73,6 +73,7 @@ int nf_check_device(void);
  *     a = w_k.z + b_k ; t = tanh(a) ; ld += log(eps + |1 + (1 - t^2) c_k|) ; z += s_k t
  * which is get_data.py:106-109 with s_k = u_hat (:106) and c_k = w_k.u_k (:107-108).
  * Outputs (all sums over the N samples given):
+ * `log_eps` is the eps INSIDE the logs (1e-7 at get_data.py:121), not a logarithm.
  *     out_F[0] = sum_n (log q_K - log p)      (get_data.py:113 before the mean)
  *     out_F[1] = sum_n log q_K                (get_data.py:94, `other_metrics`)
  *     out_F[2] = sum_n log(eps + target(z_K)) (get_data.py:95)
@@ -96,6 +97,50 @@ int nf_planar_elbo_fwd_bwd_f64(const double* eps, int64_t N, int D, int K,
                                double log_eps,
                                double* out_F, double* g_w, double* g_s, double* g_b, double* g_c,
                                void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------
+ * flows.planar_flow (normflows/normflows/flows.py:8-34, _get_uhat :37-39, m :42-43).
+ * z, out: [N][D].  per_sample != 0: w,u are [N][D] and b is [N] (the HEAD signature,
+ * flows.py:26-27); per_sample == 0: w,u are [D], b is [1] (the call the stale drivers
+ * make, src/learning_basic_flow.py:33,97).  u_hat uses ||w||^2 (flows.py:39).
+ *   semantics 0 ("package"): out = z + (sum_d u_hat_d tanh(w.z+b)) broadcast to every
+ *                            coordinate -- what flows.py:32 computes;
+ *   semantics 1 ("paper")  : out = z + u_hat tanh(w.z+b) (Rezende & Mohamed eq. 10).
+ * D <= 256.  Also the forward-only building block of distributions.sample_from_pz
+ * (distributions.py:92-102).
+ * ------------------------------------------------------------------------- */
+int nf_planar_flow_f32(const float* z, const float* w, const float* u, const float* b, int64_t N, int D,
+                       int per_sample, int semantics, float* out, void* stream);
+int nf_planar_flow_f64(const double* z, const double* w, const double* u, const double* b, int64_t N, int D,
+                       int per_sample, int semantics, double* out, void* stream);
+
+/* ---------------------------------------------------------------------------
+ * Amortised (per-sample-parameter) K-layer flow of the flow-VAE objective,
+ * normflows/normflows/optimization.py:74-85 (reparameterisation :74-75, running
+ * log-det :64,83 with (sum w)(sum u) and raw u, planar_flow :84).
+ *   z0, mu0, log_sigma0: [N][D];  W, U: [K][N][D];  Bb: [K][N]
+ * forward :  zK[N][D], logdet[N] = sum_k log(eps + |1 + (sum u_k)(sum w_k) h'(w_k.z+b_k)|),
+ *            t_save[K][N] = tanh activations kept for the backward pass (may be NULL
+ *            when no backward pass follows).
+ * backward:  given g_zK[N][D] = dF/dzK and the scalar g_logdet = dF/dlogdet[n] (the same
+ *            for every n: -1/N for optimization.py:85,92), writes dF/d(mu0, log_sigma0,
+ *            W, U, Bb) with the shapes of the inputs.
+ * No cross-sample reduction happens here; D <= 256.
+ * ------------------------------------------------------------------------- */
+int nf_planar_amortised_fwd_f32(const float* z0, const float* mu0, const float* log_sigma0, const float* W,
+                                const float* U, const float* Bb, int64_t N, int D, int K, float log_eps,
+                                float* zK, float* logdet, float* t_save, void* stream);
+int nf_planar_amortised_fwd_f64(const double* z0, const double* mu0, const double* log_sigma0, const double* W,
+                                const double* U, const double* Bb, int64_t N, int D, int K, double log_eps,
+                                double* zK, double* logdet, double* t_save, void* stream);
+int nf_planar_amortised_bwd_f32(const float* z0, const float* log_sigma0, const float* W, const float* U,
+                                const float* zK, const float* t_save, const float* g_zK, float g_logdet,
+                                int64_t N, int D, int K, float log_eps, float* g_mu0, float* g_log_sigma0,
+                                float* g_W, float* g_U, float* g_Bb, void* stream);
+int nf_planar_amortised_bwd_f64(const double* z0, const double* log_sigma0, const double* W, const double* U,
+                                const double* zK, const double* t_save, const double* g_zK, double g_logdet,
+                                int64_t N, int D, int K, double log_eps, double* g_mu0, double* g_log_sigma0,
+                                double* g_W, double* g_U, double* g_Bb, void* stream);
 
 #ifdef __cplusplus
 }

@@ -33,6 +33,16 @@ template <> struct Mth<float> {
         return fmaf(-2.0f, rcp(1.0f + e), 1.0f);
     }
     static __device__ __forceinline__ float log(float x) { return lg2(x) * 0.6931471805599453f; }
+    // Pre-scaled form used by the layer loop: the caller folds 2*log2(e) into w and b once
+    // per layer, so tanh costs FADD + FFMA + 2 MUFU per sample.
+    static constexpr float kArgScale = 2.885390081777927f;
+    static __device__ __forceinline__ float tanh_pre(float a2) { return fmaf(-2.0f, rcp(1.0f + ex2(a2)), 1.0f); }
+    // -sign(x) * |r|  in one LOP3: (r & 0x7fffffff) | (~x & 0x80000000)
+    static __device__ __forceinline__ float neg_copysign(float r, float x) {
+        unsigned o;
+        asm("lop3.b32 %0, %1, 0x80000000, %2, 0x74;" : "=r"(o) : "r"(__float_as_uint(r)), "r"(__float_as_uint(x)));
+        return __uint_as_float(o);
+    }
     // accurate variants for the once-per-sample target code
     static __device__ __forceinline__ float exp(float x) { return expf(x); }
     static __device__ __forceinline__ float logp(float x) { return logf(x); }
@@ -51,6 +61,9 @@ template <> struct Mth<double> {
     static __device__ __forceinline__ double sqrt(double x) { return ::sqrt(x); }
     static __device__ __forceinline__ double tanh(double a) { return ::tanh(a); }
     static __device__ __forceinline__ double log(double x) { return ::log(x); }
+    static constexpr double kArgScale = 1.0;
+    static __device__ __forceinline__ double tanh_pre(double a) { return ::tanh(a); }
+    static __device__ __forceinline__ double neg_copysign(double r, double x) { return ::copysign(r, -x); }
     static __device__ __forceinline__ double exp(double x) { return ::exp(x); }
     static __device__ __forceinline__ double logp(double x) { return ::log(x); }
     static __device__ __forceinline__ double log1p(double x) { return ::log1p(x); }

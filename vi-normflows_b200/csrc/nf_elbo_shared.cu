@@ -2,49 +2,63 @@
 //
 // Replaces get_data.py:97-113 (forward) and the autograd tape replay of
 // get_data.py:115 (backward).  One launch per step:
-//   * every thread owns S samples; z stays in registers across all K layers,
-//     tanh activations t_k are parked in shared memory for the reverse sweep
-//     (z is walked back with z_{k-1} = z_k - s_k t_k, nothing is recomputed);
-//   * per layer the 2D+2 gradient partials of the thread's samples are reduced
-//     across the warp with a halving butterfly and accumulated in a per-warp
-//     shared-memory table, so cross-sample reduction costs O(1) per layer per warp;
-//   * blocks are persistent (grid = SMs x occupancy) and stride over sample tiles;
-//     each block writes one row of partial sums, a second tiny kernel adds the
-//     rows in a fixed order (bitwise reproducible for a fixed launch shape).
+//   * every thread owns S samples (S=8 for float): z, the running gradient and the
+//     log-det product stay in registers across all K layers; the only per-layer state
+//     that leaves the register file is the tanh value t_k, parked in shared memory so
+//     that the reverse sweep can walk z back (z_{k-1} = z_k - s_k t_k) without a second
+//     tanh;
+//   * the per-layer cost that does not scale with the number of samples (constant
+//     fetch, loop control, the cross-lane reduction of the 2D+2 gradient partials) is
+//     paid once per S samples per lane; the reduction is a halving butterfly whose
+//     result lands in a per-warp shared-memory table;
+//   * 2*log2(e) is folded into w and b when the block stages the layer constants, so
+//     tanh is FADD + FFMA + MUFU.EX2 + MUFU.RCP; log|det| is accumulated as a running
+//     product with one MUFU.LG2 per four layers; the forward pass of the fused kernel
+//     does not touch the log-det at all (the reverse sweep needs h' and x anyway);
+//   * blocks are persistent (grid = SMs x occupancy) and stride over sample tiles; each
+//     block writes one row of partial sums and a second small kernel adds the rows in a
+//     fixed order (bitwise reproducible for a fixed launch shape).
 #include "nf_common.cuh"
 #include "nf_targets.cuh"
 
 namespace nf {
 
-constexpr int kElboThreads = 128;
+constexpr int kElboThreads = 64;
 constexpr int kMaxBlocksPerSM = 8;
+constexpr int kLogEvery = 4;          // layers per MUFU.LG2 (product of 4 factors >= eps^4 = 1e-28: no underflow)
 
 template <int D> __host__ __device__ constexpr int grad_vals() { return 2 * D + 2; }   // w[D] s[D] b c
+__host__ __device__ constexpr int pad4(int n) { return (n + 3) & ~3; }
+// forward record per layer : w*kappa [D] | b*kappa | s [D]           (padded to a multiple of 4)
+// backward record per layer: w [D] | s [D] | c | -2c                  (padded to a multiple of 4)
+template <int D> __host__ __device__ constexpr int rec_f() { return pad4(2 * D + 1); }
+template <int D> __host__ __device__ constexpr int rec_b() { return pad4(2 * D + 2); }
 
 // dynamic shared memory carve-up (in elements of T)
 template <typename T>
 struct ElboSmem {
-    int lc, tp, acc, hist, total;
+    int lcf, lcb, tp, acc, hist, total;
     __host__ __device__ ElboSmem(int K, int D, int S, int ntp_s, bool bwd, int nthreads) {
         const int V = 2 * D + 2;
-        lc = 0;
-        tp = lc + K * V;
-        acc = tp + ntp_s;
+        lcf = 0;
+        lcb = lcf + K * pad4(2 * D + 1);
+        tp = lcb + K * pad4(2 * D + 2);
+        acc = pad4(tp + ntp_s);
         hist = acc + (bwd ? (nthreads / kWarp) * K * V : 0);
         total = hist + (bwd ? K * S * nthreads : 0);
     }
 };
 
-// A thread owns S consecutive samples = S*D consecutive elements of eps.  Full
-// tiles are fetched with the widest aligned vector load that divides S*D elements
-// (LDG.128 for float D=2 S=2: lanes are 16 B apart, perfectly coalesced); the
-// ragged tail falls back to guarded scalar loads and a 0/1 mask.
-template <typename T, int D, int S>
+// A thread owns S consecutive samples = S*D consecutive elements of eps.  Full tiles
+// are fetched with the widest aligned vector load that divides S*D elements (LDG.128;
+// for float D=2 S=8 each lane reads 64 contiguous bytes); the ragged last tile falls
+// back to guarded scalar loads.
+template <typename T, int D, int S, bool MASKED>
 __device__ __forceinline__ void load_samples(const T* __restrict__ eps, long long n0, long long N,
-                                             T (&z)[S][D], T (&msk)[S]) {
+                                             T (&z)[S][D], bool (&ok)[S]) {
     constexpr int E = S * D;
     constexpr int BYTES = E * (int)sizeof(T);
-    if (n0 + S <= N) {
+    if (!MASKED) {
         T buf[E];
         const T* src = eps + n0 * D;
         if (BYTES % 16 == 0) {
@@ -63,19 +77,136 @@ __device__ __forceinline__ void load_samples(const T* __restrict__ eps, long lon
         }
 #pragma unroll
         for (int j = 0; j < S; ++j) {
-            msk[j] = (T)1;
+            ok[j] = true;
 #pragma unroll
             for (int d = 0; d < D; ++d) z[j][d] = buf[j * D + d];
         }
     } else {
 #pragma unroll
         for (int j = 0; j < S; ++j) {
-            const bool ok = n0 + j < N;
-            msk[j] = ok ? (T)1 : (T)0;
+            ok[j] = n0 + j < N;
 #pragma unroll
-            for (int d = 0; d < D; ++d) z[j][d] = ok ? eps[(n0 + j) * D + d] : (T)0.5;
+            for (int d = 0; d < D; ++d) z[j][d] = ok[j] ? eps[(n0 + j) * D + d] : (T)0.5;
         }
     }
+}
+
+// One tile = S samples per thread through all K layers (and back).  MASKED is the
+// ragged last tile: samples past N get weight 0 (select, never multiply: a masked
+// sample must not be able to leak NaN/Inf into the sums).
+template <typename T, int D, int S, int TGT, bool BWD, bool MASKED>
+__device__ __forceinline__ void elbo_tile(const T* __restrict__ eps, long long n0, long long N, int K,
+                                          const T* __restrict__ lcf, const T* __restrict__ lcb,
+                                          const T* __restrict__ tp, int ntp, T epsv,
+                                          T* __restrict__ hist_t /* hist + tid */, T* __restrict__ acc_w,
+                                          int lane, int my_slot, bool my_own, T& sum_q, T& sum_p) {
+    using M = Mth<T>;
+    constexpr int V = grad_vals<D>();
+    constexpr int RF = rec_f<D>(), RB = rec_b<D>();
+    constexpr int NT = kElboThreads;
+    const T LOG2PI = (T)1.8378770664093453;
+
+    T z[S][D], lq[S], prod[S];
+    bool ok[S];
+    load_samples<T, D, S, MASKED>(eps, n0, N, z, ok);
+#pragma unroll
+    for (int j = 0; j < S; ++j) {
+        T zz = (T)0;
+#pragma unroll
+        for (int d = 0; d < D; ++d) zz = M::fma(z[j][d], z[j][d], zz);
+        lq[j] = (T)-0.5 * (D * LOG2PI + zz);          // get_data.py:111, first term; log-det subtracted below
+        prod[j] = (T)1;
+    }
+    // ---- forward over the K layers (get_data.py:104-109) ----
+    for (int k = 0; k < K; ++k) {
+        T rf[RF];
+#pragma unroll
+        for (int i = 0; i < RF; ++i) rf[i] = lcf[k * RF + i];
+        T ck = (T)0;
+        if (!BWD) ck = lcb[k * RB + 2 * D];
+#pragma unroll
+        for (int j = 0; j < S; ++j) {
+            T a = rf[D];
+#pragma unroll
+            for (int d = 0; d < D; ++d) a = M::fma(rf[d], z[j][d], a);
+            const T t = M::tanh_pre(a);
+#pragma unroll
+            for (int d = 0; d < D; ++d) z[j][d] = M::fma(rf[D + 1 + d], t, z[j][d]);
+            if (BWD) {
+                hist_t[(k * S + j) * NT] = t;
+            } else {
+                const T hp = M::fma(-t, t, (T)1);
+                const T x = M::fma(hp, ck, (T)1);
+                prod[j] *= epsv + M::fabs(x);
+            }
+        }
+        if (!BWD && ((k % kLogEvery) == kLogEvery - 1 || k == K - 1)) {
+#pragma unroll
+            for (int j = 0; j < S; ++j) { lq[j] -= M::log(prod[j]); prod[j] = (T)1; }
+        }
+    }
+    // ---- target: log(eps + target(z_K)) and the reverse seed gz = -d log p / dz ----
+    T gz[S][D];
+#pragma unroll
+    for (int j = 0; j < S; ++j) {
+        T lp;
+        Target<T, D, TGT, BWD>::eval(z[j], tp, ntp, epsv, lp, gz[j]);
+        if (MASKED) {
+            sum_p += ok[j] ? lp : (T)0;
+            if (BWD) {
+#pragma unroll
+                for (int d = 0; d < D; ++d) gz[j][d] = ok[j] ? gz[j][d] : (T)0;
+            }
+        } else {
+            sum_p += lp;
+        }
+    }
+    if (BWD) {
+        // ---- reverse sweep: restores z, accumulates log|det| and the gradient partials ----
+        for (int k = K - 1; k >= 0; --k) {
+            T rb[RB];
+#pragma unroll
+            for (int i = 0; i < RB; ++i) rb[i] = lcb[k * RB + i];
+            const T ck = rb[2 * D], c2 = rb[2 * D + 1];
+            T v[V];
+#pragma unroll
+            for (int i = 0; i < V; ++i) v[i] = (T)0;
+#pragma unroll
+            for (int j = 0; j < S; ++j) {
+                const T t = hist_t[(k * S + j) * NT];
+#pragma unroll
+                for (int d = 0; d < D; ++d) z[j][d] = M::fma(-rb[D + d], t, z[j][d]);   // z_{k-1}
+                const T hp = M::fma(-t, t, (T)1);
+                const T x = M::fma(hp, ck, (T)1);
+                const T y = epsv + M::fabs(x);
+                prod[j] *= y;
+                T gx = M::neg_copysign(M::rcp(y), x);          // d(-log y)/dx
+                if (MASKED) gx = ok[j] ? gx : (T)0;
+                v[2 * D + 1] = M::fma(gx, hp, v[2 * D + 1]);    // g_c
+                T gt = (gx * c2) * t;                           // via h' = 1 - t^2
+#pragma unroll
+                for (int d = 0; d < D; ++d) {
+                    v[D + d] = M::fma(gz[j][d], t, v[D + d]);   // g_s
+                    gt = M::fma(gz[j][d], rb[D + d], gt);
+                }
+                const T ga = gt * hp;
+                v[2 * D] += ga;                                 // g_b
+#pragma unroll
+                for (int d = 0; d < D; ++d) {
+                    v[d] = M::fma(ga, z[j][d], v[d]);           // g_w (direct)
+                    gz[j][d] = M::fma(ga, rb[d], gz[j][d]);
+                }
+            }
+            if ((k % kLogEvery) == 0) {
+#pragma unroll
+                for (int j = 0; j < S; ++j) { lq[j] -= M::log(prod[j]); prod[j] = (T)1; }
+            }
+            warp_reduce_multi<T, V>(v, lane);
+            if (my_own) acc_w[k * V + my_slot] += v[0];
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < S; ++j) sum_q += (MASKED && !ok[j]) ? (T)0 : lq[j];
 }
 
 template <typename T, int D, int S, int TGT, bool BWD>
@@ -87,33 +218,38 @@ elbo_shared_kernel(const T* __restrict__ eps, long long N, int K,
                    T* __restrict__ partials /* [gridDim.x][K*V + 2] */) {
     using M = Mth<T>;
     constexpr int V = grad_vals<D>();
+    constexpr int RF = rec_f<D>(), RB = rec_b<D>();
     constexpr int NT = kElboThreads;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T* sm = reinterpret_cast<T*>(smem_raw);
     const int ntp_s = target_smem_count(TGT, D, ntp);
     const ElboSmem<T> L(K, D, S, ntp_s, BWD, NT);
-    T* lc = sm + L.lc;        // [K][V] : w[D] s[D] b c
+    T* lcf = sm + L.lcf;
+    T* lcb = sm + L.lcb;
     T* tp = sm + L.tp;
     T* acc = sm + L.acc;      // [NW][K][V]
     T* hist = sm + L.hist;    // [K][S][NT]
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
-    for (int i = tid; i < K * D; i += NT) {
-        const int k = i / D, d = i - k * D;
-        lc[k * V + d] = w[i];
-        lc[k * V + D + d] = s[i];
-    }
     for (int k = tid; k < K; k += NT) {
-        lc[k * V + 2 * D] = b[k];
-        lc[k * V + 2 * D + 1] = c[k];
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            const T wv = w[k * D + d], sv = s[k * D + d];
+            lcf[k * RF + d] = wv * M::kArgScale;
+            lcf[k * RF + D + 1 + d] = sv;
+            lcb[k * RB + d] = wv;
+            lcb[k * RB + D + d] = sv;
+        }
+        lcf[k * RF + D] = b[k] * M::kArgScale;
+        lcb[k * RB + 2 * D] = c[k];
+        lcb[k * RB + 2 * D + 1] = (T)-2 * c[k];
     }
     target_prepare<T>(TGT, D, tparams, ntp, tp);
     if (BWD)
         for (int i = tid; i < (NT / kWarp) * K * V; i += NT) acc[i] = (T)0;
     __syncthreads();
 
-    const T LOG2PI = (T)1.8378770664093453;
     const int my_slot = warp_slot<V>(lane);
     const bool my_own = warp_slot_owner<V>(lane);
     T* acc_w = acc + warp * K * V;
@@ -124,89 +260,13 @@ elbo_shared_kernel(const T* __restrict__ eps, long long N, int K,
 
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const long long base = tile * tile_samples;
-        T z[S][D], msk[S], ld[S], lq0[S];
-        load_samples<T, D, S>(eps, base + (long long)tid * S, N, z, msk);
-#pragma unroll
-        for (int j = 0; j < S; ++j) {
-            T zz = (T)0;
-#pragma unroll
-            for (int d = 0; d < D; ++d) zz = M::fma(z[j][d], z[j][d], zz);
-            lq0[j] = (T)-0.5 * (D * LOG2PI + zz);          // get_data.py:111, first term
-            ld[j] = (T)0;
-        }
-        // ---- forward over the K layers (get_data.py:104-109) ----
-        for (int k = 0; k < K; ++k) {
-            T wk[D], sk[D];
-#pragma unroll
-            for (int d = 0; d < D; ++d) { wk[d] = lc[k * V + d]; sk[d] = lc[k * V + D + d]; }
-            const T bk = lc[k * V + 2 * D], ck = lc[k * V + 2 * D + 1];
-#pragma unroll
-            for (int j = 0; j < S; ++j) {
-                T a = bk;
-#pragma unroll
-                for (int d = 0; d < D; ++d) a = M::fma(wk[d], z[j][d], a);
-                const T t = M::tanh(a);
-                const T hp = M::fma(-t, t, (T)1);
-                const T x = M::fma(hp, ck, (T)1);
-                ld[j] += M::log(epsv + M::fabs(x));
-#pragma unroll
-                for (int d = 0; d < D; ++d) z[j][d] = M::fma(sk[d], t, z[j][d]);
-                if (BWD) hist[(k * S + j) * NT + tid] = t;
-            }
-        }
-        // ---- target: log(eps + target(z_K)) and the reverse seed ----
-        T gz[S][D];
-#pragma unroll
-        for (int j = 0; j < S; ++j) {
-            T lp;
-            Target<T, D, TGT, BWD>::eval(z[j], tp, ntp, epsv, lp, gz[j]);
-            // select, not multiply: a masked tail sample must not leak NaN/Inf
-            const bool ok = msk[j] != (T)0;
-            sum_q += ok ? (lq0[j] - ld[j]) : (T)0;
-            sum_p += ok ? lp : (T)0;
-            if (BWD) {
-#pragma unroll
-                for (int d = 0; d < D; ++d) gz[j][d] = ok ? gz[j][d] : (T)0;
-            }
-        }
-        if (BWD) {
-            // ---- reverse sweep ----
-            for (int k = K - 1; k >= 0; --k) {
-                T wk[D], sk[D];
-#pragma unroll
-                for (int d = 0; d < D; ++d) { wk[d] = lc[k * V + d]; sk[d] = lc[k * V + D + d]; }
-                const T ck = lc[k * V + 2 * D + 1];
-                T v[V];
-#pragma unroll
-                for (int i = 0; i < V; ++i) v[i] = (T)0;
-#pragma unroll
-                for (int j = 0; j < S; ++j) {
-                    const T t = hist[(k * S + j) * NT + tid];
-#pragma unroll
-                    for (int d = 0; d < D; ++d) z[j][d] = M::fma(-sk[d], t, z[j][d]);   // z_{k-1}
-                    const T hp = M::fma(-t, t, (T)1);
-                    const T x = M::fma(hp, ck, (T)1);
-                    const T r = M::copysign(M::rcp(epsv + M::fabs(x)), x);
-                    const T gx = -r * msk[j];                    // d(-ld)/dx
-                    v[2 * D + 1] = M::fma(gx, hp, v[2 * D + 1]);  // g_c
-                    T gt = (T)-2 * t * (gx * ck);
-#pragma unroll
-                    for (int d = 0; d < D; ++d) {
-                        v[D + d] = M::fma(gz[j][d], t, v[D + d]);  // g_s
-                        gt = M::fma(gz[j][d], sk[d], gt);
-                    }
-                    const T ga = gt * hp;
-                    v[2 * D] += ga;                                // g_b
-#pragma unroll
-                    for (int d = 0; d < D; ++d) {
-                        v[d] = M::fma(ga, z[j][d], v[d]);          // g_w (direct)
-                        gz[j][d] = M::fma(ga, wk[d], gz[j][d]);
-                    }
-                }
-                warp_reduce_multi<T, V>(v, lane);
-                if (my_own) acc_w[k * V + my_slot] += v[0];
-            }
-        }
+        const long long n0 = base + (long long)tid * S;
+        if (base + tile_samples <= N)
+            elbo_tile<T, D, S, TGT, BWD, false>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist + tid, acc_w, lane,
+                                                my_slot, my_own, sum_q, sum_p);
+        else
+            elbo_tile<T, D, S, TGT, BWD, true>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist + tid, acc_w, lane,
+                                               my_slot, my_own, sum_q, sum_p);
     }
 
     // ---- block partials ----
@@ -318,18 +378,27 @@ static int launch_elbo(const T* eps, long long N, int K, const T* w, const T* s,
     return NF_OK;
 }
 
+template <typename T> struct SamplesPerThread { static constexpr int big = 8, small = 2; };
+template <> struct SamplesPerThread<double> { static constexpr int big = 4, small = 1; };
+
 template <typename T, int D, int TGT>
 static int dispatch_bwd(bool bwd, const T* eps, long long N, int K, const T* w, const T* s, const T* b, const T* c,
                         const T* tp, int ntp, T epsv, T* partials, int max_blocks, int* nb, cudaStream_t st) {
-    constexpr int S = 2;
-    // large K: the activation history of two samples per thread no longer fits next to a second block
+    // samples per thread: as many as keep >= 3 blocks of activation history resident per SM;
+    // few samples (latency-bound launches) or very deep chains fall back to the small tile
+    constexpr int SB = (D <= 2) ? SamplesPerThread<T>::big : SamplesPerThread<T>::big / 2;
+    constexpr int SS = SamplesPerThread<T>::small;
+    const ElboSmem<T> Lb(K, D, SB, target_smem_count(TGT, D, ntp), bwd, kElboThreads);
+    const bool big_fits = (size_t)Lb.total * sizeof(T) <= 75 * 1024;
+    const bool enough = N >= (long long)148 * kElboThreads * SB;
     if (bwd) {
-        const ElboSmem<T> L2(K, D, S, target_smem_count(TGT, D, ntp), true, kElboThreads);
-        if ((size_t)L2.total * sizeof(T) <= 113 * 1024)
-            return launch_elbo<T, D, S, TGT, true>(eps, N, K, w, s, b, c, tp, ntp, epsv, partials, max_blocks, nb, st);
-        return launch_elbo<T, D, 1, TGT, true>(eps, N, K, w, s, b, c, tp, ntp, epsv, partials, max_blocks, nb, st);
+        if (big_fits && enough)
+            return launch_elbo<T, D, SB, TGT, true>(eps, N, K, w, s, b, c, tp, ntp, epsv, partials, max_blocks, nb, st);
+        return launch_elbo<T, D, SS, TGT, true>(eps, N, K, w, s, b, c, tp, ntp, epsv, partials, max_blocks, nb, st);
     }
-    return launch_elbo<T, D, S, TGT, false>(eps, N, K, w, s, b, c, tp, ntp, epsv, partials, max_blocks, nb, st);
+    if (enough)
+        return launch_elbo<T, D, SB, TGT, false>(eps, N, K, w, s, b, c, tp, ntp, epsv, partials, max_blocks, nb, st);
+    return launch_elbo<T, D, SS, TGT, false>(eps, N, K, w, s, b, c, tp, ntp, epsv, partials, max_blocks, nb, st);
 }
 
 template <typename T, int D>

@@ -85,3 +85,70 @@ def planar_elbo(eps, w, s, b, c, target, target_params=None, log_eps=1e-7, backw
                 _ptr(ws), ws.numel(), ctypes.c_void_p(stream))
     _lib.check(rc)
     return out_F, g_w, g_s, g_b, g_c
+
+
+def _same(dtype, dev, *ts):
+    for t in ts:
+        if t is not None and (t.dtype != dtype or not t.is_contiguous() or t.device != dev):
+            raise NFError('all tensors must be contiguous, of one dtype and on one device')
+
+
+def planar_flow(z, w, u, b, per_sample=True, semantics='package', out=None):
+    """nf_planar_flow_*: one planar step on CUDA tensors (flows.py:8-34)."""
+    lib = _lib.load()
+    if not z.is_cuda:
+        raise NFError('planar_flow needs CUDA tensors (no CPU fallback)')
+    dtype, dev = z.dtype, z.device
+    _same(dtype, dev, z, w, u, b)
+    N, D = z.shape
+    if out is None:
+        out = torch.empty_like(z)
+    fn = getattr(lib, 'nf_planar_flow_' + _DT[dtype][0])
+    with torch.cuda.device(dev):
+        st = torch.cuda.current_stream(dev).cuda_stream
+        rc = fn(_ptr(z), _ptr(w), _ptr(u), _ptr(b), N, D, 1 if per_sample else 0,
+                {'package': 0, 'paper': 1}[semantics], _ptr(out), ctypes.c_void_p(st))
+    _lib.check(rc)
+    return out
+
+
+def amortised_forward(z0, mu0, ls0, W, U, Bb, log_eps=1e-7, save=True):
+    """nf_planar_amortised_fwd_*: (zK [N,D], logdet [N], t_save [K,N] or None)."""
+    lib = _lib.load()
+    dtype, dev = z0.dtype, z0.device
+    if not z0.is_cuda:
+        raise NFError('amortised_forward needs CUDA tensors (no CPU fallback)')
+    _same(dtype, dev, z0, mu0, ls0, W, U, Bb)
+    N, D = z0.shape
+    K = W.shape[0]
+    zK = torch.empty_like(z0)
+    logdet = torch.empty(N, dtype=dtype, device=dev)
+    tsave = torch.empty(K, N, dtype=dtype, device=dev) if save else None
+    fn = getattr(lib, 'nf_planar_amortised_fwd_' + _DT[dtype][0])
+    with torch.cuda.device(dev):
+        st = torch.cuda.current_stream(dev).cuda_stream
+        rc = fn(_ptr(z0), _ptr(mu0), _ptr(ls0), _ptr(W), _ptr(U), _ptr(Bb), N, D, K, _DT[dtype][2](log_eps),
+                _ptr(zK), _ptr(logdet), _ptr(tsave), ctypes.c_void_p(st))
+    _lib.check(rc)
+    return zK, logdet, tsave
+
+
+def amortised_backward(z0, ls0, W, U, zK, tsave, g_zK, g_logdet, log_eps=1e-7):
+    """nf_planar_amortised_bwd_*: gradients wrt (mu0, ls0, W, U, Bb)."""
+    lib = _lib.load()
+    dtype, dev = z0.dtype, z0.device
+    _same(dtype, dev, z0, ls0, W, U, zK, tsave, g_zK)
+    N, D = z0.shape
+    K = W.shape[0]
+    g_mu0, g_ls0 = torch.empty_like(z0), torch.empty_like(z0)
+    g_W, g_U = torch.empty_like(W), torch.empty_like(U)
+    g_B = torch.empty(K, N, dtype=dtype, device=dev)
+    creal = _DT[dtype][2]
+    fn = getattr(lib, 'nf_planar_amortised_bwd_' + _DT[dtype][0])
+    with torch.cuda.device(dev):
+        st = torch.cuda.current_stream(dev).cuda_stream
+        rc = fn(_ptr(z0), _ptr(ls0), _ptr(W), _ptr(U), _ptr(zK), _ptr(tsave), _ptr(g_zK), creal(g_logdet),
+                N, D, K, creal(log_eps), _ptr(g_mu0), _ptr(g_ls0), _ptr(g_W), _ptr(g_U), _ptr(g_B),
+                ctypes.c_void_p(st))
+    _lib.check(rc)
+    return g_mu0, g_ls0, g_W, g_U, g_B

@@ -1,0 +1,78 @@
+"""normflows/normflows/distributions.py: densities and sampling.
+
+The density helpers are the reference's host-side NumPy utilities (they act on small
+arrays the drivers hold on the host; inside the objectives the same math runs fused in
+the CUDA kernels -- nf_targets.cuh, nf_flow_rows.cu).  ``sample_from_pz`` pushes the
+samples through the K planar layers on the GPU.
+"""
+import numpy as np
+
+from .transformations import sigmoid
+from .flows import planar_flow
+
+
+def mvn(Z, mu, sigma_diag):                           # distributions.py:10-32
+    N, D = Z.shape
+    mu = mu.reshape(-1, D)
+    if len(sigma_diag) == 1:
+        siginv = 1 / sigma_diag
+        det_sigma = sigma_diag
+    else:                                             # a full matrix, as the reference treats it (:23-25)
+        siginv = np.linalg.inv(sigma_diag)
+        det_sigma = np.linalg.det(sigma_diag)
+    zdiff = Z - mu
+    const = (2 * np.pi) ** (-D / 2) * det_sigma ** (-1 / 2)
+    prod = np.dot(zdiff, siginv).reshape(N, D)
+    return const * np.exp(-0.5 * np.sum(prod * zdiff, axis=1)).reshape(N, 1)
+
+
+def log_mvn(Z, mu, log_sigma_diag):                   # distributions.py:35-54
+    N, D = Z.shape
+    mu = mu.reshape(-1, D)
+    logdet_sigma = np.sum(log_sigma_diag)
+    if len(log_sigma_diag) == 1:
+        siginv = np.exp(1 - log_sigma_diag)           # kept as in the reference (:46-47)
+    else:
+        siginv = np.linalg.inv(np.diag(np.exp(log_sigma_diag)))
+    const = -D / 2 * np.log(2 * np.pi) - 0.5 * logdet_sigma
+    zdiff = Z - mu
+    return const - 0.5 * np.sum(np.matmul(zdiff, siginv) * zdiff, axis=1)
+
+
+log_std_norm = lambda x: -x.shape[1] / 2 * np.log(2 * np.pi) - 0.5 * np.sum(x * x, axis=1)   # :57  # noqa: E731
+
+
+def prob_gm(Z, mu, sigma_diag, pi):                   # distributions.py:60-69
+    G = pi.shape[0] + 1
+    prob = 0
+    for g in range(G):
+        pi_g = 1 - np.sum(pi) if g == G - 1 else pi[g]
+        prob = prob + mvn(Z, mu[g], sigma_diag[g]) * pi_g
+    return prob
+
+
+def log_prob_gm(Z, mu, log_sigma_diag, logit_pi):     # distributions.py:72-83
+    pi = sigmoid(logit_pi)
+    assert mu.shape[0] == pi.shape[0] + 1, 'Number of means does not match number of components'
+    assert Z.shape[1] == mu.shape[1], 'Dimensions of random variable and mean vector not aligned'
+    return np.log(prob_gm(Z, mu, np.exp(log_sigma_diag), pi))
+
+
+def log_bern_mult(X, p):                              # distributions.py:86-89
+    eps = 1e-7
+    return np.sum(X * np.log(eps + p) + (1 - X) * np.log(eps + 1 - p))
+
+
+def sample_from_pz(mu, log_sigma_diag, W, U, b, K):   # distributions.py:92-102
+    eps = 1e-7
+    N, D = mu.shape
+    sd = np.sqrt(eps + np.exp(log_sigma_diag))
+    zk = np.random.randn(N, D)                        # global NumPy RNG, as the reference (:97)
+    zk = zk * sd + mu
+    for k in range(K):
+        zk = planar_flow(zk, W[k], U[k], b[k])        # GPU
+    return zk
+
+
+def make_samples_z(mu, log_sigma_diag, W, U, b, K):   # distributions.py:105-118
+    return sample_from_pz(mu, log_sigma_diag, W, U, b, K)
