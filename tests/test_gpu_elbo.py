@@ -158,10 +158,10 @@ def test_abi_error_codes():
     # 2-D potential with D=3 -> invalid
     with pytest.raises(nfcore.NFError):
         ops.planar_elbo(torch.randn(N, 3, device=dev), torch.randn(K, 3, device=dev), torch.randn(K, 3, device=dev), b, c, 'p1')
-    # D beyond this build
+    # D beyond this build (the wide kernel stops at 512)
     with pytest.raises(nfcore.NFError):
-        ops.planar_elbo(torch.randn(N, 5, device=dev), torch.randn(K, 5, device=dev), torch.randn(K, 5, device=dev),
-                        b, c, 'gaussdiag', torch.zeros(10, device=dev))
+        ops.planar_elbo(torch.randn(N, 600, device=dev), torch.randn(K, 600, device=dev), torch.randn(K, 600, device=dev),
+                        b, c, 'gaussdiag', torch.zeros(1200, device=dev))
     # workspace too small
     out = torch.empty(3, device=dev)
     ws = torch.empty(16, dtype=torch.uint8, device=dev)

@@ -1,0 +1,104 @@
+"""GPU parity for the per-sample-parameter flow kernels (flows.py:8-43, optimization.py:74-85)
+and for the wide-D free energy kernel, against golden vectors produced by the reference and
+against the oracle.  float64 1e-10, float32 1e-4 (relative to the largest reference entry)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN
+
+pytestmark = pytest.mark.gpu
+DEV = 'cuda:0'
+
+
+def _rel(a, ref):
+    return float(np.abs(np.asarray(a) - ref).max() / max(np.abs(ref).max(), 1e-300))
+
+
+@pytest.mark.parametrize('D', [1, 2, 40])
+@pytest.mark.parametrize('dtype,tol', [(np.float64, 1e-10), (np.float32, 1e-4)])
+def test_planar_flow_matches_reference(D, dtype, tol):
+    from normflows import flows
+    g = np.load(os.path.join(GOLDEN, f'planar_flow_D{D}.npz'))
+    out = flows.planar_flow(g['z'].astype(dtype), g['w'].astype(dtype), g['u'].astype(dtype), g['b'].astype(dtype))
+    assert out.shape == g['out'].shape and out.dtype == dtype
+    assert _rel(out, g['out']) <= tol
+
+
+def test_planar_flow_shared_params_and_errors():
+    import nfcore
+    from normflows import flows
+    from oracle import planar_np as pn
+    rs = np.random.RandomState(3)
+    z = rs.randn(300, 2)
+    w, u, b = np.array([-5., 1.]), np.array([-2., 1.]), 0.0      # src/learning_basic_flow.py:19-21
+    out = flows.planar_flow(z, w, u, b)
+    assert _rel(out, pn.planar_flow_shared(z, w, u, b)) <= 1e-10
+    out2 = flows.planar_flow(z, w.reshape(1, 2), u.reshape(1, 2), np.array([0.0]))
+    np.testing.assert_array_equal(out, out2)
+    # paper semantics differs from the package's sum-and-broadcast for D > 1
+    outp = flows.planar_flow(z, w, u, b, semantics='paper')
+    uhat = pn.get_uhat(u.reshape(1, 2), w.reshape(1, 2))[0]
+    ref = z + np.tanh(z @ w + b)[:, None] * uhat[None, :]
+    assert _rel(outp, ref) <= 1e-10
+    with pytest.raises(AssertionError):
+        flows.planar_flow(z, rs.randn(300, 3), rs.randn(300, 3), rs.randn(300))
+    with pytest.raises(nfcore.NFError):
+        flows.planar_flow(z, w, u, b, h=np.sin)
+    # torch tensors stay on the device
+    zt = torch.as_tensor(z, device=DEV)
+    assert flows.planar_flow(zt, torch.as_tensor(w, device=DEV), torch.as_tensor(u, device=DEV), 0.0).is_cuda
+
+
+@pytest.mark.parametrize('name', ['amortised_K4_D8', 'amortised_K16_D40', 'amortised_K3_D1', 'amortised_K8_D2'])
+@pytest.mark.parametrize('dtype,tol', [(torch.float64, 1e-10), (torch.float32, 2e-4)])
+def test_amortised_flow_forward_backward(name, dtype, tol):
+    from nfcore import ops
+    g = np.load(os.path.join(GOLDEN, name + '.npz'))
+    t = lambda k: torch.as_tensor(g[k]).to(DEV, dtype).contiguous()
+    z0, mu0, ls0, W, U, B = (t(k) for k in ('z0', 'mu0', 'ls0', 'W', 'U', 'B'))
+    zK, logdet, tsave = ops.amortised_forward(z0, mu0, ls0, W, U, B)
+    assert _rel(zK.cpu().numpy(), g['zK_ref']) <= tol
+    assert _rel(logdet.cpu().numpy(), g['running_sum']) <= tol
+    N, D = z0.shape
+    # F = first - beta * mean(log N(zK; 0, I)) - mean(logdet)  (oracle/make_golden.py gen_amortised)
+    beta = float(g['beta_t'])
+    F = np.mean(-D / 2 * np.log(2 * np.pi) - 0.5 * np.sum(g['z0'] ** 2, axis=0)) \
+        - beta * float(torch.mean(-D / 2 * np.log(2 * np.pi) - 0.5 * (zK.double() ** 2).sum(1))) \
+        - float(logdet.double().mean())
+    assert abs(F - float(g['F_ref'])) <= tol * abs(float(g['F_ref']))
+    g_zK = (beta / N) * zK
+    grads = ops.amortised_backward(z0, ls0, W, U, zK, tsave, g_zK.contiguous(), -1.0 / N)
+    for got, key in zip(grads, ('g_mu0', 'g_ls0', 'g_W', 'g_U', 'g_B')):
+        assert _rel(got.cpu().numpy(), g[key]) <= tol, key
+
+
+@pytest.mark.parametrize('D,K,N', [(5, 6, 300), (16, 8, 513), (33, 5, 200), (64, 7, 130), (100, 4, 77), (256, 6, 40)])
+def test_wide_free_energy_matches_oracle(D, K, N):
+    from nfcore.objective import SharedFlowObjective
+    from oracle import planar_torch as pt
+    rs = np.random.RandomState(D)
+    z0 = rs.randn(N, D)
+    sc = 1.0 / np.sqrt(D / 2)
+    params = np.concatenate([sc * 0.5 * rs.randn(2 * K * D), 0.3 * rs.randn(K)])
+    mu, ls = 0.2 * rs.randn(D), 0.3 * rs.randn(D) - 4.0 / D      # keeps exp(log_mvn) away from total underflow for small D
+    tgt = lambda z: torch.exp(pt.log_mvn(z, mu, ls))
+    F_ref, g_ref = pt.script_value_and_grad(params, z0, tgt, 1e-7, K)
+    for dtype, tol in (('float64', 1e-10), ('float32', 2e-4)):
+        obj = SharedFlowObjective(('gaussdiag', mu, ls), K, D, dtype=dtype)
+        F, grad = obj.value_and_grad(params, z0)
+        assert abs(F - F_ref) <= tol * max(1.0, abs(F_ref)), (dtype, F, F_ref)
+        assert _rel(grad, g_ref) <= tol, (dtype, _rel(grad, g_ref))
+        assert abs(obj.value(params, z0) - F_ref) <= tol * max(1.0, abs(F_ref))
+    if D <= 33:
+        G = 2
+        pi = np.array([0.4]); mmu = 0.3 * rs.randn(G, D); var = 0.8 + 0.4 * rs.rand(G, D)
+        sig = torch.tensor(np.array([np.diag(v) for v in var]))
+        tgt = lambda z: pt.prob_gm(z, torch.tensor(mmu), sig, torch.tensor(pi))
+        F_ref, g_ref = pt.script_value_and_grad(params, z0, tgt, 1e-7, K)
+        obj = SharedFlowObjective(('mixdiag', pi, mmu, var), K, D, dtype='float64')
+        F, grad = obj.value_and_grad(params, z0)
+        assert abs(F - F_ref) <= 1e-10 * max(1.0, abs(F_ref))
+        assert _rel(grad, g_ref) <= 1e-9

@@ -18,13 +18,15 @@
 //   * blocks are persistent (grid = SMs x occupancy) and stride over sample tiles; each
 //     block writes one row of partial sums and a second small kernel adds the rows in a
 //     fixed order (bitwise reproducible for a fixed launch shape).
+#include <cstdlib>
 #include "nf_common.cuh"
 #include "nf_targets.cuh"
+#include "nf_elbo_wide.cuh"
 
 namespace nf {
 
 constexpr int kElboThreads = 64;
-constexpr int kMaxBlocksPerSM = 8;
+constexpr int kMaxBlocksPerSM = 16;
 constexpr int kLogEvery = 4;          // layers per MUFU.LG2 (product of 4 factors >= eps^4 = 1e-28: no underflow)
 
 template <int D> __host__ __device__ constexpr int grad_vals() { return 2 * D + 2; }   // w[D] s[D] b c
@@ -163,6 +165,12 @@ __device__ __forceinline__ void elbo_tile(const T* __restrict__ eps, long long n
     }
     if (BWD) {
         // ---- reverse sweep: restores z, accumulates log|det| and the gradient partials ----
+        // The cross-lane reduction of layer k+1's partials (a chain of five dependent
+        // shuffles) is issued inside iteration k, next to arithmetic it does not depend on,
+        // so an in-order warp can overlap the shuffle latency with the layer math.
+        T vp[V];
+#pragma unroll
+        for (int i = 0; i < V; ++i) vp[i] = (T)0;
         for (int k = K - 1; k >= 0; --k) {
             T rb[RB];
 #pragma unroll
@@ -201,9 +209,15 @@ __device__ __forceinline__ void elbo_tile(const T* __restrict__ eps, long long n
 #pragma unroll
                 for (int j = 0; j < S; ++j) { lq[j] -= M::log(prod[j]); prod[j] = (T)1; }
             }
-            warp_reduce_multi<T, V>(v, lane);
-            if (my_own) acc_w[k * V + my_slot] += v[0];
+            if (k < K - 1) {
+                warp_reduce_multi<T, V>(vp, lane);
+                if (my_own) acc_w[(k + 1) * V + my_slot] += vp[0];
+            }
+#pragma unroll
+            for (int i = 0; i < V; ++i) vp[i] = v[i];
         }
+        warp_reduce_multi<T, V>(vp, lane);
+        if (my_own) acc_w[my_slot] += vp[0];
     }
 #pragma unroll
     for (int j = 0; j < S; ++j) sum_q += (MASKED && !ok[j]) ? (T)0 : lq[j];
@@ -294,40 +308,45 @@ elbo_shared_kernel(const T* __restrict__ eps, long long N, int K,
     }
 }
 
-// Adds the per-block rows in a fixed order: one warp per output value, lanes
-// stride over blocks, then a shuffle tree.  Scatters into the caller's arrays.
+// Adds the per-block (or per-warp) rows in a fixed order: one warp per output value, lanes
+// stride over rows, then a shuffle tree.  Scatters into the caller's arrays.  A row is
+// [K][Vk] gradient partials followed by (sum log q_K, sum log p); inside a layer record
+// g_w starts at 0, g_s at off_s, (g_b, g_c) at off_b.
 template <typename T>
-__global__ void elbo_finalize_kernel(const T* __restrict__ partials, int nblocks, int K, int D, int bwd,
-                                     T* __restrict__ out_F, T* __restrict__ g_w, T* __restrict__ g_s,
-                                     T* __restrict__ g_b, T* __restrict__ g_c) {
-    const int V = 2 * D + 2;
-    const int row = K * V + 2;
+__global__ void elbo_finalize_kernel(const T* __restrict__ partials, int nrows, int K, int D, int Vk, int off_s,
+                                     int off_b, int bwd, T* __restrict__ out_F, T* __restrict__ g_w,
+                                     T* __restrict__ g_s, T* __restrict__ g_b, T* __restrict__ g_c) {
+    const size_t row = (size_t)K * Vk + 2;
     const int lane = threadIdx.x & 31;
     const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int nw = (gridDim.x * blockDim.x) >> 5;
-    for (int i = gw; i < row; i += nw) {
-        if (!bwd && i < K * V) continue;
+    for (size_t i = gw; i < row; i += nw) {
+        const bool tail = i >= (size_t)K * Vk;
+        int k = 0, j = 0;
+        if (!tail) {
+            if (!bwd) continue;
+            k = (int)(i / Vk);
+            j = (int)(i - (size_t)k * Vk);
+            const bool used = j < D || (j >= off_s && j < off_s + D) || j == off_b || j == off_b + 1;
+            if (!used) continue;
+        }
         T a = (T)0;
-        for (int bl = lane; bl < nblocks; bl += 32) a += partials[(size_t)bl * row + i];
+        for (int r = lane; r < nrows; r += 32) a += partials[(size_t)r * row + i];
         a = warp_sum(a);
         if (lane == 0) {
-            if (i >= K * V) {
-                out_F[1 + (i - K * V)] = a;
-            } else {
-                const int k = i / V, j = i - k * V;
-                if (j < D) g_w[k * D + j] = a;
-                else if (j < 2 * D) g_s[k * D + (j - D)] = a;
-                else if (j == 2 * D) g_b[k] = a;
-                else g_c[k] = a;
-            }
+            if (tail) out_F[1 + (int)(i - (size_t)K * Vk)] = a;
+            else if (j < D) g_w[k * D + j] = a;
+            else if (j < off_s + D && j >= off_s) g_s[k * D + (j - off_s)] = a;
+            else if (j == off_b) g_b[k] = a;
+            else g_c[k] = a;
         }
     }
     // F = sum log q_K - sum log p : recomputed by one warp from the same rows (same order => same bits)
     if (gw == 0) {
         T q = (T)0, p = (T)0;
-        for (int bl = lane; bl < nblocks; bl += 32) {
-            q += partials[(size_t)bl * row + K * V];
-            p += partials[(size_t)bl * row + K * V + 1];
+        for (int r = lane; r < nrows; r += 32) {
+            q += partials[(size_t)r * row + (size_t)K * Vk];
+            p += partials[(size_t)r * row + (size_t)K * Vk + 1];
         }
         q = warp_sum(q);
         p = warp_sum(p);
@@ -391,6 +410,13 @@ static int dispatch_bwd(bool bwd, const T* eps, long long N, int K, const T* w, 
     const ElboSmem<T> Lb(K, D, SB, target_smem_count(TGT, D, ntp), bwd, kElboThreads);
     const bool big_fits = (size_t)Lb.total * sizeof(T) <= 75 * 1024;
     const bool enough = N >= (long long)148 * kElboThreads * SB;
+    if (const char* ov = getenv("NF_ELBO_S")) {      // tuning knob: force samples per thread (float builds 2,4,8)
+        const int sv = atoi(ov);
+        if (bwd && sv == 4 && sizeof(T) == 4)
+            return launch_elbo<T, D, (sizeof(T) == 4 ? 4 : SS), TGT, true>(eps, N, K, w, s, b, c, tp, ntp, epsv, partials, max_blocks, nb, st);
+        if (bwd && sv == SS)
+            return launch_elbo<T, D, SS, TGT, true>(eps, N, K, w, s, b, c, tp, ntp, epsv, partials, max_blocks, nb, st);
+    }
     if (bwd) {
         if (big_fits && enough)
             return launch_elbo<T, D, SB, TGT, true>(eps, N, K, w, s, b, c, tp, ntp, epsv, partials, max_blocks, nb, st);
@@ -425,6 +451,44 @@ static int dispatch_target(int tgt, bool bwd, const T* eps, long long N, int K, 
     return NF_ERR_UNSUPPORTED;
 }
 
+constexpr int kWideBlocksPerSM = 2;
+
+template <typename T, int C, int L, int TGT, bool BWD>
+static int launch_wide(const T* eps, long long N, int D, int K, const T* w, const T* s, const T* b, const T* c,
+                       const T* tparams, int ntp, T epsv, T* partials, int* nrows_out, cudaStream_t stream) {
+    constexpr int S = 2;
+    auto kern = elbo_wide_kernel<T, C, L, S, TGT, BWD>;
+    const size_t smem = BWD ? (size_t)K * S * kWideWarps * (32 / L) * sizeof(T) : 0;
+    if (smem > 200 * 1024) return NF_ERR_UNSUPPORTED;
+    NF_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const DevInfo di = dev_info();
+    const long long tile = (long long)kWideWarps * S * (32 / L);
+    long long grid = (long long)di.sms * kWideBlocksPerSM;
+    const long long ntiles = (N + tile - 1) / tile;
+    if (grid > ntiles) grid = ntiles;
+    if (grid < 1) grid = 1;
+    kern<<<(int)grid, kWideThreads, smem, stream>>>(eps, N, D, K, w, s, b, c, tparams, ntp, epsv, partials);
+    NF_CUDA_OK(cudaGetLastError());
+    *nrows_out = (int)grid * kWideWarps;
+    return NF_OK;
+}
+
+template <typename T, int TGT>
+static int dispatch_wide(bool bwd, const T* eps, long long N, int D, int K, const T* w, const T* s, const T* b,
+                         const T* c, const T* tp, int ntp, T epsv, T* partials, int* nrows, cudaStream_t st) {
+#define NF_WIDE(C, L)                                                                                          \
+    return bwd ? launch_wide<T, C, L, TGT, true>(eps, N, D, K, w, s, b, c, tp, ntp, epsv, partials, nrows, st) \
+               : launch_wide<T, C, L, TGT, false>(eps, N, D, K, w, s, b, c, tp, ntp, epsv, partials, nrows, st)
+    if (D <= 16) { NF_WIDE(8, 2); }
+    if (D <= 32) { NF_WIDE(8, 4); }
+    if (D <= 64) { NF_WIDE(8, 8); }
+    if (D <= 128) { NF_WIDE(8, 16); }
+    if (D <= 256) { NF_WIDE(8, 32); }
+    if (D <= 512) { NF_WIDE(16, 32); }
+#undef NF_WIDE
+    return NF_ERR_UNSUPPORTED;
+}
+
 static int max_grid_blocks() {
     const DevInfo di = dev_info();
     return (di.sms > 0 ? di.sms : 148) * kMaxBlocksPerSM;
@@ -456,18 +520,26 @@ static int elbo_entry(const T* eps, int64_t N, int D, int K, const T* w, const T
     T* partials = reinterpret_cast<T*>(workspace);
     const int max_blocks = max_grid_blocks();
     int nb = 0, rc;
+    int Vk = 2 * D + 2, off_s = D, off_b = 2 * D;
     switch (D) {
         case 1: rc = dispatch_target<T, 1>(target_id, all_g, eps, N, K, w, s, b, c, tparams, ntp, epsv, partials, max_blocks, &nb, stream); break;
         case 2: rc = dispatch_target<T, 2>(target_id, all_g, eps, N, K, w, s, b, c, tparams, ntp, epsv, partials, max_blocks, &nb, stream); break;
         case 3: rc = dispatch_target<T, 3>(target_id, all_g, eps, N, K, w, s, b, c, tparams, ntp, epsv, partials, max_blocks, &nb, stream); break;
         case 4: rc = dispatch_target<T, 4>(target_id, all_g, eps, N, K, w, s, b, c, tparams, ntp, epsv, partials, max_blocks, &nb, stream); break;
-        default: rc = NF_ERR_UNSUPPORTED; break;
+        default:
+            Vk = wide_vk(D); off_s = (D + 3) & ~3; off_b = 2 * off_s;
+            if (target_id == NF_TARGET_GAUSSDIAG)
+                rc = dispatch_wide<T, NF_TARGET_GAUSSDIAG>(all_g, eps, N, D, K, w, s, b, c, tparams, ntp, epsv, partials, &nb, stream);
+            else
+                rc = dispatch_wide<T, NF_TARGET_MIXDIAG>(all_g, eps, N, D, K, w, s, b, c, tparams, ntp, epsv, partials, &nb, stream);
+            break;
     }
     if (rc != NF_OK) return rc;
-    const int row = K * (2 * D + 2) + 2;
-    int fblocks = (row + 7) / 8;
-    if (fblocks > 64) fblocks = 64;
-    elbo_finalize_kernel<T><<<fblocks, 256, 0, stream>>>(partials, nb, K, D, all_g ? 1 : 0, out_F, g_w, g_s, g_b, g_c);
+    const size_t row = (size_t)K * Vk + 2;
+    size_t fblocks = (row + 7) / 8;
+    if (fblocks > 592) fblocks = 592;
+    elbo_finalize_kernel<T><<<(int)fblocks, 256, 0, stream>>>(partials, nb, K, D, Vk, off_s, off_b, all_g ? 1 : 0,
+                                                              out_F, g_w, g_s, g_b, g_c);
     NF_CUDA_OK(cudaGetLastError());
     return NF_OK;
 }
@@ -478,8 +550,13 @@ extern "C" {
 
 size_t nf_planar_elbo_workspace_bytes(int K, int D, int elem_size) {
     if (K < 1 || D < 1 || elem_size < 1) return 0;
-    const size_t row = (size_t)K * (2 * D + 2) + 2;
-    return row * (size_t)nf::max_grid_blocks() * (size_t)elem_size;
+    if (D <= 4) {
+        const size_t row = (size_t)K * (2 * D + 2) + 2;
+        return row * (size_t)nf::max_grid_blocks() * (size_t)elem_size;
+    }
+    const size_t row = (size_t)K * nf::wide_vk(D) + 2;      // one row per warp of the wide kernel
+    const nf::DevInfo di = nf::dev_info();
+    return row * (size_t)((di.sms > 0 ? di.sms : 148) * nf::kWideBlocksPerSM * nf::kWideWarps) * (size_t)elem_size;
 }
 
 int nf_planar_elbo_fwd_bwd_f32(const float* eps, int64_t N, int D, int K, const float* w, const float* s,
