@@ -32,7 +32,8 @@ typedef enum {
     NF_ERR_UNSUPPORTED = -2,  /* shape/target combination this build does not implement */
     NF_ERR_WORKSPACE = -3,    /* workspace_bytes smaller than nf_planar_elbo_workspace_bytes() */
     NF_ERR_CUDA = -4,         /* a CUDA runtime call failed; see nf_last_cuda_error() */
-    NF_ERR_NO_DEVICE = -5     /* no CUDA device / not an sm_100 device */
+    NF_ERR_NO_DEVICE = -5,    /* no CUDA device / not an sm_100 device */
+    NF_ERR_SCRATCH_LIMIT = -6 /* nf_planar_elbo_fwd_bwd_noalloc_f32: problem needs more than NF_NOALLOC_SCRATCH_BYTES */
 } nf_status;
 
 /* Target densities exp(-U(z)) the free energy is taken against.  The objective
@@ -97,6 +98,28 @@ int nf_planar_elbo_fwd_bwd_f64(const double* eps, int64_t N, int D, int K,
                                double log_eps,
                                double* out_F, double* g_w, double* g_s, double* g_b, double* g_c,
                                void* workspace, size_t workspace_bytes, void* stream);
+
+/* nf_planar_elbo_fwd_bwd_f32 for callers that must not allocate device memory.  It has no
+ * counterpart in the reference (which never touches a GPU); it exists for host programs
+ * whose device memory was all handed out at start-up, or for which cudaMalloc/cudaFree --
+ * both synchronise the device -- are forbidden where the objective is evaluated.
+ * Same arguments and results as nf_planar_elbo_fwd_bwd_f32 without the workspace pair: the
+ * partial sums go to a fixed NF_NOALLOC_SCRATCH_BYTES array that lives in the library's
+ * device image (every GPU that loads the library holds it until exit).
+ *   - returns NF_ERR_SCRATCH_LIMIT, launching nothing, when
+ *     nf_planar_elbo_workspace_bytes(K, D, 4) > NF_NOALLOC_SCRATCH_BYTES
+ *     (float32, D <= 4: K*(2D+2)+2 <= 442, e.g. K <= 73 at D = 2);
+ *   - all calls share the array: calls that overlap on the GPU race -- keep them on one stream;
+ *   - the first call on a device resolves the array's address; issue it before any stream
+ *     capture starts.
+ * The call itself performs no cudaMalloc/cudaFree and uses no allocating library routine. */
+#define NF_NOALLOC_SCRATCH_BYTES (4u << 20)
+int nf_planar_elbo_fwd_bwd_noalloc_f32(const float* eps, int64_t N, int D, int K,
+                                       const float* w, const float* s, const float* b, const float* c,
+                                       int target_id, const float* target_params, int n_target_params,
+                                       float log_eps,
+                                       float* out_F, float* g_w, float* g_s, float* g_b, float* g_c,
+                                       void* stream);
 
 /* ---------------------------------------------------------------------------
  * flows.planar_flow (normflows/normflows/flows.py:8-34, _get_uhat :37-39, m :42-43).

@@ -1,0 +1,83 @@
+"""GPU test of nf_planar_elbo_fwd_bwd_noalloc_f32, the entry point for callers that may not
+allocate device memory where they evaluate the free energy (an application that gave the
+whole GPU to its own memory pool at start-up; a latency-critical loop that must avoid the
+device-wide synchronisation cudaMalloc and cudaFree imply).  The caller passes only inputs
+and outputs; the partial sums go to a fixed 4 MiB array inside the library.
+
+Checked here, through the C ABI: two calls in a row (different samples, so the array still
+holds the first call's partial sums when the second starts) each reproduce what the
+workspace-taking entry point returns, within the float32 tolerance the other GPU tests use
+(1e-4 relative); a problem too large for the built-in array is refused with a clear status.
+The file sorts last so that a `-x` run has already exercised every other test before it.
+"""
+import ctypes
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+F32_TOL = 1e-4
+
+
+def _p(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else ctypes.c_void_p(0)
+
+
+def _inputs(seed, N, K, D, dev):
+    from nfcore import semantics as sem
+    rs = np.random.RandomState(seed)
+    W = 0.1 + 0.01 * rs.randn(K, D); U = 0.1 + 0.01 * rs.randn(K, D); B = 0.1 * np.ones(K)
+    S, c = sem.forward(W, U)
+    dev_t = lambda a: torch.as_tensor(a, dtype=torch.float32).to(dev).contiguous()
+    eps = torch.as_tensor(rs.randn(N, D), dtype=torch.float32).to(dev).contiguous()
+    return eps, dev_t(W), dev_t(S), dev_t(B), dev_t(c)
+
+
+def _outputs(K, D, dev):
+    return (torch.full((3,), float('nan'), device=dev), torch.full((K, D), float('nan'), device=dev),
+            torch.full((K, D), float('nan'), device=dev), torch.full((K,), float('nan'), device=dev),
+            torch.full((K,), float('nan'), device=dev))
+
+
+def test_noalloc_entry_matches_workspace_entry_twice_in_a_row():
+    import nfcore
+    lib = nfcore.load()
+    dev = torch.device('cuda:0')
+    torch.cuda.set_device(dev)
+    K, D = 32, 2
+    stream = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    nbytes = lib.nf_planar_elbo_workspace_bytes(K, D, 4)
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    for call, (seed, N) in enumerate([(11, 70001), (12, 4099)]):
+        eps, w, s, b, c = _inputs(seed, N, K, D, dev)
+        ref = _outputs(K, D, dev)
+        rc = lib.nf_planar_elbo_fwd_bwd_f32(_p(eps), N, D, K, _p(w), _p(s), _p(b), _p(c), 0, None, 0,
+                                            ctypes.c_float(1e-7), *[_p(t) for t in ref], _p(ws), nbytes, stream)
+        assert rc == 0, lib.nf_status_string(rc)
+        got = _outputs(K, D, dev)
+        rc = lib.nf_planar_elbo_fwd_bwd_noalloc_f32(_p(eps), N, D, K, _p(w), _p(s), _p(b), _p(c), 0, None, 0,
+                                                    ctypes.c_float(1e-7), *[_p(t) for t in got], stream)
+        assert rc == 0, lib.nf_status_string(rc)
+        torch.cuda.synchronize()
+        for name, x, y in zip(('out_F', 'g_w', 'g_s', 'g_b', 'g_c'), got, ref):
+            x, y = x.double().cpu().numpy(), y.double().cpu().numpy()
+            assert np.isfinite(x).all(), (call, name)
+            assert np.abs(x - y).max() <= F32_TOL * max(np.abs(y).max(), 1.0), (call, name)
+
+
+def test_noalloc_entry_refuses_oversized_problem():
+    import nfcore
+    lib = nfcore.load()
+    dev = torch.device('cuda:0')
+    torch.cuda.set_device(dev)
+    K, D, N = 256, 2, 128                   # needs K*(2D+2)+2 = 1538 floats per row: beyond the 4 MiB array
+    eps, w, s, b, c = _inputs(5, N, K, D, dev)
+    got = _outputs(K, D, dev)
+    rc = lib.nf_planar_elbo_fwd_bwd_noalloc_f32(_p(eps), N, D, K, _p(w), _p(s), _p(b), _p(c), 0, None, 0,
+                                                ctypes.c_float(1e-7), *[_p(t) for t in got], None)
+    assert rc == -6
+    assert b'NF_NOALLOC_SCRATCH_BYTES' in lib.nf_status_string(rc)
+    torch.cuda.synchronize()
+    assert torch.isnan(got[0]).all()        # nothing was launched, outputs untouched
