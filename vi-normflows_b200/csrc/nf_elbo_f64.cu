@@ -1,0 +1,14 @@
+// float64 (reference-precision mode) instantiation of the shared-parameter free-energy kernels.
+#include "nf_elbo_impl.cuh"
+
+extern "C" {
+
+int nf_planar_elbo_fwd_bwd_f64(const double* eps, int64_t N, int D, int K, const double* w, const double* s,
+                               const double* b, const double* c, int target_id, const double* target_params,
+                               int n_target_params, double log_eps, double* out_F, double* g_w, double* g_s,
+                               double* g_b, double* g_c, void* workspace, size_t workspace_bytes, void* stream) {
+    return nf::elbo_entry<double>(eps, N, D, K, w, s, b, c, target_id, target_params, n_target_params, log_eps,
+                                  out_F, g_w, g_s, g_b, g_c, workspace, workspace_bytes, stream);
+}
+
+}  // extern "C"

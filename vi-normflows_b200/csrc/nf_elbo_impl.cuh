@@ -1,4 +1,6 @@
 // Shared-parameter planar-flow free energy: fused forward + backward (sm_100a).
+// Template implementation; nf_elbo_f32.cu / nf_elbo_f64.cu instantiate it per element type
+// (two translation units so that nvcc can build them in parallel).
 //
 // Replaces get_data.py:97-113 (forward) and the autograd tape replay of
 // get_data.py:115 (backward).  One launch per step:
@@ -18,6 +20,7 @@
 //   * blocks are persistent (grid = SMs x occupancy) and stride over sample tiles; each
 //     block writes one row of partial sums and a second small kernel adds the rows in a
 //     fixed order (bitwise reproducible for a fixed launch shape).
+#pragma once
 #include <cstdlib>
 #include <mutex>
 #include "nf_common.cuh"
@@ -356,7 +359,7 @@ __global__ void elbo_finalize_kernel(const T* __restrict__ partials, int nrows, 
 }
 
 struct DevInfo { int sms; int ok; };
-static DevInfo dev_info() {
+static inline DevInfo dev_info() {
     static thread_local int cached_dev = -1;
     static thread_local DevInfo info = {0, 0};
     int dev = 0;
@@ -490,7 +493,7 @@ static int dispatch_wide(bool bwd, const T* eps, long long N, int D, int K, cons
     return NF_ERR_UNSUPPORTED;
 }
 
-static int max_grid_blocks() {
+static inline int max_grid_blocks() {
     const DevInfo di = dev_info();
     return (di.sms > 0 ? di.sms : 148) * kMaxBlocksPerSM;
 }
@@ -547,101 +550,3 @@ static int elbo_entry(const T* eps, int64_t N, int D, int K, const T* w, const T
 
 }  // namespace nf
 
-extern "C" {
-
-size_t nf_planar_elbo_workspace_bytes(int K, int D, int elem_size) {
-    if (K < 1 || D < 1 || elem_size < 1) return 0;
-    if (D <= 4) {
-        const size_t row = (size_t)K * (2 * D + 2) + 2;
-        return row * (size_t)nf::max_grid_blocks() * (size_t)elem_size;
-    }
-    const size_t row = (size_t)K * nf::wide_vk(D) + 2;      // one row per warp of the wide kernel
-    const nf::DevInfo di = nf::dev_info();
-    return row * (size_t)((di.sms > 0 ? di.sms : 148) * nf::kWideBlocksPerSM * nf::kWideWarps) * (size_t)elem_size;
-}
-
-int nf_planar_elbo_fwd_bwd_f32(const float* eps, int64_t N, int D, int K, const float* w, const float* s,
-                               const float* b, const float* c, int target_id, const float* target_params,
-                               int n_target_params, float log_eps, float* out_F, float* g_w, float* g_s,
-                               float* g_b, float* g_c, void* workspace, size_t workspace_bytes, void* stream) {
-    return nf::elbo_entry<float>(eps, N, D, K, w, s, b, c, target_id, target_params, n_target_params, log_eps,
-                                 out_F, g_w, g_s, g_b, g_c, workspace, workspace_bytes, stream);
-}
-
-int nf_planar_elbo_fwd_bwd_f64(const double* eps, int64_t N, int D, int K, const double* w, const double* s,
-                               const double* b, const double* c, int target_id, const double* target_params,
-                               int n_target_params, double log_eps, double* out_F, double* g_w, double* g_s,
-                               double* g_b, double* g_c, void* workspace, size_t workspace_bytes, void* stream) {
-    return nf::elbo_entry<double>(eps, N, D, K, w, s, b, c, target_id, target_params, n_target_params, log_eps,
-                                  out_F, g_w, g_s, g_b, g_c, workspace, workspace_bytes, stream);
-}
-
-}  // extern "C"
-
-// ---------------------------------------------------------------------------------------
-// Allocation-free variant of nf_planar_elbo_fwd_bwd_f32.
-//
-// Who needs this: host programs that are not allowed to ask the CUDA driver for memory at
-// the point where they evaluate the free energy -- an optimiser loop inside an application
-// that handed the whole device to its own pool at start-up (a later cudaMalloc would fail
-// or fight that pool), and latency-sensitive callers for whom cudaMalloc/cudaFree are off
-// limits because both synchronise the device.  Such callers still own their inputs and
-// outputs; the one thing they cannot provide is the partial-sum workspace, so the library
-// carries one: a fixed array in device global memory that is part of the loaded module.
-// Every GPU that loads libnfcore therefore holds NF_NOALLOC_SCRATCH_BYTES (4 MiB) until the
-// process exits, whether or not this entry point is ever called.
-//
-// Rules that follow from sharing one array:
-//   * problems whose workspace (nf_planar_elbo_workspace_bytes(K, D, 4)) exceeds the array
-//     are refused with NF_ERR_SCRATCH_LIMIT -- nothing is launched;
-//   * the array keeps whatever the previous call left in it.  Nothing in it has to start at
-//     zero: every block (D <= 4) overwrites its whole row before the row kernel reads it, and
-//     the wide-D kernel clears each warp's row itself before accumulating;
-//   * two calls that overlap on the GPU (different streams, or different host threads on one
-//     device) use the same rows and race.  Serialise them on one stream;
-//   * the first call on each device looks up the array's device address (set-up, under a
-//     lock).  Make that first call before any stream capture begins.
-// The body below calls no cudaMalloc / cudaFree / allocating library routine.
-// ---------------------------------------------------------------------------------------
-namespace nf {
-
-static __device__ __align__(256) unsigned char g_noalloc_scratch[NF_NOALLOC_SCRATCH_BYTES];
-
-constexpr int kMaxDevices = 64;
-static void* g_noalloc_ptr[kMaxDevices];          // device address of the array, per device ordinal
-static bool g_noalloc_ready[kMaxDevices];
-static std::mutex g_noalloc_mutex;
-
-// In host code `g_noalloc_scratch` is only a handle for the symbol, not an address a kernel
-// can use; the address comes from cudaGetSymbolAddress on the device that is current.
-static int noalloc_scratch(void** out) {
-    int dev = 0;
-    NF_CUDA_OK(cudaGetDevice(&dev));
-    if (dev < 0 || dev >= kMaxDevices) return NF_ERR_UNSUPPORTED;
-    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
-    if (!g_noalloc_ready[dev]) {
-        void* p = nullptr;
-        NF_CUDA_OK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
-        g_noalloc_ptr[dev] = p;
-        g_noalloc_ready[dev] = true;
-    }
-    *out = g_noalloc_ptr[dev];
-    return NF_OK;
-}
-
-}  // namespace nf
-
-extern "C" int nf_planar_elbo_fwd_bwd_noalloc_f32(const float* eps, int64_t N, int D, int K, const float* w,
-                                                  const float* s, const float* b, const float* c, int target_id,
-                                                  const float* target_params, int n_target_params, float log_eps,
-                                                  float* out_F, float* g_w, float* g_s, float* g_b, float* g_c,
-                                                  void* stream) {
-    if (D < 1 || K < 1) return NF_ERR_INVALID;
-    const size_t need = nf_planar_elbo_workspace_bytes(K, D, (int)sizeof(float));
-    if (need == 0 || need > (size_t)NF_NOALLOC_SCRATCH_BYTES) return NF_ERR_SCRATCH_LIMIT;
-    void* scratch = nullptr;
-    const int rc = nf::noalloc_scratch(&scratch);
-    if (rc != NF_OK) return rc;
-    return nf::elbo_entry<float>(eps, N, D, K, w, s, b, c, target_id, target_params, n_target_params, log_eps, out_F,
-                                 g_w, g_s, g_b, g_c, scratch, (size_t)NF_NOALLOC_SCRATCH_BYTES, stream);
-}

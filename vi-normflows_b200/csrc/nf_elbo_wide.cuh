@@ -1,6 +1,6 @@
 // Shared-parameter free energy for larger latent dimension (5 <= D <= 512), sm_100a.
 //
-// Same math as nf_elbo_shared.cu (get_data.py:97-115) but a sample no longer fits one
+// Same math as nf_elbo_impl.cuh (get_data.py:97-115) but a sample no longer fits one
 // thread: L lanes (2..32) share a sample, each holding C=8 (or 16) coordinates of z and
 // of the running gradient in registers.  The two dot products per layer (w.z forward,
 // gz.s backward) are finished with log2(L) xor shuffles; everything that is a scalar per
@@ -9,7 +9,7 @@
 // after the S interleaved sample groups of a warp have passed layer k they are
 // reduce-scattered across the 32/L sample groups of the warp and added to the warp's
 // private row of the partial-sum workspace in global memory (L1/L2 resident, touched by
-// one warp only => deterministic).  The row kernel in nf_elbo_shared.cu then adds rows.
+// one warp only => deterministic).  The row kernel in nf_elbo_impl.cuh then adds rows.
 // Layer constants are read straight from global memory through L1 (every warp of the SM
 // reads the same 2D+2 numbers per layer), activations t_k go to shared memory.
 #pragma once
