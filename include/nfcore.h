@@ -165,6 +165,44 @@ int nf_planar_amortised_bwd_f64(const double* z0, const double* log_sigma0, cons
                                 int64_t N, int D, int K, double log_eps, double* g_mu0, double* g_log_sigma0,
                                 double* g_W, double* g_U, double* g_Bb, void* stream);
 
+/* ---------------------------------------------------------------------------
+ * Encoder / decoder MLP: nn_models.Feedforward.forward (normflows/normflows/nn_models.py:41-84)
+ * as used by src/learning_mnist.py:60-73, and its reverse pass (the autograd tape replay of
+ * optimization.py:35 through those closures).
+ *   weights : the reference's flat vector (nn_models.py:59-80):
+ *             W1 (H x D_in, row-major) | b1 (H) | {W_l (H x H) | b_l (H)} x (L-1) | W_out (D_out x H) | b_out
+ *             nf_mlp_param_count() = Feedforward.D (nn_models.py:16-19)
+ *   x       : [N][D_in]  SAMPLE-major (the reference passes X.T, feature-major; same numbers)
+ *   out     : [N][D_out] sample-major (the reference returns (1, D_out, N))
+ *   activations: 0 none, 1 relu (transformations.py:21), 2 sigmoid (:7-8), 3 rbf exp(-x^2)
+ *             (nn_models.py:175 default_architecture).  out_act 3 is not supported backward.
+ *   fwd_ws  : nf_mlp_forward_workspace_bytes(); holds the hidden activations the backward pass needs
+ *   backward: g_out = dF/d out -> g_weights (same layout as weights), g_x (may be NULL);
+ *             bwd_ws of nf_mlp_backward_workspace_bytes().
+ * ------------------------------------------------------------------------- */
+int64_t nf_mlp_param_count(int D_in, int H, int L, int D_out);
+size_t nf_mlp_forward_workspace_bytes(int64_t N, int D_in, int H, int L, int D_out, int hidden_act, int elem_size);
+size_t nf_mlp_backward_workspace_bytes(int64_t N, int D_in, int H, int L, int D_out, int elem_size);
+int nf_mlp_forward_f32(const float* weights, const float* x, int64_t N, int D_in, int H, int L, int D_out,
+                       int hidden_act, int out_act, float* fwd_ws, float* out, void* stream);
+int nf_mlp_forward_f64(const double* weights, const double* x, int64_t N, int D_in, int H, int L, int D_out,
+                       int hidden_act, int out_act, double* fwd_ws, double* out, void* stream);
+int nf_mlp_backward_f32(const float* weights, const float* x, int64_t N, int D_in, int H, int L, int D_out,
+                        int hidden_act, int out_act, const float* fwd_ws, const float* out, const float* g_out,
+                        float* g_weights, float* g_x, float* bwd_ws, void* stream);
+int nf_mlp_backward_f64(const double* weights, const double* x, int64_t N, int D_in, int H, int L, int D_out,
+                        int hidden_act, int out_act, const double* fwd_ws, const double* out, const double* g_out,
+                        double* g_weights, double* g_x, double* bwd_ws, void* stream);
+
+/* distributions.log_bern_mult (distributions.py:86-89): out_sum[0] = sum over ALL count elements of
+ * x log(eps+p) + (1-x) log(eps+1-p) (one scalar for the whole batch, as the reference), and, when
+ * g_p != NULL, g_p[i] = g_scale * d out_sum / d p[i].  workspace: nf_bernoulli_workspace_bytes(). */
+size_t nf_bernoulli_workspace_bytes(int elem_size);
+int nf_bernoulli_ll_f32(const float* x, const float* p, int64_t count, float log_eps, float g_scale,
+                        float* out_sum, float* g_p, float* workspace, void* stream);
+int nf_bernoulli_ll_f64(const double* x, const double* p, int64_t count, double log_eps, double g_scale,
+                        double* out_sum, double* g_p, double* workspace, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

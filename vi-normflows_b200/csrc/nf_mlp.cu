@@ -1,0 +1,365 @@
+// Encoder / decoder MLP of the flow-VAE (nn_models.py:41-84 `Feedforward.forward`) and the
+// Bernoulli log-likelihood (distributions.py:86-89), forward and backward, sm_100a.
+//
+// Round-1 version: FP32/FP64 register-blocked shared-memory GEMMs on the CUDA cores with the
+// bias + activation epilogue fused (the tcgen05/TMA version of the three large layers is the
+// next step; at C4 the whole MLP is 4.7 GFLOP per step).  Activations are
+// kept sample-major [N][H] so that every layer is C[m][n] = sum_k A[m][k] W[n][k] with both
+// operands contiguous along k; the flat weight vector has exactly the reference's layout
+// (nn_models.py:59-80): W1 (H x D_in) | b1 | {W_l (H x H) | b_l} x (L-1) | W_out (D_out x H) | b_out.
+#include "nf_common.cuh"
+
+namespace nf {
+
+enum { ACT_NONE = 0, ACT_RELU = 1, ACT_SIGMOID = 2, ACT_RBF = 3 };   // rbf: exp(-x^2) (nn_models.py:175)
+
+template <typename T> __device__ __forceinline__ T act_fwd(T x, int act) {
+    using M = Mth<T>;
+    switch (act) {
+        case ACT_RELU: return x > (T)0 ? x : (T)0;                       // transformations.py:21
+        case ACT_SIGMOID: return M::div((T)1, (T)1 + M::exp(-x));        // transformations.py:7-8
+        case ACT_RBF: return M::exp(-x * x);
+        default: return x;
+    }
+}
+// derivative expressed with the saved OUTPUT y (and, for rbf, the pre-activation is recovered
+// from y = exp(-x^2) only up to sign, so rbf layers save the pre-activation instead: see below)
+template <typename T> __device__ __forceinline__ T act_bwd_from_out(T y, int act) {
+    switch (act) {
+        case ACT_RELU: return y > (T)0 ? (T)1 : (T)0;
+        case ACT_SIGMOID: return y * ((T)1 - y);
+        default: return (T)1;
+    }
+}
+
+constexpr int TM = 64, TN = 64, TK = 16, GT = 256;   // block tile and threads (16x16, 4x4 outputs each)
+
+// C[m][n] (ldc) = epi( sum_k A(m,k) * B(k,n) ),  A(m,k) = a[m*sam + k*sak],  B(k,n) = b[k*sbk + n*sbn].
+// Split-K: blockIdx.z handles k in [z*kchunk, (z+1)*kchunk) and writes to c + z*M*ldc (partials,
+// epilogue skipped) when gridDim.z > 1.
+template <typename T>
+__global__ void __launch_bounds__(GT)
+gemm_kernel(const T* __restrict__ a, long long sam, long long sak, const T* __restrict__ b, long long sbk,
+            long long sbn, T* __restrict__ c, long long ldc, int M, int N, int K, int kchunk,
+            const T* __restrict__ bias, int act, T* __restrict__ preact /* optional copy of the pre-activation */) {
+    __shared__ T As[TK][TM + 4];
+    __shared__ T Bs[TK][TN + 4];
+    const int tid = threadIdx.x;
+    const int tx = tid & 15, ty = tid >> 4;
+    const int m0 = blockIdx.y * TM, n0 = blockIdx.x * TN;
+    const int kbeg = blockIdx.z * kchunk;
+    const int kend = min(K, kbeg + kchunk);
+    T acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = (T)0;
+    // loader mapping: make the contiguous global index the fastest-varying thread index
+    const bool a_kfast = sak == 1;       // A contiguous along k
+    const bool b_kfast = sbk == 1;       // B contiguous along k
+    for (int k0 = kbeg; k0 < kend; k0 += TK) {
+#pragma unroll
+        for (int r = 0; r < (TM * TK) / GT; ++r) {
+            const int e = tid + r * GT;
+            const int kk = a_kfast ? (e % TK) : (e / TM);
+            const int mm = a_kfast ? (e / TK) : (e % TM);
+            const int gm = m0 + mm, gk = k0 + kk;
+            As[kk][mm] = (gm < M && gk < kend) ? a[(long long)gm * sam + (long long)gk * sak] : (T)0;
+        }
+#pragma unroll
+        for (int r = 0; r < (TN * TK) / GT; ++r) {
+            const int e = tid + r * GT;
+            const int kk = b_kfast ? (e % TK) : (e / TN);
+            const int nn = b_kfast ? (e / TK) : (e % TN);
+            const int gn = n0 + nn, gk = k0 + kk;
+            Bs[kk][nn] = (gn < N && gk < kend) ? b[(long long)gk * sbk + (long long)gn * sbn] : (T)0;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < TK; ++kk) {
+            T av[4], bv[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) av[i] = As[kk][ty * 4 + i];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) bv[j] = Bs[kk][tx * 4 + j];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = Mth<T>::fma(av[i], bv[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+    const bool partial = gridDim.z > 1;
+    T* cz = c + (partial ? (long long)blockIdx.z * M * ldc : 0);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int gm = m0 + ty * 4 + i;
+        if (gm >= M) continue;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int gn = n0 + tx * 4 + j;
+            if (gn >= N) continue;
+            T v = acc[i][j];
+            if (!partial) {
+                if (bias) v += bias[gn];
+                if (preact) preact[(long long)gm * ldc + gn] = v;
+                v = act_fwd(v, act);
+            }
+            cz[(long long)gm * ldc + gn] = v;
+        }
+    }
+}
+
+// out[i] = sum_z partial[z][i] (fixed order), i < count
+template <typename T>
+__global__ void splitk_reduce_kernel(const T* __restrict__ partial, int nz, long long count, T* __restrict__ out) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x) {
+        T s = (T)0;
+        for (int z = 0; z < nz; ++z) s += partial[(long long)z * count + i];
+        out[i] = s;
+    }
+}
+
+// dz = dy * act'(.)   (relu / sigmoid from the saved output, rbf from the saved pre-activation)
+template <typename T>
+__global__ void act_backward_kernel(const T* __restrict__ dy, const T* __restrict__ saved, long long count, int act,
+                                    T* __restrict__ dz) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x) {
+        const T sv = saved[i];
+        T d;
+        if (act == ACT_RBF) d = (T)-2 * sv * Mth<T>::exp(-sv * sv);
+        else d = act_bwd_from_out(sv, act);
+        dz[i] = dy[i] * d;
+    }
+}
+
+// column sums: out[n] = sum_m x[m][n]  (one warp per 32 columns, fixed order over m)
+template <typename T>
+__global__ void colsum_kernel(const T* __restrict__ x, int M, int N, T* __restrict__ out) {
+    __shared__ T red[8][33];
+    const int n = blockIdx.x * 32 + (threadIdx.x & 31);
+    const int r = threadIdx.x >> 5;
+    T s = (T)0;
+    if (n < N)
+        for (int m = r; m < M; m += 8) s += x[(long long)m * N + n];
+    red[r][threadIdx.x & 31] = s;
+    __syncthreads();
+    if (r == 0 && n < N) {
+        T t = (T)0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) t += red[i][threadIdx.x & 31];
+        out[n] = t;
+    }
+}
+
+template <typename T>
+static int launch_gemm(const T* a, long long sam, long long sak, const T* b, long long sbk, long long sbn, T* c,
+                       long long ldc, int M, int N, int K, const T* bias, int act, T* preact, int splits,
+                       T* split_ws, cudaStream_t st) {
+    dim3 grid((N + TN - 1) / TN, (M + TM - 1) / TM, splits);
+    int kchunk = (K + splits - 1) / splits;
+    kchunk = ((kchunk + TK - 1) / TK) * TK;
+    if (splits > 1) {
+        gemm_kernel<T><<<grid, GT, 0, st>>>(a, sam, sak, b, sbk, sbn, split_ws, ldc, M, N, K, kchunk, nullptr, ACT_NONE, nullptr);
+        NF_CUDA_OK(cudaGetLastError());
+        const long long count = (long long)M * ldc;
+        splitk_reduce_kernel<T><<<(int)min((count + 255) / 256, (long long)1184), 256, 0, st>>>(split_ws, splits, count, c);
+    } else {
+        gemm_kernel<T><<<grid, GT, 0, st>>>(a, sam, sak, b, sbk, sbn, c, ldc, M, N, K, kchunk, bias, act, preact);
+    }
+    NF_CUDA_OK(cudaGetLastError());
+    return NF_OK;
+}
+
+struct MlpDims { int N, D_in, H, L, D_out; };
+static inline long long mlp_param_count(const MlpDims& d) {       // nn_models.py:16-19
+    return ((long long)d.D_in * d.H + d.H) + ((long long)d.D_out * d.H + d.D_out) + (long long)(d.L - 1) * ((long long)d.H * d.H + d.H);
+}
+constexpr int kSplits = 32;      // split-K factor of the weight-gradient GEMMs (contraction over the batch)
+
+// forward workspace: L hidden activation buffers [N][H] (+ L pre-activation buffers for rbf)
+static inline size_t mlp_fwd_ws_elems(const MlpDims& d, int hidden_act) {
+    return (size_t)d.L * d.N * d.H * (hidden_act == ACT_RBF ? 2 : 1);
+}
+// backward workspace: two ping-pong dz buffers [N][max(H, D_out)] + split-K partials of the largest dW
+static inline size_t mlp_bwd_ws_elems(const MlpDims& d) {
+    const size_t wide = (size_t)max(d.H, d.D_out);
+    const size_t maxw = (size_t)max((long long)d.H * d.D_in, max((long long)d.D_out * d.H, (long long)d.H * d.H));
+    return 2 * (size_t)d.N * wide + (size_t)kSplits * maxw;
+}
+
+template <typename T>
+static int mlp_forward(const T* wts, const T* x, MlpDims d, int hidden_act, int out_act, T* ws, T* out, cudaStream_t st) {
+    if (d.N < 0 || d.D_in < 1 || d.H < 1 || d.L < 1 || d.D_out < 1 || !wts || !ws || (d.N > 0 && (!x || !out))) return NF_ERR_INVALID;
+    if (hidden_act < 0 || hidden_act > ACT_RBF || out_act < 0 || out_act > ACT_RBF) return NF_ERR_INVALID;
+    if (d.N == 0) return NF_OK;
+    const bool rbf = hidden_act == ACT_RBF;
+    const size_t layer = (size_t)d.N * d.H;
+    T* pre = rbf ? ws + (size_t)d.L * layer : nullptr;
+    const T* in = x;
+    int kin = d.D_in;
+    const T* p = wts;
+    for (int l = 0; l < d.L; ++l) {
+        const T* W = p;
+        const T* bvec = p + (size_t)d.H * kin;
+        T* a = ws + (size_t)l * layer;
+        int rc = launch_gemm<T>(in, kin, 1, W, 1, kin, a, d.H, d.N, d.H, kin, bvec, hidden_act,
+                                rbf ? pre + (size_t)l * layer : nullptr, 1, nullptr, st);
+        if (rc != NF_OK) return rc;
+        p = bvec + d.H;
+        in = a;
+        kin = d.H;
+    }
+    const T* W = p;
+    const T* bvec = p + (size_t)d.D_out * d.H;
+    return launch_gemm<T>(in, d.H, 1, W, 1, d.H, out, d.D_out, d.N, d.D_out, d.H, bvec, out_act, nullptr, 1, nullptr, st);
+}
+
+template <typename T>
+static int mlp_backward(const T* wts, const T* x, MlpDims d, int hidden_act, int out_act, const T* fws, const T* out,
+                        const T* g_out, T* g_wts, T* g_x, T* bws, cudaStream_t st) {
+    if (d.N < 1 || !wts || !x || !fws || !out || !g_out || !g_wts || !bws) return NF_ERR_INVALID;
+    if (out_act == ACT_RBF) return NF_ERR_UNSUPPORTED;
+    const bool rbf = hidden_act == ACT_RBF;
+    const size_t layer = (size_t)d.N * d.H;
+    const size_t wide = (size_t)max(d.H, d.D_out);
+    T* dz_a = bws;
+    T* dz_b = bws + (size_t)d.N * wide;
+    T* split_ws = bws + 2 * (size_t)d.N * wide;
+    const int eb = 1184;
+    // parameter offsets
+    const long long P = mlp_param_count(d);
+    long long off_out = P - ((long long)d.D_out * d.H + d.D_out);
+    // ---- output layer ----
+    const long long cnt_out = (long long)d.N * d.D_out;
+    act_backward_kernel<T><<<eb, 256, 0, st>>>(g_out, out, cnt_out, out_act, dz_a);     // dz_a: [N][D_out]
+    NF_CUDA_OK(cudaGetLastError());
+    const T* a_prev = fws + (size_t)(d.L - 1) * layer;                                   // last hidden activation
+    // dW_out[j][h] = sum_n dz[n][j] a_prev[n][h] : A(m=j,k=n) = dz[n*D_out + j], B(k=n, n'=h) = a_prev[n*H + h]
+    int rc = launch_gemm<T>(dz_a, 1, d.D_out, a_prev, d.H, 1, g_wts + off_out, d.H, d.D_out, d.H, d.N, nullptr, ACT_NONE,
+                            nullptr, kSplits, split_ws, st);
+    if (rc != NF_OK) return rc;
+    colsum_kernel<T><<<(d.D_out + 31) / 32, 256, 0, st>>>(dz_a, d.N, d.D_out, g_wts + off_out + (long long)d.D_out * d.H);
+    NF_CUDA_OK(cudaGetLastError());
+    // d a_prev[n][h] = sum_j dz[n][j] W_out[j][h] : B(k=j, n'=h) = W_out[j*H + h]
+    rc = launch_gemm<T>(dz_a, d.D_out, 1, wts + off_out, d.H, 1, dz_b, d.H, d.N, d.H, d.D_out, nullptr, ACT_NONE, nullptr, 1,
+                        nullptr, st);
+    if (rc != NF_OK) return rc;
+    // ---- hidden layers, last to first ----
+    long long off = off_out;
+    T* g_act = dz_b;      // gradient wrt the activation of layer l
+    T* other = dz_a;
+    for (int l = d.L - 1; l >= 0; --l) {
+        const int kin = l == 0 ? d.D_in : d.H;
+        off -= (long long)d.H * kin + d.H;
+        const T* saved = rbf ? fws + (size_t)d.L * layer + (size_t)l * layer : fws + (size_t)l * layer;
+        act_backward_kernel<T><<<eb, 256, 0, st>>>(g_act, saved, (long long)layer, hidden_act, other);   // other: dz [N][H]
+        NF_CUDA_OK(cudaGetLastError());
+        const T* in = l == 0 ? x : fws + (size_t)(l - 1) * layer;
+        rc = launch_gemm<T>(other, 1, d.H, in, kin, 1, g_wts + off, kin, d.H, kin, d.N, nullptr, ACT_NONE, nullptr, kSplits,
+                            split_ws, st);
+        if (rc != NF_OK) return rc;
+        colsum_kernel<T><<<(d.H + 31) / 32, 256, 0, st>>>(other, d.N, d.H, g_wts + off + (long long)d.H * kin);
+        NF_CUDA_OK(cudaGetLastError());
+        if (l > 0) {
+            rc = launch_gemm<T>(other, d.H, 1, wts + off, kin, 1, g_act, d.H, d.N, d.H, d.H, nullptr, ACT_NONE, nullptr, 1, nullptr, st);
+            if (rc != NF_OK) return rc;
+        } else if (g_x) {
+            rc = launch_gemm<T>(other, d.H, 1, wts + off, kin, 1, g_x, d.D_in, d.N, d.D_in, d.H, nullptr, ACT_NONE, nullptr, 1, nullptr, st);
+            if (rc != NF_OK) return rc;
+        }
+    }
+    return NF_OK;
+}
+
+// ---- Bernoulli log-likelihood: sum x log(eps+p) + (1-x) log(eps+1-p), and d/dp ------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+bernoulli_kernel(const T* __restrict__ x, const T* __restrict__ p, long long count, T epsv, T g_scale,
+                 T* __restrict__ partial, T* __restrict__ g_p) {
+    using M = Mth<T>;
+    T s = (T)0;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x) {
+        const T xv = x[i], pv = p[i];
+        const T a = epsv + pv, b = epsv + (T)1 - pv;
+        s += xv * M::logp(a) + ((T)1 - xv) * M::logp(b);
+        if (g_p) g_p[i] = g_scale * (M::div(xv, a) - M::div((T)1 - xv, b));
+    }
+    s = warp_sum(s);
+    __shared__ T red[8];
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        T t = (T)0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) t += red[i];
+        partial[blockIdx.x] = t;
+    }
+}
+template <typename T>
+__global__ void bernoulli_final_kernel(const T* __restrict__ partial, int n, T* __restrict__ out) {
+    T s = (T)0;
+    for (int i = threadIdx.x; i < n; i += 32) s += partial[i];
+    s = warp_sum(s);
+    if (threadIdx.x == 0) out[0] = s;
+}
+constexpr int kBernBlocks = 592;
+
+template <typename T>
+static int bernoulli_entry(const T* x, const T* p, long long count, T epsv, T g_scale, T* out, T* g_p, T* ws, cudaStream_t st) {
+    if (count < 0 || !out || !ws || (count > 0 && (!x || !p))) return NF_ERR_INVALID;
+    const int blocks = (int)max(1LL, min((long long)kBernBlocks, (count + 255) / 256));
+    bernoulli_kernel<T><<<blocks, 256, 0, st>>>(x, p, count, epsv, g_scale, ws, g_p);
+    NF_CUDA_OK(cudaGetLastError());
+    bernoulli_final_kernel<T><<<1, 32, 0, st>>>(ws, blocks, out);
+    NF_CUDA_OK(cudaGetLastError());
+    return NF_OK;
+}
+
+}  // namespace nf
+
+extern "C" {
+
+int64_t nf_mlp_param_count(int D_in, int H, int L, int D_out) {
+    nf::MlpDims d{0, D_in, H, L, D_out};
+    return nf::mlp_param_count(d);
+}
+size_t nf_mlp_forward_workspace_bytes(int64_t N, int D_in, int H, int L, int D_out, int hidden_act, int elem_size) {
+    nf::MlpDims d{(int)N, D_in, H, L, D_out};
+    return nf::mlp_fwd_ws_elems(d, hidden_act) * (size_t)elem_size;
+}
+size_t nf_mlp_backward_workspace_bytes(int64_t N, int D_in, int H, int L, int D_out, int elem_size) {
+    nf::MlpDims d{(int)N, D_in, H, L, D_out};
+    return nf::mlp_bwd_ws_elems(d) * (size_t)elem_size;
+}
+int nf_mlp_forward_f32(const float* weights, const float* x, int64_t N, int D_in, int H, int L, int D_out, int hidden_act,
+                       int out_act, float* fwd_ws, float* out, void* stream) {
+    return nf::mlp_forward<float>(weights, x, nf::MlpDims{(int)N, D_in, H, L, D_out}, hidden_act, out_act, fwd_ws, out, (cudaStream_t)stream);
+}
+int nf_mlp_forward_f64(const double* weights, const double* x, int64_t N, int D_in, int H, int L, int D_out, int hidden_act,
+                       int out_act, double* fwd_ws, double* out, void* stream) {
+    return nf::mlp_forward<double>(weights, x, nf::MlpDims{(int)N, D_in, H, L, D_out}, hidden_act, out_act, fwd_ws, out, (cudaStream_t)stream);
+}
+int nf_mlp_backward_f32(const float* weights, const float* x, int64_t N, int D_in, int H, int L, int D_out, int hidden_act,
+                        int out_act, const float* fwd_ws, const float* out, const float* g_out, float* g_weights,
+                        float* g_x, float* bwd_ws, void* stream) {
+    return nf::mlp_backward<float>(weights, x, nf::MlpDims{(int)N, D_in, H, L, D_out}, hidden_act, out_act, fwd_ws, out, g_out,
+                                   g_weights, g_x, bwd_ws, (cudaStream_t)stream);
+}
+int nf_mlp_backward_f64(const double* weights, const double* x, int64_t N, int D_in, int H, int L, int D_out, int hidden_act,
+                        int out_act, const double* fwd_ws, const double* out, const double* g_out, double* g_weights,
+                        double* g_x, double* bwd_ws, void* stream) {
+    return nf::mlp_backward<double>(weights, x, nf::MlpDims{(int)N, D_in, H, L, D_out}, hidden_act, out_act, fwd_ws, out, g_out,
+                                    g_weights, g_x, bwd_ws, (cudaStream_t)stream);
+}
+size_t nf_bernoulli_workspace_bytes(int elem_size) { return (size_t)nf::kBernBlocks * (size_t)elem_size; }
+int nf_bernoulli_ll_f32(const float* x, const float* p, int64_t count, float log_eps, float g_scale, float* out_sum,
+                        float* g_p, float* workspace, void* stream) {
+    return nf::bernoulli_entry<float>(x, p, count, log_eps, g_scale, out_sum, g_p, workspace, (cudaStream_t)stream);
+}
+int nf_bernoulli_ll_f64(const double* x, const double* p, int64_t count, double log_eps, double g_scale, double* out_sum,
+                        double* g_p, double* workspace, void* stream) {
+    return nf::bernoulli_entry<double>(x, p, count, log_eps, g_scale, out_sum, g_p, workspace, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -152,3 +152,66 @@ def amortised_backward(z0, ls0, W, U, zK, tsave, g_zK, g_logdet, log_eps=1e-7):
                 ctypes.c_void_p(st))
     _lib.check(rc)
     return g_mu0, g_ls0, g_W, g_U, g_B
+
+
+ACT_IDS = {None: 0, 'none': 0, 'identity': 0, 'relu': 1, 'sigmoid': 2, 'rbf': 3}
+
+
+def mlp_forward(weights, x, dims, hidden_act='relu', out_act=None):
+    """nf_mlp_forward_*: weights flat [P], x [N, D_in] -> (out [N, D_out], fwd_ws)."""
+    lib = _lib.load()
+    if not x.is_cuda:
+        raise NFError('mlp_forward needs CUDA tensors (no CPU fallback)')
+    dtype, dev = x.dtype, x.device
+    _same(dtype, dev, weights, x)
+    D_in, H, L, D_out = dims
+    N = x.shape[0]
+    if x.shape[1] != D_in or weights.numel() != lib.nf_mlp_param_count(D_in, H, L, D_out):
+        raise NFError('mlp_forward: shape mismatch (x %r, weights %d)' % (tuple(x.shape), weights.numel()))
+    es = _DT[dtype][1]
+    ha, oa = ACT_IDS[hidden_act], ACT_IDS[out_act]
+    ws = torch.empty(max(1, lib.nf_mlp_forward_workspace_bytes(N, D_in, H, L, D_out, ha, es) // es), dtype=dtype, device=dev)
+    out = torch.empty(N, D_out, dtype=dtype, device=dev)
+    fn = getattr(lib, 'nf_mlp_forward_' + _DT[dtype][0])
+    with torch.cuda.device(dev):
+        st = torch.cuda.current_stream(dev).cuda_stream
+        _lib.check(fn(_ptr(weights), _ptr(x), N, D_in, H, L, D_out, ha, oa, _ptr(ws), _ptr(out), ctypes.c_void_p(st)))
+    return out, ws
+
+
+def mlp_backward(weights, x, dims, hidden_act, out_act, fwd_ws, out, g_out, need_gx=False):
+    """nf_mlp_backward_*: -> (g_weights [P], g_x [N, D_in] or None)."""
+    lib = _lib.load()
+    dtype, dev = x.dtype, x.device
+    _same(dtype, dev, weights, x, fwd_ws, out, g_out)
+    D_in, H, L, D_out = dims
+    N = x.shape[0]
+    es = _DT[dtype][1]
+    bws = torch.empty(max(1, lib.nf_mlp_backward_workspace_bytes(N, D_in, H, L, D_out, es) // es), dtype=dtype, device=dev)
+    g_w = torch.empty_like(weights)
+    g_x = torch.empty_like(x) if need_gx else None
+    fn = getattr(lib, 'nf_mlp_backward_' + _DT[dtype][0])
+    with torch.cuda.device(dev):
+        st = torch.cuda.current_stream(dev).cuda_stream
+        _lib.check(fn(_ptr(weights), _ptr(x), N, D_in, H, L, D_out, ACT_IDS[hidden_act], ACT_IDS[out_act], _ptr(fwd_ws),
+                      _ptr(out), _ptr(g_out), _ptr(g_w), _ptr(g_x), _ptr(bws), ctypes.c_void_p(st)))
+    return g_w, g_x
+
+
+def bernoulli_ll(x, p, log_eps=1e-7, g_scale=None):
+    """nf_bernoulli_ll_*: (sum [1], g_p or None) with g_p = g_scale * d sum / d p."""
+    lib = _lib.load()
+    if not p.is_cuda:
+        raise NFError('bernoulli_ll needs CUDA tensors (no CPU fallback)')
+    dtype, dev = p.dtype, p.device
+    _same(dtype, dev, x, p)
+    es, creal = _DT[dtype][1], _DT[dtype][2]
+    ws = torch.empty(lib.nf_bernoulli_workspace_bytes(es) // es, dtype=dtype, device=dev)
+    out = torch.empty(1, dtype=dtype, device=dev)
+    g_p = torch.empty_like(p) if g_scale is not None else None
+    fn = getattr(lib, 'nf_bernoulli_ll_' + _DT[dtype][0])
+    with torch.cuda.device(dev):
+        st = torch.cuda.current_stream(dev).cuda_stream
+        _lib.check(fn(_ptr(x), _ptr(p), p.numel(), creal(log_eps), creal(0.0 if g_scale is None else g_scale),
+                      _ptr(out), _ptr(g_p), _ptr(ws), ctypes.c_void_p(st)))
+    return out, g_p

@@ -6,9 +6,14 @@ the CUDA kernels -- nf_targets.cuh, nf_flow_rows.cu).  ``sample_from_pz`` pushes
 samples through the K planar layers on the GPU.
 """
 import numpy as np
+import torch
 
 from .transformations import sigmoid
 from .flows import planar_flow
+
+
+def _is_t(*xs):
+    return any(isinstance(x, torch.Tensor) for x in xs)
 
 
 def mvn(Z, mu, sigma_diag):                           # distributions.py:10-32
@@ -39,7 +44,10 @@ def log_mvn(Z, mu, log_sigma_diag):                   # distributions.py:35-54
     return const - 0.5 * np.sum(np.matmul(zdiff, siginv) * zdiff, axis=1)
 
 
-log_std_norm = lambda x: -x.shape[1] / 2 * np.log(2 * np.pi) - 0.5 * np.sum(x * x, axis=1)   # :57  # noqa: E731
+def log_std_norm(x):                                  # distributions.py:57
+    if _is_t(x):                                      # inside the GPU objective: stays on the device / on the tape
+        return -x.shape[1] / 2 * np.log(2 * np.pi) - 0.5 * torch.sum(x * x, dim=1)
+    return -x.shape[1] / 2 * np.log(2 * np.pi) - 0.5 * np.sum(x * x, axis=1)
 
 
 def prob_gm(Z, mu, sigma_diag, pi):                   # distributions.py:60-69
@@ -60,6 +68,11 @@ def log_prob_gm(Z, mu, log_sigma_diag, logit_pi):     # distributions.py:72-83
 
 def log_bern_mult(X, p):                              # distributions.py:86-89
     eps = 1e-7
+    if _is_t(X, p):                                   # fused kernel (nf_bernoulli_ll), one scalar for the batch
+        from nfcore import tape
+        p = p if isinstance(p, torch.Tensor) else torch.as_tensor(p)
+        X = torch.as_tensor(X, dtype=p.dtype, device=p.device)
+        return tape.BernoulliLL.apply(X, p, eps)
     return np.sum(X * np.log(eps + p) + (1 - X) * np.log(eps + 1 - p))
 
 
