@@ -1,0 +1,32 @@
+"""Under torchrun (NCCL): the sample-sharded objective equals the single-GPU objective.
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tools/dist_check.py
+"""
+import os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, 'vi-normflows_b200')]
+import numpy as np, torch, torch.distributed as dist
+from nfcore import sharding
+from nfcore.objective import SharedFlowObjective
+
+rank, world = int(os.environ['RANK']), int(os.environ['WORLD_SIZE'])
+torch.cuda.set_device(int(os.environ['LOCAL_RANK']))
+dist.init_process_group('nccl', device_id=torch.device('cuda', int(os.environ['LOCAL_RANK'])))
+rs = np.random.RandomState(0)
+ok = True
+for (K, D, N, target) in ((32, 2, 200003, 'p1'), (8, 16, 5001, ('gaussdiag', np.zeros(16), np.zeros(16) - 0.2))):
+    z0 = rs.randn(N, D)
+    params = np.concatenate([(0.1 + 0.02 * rs.randn(2 * K * D)) / np.sqrt(D / 2), 0.1 * np.ones(K)])
+    for dtype, tol in (('float64', 1e-11), ('float32', 1e-5)):
+        full = SharedFlowObjective(target, K, D, dtype=dtype)
+        F1, g1 = full.value_and_grad(params, z0)
+        lo, hi = sharding.shard_bounds(N, rank, world)
+        sh = SharedFlowObjective(target, K, D, dtype=dtype, process_group=dist.group.WORLD)
+        F2, g2 = sh.value_and_grad(params, z0[lo:hi])
+        eF = abs(F1 - F2) / max(1, abs(F1)); eg = np.abs(g1 - g2).max() / np.abs(g1).max()
+        good = eF <= tol and eg <= tol
+        ok &= good
+        if rank == 0:
+            print('K=%d D=%d N=%d %s world=%d: |dF|=%.2e |dg|=%.2e %s' % (K, D, N, dtype, world, eF, eg, 'OK' if good else 'FAIL'), flush=True)
+dist.barrier()
+dist.destroy_process_group()
+sys.exit(0 if ok else 1)

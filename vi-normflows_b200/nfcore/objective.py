@@ -8,7 +8,7 @@ the GPU.  No CPU fallback: constructing the object without a CUDA device raises.
 import numpy as np
 import torch
 
-from . import ops, semantics as sem
+from . import ops, semantics as sem, sharding
 from ._lib import NFError
 
 _NP2T = {np.dtype('float32'): torch.float32, np.dtype('float64'): torch.float64}
@@ -153,11 +153,7 @@ class SharedFlowObjective:
         """all-reduce (when sharded) + D2H of [F parts | grads]; returns float64 array and global N."""
         n_global = n_local
         if self.group is not None:
-            import torch.distributed as dist
-            cnt = torch.tensor([float(n_local)], dtype=torch.float64, device=self.device)
-            dist.all_reduce(self._res, group=self.group)
-            dist.all_reduce(cnt, group=self.group)
-            n_global = int(cnt.item())
+            n_global = sharding.reduce_sums(self._res, n_local, self.group)
         self._res_host.copy_(self._res, non_blocking=True)
         torch.cuda.current_stream(self.device).synchronize()
         return self._res_host.numpy().astype(np.float64), n_global

@@ -1,0 +1,28 @@
+"""Sample sharding across ranks: who owns which rows, and the one exchange per step.
+
+Monte-Carlo samples (or minibatch rows) are independent, parameters are replicated, and
+every kernel returns SUMS over its local rows.  A step therefore needs exactly one
+all-reduce(sum) of the small result vector [F parts | gradient partials] plus the local row
+count; each rank then divides by the global count and applies the same update.
+Works with any torch.distributed backend (NCCL on the GPUs, gloo in the CPU tests).
+"""
+import torch
+
+
+def shard_bounds(n_rows, rank, world):
+    """Contiguous [lo, hi) slice of `n_rows` rows owned by `rank` (sizes differ by at most one)."""
+    base, rem = divmod(int(n_rows), int(world))
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def reduce_sums(sums, n_local, group=None):
+    """In-place all-reduce(sum) of `sums` (a tensor of per-rank sums) and of the row count.
+    Returns the global row count.  With group=None and no initialised process group it is a no-op."""
+    import torch.distributed as dist
+    if group is None and not (dist.is_available() and dist.is_initialized()):
+        return int(n_local)
+    cnt = torch.tensor([float(n_local)], dtype=torch.float64, device=sums.device)
+    dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group)
+    dist.all_reduce(cnt, op=dist.ReduceOp.SUM, group=group)
+    return int(round(float(cnt.item())))
