@@ -185,8 +185,11 @@ def run_ours(args):
     out = (res[:3], res[3:3 + KD].view(K_LAYERS, DIM), res[3 + KD:3 + 2 * KD].view(K_LAYERS, DIM),
            res[3 + 2 * KD:3 + 2 * KD + K_LAYERS], res[3 + 2 * KD + K_LAYERS:])
 
-    def step(i):
+    def local_step(i):
         ops.planar_elbo(eps[i % N_ROTATE], w_d, s_d, b_d, c_d, TARGET, None, 1e-7, True, out)
+
+    def step(i):
+        local_step(i)
         if world > 1:
             dist.all_reduce(res)
 
@@ -212,9 +215,9 @@ def run_ours(args):
     ms = e0.elapsed_time(e1)
     # keep the GPU busy a little longer so the sampler sees clocks under this load
     t_end = time.time() + 0.6
-    while rank == 0 and time.time() < t_end:
+    while rank == 0 and time.time() < t_end:      # rank-local kernels only: no collective outside the lock-step loop
         for i in range(20):
-            step(i)
+            local_step(i)
         torch.cuda.synchronize()
     clocks = sampler.stop() if sampler else None
     barrier()

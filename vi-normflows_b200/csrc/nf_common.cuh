@@ -43,7 +43,12 @@ template <> struct Mth<float> {
         asm("lop3.b32 %0, %1, 0x80000000, %2, 0x74;" : "=r"(o) : "r"(__float_as_uint(r)), "r"(__float_as_uint(x)));
         return __uint_as_float(o);
     }
-    // accurate variants for the once-per-sample target code
+    // MUFU-based variants for the once-per-sample target code of the hot kernels (rel. error ~1e-6)
+    static __device__ __forceinline__ float fexp(float x) { return ex2(x * 1.4426950408889634f); }
+    static __device__ __forceinline__ float flog(float x) { return lg2(x) * 0.6931471805599453f; }
+    static __device__ __forceinline__ float flog1p(float x) { return lg2(1.0f + x) * 0.6931471805599453f; }   // x in [0,1]
+    static __device__ __forceinline__ float fsqrt(float x) { float y; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+    // accurate variants
     static __device__ __forceinline__ float exp(float x) { return expf(x); }
     static __device__ __forceinline__ float logp(float x) { return logf(x); }
     static __device__ __forceinline__ float log1p(float x) { return log1pf(x); }
@@ -64,6 +69,10 @@ template <> struct Mth<double> {
     static constexpr double kArgScale = 1.0;
     static __device__ __forceinline__ double tanh_pre(double a) { return ::tanh(a); }
     static __device__ __forceinline__ double neg_copysign(double r, double x) { return ::copysign(r, -x); }
+    static __device__ __forceinline__ double fexp(double x) { return ::exp(x); }
+    static __device__ __forceinline__ double flog(double x) { return ::log(x); }
+    static __device__ __forceinline__ double flog1p(double x) { return ::log1p(x); }
+    static __device__ __forceinline__ double fsqrt(double x) { return ::sqrt(x); }
     static __device__ __forceinline__ double exp(double x) { return ::exp(x); }
     static __device__ __forceinline__ double logp(double x) { return ::log(x); }
     static __device__ __forceinline__ double log1p(double x) { return ::log1p(x); }

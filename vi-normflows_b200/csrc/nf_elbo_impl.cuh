@@ -21,6 +21,7 @@
 //     block writes one row of partial sums and a second small kernel adds the rows in a
 //     fixed order (bitwise reproducible for a fixed launch shape).
 #pragma once
+#include <cstdio>
 #include <cstdlib>
 #include <mutex>
 #include "nf_common.cuh"
@@ -33,6 +34,64 @@ constexpr int kElboThreads = 64;
 constexpr int kMaxBlocksPerSM = 16;
 constexpr int kLogEvery = 4;          // layers per MUFU.LG2 (product of 4 factors >= eps^4 = 1e-28: no underflow)
 
+// ---- tensor memory as a per-thread activation stash ---------------------------------------
+// TMEM (256 KB per SM, 128 lanes x 512 32-bit columns) is otherwise idle in this kernel.  A
+// 128-thread block maps thread t to TMEM lane t (warp w owns lanes 32w..32w+31, the only ones
+// tcgen05.ld/st let it touch), so every thread gets `columns` private 32-bit slots: the tanh
+// history of ST samples per thread lives there instead of in shared memory, which roughly
+// doubles the number of samples an SM can keep in flight.  One tcgen05.st / tcgen05.ld moves
+// the ST activations of a layer.
+template <int N> struct TmemVec;
+template <> struct TmemVec<2> {
+    static __device__ __forceinline__ void st(uint32_t a, const float* r) {
+        asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1, %2};" ::"r"(a), "r"(__float_as_uint(r[0])), "r"(__float_as_uint(r[1])) : "memory");
+    }
+    static __device__ __forceinline__ void ld(uint32_t a, float* r) {
+        uint32_t v0, v1;
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0, %1}, [%2];" : "=r"(v0), "=r"(v1) : "r"(a) : "memory");
+        r[0] = __uint_as_float(v0); r[1] = __uint_as_float(v1);
+    }
+};
+template <> struct TmemVec<4> {
+    static __device__ __forceinline__ void st(uint32_t a, const float* r) {
+        asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(__float_as_uint(r[0])),
+                     "r"(__float_as_uint(r[1])), "r"(__float_as_uint(r[2])), "r"(__float_as_uint(r[3])) : "memory");
+    }
+    static __device__ __forceinline__ void ld(uint32_t a, float* r) {
+        uint32_t v0, v1, v2, v3;
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v0), "=r"(v1), "=r"(v2), "=r"(v3) : "r"(a) : "memory");
+        r[0] = __uint_as_float(v0); r[1] = __uint_as_float(v1); r[2] = __uint_as_float(v2); r[3] = __uint_as_float(v3);
+    }
+};
+template <> struct TmemVec<8> {
+    static __device__ __forceinline__ void st(uint32_t a, const float* r) {
+        asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(a),
+                     "r"(__float_as_uint(r[0])), "r"(__float_as_uint(r[1])), "r"(__float_as_uint(r[2])), "r"(__float_as_uint(r[3])),
+                     "r"(__float_as_uint(r[4])), "r"(__float_as_uint(r[5])), "r"(__float_as_uint(r[6])), "r"(__float_as_uint(r[7])) : "memory");
+    }
+    static __device__ __forceinline__ void ld(uint32_t a, float* r) {
+        uint32_t v[8];
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                     : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]) : "r"(a) : "memory");
+#pragma unroll
+        for (int i = 0; i < 8; ++i) r[i] = __uint_as_float(v[i]);
+    }
+};
+// the double instantiation never uses TMEM (ST == 0); these overloads only keep templates well-formed
+template <int N> struct TmemVecT {
+    static __device__ __forceinline__ void st(uint32_t a, const float* r) { TmemVec<N>::st(a, r); }
+    static __device__ __forceinline__ void ld(uint32_t a, float* r) { TmemVec<N>::ld(a, r); }
+    static __device__ __forceinline__ void st(uint32_t, const double*) {}
+    static __device__ __forceinline__ void ld(uint32_t, double*) {}
+};
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__host__ __device__ constexpr int tmem_columns(int n) {       // allocation granule: power of two >= 32
+    int c = 32;
+    while (c < n) c <<= 1;
+    return c;
+}
+
 template <int D> __host__ __device__ constexpr int grad_vals() { return 2 * D + 2; }   // w[D] s[D] b c
 __host__ __device__ constexpr int pad4(int n) { return (n + 3) & ~3; }
 // forward record per layer : w*kappa [D] | b*kappa | s [D]           (padded to a multiple of 4)
@@ -44,6 +103,7 @@ template <int D> __host__ __device__ constexpr int rec_b() { return pad4(2 * D +
 template <typename T>
 struct ElboSmem {
     int lcf, lcb, tp, acc, hist, total;
+    // S = samples per thread whose tanh history lives in shared memory (the rest, if any, is in TMEM)
     __host__ __device__ ElboSmem(int K, int D, int S, int ntp_s, bool bwd, int nthreads) {
         const int V = 2 * D + 2;
         lcf = 0;
@@ -100,16 +160,17 @@ __device__ __forceinline__ void load_samples(const T* __restrict__ eps, long lon
 // One tile = S samples per thread through all K layers (and back).  MASKED is the
 // ragged last tile: samples past N get weight 0 (select, never multiply: a masked
 // sample must not be able to leak NaN/Inf into the sums).
-template <typename T, int D, int S, int TGT, bool BWD, bool MASKED>
+template <typename T, int D, int S, int ST, int NT, int TGT, bool BWD, bool MASKED>
 __device__ __forceinline__ void elbo_tile(const T* __restrict__ eps, long long n0, long long N, int K,
                                           const T* __restrict__ lcf, const T* __restrict__ lcb,
                                           const T* __restrict__ tp, int ntp, T epsv,
-                                          T* __restrict__ hist_t /* hist + tid */, T* __restrict__ acc_w,
-                                          int lane, int my_slot, bool my_own, T& sum_q, T& sum_p) {
+                                          T* __restrict__ hist_t /* hist + tid */, uint32_t taddr,
+                                          T* __restrict__ acc_w, int lane, int my_slot, bool my_own, T& sum_q,
+                                          T& sum_p) {
     using M = Mth<T>;
     constexpr int V = grad_vals<D>();
     constexpr int RF = rec_f<D>(), RB = rec_b<D>();
-    constexpr int NT = kElboThreads;
+    constexpr int SS = S - ST;          // samples whose history goes to shared memory
     const T LOG2PI = (T)1.8378770664093453;
 
     T z[S][D], lq[S], prod[S];
@@ -130,27 +191,31 @@ __device__ __forceinline__ void elbo_tile(const T* __restrict__ eps, long long n
         for (int i = 0; i < RF; ++i) rf[i] = lcf[k * RF + i];
         T ck = (T)0;
         if (!BWD) ck = lcb[k * RB + 2 * D];
+        T tt[S];
 #pragma unroll
         for (int j = 0; j < S; ++j) {
             T a = rf[D];
 #pragma unroll
             for (int d = 0; d < D; ++d) a = M::fma(rf[d], z[j][d], a);
             const T t = M::tanh_pre(a);
+            tt[j] = t;
 #pragma unroll
             for (int d = 0; d < D; ++d) z[j][d] = M::fma(rf[D + 1 + d], t, z[j][d]);
             if (BWD) {
-                hist_t[(k * S + j) * NT] = t;
+                if (j >= ST) hist_t[(k * SS + (j - ST)) * NT] = t;
             } else {
                 const T hp = M::fma(-t, t, (T)1);
                 const T x = M::fma(hp, ck, (T)1);
                 prod[j] *= epsv + M::fabs(x);
             }
         }
+        if (BWD && ST > 0) TmemVecT<ST == 0 ? 2 : ST>::st(taddr + k * ST, tt);
         if (!BWD && ((k % kLogEvery) == kLogEvery - 1 || k == K - 1)) {
 #pragma unroll
             for (int j = 0; j < S; ++j) { lq[j] -= M::log(prod[j]); prod[j] = (T)1; }
         }
     }
+    if (BWD && ST > 0) tmem_wait_st();
     // ---- target: log(eps + target(z_K)) and the reverse seed gz = -d log p / dz ----
     T gz[S][D];
 #pragma unroll
@@ -172,20 +237,27 @@ __device__ __forceinline__ void elbo_tile(const T* __restrict__ eps, long long n
         // The cross-lane reduction of layer k+1's partials (a chain of five dependent
         // shuffles) is issued inside iteration k, next to arithmetic it does not depend on,
         // so an in-order warp can overlap the shuffle latency with the layer math.
-        T vp[V];
+        // TMEM-resident history is fetched one layer ahead (the load issued while layer k+1 is processed is
+        // awaited at the top of layer k).  The loop is unrolled by two so that the "previous layer" partials and
+        // the prefetched activations alternate between two register sets instead of being copied.
+        T va[V], vb[V], ta[ST > 0 ? ST : 1], tb[ST > 0 ? ST : 1];
 #pragma unroll
-        for (int i = 0; i < V; ++i) vp[i] = (T)0;
-        for (int k = K - 1; k >= 0; --k) {
+        for (int i = 0; i < V; ++i) { va[i] = (T)0; vb[i] = (T)0; }
+        if (ST > 0) TmemVecT<ST == 0 ? 2 : ST>::ld(taddr + (K - 1) * ST, ta);
+        auto layer = [&](int k, T (&tc)[ST > 0 ? ST : 1], T (&tn)[ST > 0 ? ST : 1], T (&v)[V], T (&vp)[V]) {
+            if (ST > 0) {
+                tmem_wait_ld();
+                if (k > 0) TmemVecT<ST == 0 ? 2 : ST>::ld(taddr + (k - 1) * ST, tn);
+            }
             T rb[RB];
 #pragma unroll
             for (int i = 0; i < RB; ++i) rb[i] = lcb[k * RB + i];
             const T ck = rb[2 * D], c2 = rb[2 * D + 1];
-            T v[V];
 #pragma unroll
             for (int i = 0; i < V; ++i) v[i] = (T)0;
 #pragma unroll
             for (int j = 0; j < S; ++j) {
-                const T t = hist_t[(k * S + j) * NT];
+                const T t = (j < ST) ? tc[j < ST ? j : 0] : hist_t[(k * SS + (j - ST)) * NT];
 #pragma unroll
                 for (int d = 0; d < D; ++d) z[j][d] = M::fma(-rb[D + d], t, z[j][d]);   // z_{k-1}
                 const T hp = M::fma(-t, t, (T)1);
@@ -213,13 +285,22 @@ __device__ __forceinline__ void elbo_tile(const T* __restrict__ eps, long long n
 #pragma unroll
                 for (int j = 0; j < S; ++j) { lq[j] -= M::log(prod[j]); prod[j] = (T)1; }
             }
+            // cross-lane reduction of layer k+1's partials, issued next to arithmetic it does not depend on
             if (k < K - 1) {
                 warp_reduce_multi<T, V>(vp, lane);
                 if (my_own) acc_w[(k + 1) * V + my_slot] += vp[0];
             }
-#pragma unroll
-            for (int i = 0; i < V; ++i) vp[i] = v[i];
+        };
+        int k = K - 1;
+        for (; k >= 1; k -= 2) {
+            layer(k, ta, tb, va, vb);
+            layer(k - 1, tb, ta, vb, va);
         }
+        T (&vlast)[V] = (k == 0) ? va : vb;      // where layer 0's partials end up (odd K: the tail call below)
+        if (k == 0) layer(0, ta, tb, va, vb);
+        T vp[V];
+#pragma unroll
+        for (int i = 0; i < V; ++i) vp[i] = vlast[i];
         warp_reduce_multi<T, V>(vp, lane);
         if (my_own) acc_w[my_slot] += vp[0];
     }
@@ -227,8 +308,8 @@ __device__ __forceinline__ void elbo_tile(const T* __restrict__ eps, long long n
     for (int j = 0; j < S; ++j) sum_q += (MASKED && !ok[j]) ? (T)0 : lq[j];
 }
 
-template <typename T, int D, int S, int TGT, bool BWD>
-__global__ void __launch_bounds__(kElboThreads)
+template <typename T, int D, int S, int ST, int NT, int TGT, bool BWD>
+__global__ void __launch_bounds__(NT)
 elbo_shared_kernel(const T* __restrict__ eps, long long N, int K,
                    const T* __restrict__ w, const T* __restrict__ s,
                    const T* __restrict__ b, const T* __restrict__ c,
@@ -237,11 +318,11 @@ elbo_shared_kernel(const T* __restrict__ eps, long long N, int K,
     using M = Mth<T>;
     constexpr int V = grad_vals<D>();
     constexpr int RF = rec_f<D>(), RB = rec_b<D>();
-    constexpr int NT = kElboThreads;
+    static_assert(ST == 0 || (NT == 128 && BWD), "the TMEM stash needs one warp per TMEM quadrant");
     extern __shared__ __align__(16) unsigned char smem_raw[];
     T* sm = reinterpret_cast<T*>(smem_raw);
     const int ntp_s = target_smem_count(TGT, D, ntp);
-    const ElboSmem<T> L(K, D, S, ntp_s, BWD, NT);
+    const ElboSmem<T> L(K, D, S - ST, ntp_s, BWD, NT);
     T* lcf = sm + L.lcf;
     T* lcb = sm + L.lcb;
     T* tp = sm + L.tp;
@@ -249,6 +330,14 @@ elbo_shared_kernel(const T* __restrict__ eps, long long N, int K,
     T* hist = sm + L.hist;    // [K][S][NT]
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    __shared__ uint32_t tmem_base_smem;
+    const int tmem_cols = tmem_columns(ST * K);
+    if (ST > 0 && warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                         (uint32_t)__cvta_generic_to_shared(&tmem_base_smem)), "r"(tmem_cols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
 
     for (int k = tid; k < K; k += NT) {
 #pragma unroll
@@ -266,7 +355,13 @@ elbo_shared_kernel(const T* __restrict__ eps, long long N, int K,
     target_prepare<T>(TGT, D, tparams, ntp, tp);
     if (BWD)
         for (int i = tid; i < (NT / kWarp) * K * V; i += NT) acc[i] = (T)0;
+    if (ST > 0) asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
+    uint32_t taddr = 0;
+    if (ST > 0) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        taddr = tmem_base_smem + ((uint32_t)(warp * 32) << 16);     // lane field: this warp's quadrant
+    }
 
     const int my_slot = warp_slot<V>(lane);
     const bool my_own = warp_slot_owner<V>(lane);
@@ -280,11 +375,11 @@ elbo_shared_kernel(const T* __restrict__ eps, long long N, int K,
         const long long base = tile * tile_samples;
         const long long n0 = base + (long long)tid * S;
         if (base + tile_samples <= N)
-            elbo_tile<T, D, S, TGT, BWD, false>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist + tid, acc_w, lane,
-                                                my_slot, my_own, sum_q, sum_p);
+            elbo_tile<T, D, S, ST, NT, TGT, BWD, false>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist + tid, taddr, acc_w,
+                                                        lane, my_slot, my_own, sum_q, sum_p);
         else
-            elbo_tile<T, D, S, TGT, BWD, true>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist + tid, acc_w, lane,
-                                               my_slot, my_own, sum_q, sum_p);
+            elbo_tile<T, D, S, ST, NT, TGT, BWD, true>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist + tid, taddr, acc_w,
+                                                       lane, my_slot, my_own, sum_q, sum_p);
     }
 
     // ---- block partials ----
@@ -309,6 +404,12 @@ elbo_shared_kernel(const T* __restrict__ eps, long long N, int K,
         for (int wi = 0; wi < NT / kWarp; ++wi) { q += red[wi]; p += red[NT / kWarp + wi]; }
         out[K * V] = q;
         out[K * V + 1] = p;
+    }
+    if (ST > 0) {
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();
+        if (warp == 0)
+            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base_smem), "r"(tmem_cols) : "memory");
     }
 }
 
@@ -374,61 +475,104 @@ static inline DevInfo dev_info() {
     return info;
 }
 
-template <typename T, int D, int S, int TGT, bool BWD>
+template <typename T, int D, int S, int ST, int NT, int TGT, bool BWD>
 static int launch_elbo(const T* eps, long long N, int K, const T* w, const T* s, const T* b, const T* c,
                        const T* tparams, int ntp, T epsv, T* partials, int max_blocks, int* nblocks_out,
                        cudaStream_t stream) {
-    auto kern = elbo_shared_kernel<T, D, S, TGT, BWD>;
+    auto kern = elbo_shared_kernel<T, D, S, ST, NT, TGT, BWD>;
     const int ntp_s = target_smem_count(TGT, D, ntp);
-    const ElboSmem<T> L(K, D, S, ntp_s, BWD, kElboThreads);
-    const size_t smem = (size_t)L.total * sizeof(T);
+    const ElboSmem<T> L(K, D, S - ST, ntp_s, BWD, NT);
+    size_t smem = (size_t)L.total * sizeof(T);
     if (smem > 227 * 1024) return NF_ERR_UNSUPPORTED;
+    int tmem_limit = kMaxBlocksPerSM;
+    if (ST > 0) {
+        // at most 512 / columns blocks can hold their TMEM slice at once; pad the shared-memory request so
+        // that the hardware never co-schedules more than that on one SM (an extra block would spin in alloc)
+        if (ST * K > 512) return NF_ERR_UNSUPPORTED;
+        tmem_limit = 512 / tmem_columns(ST * K);
+        const size_t pad = (size_t)(227 * 1024) / (tmem_limit + 1) + 1024;
+        if (smem < pad) smem = pad;
+    }
     NF_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
-    NF_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kElboThreads, smem));
+    if (ST > 0) {
+        // the occupancy calculator reports 1 block/SM for any kernel that allocates TMEM; work the limits out here
+        cudaFuncAttributes fa;
+        NF_CUDA_OK(cudaFuncGetAttributes(&fa, kern));
+        const int by_regs = 65536 / (((fa.numRegs + 7) & ~7) * NT);
+        const int by_smem = (int)((size_t)(227 * 1024) / (smem + fa.sharedSizeBytes + 1024));
+        per_sm = by_regs < by_smem ? by_regs : by_smem;
+    } else {
+        NF_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, NT, smem));
+    }
     if (per_sm < 1) return NF_ERR_UNSUPPORTED;
     if (per_sm > kMaxBlocksPerSM) per_sm = kMaxBlocksPerSM;
+    if (per_sm > tmem_limit) per_sm = tmem_limit;
     const DevInfo di = dev_info();
-    const long long tile = (long long)kElboThreads * S;
+    const long long tile = (long long)NT * S;
     long long ntiles = (N + tile - 1) / tile;
     long long grid = (long long)di.sms * per_sm;
     if (grid > ntiles) grid = ntiles;
     if (grid < 1) grid = 1;
     if (grid > max_blocks) grid = max_blocks;
-    kern<<<(int)grid, kElboThreads, smem, stream>>>(eps, N, K, w, s, b, c, tparams, ntp, epsv, partials);
+    if (getenv("NF_DEBUG"))
+        fprintf(stderr, "[nfcore] elbo launch S=%d ST=%d NT=%d smem=%zu per_sm=%d tmem_limit=%d grid=%lld ntiles=%lld\n", S, ST, NT,
+                smem, per_sm, tmem_limit, grid, ntiles);
+    kern<<<(int)grid, NT, smem, stream>>>(eps, N, K, w, s, b, c, tparams, ntp, epsv, partials);
     NF_CUDA_OK(cudaGetLastError());
     *nblocks_out = (int)grid;
     return NF_OK;
 }
 
-template <typename T> struct SamplesPerThread { static constexpr int big = 8, small = 2; };
-template <> struct SamplesPerThread<double> { static constexpr int big = 4, small = 1; };
+template <typename T> struct SamplesPerThread { static constexpr int big = 8, mid = 4, small = 2; };
+template <> struct SamplesPerThread<double> { static constexpr int big = 4, mid = 2, small = 1; };
 
 template <typename T, int D, int TGT>
 static int dispatch_bwd(bool bwd, const T* eps, long long N, int K, const T* w, const T* s, const T* b, const T* c,
                         const T* tp, int ntp, T epsv, T* partials, int max_blocks, int* nb, cudaStream_t st) {
-    // samples per thread: as many as keep >= 3 blocks of activation history resident per SM;
-    // few samples (latency-bound launches) or very deep chains fall back to the small tile
-    constexpr int SB = (D <= 2) ? SamplesPerThread<T>::big : SamplesPerThread<T>::big / 2;
-    constexpr int SS = SamplesPerThread<T>::small;
-    const ElboSmem<T> Lb(K, D, SB, target_smem_count(TGT, D, ntp), bwd, kElboThreads);
-    const bool big_fits = (size_t)Lb.total * sizeof(T) <= 75 * 1024;
-    const bool enough = N >= (long long)148 * kElboThreads * SB;
-    if (const char* ov = getenv("NF_ELBO_S")) {      // tuning knob: force samples per thread (float builds 2,4,8)
-        const int sv = atoi(ov);
-        if (bwd && sv == 4 && sizeof(T) == 4)
-            return launch_elbo<T, D, (sizeof(T) == 4 ? 4 : SS), TGT, true>(eps, N, K, w, s, b, c, tp, ntp, epsv, partials, max_blocks, nb, st);
-        if (bwd && sv == SS)
-            return launch_elbo<T, D, SS, TGT, true>(eps, N, K, w, s, b, c, tp, ntp, epsv, partials, max_blocks, nb, st);
+    constexpr int NT = kElboThreads;
+    constexpr int SB = SamplesPerThread<T>::big, SM_ = SamplesPerThread<T>::mid, SS = SamplesPerThread<T>::small;
+#define NF_GO(S_, ST_, NT_, BW_) \
+    return launch_elbo<T, D, S_, ST_, NT_, TGT, BW_>(eps, N, K, w, s, b, c, tp, ntp, epsv, partials, max_blocks, nb, st)
+    if (!bwd) {
+        if (N >= (long long)148 * NT * SB) { NF_GO(SB, 0, NT, false); }
+        NF_GO(SS, 0, NT, false);
     }
-    if (bwd) {
-        if (big_fits && enough)
-            return launch_elbo<T, D, SB, TGT, true>(eps, N, K, w, s, b, c, tp, ntp, epsv, partials, max_blocks, nb, st);
-        return launch_elbo<T, D, SS, TGT, true>(eps, N, K, w, s, b, c, tp, ntp, epsv, partials, max_blocks, nb, st);
+    // tuning knob (float, D <= 2): NF_ELBO_CFG="S,ST" picks samples per thread and how many of them keep
+    // their history in TMEM
+    int cs = 0, ct = 0;
+    if (const char* ov = getenv("NF_ELBO_CFG")) sscanf(ov, "%d,%d", &cs, &ct);
+    if constexpr (sizeof(T) == 4 && D <= 2) {
+        if (cs == 8 && ct == 8) { NF_GO(8, 8, 128, true); }
+        if (cs == 8 && ct == 4) { NF_GO(8, 4, 128, true); }
+        if (cs == 7 && ct == 4) { NF_GO(7, 4, 128, true); }
+        if (cs == 6 && ct == 4) { NF_GO(6, 4, 128, true); }
+        if (cs == 5 && ct == 4) { NF_GO(5, 4, 128, true); }
+        if (cs == 4 && ct == 4) { NF_GO(4, 4, 128, true); }
+        if (cs == 4 && ct == 2) { NF_GO(4, 2, 128, true); }
+        if (cs == 8 && ct == 0) { NF_GO(8, 0, NT, true); }
+        if (cs == 4 && ct == 0) { NF_GO(4, 0, NT, true); }
+        if (cs == 2 && ct == 0) { NF_GO(2, 0, NT, true); }
     }
-    if (enough)
-        return launch_elbo<T, D, SB, TGT, false>(eps, N, K, w, s, b, c, tp, ntp, epsv, partials, max_blocks, nb, st);
-    return launch_elbo<T, D, SS, TGT, false>(eps, N, K, w, s, b, c, tp, ntp, epsv, partials, max_blocks, nb, st);
+    // float, D <= 2, enough samples: 128-thread blocks whose tanh history is split between tensor memory and
+    // shared memory (measured best on B200: profiles/r01_sweep_configs.txt)
+    if constexpr (sizeof(T) == 4 && D <= 2) {
+        if (cs == 0 && N >= (long long)148 * 128 * 8) {
+            if (K <= 16) { NF_GO(8, 8, 128, true); }
+            if (K <= 32) { NF_GO(7, 4, 128, true); }
+            if (K <= 64) { NF_GO(7, 4, 128, true); }     // 256 columns, 96 KB: two blocks per SM
+        }
+    }
+    // otherwise: as many samples per thread as keep >= 3 blocks of activation history resident per SM;
+    // short launches (latency-bound) and very deep chains fall back to smaller tiles
+    const int ntp_s = target_smem_count(TGT, D, ntp);
+    const bool enough = N >= (long long)148 * NT * SM_;
+    const ElboSmem<T> Lm(K, D, SM_, ntp_s, true, NT);
+    if (enough && (size_t)Lm.total * sizeof(T) <= 75 * 1024) { NF_GO(SM_, 0, NT, true); }
+    const ElboSmem<T> Ls(K, D, SS, ntp_s, true, NT);
+    if ((size_t)Ls.total * sizeof(T) <= 113 * 1024) { NF_GO(SS, 0, NT, true); }
+    NF_GO(1, 0, NT, true);
+#undef NF_GO
 }
 
 template <typename T, int D>

@@ -49,18 +49,18 @@ template <typename T, bool BWD>
 __device__ __forceinline__ void target_ring(const T* z, T R, T inv_sr, T inv_sx, T eps, T& lp, T* gz) {
     using M = Mth<T>;
     const T z1 = z[0], z2 = z[1];
-    const T n = M::sqrt(z1 * z1 + z2 * z2);
+    const T n = M::fsqrt(z1 * z1 + z2 * z2);
     const T f = (n - R) * inv_sr;
     const T q1 = (z1 - (T)2) * inv_sx, q2 = (z1 + (T)2) * inv_sx;
     const T a1 = (T)-0.5 * q1 * q1, a2 = (T)-0.5 * q2 * q2;
     // log(exp(a1) + exp(a2)) in max + log1p form (same value, no underflow to log(0))
     const T mx = M::fmax(a1, a2);
-    const T ed = M::exp(-M::fabs(a1 - a2));
-    const T lse = mx + M::log1p(ed);
+    const T ed = M::fexp(-M::fabs(a1 - a2));
+    const T lse = mx + M::flog1p(ed);
     const T u = (T)0.5 * f * f - lse;
-    const T dens = M::exp(-u);
+    const T dens = M::fexp(-u);
     const T den = eps + dens;
-    lp = M::logp(den);
+    lp = M::flog(den);
     if (BWD) {
         const T rho = M::div(dens, den);
         const T wbig = M::div((T)1, (T)1 + ed);
@@ -172,7 +172,7 @@ template <typename T, int D, bool BWD> struct Target<T, D, NF_TARGET_MIXDIAG, BW
                 sc[d] = df * tp[G + G * D + g * D + d];
                 q = M::fma(df, sc[d], q);
             }
-            const T e = tp[g] * M::exp((T)-0.5 * q);
+            const T e = tp[g] * M::fexp((T)-0.5 * q);
             dens += e;
             if (BWD) {
 #pragma unroll
@@ -180,7 +180,7 @@ template <typename T, int D, bool BWD> struct Target<T, D, NF_TARGET_MIXDIAG, BW
             }
         }
         const T den = eps + dens;
-        lp = M::logp(den);
+        lp = M::flog(den);
         if (BWD) {
             const T inv = M::div((T)1, den);
 #pragma unroll
@@ -201,9 +201,9 @@ template <typename T, int D, bool BWD> struct Target<T, D, NF_TARGET_GAUSSDIAG, 
             sc[d] = df * tp[1 + D + d];
             q = M::fma(df, sc[d], q);
         }
-        const T dens = M::exp(tp[0] - (T)0.5 * q);
+        const T dens = M::fexp(tp[0] - (T)0.5 * q);
         const T den = eps + dens;
-        lp = M::logp(den);
+        lp = M::flog(den);
         if (BWD) {
             const T rho = M::div(dens, den);
 #pragma unroll
