@@ -99,6 +99,30 @@ int nf_planar_elbo_fwd_bwd_f64(const double* eps, int64_t N, int D, int K,
                                double* out_F, double* g_w, double* g_s, double* g_b, double* g_c,
                                void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---------------------------------------------------------------------------
+ * Host-buffer form of the shared-parameter free energy: the call the reference's
+ * `objective(params, t)` / `gradient(params, t)` make, with everything in host memory
+ * (get_data.py:97-115: NumPy parameters, freshly drawn NumPy z0).  A session owns the device
+ * staging for one (max_samples, D, K, element size); nf_session_elbo_host_* sends the samples in
+ * chunks on a copy stream, runs the objective kernel on each chunk as it lands, sums all partial
+ * rows once, copies the result back and returns when `out_host` is valid (it synchronises).
+ *   eps_host          : [N][D]; pinned memory lets the copies overlap the kernels
+ *   layer_consts_host : [w (K*D) | s (K*D) | b (K) | c (K)]
+ *   out_host          : [out_F (3) | g_w (K*D) | g_s (K*D) | g_b (K) | g_c (K)]  (gradients only
+ *                       when backward != 0)
+ * Session creation / destruction allocate and free device and pinned memory; the per-call entry
+ * points do not.  A session is not thread-safe.
+ * ------------------------------------------------------------------------- */
+typedef struct nf_session nf_session;
+int nf_session_create(nf_session** out, int64_t max_samples, int D, int K, int elem_size);
+void nf_session_destroy(nf_session* s);
+int nf_session_elbo_host_f32(nf_session* s, const float* eps_host, int64_t N, const float* layer_consts_host,
+                             int target_id, const float* target_params_host, int n_target_params,
+                             float log_eps, int backward, float* out_host);
+int nf_session_elbo_host_f64(nf_session* s, const double* eps_host, int64_t N, const double* layer_consts_host,
+                             int target_id, const double* target_params_host, int n_target_params,
+                             double log_eps, int backward, double* out_host);
+
 /* nf_planar_elbo_fwd_bwd_f32 for callers that must not allocate device memory.  It has no
  * counterpart in the reference (which never touches a GPU); it exists for host programs
  * whose device memory was all handed out at start-up, or for which cudaMalloc/cudaFree --

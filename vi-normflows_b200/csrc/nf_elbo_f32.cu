@@ -23,6 +23,18 @@ int nf_planar_elbo_fwd_bwd_f32(const float* eps, int64_t N, int D, int K, const 
                                  out_F, g_w, g_s, g_b, g_c, workspace, workspace_bytes, stream);
 }
 
+// ---- host-buffer sessions (see nfcore.h) ----
+int nf_session_create(nf_session** out, int64_t max_samples, int D, int K, int elem_size) {
+    return nf::session_create(reinterpret_cast<nf::Session**>(out), max_samples, D, K, elem_size);
+}
+void nf_session_destroy(nf_session* s) { nf::session_free(reinterpret_cast<nf::Session*>(s)); }
+int nf_session_elbo_host_f32(nf_session* s, const float* eps_host, int64_t N, const float* layer_consts_host, int target_id,
+                             const float* target_params_host, int n_target_params, float log_eps, int backward,
+                             float* out_host) {
+    return nf::session_elbo_host<float>(reinterpret_cast<nf::Session*>(s), eps_host, N, layer_consts_host, target_id,
+                                        target_params_host, n_target_params, log_eps, backward, out_host);
+}
+
 }  // extern "C"
 
 // ---------------------------------------------------------------------------------------

@@ -11,4 +11,11 @@ int nf_planar_elbo_fwd_bwd_f64(const double* eps, int64_t N, int D, int K, const
                                   out_F, g_w, g_s, g_b, g_c, workspace, workspace_bytes, stream);
 }
 
+int nf_session_elbo_host_f64(nf_session* s, const double* eps_host, int64_t N, const double* layer_consts_host, int target_id,
+                             const double* target_params_host, int n_target_params, double log_eps, int backward,
+                             double* out_host) {
+    return nf::session_elbo_host<double>(reinterpret_cast<nf::Session*>(s), eps_host, N, layer_consts_host, target_id,
+                                         target_params_host, n_target_params, log_eps, backward, out_host);
+}
+
 }  // extern "C"

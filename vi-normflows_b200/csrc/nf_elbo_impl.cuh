@@ -330,6 +330,10 @@ elbo_shared_kernel(const T* __restrict__ eps, long long N, int K,
     T* hist = sm + L.hist;    // [K][S][NT]
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // programmatic dependent launch: this grid may start while the previous kernel on the stream drains;
+    // nothing produced by earlier work (constants, the workspace rows a row kernel is still reading) is
+    // touched before this returns
+    asm volatile("griddepcontrol.wait;" ::: "memory");
 
     __shared__ uint32_t tmem_base_smem;
     const int tmem_cols = tmem_columns(ST * K);
@@ -421,6 +425,7 @@ template <typename T>
 __global__ void elbo_finalize_kernel(const T* __restrict__ partials, int nrows, int K, int D, int Vk, int off_s,
                                      int off_b, int bwd, T* __restrict__ out_F, T* __restrict__ g_w,
                                      T* __restrict__ g_s, T* __restrict__ g_b, T* __restrict__ g_c) {
+    asm volatile("griddepcontrol.wait;" ::: "memory");     // see elbo_shared_kernel
     const size_t row = (size_t)K * Vk + 2;
     const int lane = threadIdx.x & 31;
     const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -457,6 +462,19 @@ __global__ void elbo_finalize_kernel(const T* __restrict__ partials, int nrows, 
         p = warp_sum(p);
         if (lane == 0) out_F[0] = q - p;
     }
+}
+
+// Launch with the programmatic-stream-serialization attribute: the kernel's launch latency and prologue
+// overlap the tail of its predecessor; the kernel itself waits (griddepcontrol.wait) before touching memory.
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
 }
 
 struct DevInfo { int sms; int ok; };
@@ -518,8 +536,7 @@ static int launch_elbo(const T* eps, long long N, int K, const T* w, const T* s,
     if (getenv("NF_DEBUG"))
         fprintf(stderr, "[nfcore] elbo launch S=%d ST=%d NT=%d smem=%zu per_sm=%d tmem_limit=%d grid=%lld ntiles=%lld\n", S, ST, NT,
                 smem, per_sm, tmem_limit, grid, ntiles);
-    kern<<<(int)grid, NT, smem, stream>>>(eps, N, K, w, s, b, c, tparams, ntp, epsv, partials);
-    NF_CUDA_OK(cudaGetLastError());
+    NF_CUDA_OK(launch_pdl(kern, dim3((unsigned)grid), dim3(NT), smem, stream, eps, N, K, w, s, b, c, tparams, ntp, epsv, partials));
     *nblocks_out = (int)grid;
     return NF_OK;
 }
@@ -642,17 +659,19 @@ static inline int max_grid_blocks() {
     return (di.sms > 0 ? di.sms : 148) * kMaxBlocksPerSM;
 }
 
+struct ElboRowLayout { int Vk, off_s, off_b; };
+static inline ElboRowLayout elbo_row_layout(int D) {
+    if (D <= 4) return {2 * D + 2, D, 2 * D};
+    const int Dp = (D + 3) & ~3;
+    return {wide_vk(D), Dp, 2 * Dp};
+}
+
 template <typename T>
-static int elbo_entry(const T* eps, int64_t N, int D, int K, const T* w, const T* s, const T* b, const T* c,
-                      int target_id, const T* tparams, int ntp, T epsv, T* out_F, T* g_w, T* g_s, T* g_b, T* g_c,
-                      void* workspace, size_t workspace_bytes, void* stream_) {
-    cudaStream_t stream = (cudaStream_t)stream_;
+static int elbo_validate(const T* eps, int64_t N, int D, int K, const T* w, const T* s, const T* b, const T* c,
+                         int target_id, const T* tparams, int ntp) {
     if (!eps && N > 0) return NF_ERR_INVALID;
     if ((reinterpret_cast<uintptr_t>(eps) & 15) != 0) return NF_ERR_INVALID;   // vector loads
-    if (N < 0 || D < 1 || K < 1 || !w || !s || !b || !c || !out_F || !workspace) return NF_ERR_INVALID;
-    const bool any_g = g_w || g_s || g_b || g_c;
-    const bool all_g = g_w && g_s && g_b && g_c;
-    if (any_g && !all_g) return NF_ERR_INVALID;
+    if (N < 0 || D < 1 || K < 1 || !w || !s || !b || !c) return NF_ERR_INVALID;
     if (target_id == NF_TARGET_MIXDIAG) {
         if (!tparams || ntp < 1 + 2 * D || ntp % (1 + 2 * D) != 0) return NF_ERR_INVALID;
     } else if (target_id == NF_TARGET_GAUSSDIAG) {
@@ -664,31 +683,165 @@ static int elbo_entry(const T* eps, int64_t N, int D, int K, const T* w, const T
     }
     const DevInfo di = dev_info();
     if (!di.ok) return NF_ERR_NO_DEVICE;
-    if (workspace_bytes < nf_planar_elbo_workspace_bytes(K, D, (int)sizeof(T))) return NF_ERR_WORKSPACE;
-    T* partials = reinterpret_cast<T*>(workspace);
+    return NF_OK;
+}
+
+// objective kernel only: fills `partials` rows [0, *nrows)
+template <typename T>
+static int elbo_main(bool bwd, const T* eps, int64_t N, int D, int K, const T* w, const T* s, const T* b, const T* c,
+                     int target_id, const T* tparams, int ntp, T epsv, T* partials, int* nrows, cudaStream_t stream) {
     const int max_blocks = max_grid_blocks();
-    int nb = 0, rc;
-    int Vk = 2 * D + 2, off_s = D, off_b = 2 * D;
     switch (D) {
-        case 1: rc = dispatch_target<T, 1>(target_id, all_g, eps, N, K, w, s, b, c, tparams, ntp, epsv, partials, max_blocks, &nb, stream); break;
-        case 2: rc = dispatch_target<T, 2>(target_id, all_g, eps, N, K, w, s, b, c, tparams, ntp, epsv, partials, max_blocks, &nb, stream); break;
-        case 3: rc = dispatch_target<T, 3>(target_id, all_g, eps, N, K, w, s, b, c, tparams, ntp, epsv, partials, max_blocks, &nb, stream); break;
-        case 4: rc = dispatch_target<T, 4>(target_id, all_g, eps, N, K, w, s, b, c, tparams, ntp, epsv, partials, max_blocks, &nb, stream); break;
+        case 1: return dispatch_target<T, 1>(target_id, bwd, eps, N, K, w, s, b, c, tparams, ntp, epsv, partials, max_blocks, nrows, stream);
+        case 2: return dispatch_target<T, 2>(target_id, bwd, eps, N, K, w, s, b, c, tparams, ntp, epsv, partials, max_blocks, nrows, stream);
+        case 3: return dispatch_target<T, 3>(target_id, bwd, eps, N, K, w, s, b, c, tparams, ntp, epsv, partials, max_blocks, nrows, stream);
+        case 4: return dispatch_target<T, 4>(target_id, bwd, eps, N, K, w, s, b, c, tparams, ntp, epsv, partials, max_blocks, nrows, stream);
         default:
-            Vk = wide_vk(D); off_s = (D + 3) & ~3; off_b = 2 * off_s;
             if (target_id == NF_TARGET_GAUSSDIAG)
-                rc = dispatch_wide<T, NF_TARGET_GAUSSDIAG>(all_g, eps, N, D, K, w, s, b, c, tparams, ntp, epsv, partials, &nb, stream);
-            else
-                rc = dispatch_wide<T, NF_TARGET_MIXDIAG>(all_g, eps, N, D, K, w, s, b, c, tparams, ntp, epsv, partials, &nb, stream);
-            break;
+                return dispatch_wide<T, NF_TARGET_GAUSSDIAG>(bwd, eps, N, D, K, w, s, b, c, tparams, ntp, epsv, partials, nrows, stream);
+            return dispatch_wide<T, NF_TARGET_MIXDIAG>(bwd, eps, N, D, K, w, s, b, c, tparams, ntp, epsv, partials, nrows, stream);
     }
-    if (rc != NF_OK) return rc;
-    const size_t row = (size_t)K * Vk + 2;
+}
+
+// fixed-order sum of `nrows` partial rows into the caller's outputs
+template <typename T>
+static int elbo_finish(bool bwd, const T* partials, int nrows, int D, int K, T* out_F, T* g_w, T* g_s, T* g_b, T* g_c,
+                       cudaStream_t stream) {
+    const ElboRowLayout L = elbo_row_layout(D);
+    const size_t row = (size_t)K * L.Vk + 2;
     size_t fblocks = (row + 7) / 8;
     if (fblocks > 592) fblocks = 592;
-    elbo_finalize_kernel<T><<<(int)fblocks, 256, 0, stream>>>(partials, nb, K, D, Vk, off_s, off_b, all_g ? 1 : 0,
-                                                              out_F, g_w, g_s, g_b, g_c);
-    NF_CUDA_OK(cudaGetLastError());
+    NF_CUDA_OK(launch_pdl(elbo_finalize_kernel<T>, dim3((unsigned)fblocks), dim3(256), 0, stream, partials, nrows, K, D, L.Vk,
+                          L.off_s, L.off_b, bwd ? 1 : 0, out_F, g_w, g_s, g_b, g_c));
+    return NF_OK;
+}
+
+template <typename T>
+static int elbo_entry(const T* eps, int64_t N, int D, int K, const T* w, const T* s, const T* b, const T* c,
+                      int target_id, const T* tparams, int ntp, T epsv, T* out_F, T* g_w, T* g_s, T* g_b, T* g_c,
+                      void* workspace, size_t workspace_bytes, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (!out_F || !workspace) return NF_ERR_INVALID;
+    const bool any_g = g_w || g_s || g_b || g_c;
+    const bool all_g = g_w && g_s && g_b && g_c;
+    if (any_g && !all_g) return NF_ERR_INVALID;
+    int rc = elbo_validate<T>(eps, N, D, K, w, s, b, c, target_id, tparams, ntp);
+    if (rc != NF_OK) return rc;
+    if (workspace_bytes < nf_planar_elbo_workspace_bytes(K, D, (int)sizeof(T))) return NF_ERR_WORKSPACE;
+    T* partials = reinterpret_cast<T*>(workspace);
+    int nb = 0;
+    rc = elbo_main<T>(all_g, eps, N, D, K, w, s, b, c, target_id, tparams, ntp, epsv, partials, &nb, stream);
+    if (rc != NF_OK) return rc;
+    return elbo_finish<T>(all_g, partials, nb, D, K, out_F, g_w, g_s, g_b, g_c, stream);
+}
+
+// ---- host-buffer session: H2D of the samples overlapped with the objective kernel -------------
+// The reference's objective takes host arrays (get_data.py:97: params and the freshly drawn z0 live
+// in NumPy).  A session owns the device-side staging for that call shape: the samples are sent in
+// chunks on a copy stream while the compute stream runs the objective kernel on the chunks that
+// have landed; all chunks write partial-sum rows into one workspace and a single row kernel sums them.
+constexpr int kSessionMaxChunks = 8;
+constexpr int64_t kSessionChunkSamples = 1 << 18;
+
+struct Session {
+    int dev = 0, D = 0, K = 0;
+    size_t elem = 0;
+    int64_t cap = 0;
+    cudaStream_t s_copy = nullptr, s_comp = nullptr;
+    cudaEvent_t ev[kSessionMaxChunks] = {};
+    void *eps_dev = nullptr, *lc_dev = nullptr, *tp_dev = nullptr, *out_dev = nullptr, *ws_dev = nullptr;
+    void *lc_pin = nullptr, *out_pin = nullptr;
+    size_t ws_chunk_bytes = 0, tp_cap = 0;
+    int n_out = 0;
+};
+
+static inline void session_free(Session* S) {
+    if (!S) return;
+    cudaSetDevice(S->dev);
+    if (S->s_comp) cudaStreamSynchronize(S->s_comp);
+    for (auto& e : S->ev) if (e) cudaEventDestroy(e);
+    if (S->s_copy) cudaStreamDestroy(S->s_copy);
+    if (S->s_comp) cudaStreamDestroy(S->s_comp);
+    cudaFree(S->eps_dev); cudaFree(S->lc_dev); cudaFree(S->tp_dev); cudaFree(S->out_dev); cudaFree(S->ws_dev);
+    cudaFreeHost(S->lc_pin); cudaFreeHost(S->out_pin);
+    delete S;
+}
+
+static inline int session_create(Session** out, int64_t max_samples, int D, int K, int elem_size) {
+    if (!out || max_samples < 1 || D < 1 || K < 1 || (elem_size != 4 && elem_size != 8)) return NF_ERR_INVALID;
+    const DevInfo di = dev_info();
+    if (!di.ok) return NF_ERR_NO_DEVICE;
+    Session* S = new Session();
+    cudaGetDevice(&S->dev);
+    S->D = D; S->K = K; S->elem = (size_t)elem_size; S->cap = max_samples;
+    S->n_out = 3 + 2 * K * D + 2 * K;
+    S->ws_chunk_bytes = nf_planar_elbo_workspace_bytes(K, D, elem_size);
+    S->tp_cap = 4096;
+    cudaError_t e = cudaSuccess;
+    auto ok = [&](cudaError_t r) { if (e == cudaSuccess && r != cudaSuccess) e = r; };
+    ok(cudaStreamCreateWithFlags(&S->s_copy, cudaStreamNonBlocking));
+    ok(cudaStreamCreateWithFlags(&S->s_comp, cudaStreamNonBlocking));
+    for (auto& ev : S->ev) ok(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    ok(cudaMalloc(&S->eps_dev, (size_t)max_samples * D * S->elem));
+    ok(cudaMalloc(&S->lc_dev, (size_t)(2 * K * D + 2 * K) * S->elem));
+    ok(cudaMalloc(&S->tp_dev, S->tp_cap * S->elem));
+    ok(cudaMalloc(&S->out_dev, (size_t)S->n_out * S->elem));
+    ok(cudaMalloc(&S->ws_dev, S->ws_chunk_bytes * kSessionMaxChunks));
+    ok(cudaMallocHost(&S->lc_pin, (size_t)(2 * K * D + 2 * K + S->tp_cap) * S->elem));
+    ok(cudaMallocHost(&S->out_pin, (size_t)S->n_out * S->elem));
+    if (e != cudaSuccess) { nf_set_last_cuda_error(e); session_free(S); return NF_ERR_CUDA; }
+    *out = S;
+    return NF_OK;
+}
+
+template <typename T>
+static int session_elbo_host(Session* S, const T* eps_host, int64_t N, const T* lc_host, int target_id,
+                             const T* tp_host, int ntp, T epsv, int backward, T* out_host) {
+    if (!S || S->elem != sizeof(T) || N < 0 || N > S->cap || !lc_host || !out_host || (N > 0 && !eps_host)) return NF_ERR_INVALID;
+    if (ntp < 0 || (size_t)ntp > S->tp_cap || (ntp > 0 && !tp_host)) return NF_ERR_INVALID;
+    NF_CUDA_OK(cudaSetDevice(S->dev));
+    const int D = S->D, K = S->K;
+    const int nlc = 2 * K * D + 2 * K;
+    T* lc_pin = reinterpret_cast<T*>(S->lc_pin);
+    for (int i = 0; i < nlc; ++i) lc_pin[i] = lc_host[i];
+    for (int i = 0; i < ntp; ++i) lc_pin[nlc + i] = tp_host[i];
+    T* lc = reinterpret_cast<T*>(S->lc_dev);
+    T* tp = reinterpret_cast<T*>(S->tp_dev);
+    NF_CUDA_OK(cudaMemcpyAsync(lc, lc_pin, (size_t)nlc * sizeof(T), cudaMemcpyHostToDevice, S->s_comp));
+    if (ntp > 0) NF_CUDA_OK(cudaMemcpyAsync(tp, lc_pin + nlc, (size_t)ntp * sizeof(T), cudaMemcpyHostToDevice, S->s_comp));
+    const T *w = lc, *s = lc + K * D, *b = lc + 2 * K * D, *c = lc + 2 * K * D + K;
+    T* eps = reinterpret_cast<T*>(S->eps_dev);
+    int rc = elbo_validate<T>(eps, N, D, K, w, s, b, c, target_id, ntp > 0 ? tp : nullptr, ntp);
+    if (rc != NF_OK) return rc;
+    int nch = (int)((N + kSessionChunkSamples - 1) / kSessionChunkSamples);
+    if (nch < 1) nch = 1;
+    if (nch > kSessionMaxChunks) nch = kSessionMaxChunks;
+    int64_t per = ((N + nch - 1) / nch + 1023) & ~(int64_t)1023;       // keeps every chunk 16-byte aligned
+    const ElboRowLayout L = elbo_row_layout(D);
+    const size_t row = (size_t)K * L.Vk + 2;
+    T* partials = reinterpret_cast<T*>(S->ws_dev);
+    int rows = 0;
+    for (int i = 0; i < nch; ++i) {
+        const int64_t lo = (int64_t)i * per;
+        const int64_t n = (lo >= N) ? 0 : ((N - lo < per) ? N - lo : per);
+        if (n <= 0 && i > 0) break;
+        if (n > 0) NF_CUDA_OK(cudaMemcpyAsync(eps + lo * D, eps_host + lo * D, (size_t)n * D * sizeof(T), cudaMemcpyHostToDevice, S->s_copy));
+        NF_CUDA_OK(cudaEventRecord(S->ev[i], S->s_copy));
+        NF_CUDA_OK(cudaStreamWaitEvent(S->s_comp, S->ev[i], 0));
+        int nb = 0;
+        rc = elbo_main<T>(backward != 0, eps + lo * D, n, D, K, w, s, b, c, target_id, ntp > 0 ? tp : nullptr, ntp, epsv,
+                          partials + (size_t)rows * row, &nb, S->s_comp);
+        if (rc != NF_OK) return rc;
+        rows += nb;
+    }
+    T* out = reinterpret_cast<T*>(S->out_dev);
+    rc = elbo_finish<T>(backward != 0, partials, rows, D, K, out, out + 3, out + 3 + K * D, out + 3 + 2 * K * D,
+                        out + 3 + 2 * K * D + K, S->s_comp);
+    if (rc != NF_OK) return rc;
+    NF_CUDA_OK(cudaMemcpyAsync(S->out_pin, out, (size_t)S->n_out * sizeof(T), cudaMemcpyDeviceToHost, S->s_comp));
+    NF_CUDA_OK(cudaStreamSynchronize(S->s_comp));
+    const T* op = reinterpret_cast<const T*>(S->out_pin);
+    for (int i = 0; i < S->n_out; ++i) out_host[i] = op[i];
     return NF_OK;
 }
 

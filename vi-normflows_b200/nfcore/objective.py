@@ -5,10 +5,12 @@ NumPy in / NumPy out, exactly like the reference's ``objective(params, t)`` and
 ``gradient(params, t)``; the arithmetic over the samples happens in libnfcore on
 the GPU.  No CPU fallback: constructing the object without a CUDA device raises.
 """
+import ctypes
+
 import numpy as np
 import torch
 
-from . import ops, semantics as sem, sharding
+from . import _lib, ops, semantics as sem, sharding
 from ._lib import NFError
 
 _NP2T = {np.dtype('float32'): torch.float32, np.dtype('float64'): torch.float64}
@@ -93,6 +95,60 @@ class SharedFlowObjective:
         self._eps_pinned = None
         self.group = process_group
         self.launches = 0
+        self._session = None
+        self._session_cap = 0
+        self._tparams_host = None if tparams is None else np.ascontiguousarray(tparams.astype(self.np_dtype))
+
+    def __del__(self):
+        try:
+            if self._session is not None:
+                _lib.load().nf_session_destroy(self._session)
+                self._session = None
+        except Exception:
+            pass
+
+    # -- host-buffer path: nf_session_elbo_host_* (chunked H2D overlapped with the kernels) ----
+    def _host_eval(self, params, z0, backward):
+        """z0 in host memory (NumPy array or CPU torch tensor, pinned or not) -> float64 result vector
+        [F parts (3) | g_w | g_s | g_b | g_c] (sums) and (W, U)."""
+        lib = _lib.load()
+        if isinstance(z0, torch.Tensor):
+            if z0.dtype != self.dtype or not z0.is_contiguous():
+                z0 = z0.to(self.dtype).contiguous()
+            ptr, N = z0.data_ptr(), z0.shape[0]
+            shape = tuple(z0.shape)
+        else:
+            z0 = np.ascontiguousarray(z0, dtype=self.np_dtype)
+            ptr, N = z0.ctypes.data, z0.shape[0]
+            shape = z0.shape
+        if len(shape) != 2 or shape[1] != self.D:
+            raise NFError('z0 must have shape (N, %d), got %r' % (self.D, shape))
+        K, D = self.K, self.D
+        if self._session is None or N > self._session_cap:
+            if self._session is not None:
+                lib.nf_session_destroy(self._session)
+                self._session = None
+            cap = max(int(N), 1)
+            h = ctypes.c_void_p()
+            with torch.cuda.device(self.device):
+                _lib.check(lib.nf_session_create(ctypes.byref(h), cap, D, K, self.np_dtype.itemsize))
+            self._session, self._session_cap = h, cap
+        W, U, B = sem.unpack(np.asarray(params, dtype=np.float64), K, D)
+        S, c = sem.forward(W, U, self.semantics)
+        lc = np.concatenate([W.ravel(), S.ravel(), B, c]).astype(self.np_dtype)
+        out = np.empty(3 + self.n_lc, dtype=self.np_dtype)
+        tp = self._tparams_host
+        fn = lib.nf_session_elbo_host_f32 if self.np_dtype == np.float32 else lib.nf_session_elbo_host_f64
+        creal = ctypes.c_float if self.np_dtype == np.float32 else ctypes.c_double
+        rc = fn(self._session, ctypes.c_void_p(ptr), N, ctypes.c_void_p(lc.ctypes.data), ops.TARGET_IDS[self.target_name],
+                ctypes.c_void_p(tp.ctypes.data) if tp is not None else None, 0 if tp is None else tp.size,
+                creal(self.log_eps), 1 if backward else 0, ctypes.c_void_p(out.ctypes.data))
+        _lib.check(rc)
+        self.launches += 2
+        return out.astype(np.float64), N, W, U
+
+    def _is_host(self, z0):
+        return self.group is None and not (isinstance(z0, torch.Tensor) and z0.is_cuda)
 
     # -- sample staging ------------------------------------------------------------------
     def stage_samples(self, z0):
@@ -159,9 +215,12 @@ class SharedFlowObjective:
         return self._res_host.numpy().astype(np.float64), n_global
 
     def value_and_grad(self, params, z0):
-        eps_dev = self.stage_samples(z0)
-        W, U = self._launch(params, eps_dev, True)
-        res, n = self._fetch(eps_dev.shape[0])
+        if self._is_host(z0):
+            res, n, W, U = self._host_eval(params, z0, True)
+        else:
+            eps_dev = self.stage_samples(z0)
+            W, U = self._launch(params, eps_dev, True)
+            res, n = self._fetch(eps_dev.shape[0])
         K, D = self.K, self.D
         g_w = res[3:3 + K * D].reshape(K, D)
         g_s = res[3 + K * D:3 + 2 * K * D].reshape(K, D)
@@ -171,6 +230,9 @@ class SharedFlowObjective:
         return res[0] / n, sem.pack(dW, dU, dB) / n
 
     def value(self, params, z0):
+        if self._is_host(z0):
+            res, n, _, _ = self._host_eval(params, z0, False)
+            return res[0] / max(n, 1)
         eps_dev = self.stage_samples(z0)
         self._launch(params, eps_dev, False)
         res, n = self._fetch(eps_dev.shape[0])
@@ -178,6 +240,9 @@ class SharedFlowObjective:
 
     def metrics(self, params, z0):
         """(mean log q_K, mean log p) -- get_data.py:80-95 ``other_metrics``."""
+        if self._is_host(z0):
+            res, n, _, _ = self._host_eval(params, z0, False)
+            return res[1] / max(n, 1), res[2] / max(n, 1)
         eps_dev = self.stage_samples(z0)
         self._launch(params, eps_dev, False)
         res, n = self._fetch(eps_dev.shape[0])
