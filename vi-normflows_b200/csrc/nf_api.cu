@@ -28,9 +28,9 @@ int nf_built_for_sm(void) { return 100; }
 int nf_check_device(void) {
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return NF_ERR_NO_DEVICE;
-    cudaDeviceProp p;
-    if (cudaGetDeviceProperties(&p, dev) != cudaSuccess) return NF_ERR_NO_DEVICE;
-    return p.major == 10 ? NF_OK : NF_ERR_NO_DEVICE;
+    int major = 0;     // attribute query: cheap (cudaGetDeviceProperties takes milliseconds)
+    if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess) return NF_ERR_NO_DEVICE;
+    return major == 10 ? NF_OK : NF_ERR_NO_DEVICE;
 }
 
 }  // extern "C"

@@ -484,10 +484,11 @@ static inline DevInfo dev_info() {
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return {0, 0};
     if (dev != cached_dev) {
-        cudaDeviceProp p;
-        if (cudaGetDeviceProperties(&p, dev) != cudaSuccess) return {0, 0};
-        info.sms = p.multiProcessorCount;
-        info.ok = (p.major == 10);
+        int sms = 0, major = 0;
+        if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return {0, 0};
+        if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess) return {0, 0};
+        info.sms = sms;
+        info.ok = (major == 10);
         cached_dev = dev;
     }
     return info;

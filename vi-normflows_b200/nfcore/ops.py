@@ -19,10 +19,16 @@ def _ptr(t):
     return ctypes.c_void_p(t.data_ptr()) if t is not None else ctypes.c_void_p(0)
 
 
+_checked_devices = set()
+
+
 def require_cuda():
     if not torch.cuda.is_available():
         raise NFError('no CUDA device: libnfcore has no CPU fallback')
-    _lib.check(_lib.load().nf_check_device())
+    dev = torch.cuda.current_device()
+    if dev not in _checked_devices:
+        _lib.check(_lib.load().nf_check_device())
+        _checked_devices.add(dev)
 
 
 _workspaces = {}
