@@ -227,6 +227,16 @@ int nf_bernoulli_ll_f32(const float* x, const float* p, int64_t count, float log
 int nf_bernoulli_ll_f64(const double* x, const double* p, int64_t count, double log_eps, double g_scale,
                         double* out_sum, double* g_p, double* workspace, void* stream);
 
+/* Tensor-core GEMM used by the MLP entry points above, exposed for testing and reuse:
+ *   C[m][n] = act( sum_k A[m][k] B[n][k] + bias[n] ),  A: [M][K] (lda), B: [N][K] (ldb), float32.
+ * TMA tile loads, tcgen05.mma kind::tf32 with an in-shared-memory hi/lo split of both operands
+ * (three MMAs per k-step) so that results stay at float32 accuracy; accumulator in TMEM.
+ * C (ldc) and/or its transpose CT[n][m] (ldct) are written; act: 0 none, 1 relu, 2 sigmoid.
+ * lda, ldb must be multiples of 4 and A, B 16-byte aligned, else NF_ERR_UNSUPPORTED.
+ * (The reference's counterpart is the np.matmul chain of nn_models.py:59-84.) */
+int nf_gemm_tn_tf32x3(const float* A, int64_t lda, const float* B, int64_t ldb, int M, int N, int K,
+                      float* C, int64_t ldc, float* CT, int64_t ldct, const float* bias, int act, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

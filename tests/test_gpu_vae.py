@@ -38,12 +38,13 @@ def test_feedforward_forward_matches_reference():
     assert _rel(out32, g['out']) <= 1e-4
 
 
-@pytest.mark.parametrize('hidden,out_act', [('relu', None), ('relu', 'sigmoid'), ('rbf', None)])
-def test_mlp_backward_matches_autograd(hidden, out_act):
+@pytest.mark.parametrize('hidden,out_act,dims,N', [
+    ('relu', None, (37, 24, 3, 19), 150), ('relu', 'sigmoid', (37, 24, 3, 19), 150), ('rbf', None, (37, 24, 3, 19), 150),
+    # shapes the tensor-core (tcgen05, TF32x3) path takes: every dimension a multiple of 4, batch >= 128
+    ('relu', None, (784, 64, 3, 1376), 384), ('relu', 'sigmoid', (40, 64, 3, 784), 256), ('relu', None, (64, 64, 1, 64), 1000)])
+def test_mlp_backward_matches_autograd(hidden, out_act, dims, N):
     from nfcore import ops
     torch.manual_seed(0)
-    dims = (37, 24, 3, 19)
-    N = 150
     dev = 'cuda:0'
     P = (dims[0] * dims[1] + dims[1]) + (dims[3] * dims[1] + dims[3]) + (dims[2] - 1) * (dims[1] ** 2 + dims[1])
     w = (0.3 * torch.randn(P, dtype=torch.float64)).requires_grad_(True)
@@ -72,6 +73,32 @@ def test_mlp_backward_matches_autograd(hidden, out_act):
         g_w, g_x = ops.mlp_backward(wd, xd, dims, hidden, out_act, ws, out, gd, need_gx=True)
         assert _rel(g_w.cpu().double().numpy(), gw_ref.numpy()) <= tol
         assert _rel(g_x.cpu().double().numpy(), gx_ref.numpy()) <= tol
+
+
+@pytest.mark.parametrize('M,N,K,act', [(128, 64, 32, 0), (300, 100, 40, 1), (4096, 64, 784, 2), (64, 784, 4096, 0)])
+def test_tensor_core_gemm_is_float32_accurate(M, N, K, act):
+    """nf_gemm_tn_tf32x3 (TMA + tcgen05 TF32 with the hi/lo split) against a float64 matmul."""
+    import ctypes
+    import nfcore
+    lib = nfcore.load()
+    torch.manual_seed(M + N + K)
+    dev = 'cuda:0'
+    A = torch.randn(M, K, device=dev)
+    B = torch.randn(N, K, device=dev) / K ** 0.5
+    bias = torch.randn(N, device=dev)
+    C = torch.full((M, N), float('nan'), device=dev)
+    CT = torch.full((N, M), float('nan'), device=dev)
+    p = lambda t: ctypes.c_void_p(t.data_ptr())
+    rc = lib.nf_gemm_tn_tf32x3(p(A), K, p(B), K, M, N, K, p(C), N, p(CT), M, p(bias), act,
+                               ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == 0
+    torch.cuda.synchronize()
+    ref = A.double() @ B.double().T + bias.double()
+    ref = torch.relu(ref) if act == 1 else (torch.sigmoid(ref) if act == 2 else ref)
+    assert _rel(C.double().cpu().numpy(), ref.cpu().numpy()) <= 5e-5
+    assert torch.equal(C, CT.T)
+    # a single TF32 pass would be ~5e-4: the split really is in effect
+    assert _rel(C.double().cpu().numpy(), ref.cpu().numpy()) < 1e-4
 
 
 def test_bernoulli_ll_matches_oracle():

@@ -1,0 +1,294 @@
+// Tensor-core GEMM for the flow-VAE MLP (nn_models.py:59-84 and its reverse pass), sm_100a:
+// TMA tile loads -> shared memory -> tcgen05.mma (kind::tf32) -> TMEM accumulator -> fused epilogue.
+//
+//   C[m][n] = epi( sum_k A[m][k] * B[n][k] )       A: [M][K], B: [N][K], both row-major (K contiguous)
+//
+// FP32 parity on TF32 tensor cores: the reference computes in float64 and the float32 mode must
+// stay within 1e-4, which one TF32 pass (10-bit mantissa) does not.  Every operand tile is therefore
+// split in shared memory into hi = x with the low 13 mantissa bits cleared (exact in TF32) and
+// lo = x - hi, and each k-step issues three MMAs into the same accumulator:
+//   hi_a*hi_b + lo_a*hi_b + hi_a*lo_b     (the dropped lo*lo term is ~2^-22 relative).
+// The split is elementwise, so it is indifferent to the 128-byte swizzle TMA applied to the tile.
+//
+// Warp roles (256 threads, one 128 x 64 output tile per CTA):
+//   warp 0    TMA producer: per stage one A box (128 rows x 32 floats) and one B box (64 x 32)
+//   warp 1    TMEM allocation + MMA issue (one elected lane), tcgen05.commit to free stages
+//   warps 4-7 split the landed tiles (generic proxy -> fence.proxy.async), then the epilogue:
+//             tcgen05.ld of the accumulator, bias / activation / activation-derivative mask, stores of
+//             C and (optionally) of its transpose for the weight-gradient GEMMs.
+#include <cuda.h>
+#include <cudaTypedefs.h>
+#include "nf_common.cuh"
+
+namespace nf {
+namespace tc {
+
+constexpr int BM = 128, BN = 64, BK = 32;          // tile (BK floats = 128 bytes = one swizzle row)
+constexpr int STAGES = 3;
+constexpr int A_BYTES = BM * BK * 4, B_BYTES = BN * BK * 4;
+constexpr int STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;      // hi + lo of both operands
+constexpr int THREADS = 256;
+constexpr int SPLIT_THREADS = 192;                  // warps 2-7 split; warps 4-7 also run the epilogue
+constexpr int TMEM_COLS = 64;
+
+enum { EPI_ACT_NONE = 0, EPI_ACT_RELU = 1, EPI_ACT_SIGMOID = 2 };
+enum { EPI_MASK_NONE = 0, EPI_MASK_RELU = 1, EPI_MASK_SIGMOID = 2 };   // multiply by act'(saved output)
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    while (!mbar_try_wait(bar, parity)) {}
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+                     smem_u32(dst)), "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar)) : "memory");
+}
+// K-major, 128-byte swizzle: rows are 128 B apart inside an 8-row atom, atoms 1024 B apart
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr >> 4) & 0x3FFF);         // start address
+    d |= (uint64_t)1 << 16;                         // leading byte offset (unused for swizzled K-major)
+    d |= (uint64_t)(1024 >> 4) << 32;               // stride byte offset: next 8-row atom
+    d |= (uint64_t)1 << 46;                         // descriptor version (Blackwell)
+    d |= (uint64_t)2 << 61;                         // SWIZZLE_128B
+    return d;
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, bool accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc),
+        "r"((uint32_t)accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+struct Params {
+    int M, N, K;
+    float* C; long long ldc;             // [M][N] or null
+    float* CT; long long ldct;           // [N][M] or null
+    const float* bias;                   // [N] or null
+    int act;                             // EPI_ACT_*
+    const float* mask_src; long long ldm; int mask;     // multiply by act'(mask_src[m][n])
+};
+
+__global__ void __launch_bounds__(THREADS, 1)
+gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, Params p) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    __shared__ uint64_t full_bar[STAGES], split_bar[STAGES], empty_bar[STAGES], acc_bar;
+    __shared__ uint32_t tmem_base;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+    const int nkb = (p.K + BK - 1) / BK;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&split_bar[s], SPLIT_THREADS);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(&acc_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base)), "r"(TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_d = tmem_base;
+
+    if (warp == 0) {
+        // ---------------- TMA producer ----------------
+        if (lane == 0) {
+            for (int kb = 0; kb < nkb; ++kb) {
+                const int s = kb % STAGES, it = kb / STAGES;
+                if (it > 0) mbar_wait(&empty_bar[s], (it - 1) & 1);
+                uint8_t* st = smem + (size_t)s * STAGE_BYTES;
+                mbar_expect_tx(&full_bar[s], A_BYTES + B_BYTES);
+                tma_load_2d(st, &map_a, kb * BK, m0, &full_bar[s]);                  // A hi slot (raw data)
+                tma_load_2d(st + 2 * A_BYTES, &map_b, kb * BK, n0, &full_bar[s]);    // B hi slot (raw data)
+            }
+        }
+    } else if (warp == 1) {
+        // ---------------- MMA issuer ----------------
+        // instruction descriptor: D=f32, A=B=tf32, both K-major, N=64, M=128
+        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+        for (int kb = 0; kb < nkb; ++kb) {
+            const int s = kb % STAGES, it = kb / STAGES;
+            mbar_wait(&split_bar[s], it & 1);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            if (lane == 0) {
+                const uint32_t a_hi = smem_u32(smem + (size_t)s * STAGE_BYTES);
+                const uint32_t a_lo = a_hi + A_BYTES;
+                const uint32_t b_hi = a_hi + 2 * A_BYTES;
+                const uint32_t b_lo = b_hi + B_BYTES;
+#pragma unroll
+                for (int k = 0; k < BK / 8; ++k) {
+                    const uint32_t off = k * 32;       // 8 tf32 = 32 bytes along K inside the swizzle row
+                    umma_tf32(tmem_d, umma_desc(a_hi + off), umma_desc(b_hi + off), idesc, (kb | k) != 0);
+                    umma_tf32(tmem_d, umma_desc(a_lo + off), umma_desc(b_hi + off), idesc, true);
+                    umma_tf32(tmem_d, umma_desc(a_hi + off), umma_desc(b_lo + off), idesc, true);
+                }
+                umma_commit(&empty_bar[s]);                 // stage reusable once these MMAs have read it
+                if (kb == nkb - 1) umma_commit(&acc_bar);   // accumulator complete
+            }
+            __syncwarp();
+        }
+    } else {
+        // ---------------- split hi/lo (warps 2-7), then epilogue (warps 4-7) ----------------
+        const int t = threadIdx.x - 64;
+        for (int kb = 0; kb < nkb; ++kb) {
+            const int s = kb % STAGES, it = kb / STAGES;
+            mbar_wait(&full_bar[s], it & 1);
+            uint8_t* st = smem + (size_t)s * STAGE_BYTES;
+            // A: hi in place at [0, A_BYTES), lo at [A_BYTES, 2 A_BYTES); B likewise after 2 A_BYTES
+#pragma unroll 4
+            for (int i = t; i < (A_BYTES + B_BYTES) / 16; i += SPLIT_THREADS) {
+                const bool isA = i < A_BYTES / 16;
+                uint8_t* hi = isA ? st + (size_t)i * 16 : st + 2 * A_BYTES + (size_t)(i - A_BYTES / 16) * 16;
+                uint8_t* lo = hi + (isA ? A_BYTES : B_BYTES);
+                float4 v = *reinterpret_cast<float4*>(hi);
+                float4 h, l;
+                h.x = __uint_as_float(__float_as_uint(v.x) & 0xFFFFE000u); l.x = v.x - h.x;
+                h.y = __uint_as_float(__float_as_uint(v.y) & 0xFFFFE000u); l.y = v.y - h.y;
+                h.z = __uint_as_float(__float_as_uint(v.z) & 0xFFFFE000u); l.z = v.z - h.z;
+                h.w = __uint_as_float(__float_as_uint(v.w) & 0xFFFFE000u); l.w = v.w - h.w;
+                *reinterpret_cast<float4*>(hi) = h;
+                *reinterpret_cast<float4*>(lo) = l;
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy writes -> visible to UMMA
+            mbar_arrive(&split_bar[s]);
+        }
+        // epilogue: warp q = warp - 4 owns TMEM lanes 32q .. 32q+31 = rows m0 + 32q + lane
+        if (warp >= 4) {
+        mbar_wait(&acc_bar, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const int q = warp - 4;
+        const int m = m0 + 32 * q + lane;
+#pragma unroll
+        for (int c0 = 0; c0 < BN; c0 += 16) {
+            uint32_t r[16];
+            const uint32_t taddr = tmem_d + ((uint32_t)(32 * q) << 16) + (uint32_t)c0;
+            asm volatile(
+                "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+                  "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                : "r"(taddr) : "memory");
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const int n = n0 + c0 + i;
+                float v = __uint_as_float(r[i]);
+                if (n < p.N) {
+                    if (p.bias) v += p.bias[n];
+                    if (p.act == EPI_ACT_RELU) v = v > 0.f ? v : 0.f;
+                    else if (p.act == EPI_ACT_SIGMOID) v = 1.f / (1.f + expf(-v));
+                    if (m < p.M) {
+                        if (p.mask != EPI_MASK_NONE) {
+                            const float y = p.mask_src[(long long)m * p.ldm + n];
+                            v *= (p.mask == EPI_MASK_RELU) ? (y > 0.f ? 1.f : 0.f) : y * (1.f - y);
+                        }
+                        if (p.C) p.C[(long long)m * p.ldc + n] = v;
+                        if (p.CT) p.CT[(long long)n * p.ldct + m] = v;
+                    }
+                }
+            }
+        }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 1)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(TMEM_COLS) : "memory");
+}
+
+static PFN_cuTensorMapEncodeTiled get_encoder() {
+    static PFN_cuTensorMapEncodeTiled fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qr) == cudaSuccess && qr == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled>(p);
+    }
+    return fn;
+}
+
+// row-major [rows][cols] float matrix with leading dimension ld (elements); box = box_rows x 32 columns.
+// Encoding a map costs several microseconds on the host; the MLP re-uses the same buffers step after
+// step (the framework's caching allocator hands the same addresses back), so maps are memoised.
+struct MapKey { const float* base; long long rows, cols, ld; int box_rows; };
+static bool make_map(CUtensorMap* map, const float* base, long long rows, long long cols, long long ld, int box_rows) {
+    constexpr int kCache = 128;
+    static thread_local MapKey keys[kCache];
+    static thread_local CUtensorMap vals[kCache];
+    static thread_local int used = 0, next = 0;
+    for (int i = 0; i < used; ++i) {
+        const MapKey& k = keys[i];
+        if (k.base == base && k.rows == rows && k.cols == cols && k.ld == ld && k.box_rows == box_rows) { *map = vals[i]; return true; }
+    }
+    PFN_cuTensorMapEncodeTiled enc = get_encoder();
+    if (!enc) return false;
+    cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t gstride[1] = {(cuuint64_t)ld * 4};
+    cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    if (enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstride, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+        return false;
+    const int slot = used < kCache ? used++ : (next++ % kCache);
+    keys[slot] = MapKey{base, rows, cols, ld, box_rows};
+    vals[slot] = *map;
+    return true;
+}
+
+}  // namespace tc
+
+// C = epi(A B^T); returns NF_ERR_UNSUPPORTED when TMA cannot describe the operands (the caller then
+// uses the CUDA-core GEMM).  A: [M][K] ld lda, B: [N][K] ld ldb.
+int tc_gemm_f32(const float* A, long long lda, const float* B, long long ldb, int M, int N, int K, float* C, long long ldc,
+                float* CT, long long ldct, const float* bias, int act, const float* mask_src, long long ldm, int mask,
+                cudaStream_t st) {
+    if (M < 1 || N < 1 || K < 1) return NF_ERR_INVALID;
+    if ((lda % 4) || (ldb % 4) || ((uintptr_t)A & 15) || ((uintptr_t)B & 15)) return NF_ERR_UNSUPPORTED;   // 16-byte strides
+    CUtensorMap ma, mb;
+    if (!tc::make_map(&ma, A, M, K, lda, tc::BM) || !tc::make_map(&mb, B, N, K, ldb, tc::BN)) return NF_ERR_UNSUPPORTED;
+    tc::Params p{M, N, K, C, ldc, CT, ldct, bias, act, mask_src, ldm, mask};
+    const size_t smem = (size_t)tc::STAGES * tc::STAGE_BYTES + 1024;
+    static bool attr_done = false;
+    if (!attr_done) {
+        NF_CUDA_OK(cudaFuncSetAttribute(tc::gemm_tf32x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_done = true;
+    }
+    dim3 grid((N + tc::BN - 1) / tc::BN, (M + tc::BM - 1) / tc::BM);
+    tc::gemm_tf32x3_kernel<<<grid, tc::THREADS, smem, st>>>(ma, mb, p);
+    NF_CUDA_OK(cudaGetLastError());
+    return NF_OK;
+}
+
+}  // namespace nf
+
+extern "C" int nf_gemm_tn_tf32x3(const float* A, int64_t lda, const float* B, int64_t ldb, int M, int N, int K, float* C,
+                                 int64_t ldc, float* CT, int64_t ldct, const float* bias, int act, void* stream) {
+    return nf::tc_gemm_f32(A, lda, B, ldb, M, N, K, C, ldc, CT, ldct, bias, act, nullptr, 0, 0, (cudaStream_t)stream);
+}

@@ -7,9 +7,15 @@
 // kept sample-major [N][H] so that every layer is C[m][n] = sum_k A[m][k] W[n][k] with both
 // operands contiguous along k; the flat weight vector has exactly the reference's layout
 // (nn_models.py:59-80): W1 (H x D_in) | b1 | {W_l (H x H) | b_l} x (L-1) | W_out (D_out x H) | b_out.
+#include <cstdlib>
 #include "nf_common.cuh"
 
 namespace nf {
+
+// tensor-core GEMM (nf_gemm_tc.cu): C = epi(A B^T), both operands K-contiguous
+int tc_gemm_f32(const float* A, long long lda, const float* B, long long ldb, int M, int N, int K, float* C, long long ldc,
+                float* CT, long long ldct, const float* bias, int act, const float* mask_src, long long ldm, int mask,
+                cudaStream_t st);
 
 enum { ACT_NONE = 0, ACT_RELU = 1, ACT_SIGMOID = 2, ACT_RBF = 3 };   // rbf: exp(-x^2) (nn_models.py:175)
 
@@ -171,6 +177,30 @@ static int launch_gemm(const T* a, long long sam, long long sak, const T* b, lon
     return NF_OK;
 }
 
+
+// out[c][r] = in[r][c]   (32x32 tiles through shared memory; both sides coalesced)
+template <typename T>
+__global__ void transpose_kernel(const T* __restrict__ in, int R, int Ccols, T* __restrict__ out) {
+    __shared__ T tile[32][33];
+    const int r0 = blockIdx.y * 32, c0 = blockIdx.x * 32;
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int r = r0 + i, c = c0 + threadIdx.x;
+        tile[i][threadIdx.x] = (r < R && c < Ccols) ? in[(long long)r * Ccols + c] : (T)0;
+    }
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int c = c0 + i, r = r0 + threadIdx.x;
+        if (c < Ccols && r < R) out[(long long)c * R + r] = tile[threadIdx.x][i];
+    }
+}
+template <typename T>
+static int launch_transpose(const T* in, int R, int Ccols, T* out, cudaStream_t st) {
+    dim3 grid((Ccols + 31) / 32, (R + 31) / 32), block(32, 8);
+    transpose_kernel<T><<<grid, block, 0, st>>>(in, R, Ccols, out);
+    NF_CUDA_OK(cudaGetLastError());
+    return NF_OK;
+}
+
 struct MlpDims { int N, D_in, H, L, D_out; };
 static inline long long mlp_param_count(const MlpDims& d) {       // nn_models.py:16-19
     return ((long long)d.D_in * d.H + d.H) + ((long long)d.D_out * d.H + d.D_out) + (long long)(d.L - 1) * ((long long)d.H * d.H + d.H);
@@ -178,21 +208,64 @@ static inline long long mlp_param_count(const MlpDims& d) {       // nn_models.p
 constexpr int kSplits = 32;      // split-K factor of the weight-gradient GEMMs (contraction over the batch)
 
 // forward workspace: L hidden activation buffers [N][H] (+ L pre-activation buffers for rbf)
+// (the tensor-core path also keeps the transposed activations [L][H][N] and x^T [D_in][N])
 static inline size_t mlp_fwd_ws_elems(const MlpDims& d, int hidden_act) {
-    return (size_t)d.L * d.N * d.H * (hidden_act == ACT_RBF ? 2 : 1);
+    return (size_t)d.L * d.N * d.H * 2 + (size_t)d.D_in * d.N;
 }
 // backward workspace: two ping-pong dz buffers [N][max(H, D_out)] + split-K partials of the largest dW
 static inline size_t mlp_bwd_ws_elems(const MlpDims& d) {
     const size_t wide = (size_t)max(d.H, d.D_out);
     const size_t maxw = (size_t)max((long long)d.H * d.D_in, max((long long)d.D_out * d.H, (long long)d.H * d.H));
-    return 2 * (size_t)d.N * wide + (size_t)kSplits * maxw;
+    return 4 * (size_t)d.N * wide + (size_t)(kSplits + 1) * maxw;      // dz x2, dz^T x2, W^T, split-K partials
 }
+
+static inline bool mlp_use_tc(const MlpDims& d, int hidden_act, int out_act, size_t elem) {
+    if (elem != 4 || getenv("NF_MLP_SIMT")) return false;
+    if (hidden_act != ACT_RELU && hidden_act != ACT_NONE) return false;
+    if (out_act == ACT_RBF) return false;
+    return d.N % 4 == 0 && d.D_in % 4 == 0 && d.H % 4 == 0 && d.D_out % 4 == 0 && d.N >= 128;
+}
+
+// ---- tensor-core path (float32): every GEMM is C = A B^T with K-contiguous operands; the epilogues
+// also write the transposed activations / gradients the weight-gradient GEMMs contract over ----
+static int mlp_forward_tc(const float* wts, const float* x, MlpDims d, int hidden_act, int out_act, float* ws, float* out,
+                          cudaStream_t st) {
+    const size_t layer = (size_t)d.N * d.H;
+    float* acts = ws;
+    float* actsT = ws + (size_t)d.L * layer;
+    float* xT = ws + 2 * (size_t)d.L * layer;
+    int rc = launch_transpose<float>(x, d.N, d.D_in, xT, st);
+    if (rc != NF_OK) return rc;
+    const float* in = x;
+    int kin = d.D_in;
+    const float* p = wts;
+    for (int l = 0; l < d.L; ++l) {
+        const float* W = p;
+        const float* bvec = p + (size_t)d.H * kin;
+        rc = tc_gemm_f32(in, kin, W, kin, d.N, d.H, kin, acts + (size_t)l * layer, d.H, actsT + (size_t)l * layer, d.N, bvec,
+                         hidden_act, nullptr, 0, 0, st);
+        if (rc != NF_OK) return rc;
+        p = bvec + d.H;
+        in = acts + (size_t)l * layer;
+        kin = d.H;
+    }
+    const float* W = p;
+    const float* bvec = p + (size_t)d.D_out * d.H;
+    return tc_gemm_f32(in, d.H, W, d.H, d.N, d.D_out, d.H, out, d.D_out, nullptr, 0, bvec, out_act, nullptr, 0, 0, st);
+}
+
+static int mlp_backward_tc(const float* wts, const float* x, MlpDims d, int hidden_act, int out_act, const float* fws,
+                           const float* out, const float* g_out, float* g_wts, float* g_x, float* bws, cudaStream_t st);
+
 
 template <typename T>
 static int mlp_forward(const T* wts, const T* x, MlpDims d, int hidden_act, int out_act, T* ws, T* out, cudaStream_t st) {
     if (d.N < 0 || d.D_in < 1 || d.H < 1 || d.L < 1 || d.D_out < 1 || !wts || !ws || (d.N > 0 && (!x || !out))) return NF_ERR_INVALID;
     if (hidden_act < 0 || hidden_act > ACT_RBF || out_act < 0 || out_act > ACT_RBF) return NF_ERR_INVALID;
     if (d.N == 0) return NF_OK;
+    if constexpr (sizeof(T) == 4) {
+        if (mlp_use_tc(d, hidden_act, out_act, sizeof(T))) return mlp_forward_tc(wts, x, d, hidden_act, out_act, ws, out, st);
+    }
     const bool rbf = hidden_act == ACT_RBF;
     const size_t layer = (size_t)d.N * d.H;
     T* pre = rbf ? ws + (size_t)d.L * layer : nullptr;
@@ -220,12 +293,16 @@ static int mlp_backward(const T* wts, const T* x, MlpDims d, int hidden_act, int
                         const T* g_out, T* g_wts, T* g_x, T* bws, cudaStream_t st) {
     if (d.N < 1 || !wts || !x || !fws || !out || !g_out || !g_wts || !bws) return NF_ERR_INVALID;
     if (out_act == ACT_RBF) return NF_ERR_UNSUPPORTED;
+    if constexpr (sizeof(T) == 4) {
+        if (mlp_use_tc(d, hidden_act, out_act, sizeof(T)))
+            return mlp_backward_tc(wts, x, d, hidden_act, out_act, fws, out, g_out, g_wts, g_x, bws, st);
+    }
     const bool rbf = hidden_act == ACT_RBF;
     const size_t layer = (size_t)d.N * d.H;
     const size_t wide = (size_t)max(d.H, d.D_out);
     T* dz_a = bws;
     T* dz_b = bws + (size_t)d.N * wide;
-    T* split_ws = bws + 2 * (size_t)d.N * wide;
+    T* split_ws = bws + 4 * (size_t)d.N * wide + (size_t)max((long long)d.H * d.D_in, max((long long)d.D_out * d.H, (long long)d.H * d.H));
     const int eb = 1184;
     // parameter offsets
     const long long P = mlp_param_count(d);
@@ -267,6 +344,58 @@ static int mlp_backward(const T* wts, const T* x, MlpDims d, int hidden_act, int
         } else if (g_x) {
             rc = launch_gemm<T>(other, d.H, 1, wts + off, kin, 1, g_x, d.D_in, d.N, d.D_in, d.H, nullptr, ACT_NONE, nullptr, 1, nullptr, st);
             if (rc != NF_OK) return rc;
+        }
+    }
+    return NF_OK;
+}
+
+static int mlp_backward_tc(const float* wts, const float* x, MlpDims d, int hidden_act, int out_act, const float* fws,
+                           const float* out, const float* g_out, float* g_wts, float* g_x, float* bws, cudaStream_t st) {
+    const size_t layer = (size_t)d.N * d.H;
+    const size_t wide = (size_t)max(d.H, d.D_out);
+    const float* acts = fws;
+    const float* actsT = fws + (size_t)d.L * layer;
+    const float* xT = fws + 2 * (size_t)d.L * layer;
+    float* dz_cur = bws;                                  // [N][<=wide]
+    float* dz_oth = bws + (size_t)d.N * wide;
+    float* dzT_cur = bws + 2 * (size_t)d.N * wide;        // [<=wide][N]
+    float* dzT_oth = bws + 3 * (size_t)d.N * wide;
+    float* WT = bws + 4 * (size_t)d.N * wide;             // transposed weight scratch
+    const int mask = hidden_act == ACT_RELU ? 1 : 0;
+    const long long P = mlp_param_count(d);
+    long long off = P - ((long long)d.D_out * d.H + d.D_out);
+    int rc;
+    // ---- output layer: dz = g_out * act'(out) ----
+    act_backward_kernel<float><<<1184, 256, 0, st>>>(g_out, out, (long long)d.N * d.D_out, out_act, dz_cur);
+    NF_CUDA_OK(cudaGetLastError());
+    if ((rc = launch_transpose<float>(dz_cur, d.N, d.D_out, dzT_cur, st)) != NF_OK) return rc;
+    // dW_out[j][h] = sum_n dz^T[j][n] a^T[h][n]
+    if ((rc = tc_gemm_f32(dzT_cur, d.N, actsT + (size_t)(d.L - 1) * layer, d.N, d.D_out, d.H, d.N, g_wts + off, d.H, nullptr, 0,
+                          nullptr, 0, nullptr, 0, 0, st)) != NF_OK) return rc;
+    colsum_kernel<float><<<(d.D_out + 31) / 32, 256, 0, st>>>(dz_cur, d.N, d.D_out, g_wts + off + (long long)d.D_out * d.H);
+    NF_CUDA_OK(cudaGetLastError());
+    // dz_{L-1}[n][h] = (sum_j dz[n][j] W_out[j][h]) * act'(a_{L-1}[n][h])
+    if ((rc = launch_transpose<float>(wts + off, d.D_out, d.H, WT, st)) != NF_OK) return rc;
+    if ((rc = tc_gemm_f32(dz_cur, d.D_out, WT, d.D_out, d.N, d.H, d.D_out, dz_oth, d.H, dzT_oth, d.N, nullptr, 0,
+                          acts + (size_t)(d.L - 1) * layer, d.H, mask, st)) != NF_OK) return rc;
+    { float* t = dz_cur; dz_cur = dz_oth; dz_oth = t; t = dzT_cur; dzT_cur = dzT_oth; dzT_oth = t; }
+    for (int l = d.L - 1; l >= 0; --l) {
+        const int kin = l == 0 ? d.D_in : d.H;
+        off -= (long long)d.H * kin + d.H;
+        const float* inT = l == 0 ? xT : actsT + (size_t)(l - 1) * layer;
+        // dW_l[j][k] = sum_n dz^T[j][n] in^T[k][n]
+        if ((rc = tc_gemm_f32(dzT_cur, d.N, inT, d.N, d.H, kin, d.N, g_wts + off, kin, nullptr, 0, nullptr, 0, nullptr, 0, 0, st)) != NF_OK) return rc;
+        colsum_kernel<float><<<(d.H + 31) / 32, 256, 0, st>>>(dz_cur, d.N, d.H, g_wts + off + (long long)d.H * kin);
+        NF_CUDA_OK(cudaGetLastError());
+        if (l > 0 || g_x) {
+            if ((rc = launch_transpose<float>(wts + off, d.H, kin, WT, st)) != NF_OK) return rc;      // [kin][H]
+            if (l > 0) {
+                if ((rc = tc_gemm_f32(dz_cur, d.H, WT, d.H, d.N, kin, d.H, dz_oth, kin, dzT_oth, d.N, nullptr, 0,
+                                      acts + (size_t)(l - 1) * layer, d.H, mask, st)) != NF_OK) return rc;
+                float* t = dz_cur; dz_cur = dz_oth; dz_oth = t; t = dzT_cur; dzT_cur = dzT_oth; dzT_oth = t;
+            } else {
+                if ((rc = tc_gemm_f32(dz_cur, d.H, WT, d.H, d.N, kin, d.H, g_x, kin, nullptr, 0, nullptr, 0, nullptr, 0, 0, st)) != NF_OK) return rc;
+            }
         }
     }
     return NF_OK;
