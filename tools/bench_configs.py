@@ -82,7 +82,7 @@ def main():
     enc, dec, encode, decode, unpack, logp = _mnist_closures(K, D)
     X = (np.random.RandomState(2).rand(Bsz, 784) < 0.13).astype(np.float32)
     p = np.random.RandomState(3).randn(enc.D + dec.D) * 0.05
-    F = optimization.make_free_energy(logp, X, D, K, encode, decode, 10000, Bsz, dtype=torch.float32, batch_iter=lambda t: X)
+    F = optimization.make_free_energy(logp, X, D, K, encode, decode, 10000, Bsz, dtype=torch.float32)
     objective, gradient = optimization.gradient_create(F, D, Bsz, unpack, dtype=torch.float32)
     for _ in range(3): gradient(p, 0)
     torch.cuda.synchronize(); t0 = time.perf_counter()

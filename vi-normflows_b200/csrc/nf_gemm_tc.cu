@@ -16,6 +16,8 @@
 //   warps 4-7 split the landed tiles (generic proxy -> fence.proxy.async), then the epilogue:
 //             tcgen05.ld of the accumulator, bias / activation / activation-derivative mask, stores of
 //             C and (optionally) of its transpose for the weight-gradient GEMMs.
+#include <cstdio>
+#include <cstdlib>
 #include <cuda.h>
 #include <cudaTypedefs.h>
 #include "nf_common.cuh"
@@ -86,6 +88,9 @@ struct Params {
     const float* bias;                   // [N] or null
     int act;                             // EPI_ACT_*
     const float* mask_src; long long ldm; int mask;     // multiply by act'(mask_src[m][n])
+    long long* dbg;                      // optional phase timestamps of CTA (0,0) (bring-up aid), else null
+    int kb_per_split;                    // split-K: blockIdx.z owns k-blocks [z*kb_per_split, (z+1)*kb_per_split)
+    long long split_stride;              // and writes its partial tile to C + z*split_stride
 };
 
 __global__ void __launch_bounds__(THREADS, 1)
@@ -94,10 +99,16 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     __shared__ uint64_t full_bar[STAGES], split_bar[STAGES], empty_bar[STAGES], acc_bar;
     __shared__ uint32_t tmem_base;
+    __shared__ float sbias[BN];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
-    const int nkb = (p.K + BK - 1) / BK;
+    const bool dbg = p.dbg && blockIdx.x == 0 && blockIdx.y == 0;
+    if (dbg && threadIdx.x == 0) p.dbg[0] = clock64();
+    const int nkb_all = (p.K + BK - 1) / BK;
+    const int kb0 = blockIdx.z * p.kb_per_split;
+    const int nkb = max(0, min(p.kb_per_split, nkb_all - kb0));
+    if (p.C) p.C += (long long)blockIdx.z * p.split_stride;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES; ++s) {
@@ -108,6 +119,10 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
         mbar_init(&acc_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    if (warp == 2 || warp == 3) {      // bias slice of this tile (zero when absent / out of range)
+        const int i = threadIdx.x - 64;
+        sbias[i] = (p.bias && n0 + i < p.N) ? p.bias[n0 + i] : 0.f;
+    }
     if (warp == 1) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base)), "r"(TMEM_COLS) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -116,6 +131,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_d = tmem_base;
+    if (dbg && threadIdx.x == 0) p.dbg[1] = clock64();
 
     if (warp == 0) {
         // ---------------- TMA producer ----------------
@@ -125,14 +141,15 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
                 if (it > 0) mbar_wait(&empty_bar[s], (it - 1) & 1);
                 uint8_t* st = smem + (size_t)s * STAGE_BYTES;
                 mbar_expect_tx(&full_bar[s], A_BYTES + B_BYTES);
-                tma_load_2d(st, &map_a, kb * BK, m0, &full_bar[s]);                  // A hi slot (raw data)
-                tma_load_2d(st + 2 * A_BYTES, &map_b, kb * BK, n0, &full_bar[s]);    // B hi slot (raw data)
+                tma_load_2d(st, &map_a, (kb0 + kb) * BK, m0, &full_bar[s]);                  // A hi slot (raw data)
+                tma_load_2d(st + 2 * A_BYTES, &map_b, (kb0 + kb) * BK, n0, &full_bar[s]);    // B hi slot (raw data)
             }
         }
     } else if (warp == 1) {
         // ---------------- MMA issuer ----------------
         // instruction descriptor: D=f32, A=B=tf32, both K-major, N=64, M=128
         const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+        if (nkb == 0 && lane == 0) umma_commit(&acc_bar);
         for (int kb = 0; kb < nkb; ++kb) {
             const int s = kb % STAGES, it = kb / STAGES;
             mbar_wait(&split_bar[s], it & 1);
@@ -149,6 +166,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
                     umma_tf32(tmem_d, umma_desc(a_lo + off), umma_desc(b_hi + off), idesc, true);
                     umma_tf32(tmem_d, umma_desc(a_hi + off), umma_desc(b_lo + off), idesc, true);
                 }
+                if (dbg && kb == 0) p.dbg[4] = clock64();
                 umma_commit(&empty_bar[s]);                 // stage reusable once these MMAs have read it
                 if (kb == nkb - 1) umma_commit(&acc_bar);   // accumulator complete
             }
@@ -182,9 +200,16 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
         // epilogue: warp q = warp - 4 owns TMEM lanes 32q .. 32q+31 = rows m0 + 32q + lane
         if (warp >= 4) {
         mbar_wait(&acc_bar, 0);
+        if (dbg && t == 64) p.dbg[5] = clock64();
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const int q = warp - 4;
         const int m = m0 + 32 * q + lane;
+        // The accumulator arrives one ROW per thread; storing it like that would touch 32 different
+        // cache lines per instruction.  Each warp therefore parks its 32 x 64 slab in shared memory
+        // (the pipeline stages are free by now; pitch 65 keeps both access patterns conflict-free)
+        // and writes C row by row, 128 contiguous bytes per instruction.  C^T is written straight
+        // from registers: consecutive lanes hold consecutive m, which is the contiguous index there.
+        float* slab = reinterpret_cast<float*>(smem) + (size_t)q * 32 * 65;
 #pragma unroll
         for (int c0 = 0; c0 < BN; c0 += 16) {
             uint32_t r[16];
@@ -198,26 +223,75 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
                 const int n = n0 + c0 + i;
-                float v = __uint_as_float(r[i]);
+                float v = nkb > 0 ? __uint_as_float(r[i]) : 0.f;
                 if (n < p.N) {
-                    if (p.bias) v += p.bias[n];
+                    v += sbias[c0 + i];
                     if (p.act == EPI_ACT_RELU) v = v > 0.f ? v : 0.f;
-                    else if (p.act == EPI_ACT_SIGMOID) v = 1.f / (1.f + expf(-v));
-                    if (m < p.M) {
-                        if (p.mask != EPI_MASK_NONE) {
-                            const float y = p.mask_src[(long long)m * p.ldm + n];
-                            v *= (p.mask == EPI_MASK_RELU) ? (y > 0.f ? 1.f : 0.f) : y * (1.f - y);
-                        }
-                        if (p.C) p.C[(long long)m * p.ldc + n] = v;
-                        if (p.CT) p.CT[(long long)n * p.ldct + m] = v;
+                    else if (p.act == EPI_ACT_SIGMOID) v = 1.f / (1.f + __expf(-v));
+                }
+                slab[lane * 65 + c0 + i] = v;
+            }
+        }
+        __syncwarp();
+        if (dbg && t == 64) p.dbg[2] = clock64();
+        // batches of 8 rows: all shared-memory reads of a batch are issued before its stores, so the lone
+        // epilogue warp of each scheduler keeps several memory operations in flight
+        const int rows_here = min(32, p.M - (m0 + 32 * q));
+#pragma unroll 1
+        for (int r0 = 0; r0 < 32; r0 += 8) {
+            float v[8][BN / 32];
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+#pragma unroll
+                for (int h = 0; h < BN / 32; ++h) v[j][h] = slab[(r0 + j) * 65 + lane + 32 * h];
+            if (p.mask != EPI_MASK_NONE) {
+                float y[8][BN / 32];
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+#pragma unroll
+                    for (int h = 0; h < BN / 32; ++h) {
+                        const int n = n0 + lane + 32 * h;
+                        y[j][h] = (r0 + j < rows_here && n < p.N) ? __ldg(p.mask_src + (long long)(m0 + 32 * q + r0 + j) * p.ldm + n) : 0.f;
                     }
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+#pragma unroll
+                    for (int h = 0; h < BN / 32; ++h) {
+                        v[j][h] *= (p.mask == EPI_MASK_RELU) ? (y[j][h] > 0.f ? 1.f : 0.f) : y[j][h] * (1.f - y[j][h]);
+                        slab[(r0 + j) * 65 + lane + 32 * h] = v[j][h];
+                    }
+            }
+            if (p.C) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+#pragma unroll
+                    for (int h = 0; h < BN / 32; ++h) {
+                        const int n = n0 + lane + 32 * h;
+                        if (r0 + j < rows_here && n < p.N) p.C[(long long)(m0 + 32 * q + r0 + j) * p.ldc + n] = v[j][h];
+                    }
+            }
+        }
+        if (dbg && t == 64) p.dbg[3] = clock64();
+        if (p.CT) {
+            __syncwarp();
+            if (m < p.M) {
+#pragma unroll 1
+                for (int i0 = 0; i0 < BN; i0 += 16) {
+                    float v[16];
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) v[i] = slab[lane * 65 + i0 + i];
+#pragma unroll
+                    for (int i = 0; i < 16; ++i)
+                        if (n0 + i0 + i < p.N) p.CT[(long long)(n0 + i0 + i) * p.ldct + m] = v[i];
                 }
             }
         }
         }
     }
+    if (dbg && threadIdx.x == 128) p.dbg[6] = clock64();
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
+    if (dbg && threadIdx.x == 0) p.dbg[7] = clock64();
     if (warp == 1)
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(TMEM_COLS) : "memory");
 }
@@ -266,23 +340,49 @@ static bool make_map(CUtensorMap* map, const float* base, long long rows, long l
 
 // C = epi(A B^T); returns NF_ERR_UNSUPPORTED when TMA cannot describe the operands (the caller then
 // uses the CUDA-core GEMM).  A: [M][K] ld lda, B: [N][K] ld ldb.
+__global__ void tc_splitk_reduce_kernel(const float* __restrict__ part, int nz, long long count, float* __restrict__ out) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x) {
+        float s = 0.f;
+        for (int z = 0; z < nz; ++z) s += part[(long long)z * count + i];      // fixed order
+        out[i] = s;
+    }
+}
+
+// splits > 1: the contraction is cut into `splits` ranges, each CTA layer writes a partial [M][N] tile set
+// into split_ws (splits*M*N floats) and a second kernel adds them in a fixed order (no bias/activation/C^T).
 int tc_gemm_f32(const float* A, long long lda, const float* B, long long ldb, int M, int N, int K, float* C, long long ldc,
                 float* CT, long long ldct, const float* bias, int act, const float* mask_src, long long ldm, int mask,
-                cudaStream_t st) {
+                cudaStream_t st, int splits = 1, float* split_ws = nullptr) {
     if (M < 1 || N < 1 || K < 1) return NF_ERR_INVALID;
     if ((lda % 4) || (ldb % 4) || ((uintptr_t)A & 15) || ((uintptr_t)B & 15)) return NF_ERR_UNSUPPORTED;   // 16-byte strides
     CUtensorMap ma, mb;
     if (!tc::make_map(&ma, A, M, K, lda, tc::BM) || !tc::make_map(&mb, B, N, K, ldb, tc::BN)) return NF_ERR_UNSUPPORTED;
-    tc::Params p{M, N, K, C, ldc, CT, ldct, bias, act, mask_src, ldm, mask};
+    static long long* dbg_buf = nullptr;
+    if (getenv("NF_GEMM_DBG") && !dbg_buf) cudaMallocManaged(&dbg_buf, 64);
+    const int nkb_all = (K + tc::BK - 1) / tc::BK;
+    if (splits > nkb_all) splits = nkb_all;
+    if (splits < 1 || !split_ws || bias || act || CT || mask || ldc != N) splits = 1;
+    const int kbps = (nkb_all + splits - 1) / splits;
+    tc::Params p{M, N, K, splits > 1 ? split_ws : C, ldc, CT, ldct, bias, act, mask_src, ldm, mask, dbg_buf, kbps, (long long)M * N};
     const size_t smem = (size_t)tc::STAGES * tc::STAGE_BYTES + 1024;
     static bool attr_done = false;
     if (!attr_done) {
         NF_CUDA_OK(cudaFuncSetAttribute(tc::gemm_tf32x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_done = true;
     }
-    dim3 grid((N + tc::BN - 1) / tc::BN, (M + tc::BM - 1) / tc::BM);
+    dim3 grid((N + tc::BN - 1) / tc::BN, (M + tc::BM - 1) / tc::BM, splits);
     tc::gemm_tf32x3_kernel<<<grid, tc::THREADS, smem, st>>>(ma, mb, p);
     NF_CUDA_OK(cudaGetLastError());
+    if (splits > 1) {
+        const long long count = (long long)M * N;
+        tc_splitk_reduce_kernel<<<(int)((count + 255) / 256 < 1184 ? (count + 255) / 256 : 1184), 256, 0, st>>>(split_ws, splits, count, C);
+        NF_CUDA_OK(cudaGetLastError());
+    }
+    if (dbg_buf) {
+        cudaStreamSynchronize(st);
+        fprintf(stderr, "[gemm dbg] M=%d N=%d K=%d setup=%lld | epilogue: tmem->smem %lld, C rows %lld, CT %lld clk\n", M, N, K,
+                dbg_buf[1] - dbg_buf[0], dbg_buf[2] - dbg_buf[5], dbg_buf[3] - dbg_buf[2], dbg_buf[6] - dbg_buf[3]);
+    }
     return NF_OK;
 }
 

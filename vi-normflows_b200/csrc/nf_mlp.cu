@@ -15,7 +15,7 @@ namespace nf {
 // tensor-core GEMM (nf_gemm_tc.cu): C = epi(A B^T), both operands K-contiguous
 int tc_gemm_f32(const float* A, long long lda, const float* B, long long ldb, int M, int N, int K, float* C, long long ldc,
                 float* CT, long long ldct, const float* bias, int act, const float* mask_src, long long ldm, int mask,
-                cudaStream_t st);
+                cudaStream_t st, int splits = 1, float* split_ws = nullptr);
 
 enum { ACT_NONE = 0, ACT_RELU = 1, ACT_SIGMOID = 2, ACT_RBF = 3 };   // rbf: exp(-x^2) (nn_models.py:175)
 
@@ -139,23 +139,40 @@ __global__ void act_backward_kernel(const T* __restrict__ dy, const T* __restric
     }
 }
 
-// column sums: out[n] = sum_m x[m][n]  (one warp per 32 columns, fixed order over m)
+// column sums out[n] = sum_m x[m][n], two fixed-order stages: blockIdx.y sums a slab of rows for 32
+// columns into part[slab][n]; with gridDim.y == 1 the result goes straight to out.
+constexpr int kColsumSlabs = 64;
 template <typename T>
-__global__ void colsum_kernel(const T* __restrict__ x, int M, int N, T* __restrict__ out) {
+__global__ void colsum_kernel(const T* __restrict__ x, int M, int N, T* __restrict__ out, int rows_per_slab) {
     __shared__ T red[8][33];
     const int n = blockIdx.x * 32 + (threadIdx.x & 31);
     const int r = threadIdx.x >> 5;
+    const int m_lo = blockIdx.y * rows_per_slab;
+    const int m_hi = min(M, m_lo + rows_per_slab);
     T s = (T)0;
     if (n < N)
-        for (int m = r; m < M; m += 8) s += x[(long long)m * N + n];
+        for (int m = m_lo + r; m < m_hi; m += 8) s += x[(long long)m * N + n];
     red[r][threadIdx.x & 31] = s;
     __syncthreads();
     if (r == 0 && n < N) {
         T t = (T)0;
 #pragma unroll
         for (int i = 0; i < 8; ++i) t += red[i][threadIdx.x & 31];
-        out[n] = t;
+        out[(long long)blockIdx.y * N + n] = t;
     }
+}
+// bias gradient: column sums of dz [M][N] via `scratch` (kColsumSlabs * N elements)
+template <typename T>
+static int launch_colsum(const T* x, int M, int N, T* out, T* scratch, cudaStream_t st) {
+    if (M < 4 * kColsumSlabs || !scratch) {
+        colsum_kernel<T><<<dim3((N + 31) / 32, 1), 256, 0, st>>>(x, M, N, out, M);
+    } else {
+        const int rps = (M + kColsumSlabs - 1) / kColsumSlabs;
+        colsum_kernel<T><<<dim3((N + 31) / 32, kColsumSlabs), 256, 0, st>>>(x, M, N, scratch, rps);
+        colsum_kernel<T><<<dim3((N + 31) / 32, 1), 256, 0, st>>>(scratch, kColsumSlabs, N, out, kColsumSlabs);
+    }
+    NF_CUDA_OK(cudaGetLastError());
+    return NF_OK;
 }
 
 template <typename T>
@@ -316,8 +333,7 @@ static int mlp_backward(const T* wts, const T* x, MlpDims d, int hidden_act, int
     int rc = launch_gemm<T>(dz_a, 1, d.D_out, a_prev, d.H, 1, g_wts + off_out, d.H, d.D_out, d.H, d.N, nullptr, ACT_NONE,
                             nullptr, kSplits, split_ws, st);
     if (rc != NF_OK) return rc;
-    colsum_kernel<T><<<(d.D_out + 31) / 32, 256, 0, st>>>(dz_a, d.N, d.D_out, g_wts + off_out + (long long)d.D_out * d.H);
-    NF_CUDA_OK(cudaGetLastError());
+    if ((rc = launch_colsum<T>(dz_a, d.N, d.D_out, g_wts + off_out + (long long)d.D_out * d.H, split_ws, st)) != NF_OK) return rc;
     // d a_prev[n][h] = sum_j dz[n][j] W_out[j][h] : B(k=j, n'=h) = W_out[j*H + h]
     rc = launch_gemm<T>(dz_a, d.D_out, 1, wts + off_out, d.H, 1, dz_b, d.H, d.N, d.H, d.D_out, nullptr, ACT_NONE, nullptr, 1,
                         nullptr, st);
@@ -336,8 +352,7 @@ static int mlp_backward(const T* wts, const T* x, MlpDims d, int hidden_act, int
         rc = launch_gemm<T>(other, 1, d.H, in, kin, 1, g_wts + off, kin, d.H, kin, d.N, nullptr, ACT_NONE, nullptr, kSplits,
                             split_ws, st);
         if (rc != NF_OK) return rc;
-        colsum_kernel<T><<<(d.H + 31) / 32, 256, 0, st>>>(other, d.N, d.H, g_wts + off + (long long)d.H * kin);
-        NF_CUDA_OK(cudaGetLastError());
+        if ((rc = launch_colsum<T>(other, d.N, d.H, g_wts + off + (long long)d.H * kin, split_ws, st)) != NF_OK) return rc;
         if (l > 0) {
             rc = launch_gemm<T>(other, d.H, 1, wts + off, kin, 1, g_act, d.H, d.N, d.H, d.H, nullptr, ACT_NONE, nullptr, 1, nullptr, st);
             if (rc != NF_OK) return rc;
@@ -361,6 +376,8 @@ static int mlp_backward_tc(const float* wts, const float* x, MlpDims d, int hidd
     float* dzT_cur = bws + 2 * (size_t)d.N * wide;        // [<=wide][N]
     float* dzT_oth = bws + 3 * (size_t)d.N * wide;
     float* WT = bws + 4 * (size_t)d.N * wide;             // transposed weight scratch
+    float* split_ws = WT + (size_t)max((long long)d.H * d.D_in, max((long long)d.D_out * d.H, (long long)d.H * d.H));
+    const int ksplit = d.N >= 2048 ? 16 : (d.N >= 512 ? 4 : 1);       // weight gradients contract over the batch
     const int mask = hidden_act == ACT_RELU ? 1 : 0;
     const long long P = mlp_param_count(d);
     long long off = P - ((long long)d.D_out * d.H + d.D_out);
@@ -371,9 +388,8 @@ static int mlp_backward_tc(const float* wts, const float* x, MlpDims d, int hidd
     if ((rc = launch_transpose<float>(dz_cur, d.N, d.D_out, dzT_cur, st)) != NF_OK) return rc;
     // dW_out[j][h] = sum_n dz^T[j][n] a^T[h][n]
     if ((rc = tc_gemm_f32(dzT_cur, d.N, actsT + (size_t)(d.L - 1) * layer, d.N, d.D_out, d.H, d.N, g_wts + off, d.H, nullptr, 0,
-                          nullptr, 0, nullptr, 0, 0, st)) != NF_OK) return rc;
-    colsum_kernel<float><<<(d.D_out + 31) / 32, 256, 0, st>>>(dz_cur, d.N, d.D_out, g_wts + off + (long long)d.D_out * d.H);
-    NF_CUDA_OK(cudaGetLastError());
+                          nullptr, 0, nullptr, 0, 0, st, ksplit, split_ws)) != NF_OK) return rc;
+    if ((rc = launch_colsum<float>(dz_cur, d.N, d.D_out, g_wts + off + (long long)d.D_out * d.H, split_ws, st)) != NF_OK) return rc;
     // dz_{L-1}[n][h] = (sum_j dz[n][j] W_out[j][h]) * act'(a_{L-1}[n][h])
     if ((rc = launch_transpose<float>(wts + off, d.D_out, d.H, WT, st)) != NF_OK) return rc;
     if ((rc = tc_gemm_f32(dz_cur, d.D_out, WT, d.D_out, d.N, d.H, d.D_out, dz_oth, d.H, dzT_oth, d.N, nullptr, 0,
@@ -384,9 +400,8 @@ static int mlp_backward_tc(const float* wts, const float* x, MlpDims d, int hidd
         off -= (long long)d.H * kin + d.H;
         const float* inT = l == 0 ? xT : actsT + (size_t)(l - 1) * layer;
         // dW_l[j][k] = sum_n dz^T[j][n] in^T[k][n]
-        if ((rc = tc_gemm_f32(dzT_cur, d.N, inT, d.N, d.H, kin, d.N, g_wts + off, kin, nullptr, 0, nullptr, 0, nullptr, 0, 0, st)) != NF_OK) return rc;
-        colsum_kernel<float><<<(d.H + 31) / 32, 256, 0, st>>>(dz_cur, d.N, d.H, g_wts + off + (long long)d.H * kin);
-        NF_CUDA_OK(cudaGetLastError());
+        if ((rc = tc_gemm_f32(dzT_cur, d.N, inT, d.N, d.H, kin, d.N, g_wts + off, kin, nullptr, 0, nullptr, 0, nullptr, 0, 0, st, ksplit, split_ws)) != NF_OK) return rc;
+        if ((rc = launch_colsum<float>(dz_cur, d.N, d.H, g_wts + off + (long long)d.H * kin, split_ws, st)) != NF_OK) return rc;
         if (l > 0 || g_x) {
             if ((rc = launch_transpose<float>(wts + off, d.H, kin, WT, st)) != NF_OK) return rc;      // [kin][H]
             if (l > 0) {

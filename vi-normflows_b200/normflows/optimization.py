@@ -21,7 +21,8 @@ from autograd.misc.optimizers import adam, rmsprop  # noqa: F401  (same names th
 from nfcore import ops, tape
 
 from .flows import planar_flow  # noqa: F401
-from .utils import clear_figs, get_samples_from_params, compare_reconstruction, make_batch_iter  # noqa: F401
+from .utils import (clear_figs, get_samples_from_params, compare_reconstruction, make_batch_iter,  # noqa: F401
+                    make_batch_schedule)
 from .config import results
 
 rs = npr.RandomState(0)                     # optimization.py:13
@@ -63,12 +64,19 @@ def make_free_energy(logp, X, D, K, encode, decode, max_iter, batch_size, dtype=
     """The F(phi, theta, t) of optimization.py:66-92 as a function of CUDA tensors."""
     dt = default_dtype() if dtype is None else dtype
     dev = torch.device('cuda', torch.cuda.current_device())
+    X_dev = None
     if batch_iter is None:
-        batch_iter = make_batch_iter(X, batch_size, max_iter)          # optimization.py:55 (global np.random)
+        # optimization.py:55: same schedule, same consumption of the global NumPy RNG as make_batch_iter,
+        # but the data set is uploaded once and mini-batches are gathered on the device
+        batch_indices = make_batch_schedule(X.shape[0], batch_size, max_iter)
+        X_dev = torch.as_tensor(np.ascontiguousarray(X)).to(dev, dt)
 
     def F(phi, theta, t):
         eps = 1e-7
-        Xbatch = torch.as_tensor(np.ascontiguousarray(batch_iter(t))).to(dev, dt)         # :68
+        if X_dev is not None:
+            Xbatch = X_dev.index_select(0, torch.as_tensor(batch_indices(t), device=dev))  # :68
+        else:
+            Xbatch = torch.as_tensor(np.ascontiguousarray(batch_iter(t))).to(dev, dt)
         z0_np = rs.randn(Xbatch.shape[0], D)                                              # :69 (module RandomState)
         z0 = torch.as_tensor(z0_np).to(dev, dt)
         mu0, log_sigma_diag0, W, U, B = encode(phi, Xbatch)                               # :70

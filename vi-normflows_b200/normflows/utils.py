@@ -35,6 +35,21 @@ def compare_reconstruction(phi, theta, x_true, encode, decode, K, t):    # utils
     return xhat
 
 
+def make_batch_schedule(N, batch_size, max_iter):
+    """The index schedule of utils.py:41-52: per epoch one global-RNG permutation split into batches.
+    Consumes np.random exactly like the reference's make_batch_iter."""
+    n_batches = int(np.ceil(N / batch_size))
+    n_epochs = int(np.ceil(max_iter / n_batches))
+    idx = np.arange(N)
+    sched = []
+    for i in range(n_epochs):
+        sched.append(np.array_split(np.random.permutation(idx), n_batches))
+
+    def batch_indices(t):
+        return sched[int(np.floor(t / n_batches))][t % n_batches]
+    return batch_indices
+
+
 def make_batch_iter(X, batch_size, max_iter):        # utils.py:41-60 (global np.random.permutation)
     N, D = X.shape
     n_batches = int(np.ceil(N / batch_size))
