@@ -17,4 +17,8 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-fil
 python bench.py --steps 20 --warmup 3 > $OUT/bench_short2.json 2> $OUT/bench_short2.err &&
 ncu --set full --clock-control none --import-source on -k regex:elbo_shared_kernel -s 6 -c 2 -o $OUT/prof_elbo \
     python bench.py --steps 20 --warmup 3 > $OUT/ncu_full.log 2>&1
+timeout 60 python tools/gemm_one.py 4096 1376 64 > $OUT/gemm_plain.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:gemm_tf32x3 -s 2 -c 1 -o $OUT/prof_gemm \
+    python tools/gemm_one.py 4096 1376 64 > $OUT/ncu_gemm.log 2>&1
+timeout 300 python tools/bench_configs.py > $OUT/configs.txt 2>&1
 ls -la $OUT

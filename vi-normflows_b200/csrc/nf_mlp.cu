@@ -1,9 +1,10 @@
 // Encoder / decoder MLP of the flow-VAE (nn_models.py:41-84 `Feedforward.forward`) and the
 // Bernoulli log-likelihood (distributions.py:86-89), forward and backward, sm_100a.
 //
-// Round-1 version: FP32/FP64 register-blocked shared-memory GEMMs on the CUDA cores with the
-// bias + activation epilogue fused (the tcgen05/TMA version of the three large layers is the
-// next step; at C4 the whole MLP is 4.7 GFLOP per step).  Activations are
+// Two GEMM back ends: float32 problems whose dimensions TMA can describe (multiples of 4, batch >= 128)
+// run on the tensor cores (nf_gemm_tc.cu: TMA + tcgen05.mma kind::tf32 with a hi/lo operand split that
+// keeps float32 accuracy); everything else (float64, rbf activations, odd shapes) runs on the
+// register-blocked shared-memory CUDA-core GEMM below.  Bias + activation are fused in both.  Activations are
 // kept sample-major [N][H] so that every layer is C[m][n] = sum_k A[m][k] W[n][k] with both
 // operands contiguous along k; the flat weight vector has exactly the reference's layout
 // (nn_models.py:59-80): W1 (H x D_in) | b1 | {W_l (H x H) | b_l} x (L-1) | W_out (D_out x H) | b_out.
