@@ -12,7 +12,7 @@ size_t nf_planar_elbo_workspace_bytes(int K, int D, int elem_size) {
     }
     const size_t row = (size_t)K * nf::wide_vk(D) + 2;      // one row per warp of the wide kernel
     const nf::DevInfo di = nf::dev_info();
-    return row * (size_t)((di.sms > 0 ? di.sms : 148) * nf::kWideBlocksPerSM * nf::kWideWarps) * (size_t)elem_size;
+    return row * (size_t)((di.sms > 0 ? di.sms : 148) * nf::wide_blocks_per_sm(K, D, (size_t)elem_size) * nf::kWideWarps) * (size_t)elem_size;
 }
 
 int nf_planar_elbo_fwd_bwd_f32(const float* eps, int64_t N, int D, int K, const float* w, const float* s,

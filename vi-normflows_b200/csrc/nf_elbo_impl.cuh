@@ -617,19 +617,34 @@ static int dispatch_target(int tgt, bool bwd, const T* eps, long long N, int K, 
     return NF_ERR_UNSUPPORTED;
 }
 
-constexpr int kWideBlocksPerSM = 2;
+// Rows of the wide kernel live in global memory and are read-modified-written once per layer: keep all of
+// them L2-resident (126 MB) -- at most ~96 MB of rows, between 1 and 8 blocks per SM.
+static inline int wide_blocks_per_sm(int K, int D, size_t elem) {
+    const DevInfo di = dev_info();
+    const size_t rowbytes = ((size_t)K * wide_vk(D) + 2) * elem;
+    const size_t per_block = rowbytes * kWideWarps;
+    long long bps = (long long)((size_t)96000000 / ((size_t)(di.sms > 0 ? di.sms : 148) * per_block));
+    if (bps < 1) bps = 1;
+    if (bps > 8) bps = 8;
+    return (int)bps;
+}
 
 template <typename T, int C, int L, int TGT, bool BWD>
 static int launch_wide(const T* eps, long long N, int D, int K, const T* w, const T* s, const T* b, const T* c,
                        const T* tparams, int ntp, T epsv, T* partials, int* nrows_out, cudaStream_t stream) {
-    constexpr int S = 2;
+    constexpr int S = (L >= 32 && C == 8) ? 6 : ((L >= 8) ? 4 : 2);      // more interleaved sample groups where a warp holds few samples
     auto kern = elbo_wide_kernel<T, C, L, S, TGT, BWD>;
     const size_t smem = BWD ? (size_t)K * S * kWideWarps * (32 / L) * sizeof(T) : 0;
     if (smem > 200 * 1024) return NF_ERR_UNSUPPORTED;
     NF_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const DevInfo di = dev_info();
     const long long tile = (long long)kWideWarps * S * (32 / L);
-    long long grid = (long long)di.sms * kWideBlocksPerSM;
+    int bps = wide_blocks_per_sm(K, D, sizeof(T));
+    int occ = 0;
+    NF_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kWideThreads, smem));
+    if (occ < 1) return NF_ERR_UNSUPPORTED;
+    if (bps > occ) bps = occ;
+    long long grid = (long long)di.sms * bps;
     const long long ntiles = (N + tile - 1) / tile;
     if (grid > ntiles) grid = ntiles;
     if (grid < 1) grid = 1;

@@ -124,16 +124,30 @@ elbo_wide_kernel(const T* __restrict__ eps, long long N, int D, int K,
             lq[j] = (T)-0.5 * (D * LOG2PI + zz);
             prod[j] = (T)1;
         }
-        // ---- forward ----
+        // ---- forward ----  (layer constants are fetched one layer ahead: they come from L1/L2, and a
+        // warp that owns only S sample groups has nothing else to hide that latency behind)
+        T wn[C], sn[C];
+#pragma unroll
+        for (int i = 0; i < C; ++i) {
+            const int d = d0 + i;
+            wn[i] = d < D ? __ldg(w + d) : (T)0;
+            sn[i] = d < D ? __ldg(s + d) : (T)0;
+        }
+        T bn = __ldg(b), cn = __ldg(c);
         for (int k = 0; k < K; ++k) {
             T wk[C], sk[C];
 #pragma unroll
-            for (int i = 0; i < C; ++i) {
-                const int d = d0 + i;
-                wk[i] = d < D ? __ldg(w + (size_t)k * D + d) : (T)0;
-                sk[i] = d < D ? __ldg(s + (size_t)k * D + d) : (T)0;
+            for (int i = 0; i < C; ++i) { wk[i] = wn[i]; sk[i] = sn[i]; }
+            const T bk = bn, ck = cn;
+            if (k + 1 < K) {
+#pragma unroll
+                for (int i = 0; i < C; ++i) {
+                    const int d = d0 + i;
+                    wn[i] = d < D ? __ldg(w + (size_t)(k + 1) * D + d) : (T)0;
+                    sn[i] = d < D ? __ldg(s + (size_t)(k + 1) * D + d) : (T)0;
+                }
+                bn = __ldg(b + k + 1); cn = __ldg(c + k + 1);
             }
-            const T bk = __ldg(b + k), ck = __ldg(c + k);
 #pragma unroll
             for (int j = 0; j < S; ++j) {
                 T a = (T)0;
@@ -214,15 +228,44 @@ elbo_wide_kernel(const T* __restrict__ eps, long long N, int D, int K,
             if (l == 0 && ok[j]) sum_p += lp;
         }
         if (BWD) {
+            // where this lane's KEEP reduced values live inside a layer record, and whether they are real coordinates
+            int roff[KEEP];
+            bool rok[KEEP];
+#pragma unroll
+            for (int i = 0; i < KEEP; ++i) {
+                const int e = g * KEEP + i;                 // element of [g_w(C) | g_s(C)]; slice number == g
+                const int d = d0 + (e < C ? e : e - C);
+                rok[i] = d < D;
+                roff[i] = e < C ? d : Dp + d;
+            }
+#pragma unroll
+            for (int i = 0; i < C; ++i) {
+                const int d = d0 + i;
+                wn[i] = d < D ? __ldg(w + (size_t)(K - 1) * D + d) : (T)0;
+                sn[i] = d < D ? __ldg(s + (size_t)(K - 1) * D + d) : (T)0;
+            }
+            cn = __ldg(c + K - 1);
             for (int k = K - 1; k >= 0; --k) {
                 T wk[C], sk[C];
 #pragma unroll
-                for (int i = 0; i < C; ++i) {
-                    const int d = d0 + i;
-                    wk[i] = d < D ? __ldg(w + (size_t)k * D + d) : (T)0;
-                    sk[i] = d < D ? __ldg(s + (size_t)k * D + d) : (T)0;
+                for (int i = 0; i < C; ++i) { wk[i] = wn[i]; sk[i] = sn[i]; }
+                const T ck = cn;
+                if (k > 0) {
+#pragma unroll
+                    for (int i = 0; i < C; ++i) {
+                        const int d = d0 + i;
+                        wn[i] = d < D ? __ldg(w + (size_t)(k - 1) * D + d) : (T)0;
+                        sn[i] = d < D ? __ldg(s + (size_t)(k - 1) * D + d) : (T)0;
+                    }
+                    cn = __ldg(c + k - 1);
                 }
-                const T ck = __ldg(c + k);
+                // the running totals of this layer are read now and written back after the layer math
+                T* rk = row + (size_t)k * Vk;
+                T old[KEEP];
+#pragma unroll
+                for (int i = 0; i < KEEP; ++i) old[i] = rok[i] ? rk[roff[i]] : (T)0;
+                T old_b = (T)0, old_c = (T)0;
+                if (lane == 0) { old_b = rk[2 * Dp]; old_c = rk[2 * Dp + 1]; }
                 T v[NV];
 #pragma unroll
                 for (int i = 0; i < NV; ++i) v[i] = (T)0;
@@ -260,20 +303,12 @@ elbo_wide_kernel(const T* __restrict__ eps, long long N, int D, int K,
                 }
                 // reduce over the sample groups of the warp and add to the warp's row
                 ReduceScatter<T, NV, 16, L>::run(v, lane);
-                T* rk = row + (size_t)k * Vk;
 #pragma unroll
-                for (int i = 0; i < KEEP; ++i) {
-                    // slice number: group index with lane bit 16 as MSB == g
-                    const int e = g * KEEP + i;                 // element of [g_w(C) | g_s(C)]
-                    const int d = d0 + (e < C ? e : e - C);
-                    if (d < D) {
-                        T* p = rk + (e < C ? d : Dp + d);
-                        *p += v[i];
-                    }
-                }
+                for (int i = 0; i < KEEP; ++i)
+                    if (rok[i]) rk[roff[i]] = old[i] + v[i];
                 gb = cross_group_sum<T, L>(gb);
                 gcc = cross_group_sum<T, L>(gcc);
-                if (lane == 0) { rk[2 * Dp] += gb; rk[2 * Dp + 1] += gcc; }
+                if (lane == 0) { rk[2 * Dp] = old_b + gb; rk[2 * Dp + 1] = old_c + gcc; }
             }
         }
 #pragma unroll
