@@ -128,6 +128,11 @@ def run_reference(args):
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
         return
+    # torchrun exports OMP_NUM_THREADS=1; the reference arm is entitled to every host core
+    try:
+        torch.set_num_threads(max(1, os.cpu_count() or 1))
+    except RuntimeError:
+        pass
     # bounded sample: largest power of two <= 2^18 samples/step that keeps the whole run near 90 s
     n_cpu = 1 << 18
     _, t1 = time_cpu(n_cpu, 1, 1)
@@ -185,13 +190,26 @@ def run_ours(args):
     out = (res[:3], res[3:3 + KD].view(K_LAYERS, DIM), res[3 + KD:3 + 2 * KD].view(K_LAYERS, DIM),
            res[3 + 2 * KD:3 + 2 * KD + K_LAYERS], res[3 + 2 * KD + K_LAYERS:])
 
+    small_ar = None
+    if world > 1 and os.environ.get('NF_BENCH_NCCL', '0') != '1':
+        try:
+            from nfcore.peer import SmallAllReduce
+            small_ar = SmallAllReduce(dist.group.WORLD, dev)      # one-shot exchange over NVLink peer memory
+        except Exception as e:                                    # no P2P mapping: NCCL carries the vector
+            if rank == 0:
+                print('bench: peer all-reduce unavailable (%s); using NCCL' % e, file=sys.stderr)
+            small_ar = None
+
     def local_step(i):
         ops.planar_elbo(eps[i % N_ROTATE], w_d, s_d, b_d, c_d, TARGET, None, 1e-7, True, out)
 
     def step(i):
         local_step(i)
         if world > 1:
-            dist.all_reduce(res)
+            if small_ar is not None:
+                small_ar(res)
+            else:
+                dist.all_reduce(res)
 
     def barrier():
         if world > 1:
@@ -274,7 +292,7 @@ def run_ours(args):
             'achieved_hbm_gbs': per_gpu * BYTES_PER_SAMPLE / 1e9, 'peak_hbm_gbs': hbm_peak / 1e9,
             'frac_mufu_at_clock_under_load': (per_gpu * MUFU_PER_SAMPLE / (sms * 16 * f_load)) if f_load else None,
             'kernel_ms': ms_per_step, 'kernel_note': 'events bracket objective kernel + partial-sum kernel'
-                                                     + (' + NCCL all-reduce' if world > 1 else ''),
+                                                     + ((' + one-shot NVLink all-reduce kernel' if small_ar is not None else ' + NCCL all-reduce') if world > 1 else ''),
         }
         n_cpu = 1 << 18
         cpu_value, cpu_dt = time_cpu(n_cpu, 6, 1) if world == 1 else (None, None)
@@ -303,7 +321,9 @@ def run_ours(args):
             'roofline': roofline,
             'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
                     'F': float(F_e2e)},
-            'gpu_launches': 2 * args.steps,
+            'gpu_launches': (3 if small_ar is not None else 2) * args.steps,
+            'exchange': None if world == 1 else ('nf_allreduce_small_f32 (NVLink peer stores, %d floats)' % nres if small_ar is not None
+                                                 else 'ncclAllReduce (%d floats)' % nres),
             'clocks': clocks,
         }
         if big is not None:

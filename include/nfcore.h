@@ -237,6 +237,22 @@ int nf_bernoulli_ll_f64(const double* x, const double* p, int64_t count, double 
 int nf_gemm_tn_tf32x3(const float* A, int64_t lda, const float* B, int64_t ldb, int M, int N, int K,
                       float* C, int64_t ldc, float* CT, int64_t ldct, const float* bias, int act, void* stream);
 
+/* ---------------------------------------------------------------------------
+ * One-shot all-reduce(sum) of a small float32 vector (n <= nf_allreduce_small_max_count()) across the
+ * <= 8 GPUs of one box, over NVLink peer memory.  No counterpart in the reference (it is single-process);
+ * it is the exchange step of the sample-sharded objective: one vector of
+ * [F parts | gradient partials] per step.
+ *   peer_buffers[r] : device pointer, valid in THIS process, to rank r's exchange buffer of
+ *                     nf_allreduce_small_buffer_bytes(world) bytes (peer-mapped, zero-filled once).
+ *   seq             : 1, 2, 3, ... the same on every rank for the same step.
+ *   status[0]       : set to 1 by the kernel if a peer did not arrive within the bounded spin.
+ * All ranks add the slots in rank order, so every rank ends with bitwise identical sums.
+ * ------------------------------------------------------------------------- */
+size_t nf_allreduce_small_buffer_bytes(int world);
+int nf_allreduce_small_max_count(void);
+int nf_allreduce_small_f32(void* const* peer_buffers, int world, int rank, const float* src, float* dst, int n,
+                           uint64_t seq, int* status, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -27,6 +27,22 @@ for (K, D, N, target) in ((32, 2, 200003, 'p1'), (8, 16, 5001, ('gaussdiag', np.
         ok &= good
         if rank == 0:
             print('K=%d D=%d N=%d %s world=%d: |dF|=%.2e |dg|=%.2e %s' % (K, D, N, dtype, world, eF, eg, 'OK' if good else 'FAIL'), flush=True)
+# the NVLink one-shot exchange against NCCL, repeated so that both slot sets and the sequence logic are exercised
+from nfcore.peer import SmallAllReduce
+ar = SmallAllReduce(dist.group.WORLD)
+g = torch.Generator(device='cuda').manual_seed(100 + rank)
+for it in range(50):
+    v = torch.randn(195, device='cuda', generator=g)
+    ref = v.clone(); dist.all_reduce(ref)
+    out = ar(v.clone())
+    torch.cuda.synchronize()
+    err = float((out - ref).abs().max())
+    if err > 1e-5:
+        ok = False
+        print('rank %d it %d peer all-reduce mismatch %.3e' % (rank, it, err), flush=True)
+ar.check()
+if rank == 0:
+    print('peer all-reduce (50 rounds) %s' % ('OK' if ok else 'FAIL'), flush=True)
 dist.barrier()
 dist.destroy_process_group()
 sys.exit(0 if ok else 1)
