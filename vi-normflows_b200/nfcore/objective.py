@@ -95,6 +95,14 @@ class SharedFlowObjective:
         self._eps_pinned = None
         self.group = process_group
         self.launches = 0
+        self._small_ar = None
+        self._n_cache = {}
+        if process_group is not None and self.dtype == torch.float32 and 3 + self.n_lc <= 1024:
+            try:    # one-shot exchange over NVLink peer memory; NCCL when the peers cannot be mapped
+                from .peer import SmallAllReduce
+                self._small_ar = SmallAllReduce(process_group, self.device)
+            except Exception:
+                self._small_ar = None
         self._session = None
         self._session_cap = 0
         self._tparams_host = None if tparams is None else np.ascontiguousarray(tparams.astype(self.np_dtype))
@@ -209,7 +217,14 @@ class SharedFlowObjective:
         """all-reduce (when sharded) + D2H of [F parts | grads]; returns float64 array and global N."""
         n_global = n_local
         if self.group is not None:
-            n_global = sharding.reduce_sums(self._res, n_local, self.group)
+            if self._small_ar is not None:
+                # the row count only changes when the caller changes its shard: exchange it once per value
+                if n_local not in self._n_cache:
+                    self._n_cache[n_local] = sharding.reduce_sums(torch.zeros(1, device=self.device), n_local, self.group)
+                n_global = self._n_cache[n_local]
+                self._small_ar(self._res)
+            else:
+                n_global = sharding.reduce_sums(self._res, n_local, self.group)
         self._res_host.copy_(self._res, non_blocking=True)
         torch.cuda.current_stream(self.device).synchronize()
         return self._res_host.numpy().astype(np.float64), n_global
