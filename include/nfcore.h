@@ -123,6 +123,31 @@ int nf_session_elbo_host_f64(nf_session* s, const double* eps_host, int64_t N, c
                              int target_id, const double* target_params_host, int n_target_params,
                              double log_eps, int backward, double* out_host);
 
+/* ---------------------------------------------------------------------------
+ * The whole optimisation loop of the script path on the device: get_data.py:119-142 `optimise`
+ * (rmsprop), experimentation.py:99-109 (sgd), updated_experimentation.ipynb cell 1 (adam), with the
+ * update rules of autograd 1.3's autograd.misc.optimizers.  Per iteration the library enqueues three
+ * kernels -- apply the previous update + derive (s, c) from (W, U) (get_data.py:106-108), the objective
+ * kernel on that iteration's samples, the row kernel -- and never copies parameters to the host.
+ *   eps_all   : [n_iters][N][D] samples, iteration t uses slice t (the draw the reference makes inside
+ *               `gradient(params, t)`, get_data.py:100-101)
+ *   params    : [W (K*D) | U (K*D) | B (K)], updated in place (get_data.py:74-78 layout)
+ *   optimizer : 0 sgd (h1 = mass), 1 rmsprop (h1 = gamma, h2 = eps), 2 adam (h1 = b1, h2 = b2, h3 = eps)
+ *   opt_state : 2*(2KD+K) elements of scratch for the optimiser (initialised by the call)
+ *   trace_F   : [n_iters] free energy seen by each gradient evaluation, or NULL
+ *   workspace : nf_script_train_workspace_bytes(K, D, elem_size)
+ * D <= 4 or the wide-D targets, script semantics.  Asynchronous on `stream`.
+ * ------------------------------------------------------------------------- */
+size_t nf_script_train_workspace_bytes(int K, int D, int elem_size);
+int nf_script_train_f32(const float* eps_all, int64_t n_iters, int64_t N, int D, int K, float* params, int target_id,
+                        const float* target_params, int n_target_params, float log_eps, int optimizer,
+                        float step_size, float h1, float h2, float h3, float* opt_state, float* trace_F,
+                        void* workspace, size_t workspace_bytes, void* stream);
+int nf_script_train_f64(const double* eps_all, int64_t n_iters, int64_t N, int D, int K, double* params, int target_id,
+                        const double* target_params, int n_target_params, double log_eps, int optimizer,
+                        double step_size, double h1, double h2, double h3, double* opt_state, double* trace_F,
+                        void* workspace, size_t workspace_bytes, void* stream);
+
 /* nf_planar_elbo_fwd_bwd_f32 for callers that must not allocate device memory.  It has no
  * counterpart in the reference (which never touches a GPU); it exists for host programs
  * whose device memory was all handed out at start-up, or for which cudaMalloc/cudaFree --

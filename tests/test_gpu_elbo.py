@@ -173,3 +173,52 @@ def test_abi_error_codes():
     oF, gw, gs, gb, gc = ops.planar_elbo(torch.empty(0, D, device=dev), w, s, b, c, 'p1')
     torch.cuda.synchronize()
     assert float(oF.abs().max()) == 0.0 and float(gw.abs().max()) == 0.0
+
+
+@pytest.mark.parametrize('optimizer,step', [('adam', 1e-3), ('rmsprop', 5e-4), ('sgd', 5e-4)])
+def test_device_training_loop_tracks_host_loop(optimizer, step):
+    """BASELINE config 1 (K=8, D=2, N=100, float64, 200 steps): the on-device loop (nf_script_train_f64) against the
+    host loop `optimizer(gradient, init, ...)` of autograd.misc.optimizers fed with the oracle's gradients on the same
+    draws.  The map is chaotic only over long horizons; 200 steps stay within 1e-8."""
+    from autograd.misc import optimizers
+    from nfcore.objective import SharedFlowObjective
+    from oracle import planar_torch as pt
+    K, D, N, T = 8, 2, 100, 200
+    rs = np.random.RandomState(0)
+    eps_all = rs.randn(T, N, D)
+    init = np.concatenate([0.1 * np.ones(2 * K * D), 0.1 * np.ones(K)])
+    mu, ls = np.array([1.0, -1.0]), np.log(np.array([0.5, 2.0]))
+    tgt = lambda z: torch.exp(pt.log_mvn(z, mu, ls))
+    trace_ref = []
+
+    def grad(x, i):
+        F, g = pt.script_value_and_grad(x, eps_all[i], tgt, 1e-7, K)
+        trace_ref.append(F)
+        return g
+    x_ref = getattr(optimizers, optimizer)(grad, init, None, T, step)
+    obj = SharedFlowObjective(('gaussdiag', mu, ls), K, D, dtype='float64')
+    x_dev, trace = obj.train(init, eps_all, optimizer=optimizer, step_size=step)
+    assert np.abs(x_dev - x_ref).max() <= 1e-8 * max(1.0, np.abs(x_ref).max())
+    assert np.abs(trace - np.array(trace_ref)).max() <= 1e-8 * max(1.0, np.abs(trace_ref).max())
+    assert abs(x_ref - init).max() > 1e-3            # the parameters really moved
+
+
+def test_optimise_matches_reference_rng_consumption():
+    """normflows.objectives.optimise (get_data.py:119-142): RNG draws per run = num_iter gradients + 2 per callback
+    at t % 100 == 0 + 2 final, exactly the reference's pattern."""
+    from normflows import objectives
+    calls = {'n': 0}
+    orig = np.random.multivariate_normal
+
+    def counting(mean, cov, size=None):
+        calls['n'] += 1
+        return orig(mean, cov, size)
+    np.random.multivariate_normal = counting
+    try:
+        np.random.seed(3)
+        x = objectives.optimise('p1', 100, 250, 5e-4, 4, verbose=False)
+    finally:
+        np.random.multivariate_normal = orig
+    assert x.shape == (4 * 2 * 2 + 4,) and np.isfinite(x).all()
+    assert calls['n'] == 250 + 2 * 3 + 2            # callbacks at t = 0, 100, 200; final metrics
+    assert np.abs(x - 0.1).max() > 1e-3

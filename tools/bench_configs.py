@@ -61,6 +61,13 @@ def main():
     dt = (time.perf_counter() - t0) / 300
     print('%-34s K=8   D=2    N=100   %9.1f us/step  %.0f objective+gradient calls/s (host API, float64)' % ('C1 gaussian, NumPy API', dt * 1e6, 1 / dt), flush=True)
     res.append({'case': 'C1', 'us_per_call': dt * 1e6})
+    eps_all = rs.randn(2000, 100, 2)
+    obj.train(params, eps_all[:50], optimizer='adam', step_size=1e-3)
+    t0 = time.perf_counter()
+    obj.train(params, eps_all, optimizer='adam', step_size=1e-3)
+    dt2 = (time.perf_counter() - t0) / 2000
+    print('%-34s K=8   D=2    N=100   %9.1f us/step  %.0f Adam steps/s (nf_script_train_f64: loop on the device, incl. upload of all draws)' % ('C1 gaussian, device loop', dt2 * 1e6, 1 / dt2), flush=True)
+    res.append({'case': 'C1 device loop', 'us_per_step': dt2 * 1e6})
     # C2
     for K in (16, 32):
         for t in ('p1', 'p2', 'p3', 'p4'):

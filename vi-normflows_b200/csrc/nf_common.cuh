@@ -124,28 +124,39 @@ __device__ __forceinline__ void warp_reduce_multi(T (&v)[V], int lane) {
     }
 }
 
-// Which original index ends up in v[0] of `lane` after warp_reduce_multi<T,V>.
+// Which original index ends up in v[0] of `lane` after warp_reduce_multi<T,V>, and whether `lane` is the
+// lowest lane holding that index (the one that publishes it).  Evaluated at compile time into a 32-entry
+// table: a kernel prologue only does one table lookup per thread.
 template <int V>
-__host__ __device__ inline int warp_slot(int lane) {
-    int idx[V];
-    for (int i = 0; i < V; ++i) idx[i] = i;
-    int n = V;
-    for (int m = 16; m > 0; m >>= 1) {
-        const bool up = (lane & m) != 0;
-        const int h = (n + 1) / 2;
-        for (int i = 0; i < n - h; ++i) idx[i] = up ? idx[i + h] : idx[i];
-        n = h;
+struct WarpSlotTable {
+    int slot[32];
+    bool own[32];
+    constexpr WarpSlotTable() : slot{}, own{} {
+        for (int lane = 0; lane < 32; ++lane) {
+            int idx[V] = {};
+            for (int i = 0; i < V; ++i) idx[i] = i;
+            int n = V;
+            for (int m = 16; m > 0; m >>= 1) {
+                const bool up = (lane & m) != 0;
+                const int h = (n + 1) / 2;
+                for (int i = 0; i < n - h; ++i) idx[i] = up ? idx[i + h] : idx[i];
+                n = h;
+            }
+            slot[lane] = idx[0];
+        }
+        for (int lane = 0; lane < 32; ++lane) {
+            bool first = true;
+            for (int l = 0; l < lane; ++l)
+                if (slot[l] == slot[lane]) first = false;
+            own[lane] = first;
+        }
     }
-    return idx[0];
-}
+};
+template <int V> __device__ constexpr WarpSlotTable<V> kWarpSlotTable{};
 
-// Lowest lane that owns original index `slot` (the one that publishes it).
 template <int V>
-__host__ __device__ inline bool warp_slot_owner(int lane) {
-    const int me = warp_slot<V>(lane);
-    for (int l = 0; l < lane; ++l)
-        if (warp_slot<V>(l) == me) return false;
-    return true;
-}
+__device__ __forceinline__ int warp_slot(int lane) { return kWarpSlotTable<V>.slot[lane]; }
+template <int V>
+__device__ __forceinline__ bool warp_slot_owner(int lane) { return kWarpSlotTable<V>.own[lane]; }
 
 }  // namespace nf

@@ -35,6 +35,20 @@ int nf_session_elbo_host_f32(nf_session* s, const float* eps_host, int64_t N, co
                                         target_params_host, n_target_params, log_eps, backward, out_host);
 }
 
+int nf_script_train_f32(const float* eps_all, int64_t n_iters, int64_t N, int D, int K, float* params, int target_id,
+                        const float* target_params, int n_target_params, float log_eps, int optimizer, float step_size, float h1,
+                        float h2, float h3, float* opt_state, float* trace_F, void* workspace, size_t workspace_bytes, void* stream) {
+    return nf::script_train<float>(eps_all, n_iters, N, D, K, params, target_id, target_params, n_target_params, log_eps, optimizer,
+                                step_size, h1, h2, h3, opt_state, trace_F, workspace, workspace_bytes, stream);
+}
+
+size_t nf_script_train_workspace_bytes(int K, int D, int elem_size) {
+    if (K < 1 || D < 1 || elem_size < 1) return 0;
+    const size_t nlc = (size_t)2 * K * D + 2 * K, nres = 3 + nlc;
+    const size_t head = ((nlc + nres) * (size_t)elem_size + 255) & ~(size_t)255;
+    return head + nf_planar_elbo_workspace_bytes(K, D, elem_size);
+}
+
 }  // extern "C"
 
 // ---------------------------------------------------------------------------------------

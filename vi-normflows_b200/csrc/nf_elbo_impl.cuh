@@ -24,6 +24,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <mutex>
+#include <vector>
 #include "nf_common.cuh"
 #include "nf_targets.cuh"
 #include "nf_elbo_wide.cuh"
@@ -858,6 +859,144 @@ static int session_elbo_host(Session* S, const T* eps_host, int64_t N, const T* 
     NF_CUDA_OK(cudaStreamSynchronize(S->s_comp));
     const T* op = reinterpret_cast<const T*>(S->out_pin);
     for (int i = 0; i < S->n_out; ++i) out_host[i] = op[i];
+    return NF_OK;
+}
+
+// ---- whole optimisation loop on the device (get_data.py:119-142 `optimise`, experimentation.py:99-109) ----
+// One tiny kernel per iteration applies the previous iteration's update (chain rule from the kernel's
+// (g_w, g_s, g_b, g_c) back to (dW, dU, dB), then sgd / rmsprop / adam with autograd 1.3's update rules) and
+// prepares the next iteration's layer constants (s = u_hat, c = w.u, get_data.py:106-108); the objective kernel
+// and the row kernel follow.  The host only enqueues: no parameter round trip per step.
+enum { OPT_SGD = 0, OPT_RMSPROP = 1, OPT_ADAM = 2 };
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+script_step_kernel(T* __restrict__ params /*[2KD+K]*/, T* __restrict__ lc /*w|s|b|c*/, const T* __restrict__ res /*[3+2KD+2K]*/,
+                   T* __restrict__ state /*[2P]*/, int K, int D, long long n_samples, int apply_update, long long iter,
+                   int optimizer, T step, T h1, T h2, T h3, T* __restrict__ trace_F, int paper) {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    const int P = 2 * K * D + K;
+    T* W = params;
+    T* U = params + K * D;
+    T* B = params + 2 * K * D;
+    // one thread per layer does the K x D algebra of that layer (K <= 256 per block pass)
+    for (int k = threadIdx.x; k < K; k += blockDim.x) {
+        if (apply_update) {
+            const T inv_n = (T)1 / (T)n_samples;
+            const T* g_w = res + 3 + k * D;
+            const T* g_s = res + 3 + K * D + k * D;
+            const T g_b = res[3 + 2 * K * D + k];
+            const T g_c = res[3 + 2 * K * D + K + k];
+            T wu = 0, n2 = 0, gsw = 0;
+            for (int d = 0; d < D; ++d) {
+                wu += W[k * D + d] * U[k * D + d];
+                n2 += W[k * D + d] * W[k * D + d];
+                gsw += g_s[d] * W[k * D + d];
+            }
+            const T alpha = (T)-1 + ::log((T)1 + ::exp(wu)) - wu;        // m(wu) - wu
+            const T dalpha = (T)1 / ((T)1 + ::exp(-wu)) - (T)1;
+            const T nrm = ::sqrt(n2);
+            const T npow = paper ? n2 : nrm;
+            const T pexp = paper ? (T)2 : (T)1;
+            // (paper semantics folds g_c through c = w.s; the script path has c = w.u)
+            for (int d = 0; d < D; ++d) {
+                const T w = W[k * D + d], u = U[k * D + d];
+                T gs = g_s[d], gw = g_w[d], gc_u = g_c, gc_w = g_c;
+                T dU = gs + (dalpha * gsw / npow) * w + gc_u * w;
+                T dW = gw + (dalpha * gsw / npow) * u + (alpha / npow) * gs - (alpha * pexp * gsw / (npow * n2)) * w + gc_w * u;
+                T grads[2] = {dW * inv_n, dU * inv_n};
+                T* ps[2] = {&W[k * D + d], &U[k * D + d]};
+                const int idx[2] = {k * D + d, K * D + k * D + d};
+                for (int q = 0; q < 2; ++q) {
+                    const T g = grads[q];
+                    T x = *ps[q];
+                    T* s0 = state + idx[q];
+                    T* s1 = state + P + idx[q];
+                    if (optimizer == OPT_SGD) { *s0 = h1 * *s0 - ((T)1 - h1) * g; x += step * *s0; }
+                    else if (optimizer == OPT_RMSPROP) { *s0 = *s0 * h1 + g * g * ((T)1 - h1); x -= step * g / (::sqrt(*s0) + h2); }
+                    else {
+                        *s0 = ((T)1 - h1) * g + h1 * *s0;
+                        *s1 = ((T)1 - h2) * g * g + h2 * *s1;
+                        const T mh = *s0 / ((T)1 - ::pow(h1, (T)(iter))), vh = *s1 / ((T)1 - ::pow(h2, (T)(iter)));
+                        x -= step * mh / (::sqrt(vh) + h3);
+                    }
+                    *ps[q] = x;
+                }
+            }
+            {
+                const T g = g_b * inv_n;
+                const int ib = 2 * K * D + k;
+                T x = B[k];
+                T* s0 = state + ib;
+                T* s1 = state + P + ib;
+                if (optimizer == OPT_SGD) { *s0 = h1 * *s0 - ((T)1 - h1) * g; x += step * *s0; }
+                else if (optimizer == OPT_RMSPROP) { *s0 = *s0 * h1 + g * g * ((T)1 - h1); x -= step * g / (::sqrt(*s0) + h2); }
+                else {
+                    *s0 = ((T)1 - h1) * g + h1 * *s0;
+                    *s1 = ((T)1 - h2) * g * g + h2 * *s1;
+                    const T mh = *s0 / ((T)1 - ::pow(h1, (T)(iter))), vh = *s1 / ((T)1 - ::pow(h2, (T)(iter)));
+                    x -= step * mh / (::sqrt(vh) + h3);
+                }
+                B[k] = x;
+            }
+        }
+    }
+    __syncthreads();
+    if (apply_update && trace_F && threadIdx.x == 0) trace_F[iter - 1] = res[0] / (T)n_samples;
+    // constants for the next objective evaluation
+    for (int k = threadIdx.x; k < K; k += blockDim.x) {
+        T wu = 0, n2 = 0;
+        for (int d = 0; d < D; ++d) { wu += W[k * D + d] * U[k * D + d]; n2 += W[k * D + d] * W[k * D + d]; }
+        const T alpha = (T)-1 + ::log((T)1 + ::exp(wu)) - wu;
+        const T npow = paper ? n2 : ::sqrt(n2);
+        T ws = 0;
+        for (int d = 0; d < D; ++d) {
+            const T sv = U[k * D + d] + alpha * W[k * D + d] / npow;
+            lc[k * D + d] = W[k * D + d];
+            lc[K * D + k * D + d] = sv;
+            ws += W[k * D + d] * sv;
+        }
+        lc[2 * K * D + k] = B[k];
+        lc[2 * K * D + K + k] = paper ? ws : wu;
+    }
+}
+
+template <typename T>
+static int script_train(const T* eps_all, int64_t n_iters, int64_t N, int D, int K, T* params, int target_id,
+                        const T* tparams, int ntp, T epsv, int optimizer, T step, T h1, T h2, T h3, T* state,
+                        T* trace_F, void* workspace, size_t workspace_bytes, void* stream_) {
+    cudaStream_t st = (cudaStream_t)stream_;
+    if (n_iters < 0 || N < 1 || !params || !state || !workspace || optimizer < 0 || optimizer > 2) return NF_ERR_INVALID;
+    const size_t P = (size_t)2 * K * D + K, nlc = (size_t)2 * K * D + 2 * K, nres = 3 + nlc;
+    // workspace: [lc | res | pad to 256 B | rows]
+    const size_t head = ((nlc + nres) * sizeof(T) + 255) & ~(size_t)255;
+    const size_t need = head + nf_planar_elbo_workspace_bytes(K, D, (int)sizeof(T));
+    if (workspace_bytes < need) return NF_ERR_WORKSPACE;
+    T* lc = reinterpret_cast<T*>(workspace);
+    T* res = lc + nlc;
+    T* rows = reinterpret_cast<T*>(reinterpret_cast<unsigned char*>(workspace) + head);
+    const T *w = lc, *s = lc + K * D, *b = lc + 2 * K * D, *c = lc + 2 * K * D + K;
+    int rc = elbo_validate<T>(eps_all, N, D, K, w, s, b, c, target_id, tparams, ntp);
+    if (rc != NF_OK) return rc;
+    // optimiser state: rmsprop starts its running average at ones (autograd 1.3), the others at zero
+    NF_CUDA_OK(cudaMemsetAsync(state, 0, 2 * P * sizeof(T), st));
+    if (optimizer == OPT_RMSPROP) {
+        // fill with ones through the update kernel's first pass would complicate it: use a small fill
+        std::vector<T> ones(P, (T)1);
+        NF_CUDA_OK(cudaMemcpyAsync(state, ones.data(), P * sizeof(T), cudaMemcpyHostToDevice, st));
+        NF_CUDA_OK(cudaStreamSynchronize(st));
+    }
+    for (int64_t it = 0; it <= n_iters; ++it) {
+        // apply update of iteration it-1 (if any), then prepare constants for iteration it
+        NF_CUDA_OK(launch_pdl(script_step_kernel<T>, dim3(1), dim3(256), 0, st, params, lc, (const T*)res, state, K, D,
+                              (long long)N, it > 0 ? 1 : 0, (long long)it, optimizer, step, h1, h2, h3, trace_F, 0));
+        if (it == n_iters) break;
+        int nb = 0;
+        rc = elbo_main<T>(true, eps_all + (size_t)it * N * D, N, D, K, w, s, b, c, target_id, tparams, ntp, epsv, rows, &nb, st);
+        if (rc != NF_OK) return rc;
+        rc = elbo_finish<T>(true, rows, nb, D, K, res, res + 3, res + 3 + K * D, res + 3 + 2 * K * D, res + 3 + 2 * K * D + K, st);
+        if (rc != NF_OK) return rc;
+    }
     return NF_OK;
 }
 

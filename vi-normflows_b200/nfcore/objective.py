@@ -262,3 +262,45 @@ class SharedFlowObjective:
         self._launch(params, eps_dev, False)
         res, n = self._fetch(eps_dev.shape[0])
         return res[1] / n, res[2] / n
+
+
+    # -- whole optimisation loop on the device (nf_script_train_*) ---------------------------------------
+    _OPT = {'sgd': (0, lambda h: (h.get('mass', 0.9), 0.0, 0.0)),
+            'rmsprop': (1, lambda h: (h.get('gamma', 0.9), h.get('eps', 1e-8), 0.0)),
+            'adam': (2, lambda h: (h.get('b1', 0.9), h.get('b2', 0.999), h.get('eps', 1e-8)))}
+
+    def train(self, params, eps_all, optimizer='adam', step_size=1e-3, **hyper):
+        """Run len(eps_all) optimiser iterations without leaving the GPU.
+
+        eps_all: (n_iters, N, D) samples, slice t being the draw of iteration t.  Update rules and defaults
+        are autograd 1.3's (autograd.misc.optimizers).  Returns (final params float64, trace of F per iteration).
+        Script semantics only; not available with a process group."""
+        if self.group is not None or self.semantics != 'script':
+            raise NFError('train(): single-process, script semantics only')
+        lib = _lib.load()
+        eps_all = np.ascontiguousarray(eps_all, dtype=self.np_dtype)
+        if eps_all.ndim != 3 or eps_all.shape[2] != self.D:
+            raise NFError('eps_all must have shape (n_iters, N, %d)' % self.D)
+        n_iters, N, D = eps_all.shape
+        K = self.K
+        P = 2 * K * D + K
+        dev = self.device
+        code, hp = self._OPT[optimizer]
+        h1, h2, h3 = hp(hyper)
+        eps_dev = torch.as_tensor(eps_all).to(dev)
+        p_dev = torch.as_tensor(np.asarray(params, dtype=np.float64).astype(self.np_dtype)).to(dev)
+        state = torch.empty(2 * P, dtype=self.dtype, device=dev)
+        trace = torch.empty(max(n_iters, 1), dtype=self.dtype, device=dev)
+        nws = lib.nf_script_train_workspace_bytes(K, D, self.np_dtype.itemsize)
+        ws = torch.empty(nws, dtype=torch.uint8, device=dev)
+        fn = lib.nf_script_train_f32 if self.np_dtype == np.float32 else lib.nf_script_train_f64
+        creal = ctypes.c_float if self.np_dtype == np.float32 else ctypes.c_double
+        vp = lambda t: ctypes.c_void_p(t.data_ptr()) if t is not None else None
+        with torch.cuda.device(dev):
+            st = torch.cuda.current_stream(dev).cuda_stream
+            rc = fn(vp(eps_dev), n_iters, N, D, K, vp(p_dev), ops.TARGET_IDS[self.target_name], vp(self.tparams),
+                    0 if self.tparams is None else self.tparams.numel(), creal(self.log_eps), code, creal(step_size),
+                    creal(h1), creal(h2), creal(h3), vp(state), vp(trace), vp(ws), nws, ctypes.c_void_p(st))
+        _lib.check(rc)
+        self.launches += 3 * n_iters + 1
+        return p_dev.double().cpu().numpy(), trace[:n_iters].double().cpu().numpy()
