@@ -222,3 +222,31 @@ def test_optimise_matches_reference_rng_consumption():
     assert x.shape == (4 * 2 * 2 + 4,) and np.isfinite(x).all()
     assert calls['n'] == 250 + 2 * 3 + 2            # callbacks at t = 0, 100, 200; final metrics
     assert np.abs(x - 0.1).max() > 1e-3
+
+
+def test_gradient_create_draws_like_the_reference():
+    """normflows.objectives.gradient_create (get_data.py:72-117): one global-RNG multivariate_normal draw per
+    objective / gradient / other_metrics call, and the values the reference would produce on those draws."""
+    from normflows import objectives
+    from oracle import planar_torch as pt
+    K, D, N = 6, 2, 500
+    rs = np.random.RandomState(1)
+    params = np.concatenate([0.1 + 0.05 * rs.randn(2 * K * D), 0.1 * np.ones(K)])
+
+    def p3(z):          # the reference passes its own function object; it is recognised by name
+        raise AssertionError('never called: the potential is fused into the kernel')
+    objective, gradient, unpack_params, other_metrics = objectives.gradient_create(p3, 1e-7, D, N, K, dtype='float64')
+    np.random.seed(5)
+    F = objective(params, 0)
+    g = gradient(params, 0)
+    mq, mp = other_metrics(params, 0)
+    np.random.seed(5)
+    z = [np.random.multivariate_normal(np.zeros(D), np.eye(D), N) for _ in range(3)]
+    F_ref, _ = pt.script_value_and_grad(params, z[0], pt.p3, 1e-7, K)
+    _, g_ref = pt.script_value_and_grad(params, z[1], pt.p3, 1e-7, K)
+    lq, lp, _ = pt.script_terms(torch.tensor(params), torch.tensor(z[2]), pt.p3, 1e-7, K)
+    assert abs(F - F_ref) <= 1e-10 * max(1, abs(F_ref))
+    assert _relerr(g, g_ref) <= 1e-10
+    assert abs(mq - float(lq.mean())) <= 1e-10 * abs(float(lq.mean())) and abs(mp - float(lp.mean())) <= 1e-10 * max(1, abs(float(lp.mean())))
+    W, U, B = unpack_params(params)
+    assert W.shape == (K, D) and U.shape == (K, D) and B.shape == (K,)
