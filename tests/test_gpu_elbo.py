@@ -113,12 +113,13 @@ def test_large_K_uses_single_sample_tiles():
     assert _relerr(grad, g_ref) <= 1e-9
 
 
-def test_full_size_properties():
-    """BASELINE size (K=32, D=2, N=2^20): run-to-run bitwise determinism, additivity over a
-    split of the sample set, and float32 vs float64 agreement."""
+@pytest.mark.parametrize('K,N', [(32, 1 << 20), (16, 1 << 20), (64, 1 << 21)])
+def test_full_size_properties(K, N):
+    """BASELINE sizes (D=2; K=16/32 at 2^20 samples, K=64 at 2^21 -- the three tensor-memory configurations of the
+    kernel): run-to-run bitwise determinism, additivity over a split of the sample set, float32 vs float64 agreement."""
     from nfcore import ops, semantics as sem
     torch.manual_seed(1234)
-    K, D, N = 32, 2, 1 << 20
+    D = 2
     dev = torch.device('cuda:0')
     eps64 = torch.randn(N, D, dtype=torch.float64, device=dev)
     rs = np.random.RandomState(7)

@@ -102,3 +102,25 @@ def test_wide_free_energy_matches_oracle(D, K, N):
         F, grad = obj.value_and_grad(params, z0)
         assert abs(F - F_ref) <= 1e-10 * max(1.0, abs(F_ref))
         assert _rel(grad, g_ref) <= 1e-9
+
+
+def test_amortised_flow_full_size_float32_vs_float64():
+    """BASELINE config 4 shapes (B=4096, D=40, K=16): float32 kernels against the float64 kernels (which the
+    small golden cases pin to the reference), forward and backward."""
+    from nfcore import ops
+    torch.manual_seed(7)
+    K, N, D = 16, 4096, 40
+    g = lambda *shape: torch.randn(*shape, dtype=torch.float64, device=DEV)
+    z0, mu0, ls0 = g(N, D), 0.3 * g(N, D), 0.3 * g(N, D)
+    # flow parameters of the size an encoder at its initialisation emits: keeps every sample away from the
+    # log|1 + h'c| singularity, where float32 inputs alone (not the kernel) decide the last digits
+    W, U, B = 0.3 * g(K, N, D) / D ** 0.5, 0.3 * g(K, N, D) / D ** 0.5, 0.3 * g(K, N)
+    g_zK = g(N, D) / N
+    out = {}
+    for dt in (torch.float64, torch.float32):
+        a = [t.to(dt).contiguous() for t in (z0, mu0, ls0, W, U, B)]
+        zK, logdet, tsave = ops.amortised_forward(*a)
+        grads = ops.amortised_backward(a[0], a[2], a[3], a[4], zK, tsave, g_zK.to(dt).contiguous(), -1.0 / N)
+        out[dt] = [t.double().cpu().numpy() for t in (zK, logdet) + tuple(grads)]
+    for x32, x64 in zip(out[torch.float32], out[torch.float64]):
+        assert _rel(x32, x64) <= 2e-4

@@ -85,6 +85,10 @@ def test_resolve_target():
     np.testing.assert_allclose(tp, [0.3, 0.7, -1, 3, 1, 1])
     name, tp = resolve_target(('mixdiag', [0.3], [[0, 1], [2, 3]], [[1, 1], [2, 2]]), 2)
     np.testing.assert_allclose(tp[:2], [0.3, 0.7])
+    name, tp2 = resolve_target(('mixdiag', [0.3], [[0, 1], [2, 3]], [np.diag([1., 1.]), np.diag([2., 2.])]), 2)
+    np.testing.assert_allclose(tp2, tp)
+    with pytest.raises(nfcore.NFError):
+        resolve_target(('mixdiag', [0.3], [[0, 1], [2, 3]], [np.array([[1., .2], [.2, 1.]]), np.diag([2., 2.])]), 2)
     with pytest.raises(nfcore.NFError):
         resolve_target(lambda z: z, 2)
     with pytest.raises(nfcore.NFError):

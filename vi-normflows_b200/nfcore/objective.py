@@ -49,6 +49,11 @@ def resolve_target(target, D):
     if kind == 'mixdiag':
         pi, mu, var = (np.asarray(a, dtype=np.float64) for a in target[1:])
         mu = mu.reshape(-1, D)
+        if var.ndim == 3:      # distributions.py:23-25 takes (G, D, D) covariance matrices; only diagonal ones are fused
+            off = var - np.array([np.diag(np.diag(v)) for v in var])
+            if np.abs(off).max() > 0:
+                raise NFError('mixdiag: covariance matrices must be diagonal to be fused into the kernel')
+            var = np.array([np.diag(v) for v in var])
         var = var.reshape(-1, D)
         G = mu.shape[0]
         if pi.shape[0] == G - 1:            # distributions.py:63-66: last weight is 1 - sum(pi)
