@@ -96,8 +96,8 @@ __device__ __forceinline__ T warp_sum(T v) {
 }
 
 // Multi-value warp reduction ("halving butterfly").  On entry every lane holds V
-// partial sums v[0..V).  On exit v[0] of lane L holds the warp-wide total of
-// original index warp_slot<V>(L); other v[] entries are garbage.  At each of the
+// partial sums v[0..V).  On exit v[j], j < ceil(V/32), of lane L holds the warp-wide total of
+// original index warp_slot<V>(L, j); other v[] entries are garbage.  At each of the
 // five xor stages the surviving values are paired: the lane whose stage bit is
 // set keeps the upper member of the pair and ships the lower one, so the count
 // of live values halves while the number of lanes covered doubles.  Cost
@@ -129,8 +129,9 @@ __device__ __forceinline__ void warp_reduce_multi(T (&v)[V], int lane) {
 // table: a kernel prologue only does one table lookup per thread.
 template <int V>
 struct WarpSlotTable {
-    int slot[32];
-    bool own[32];
+    static constexpr int KEEP = (V + 31) / 32;      // values left per lane after the five stages (1 for V <= 32)
+    int slot[32][KEEP];
+    bool own[32][KEEP];
     constexpr WarpSlotTable() : slot{}, own{} {
         for (int lane = 0; lane < 32; ++lane) {
             int idx[V] = {};
@@ -142,21 +143,23 @@ struct WarpSlotTable {
                 for (int i = 0; i < n - h; ++i) idx[i] = up ? idx[i + h] : idx[i];
                 n = h;
             }
-            slot[lane] = idx[0];
+            for (int j = 0; j < KEEP; ++j) slot[lane][j] = j < n ? idx[j] : -1;
         }
-        for (int lane = 0; lane < 32; ++lane) {
-            bool first = true;
-            for (int l = 0; l < lane; ++l)
-                if (slot[l] == slot[lane]) first = false;
-            own[lane] = first;
-        }
+        for (int lane = 0; lane < 32; ++lane)
+            for (int j = 0; j < KEEP; ++j) {
+                bool first = slot[lane][j] >= 0;
+                for (int l = 0; l < lane; ++l)
+                    for (int jj = 0; jj < KEEP; ++jj)
+                        if (slot[l][jj] == slot[lane][j]) first = false;
+                own[lane][j] = first;
+            }
     }
 };
 template <int V> __device__ constexpr WarpSlotTable<V> kWarpSlotTable{};
 
 template <int V>
-__device__ __forceinline__ int warp_slot(int lane) { return kWarpSlotTable<V>.slot[lane]; }
+__device__ __forceinline__ int warp_slot(int lane, int j = 0) { return kWarpSlotTable<V>.slot[lane][j]; }
 template <int V>
-__device__ __forceinline__ bool warp_slot_owner(int lane) { return kWarpSlotTable<V>.own[lane]; }
+__device__ __forceinline__ bool warp_slot_owner(int lane, int j = 0) { return kWarpSlotTable<V>.own[lane][j]; }
 
 }  // namespace nf

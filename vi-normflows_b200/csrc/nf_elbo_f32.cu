@@ -6,7 +6,7 @@ extern "C" {
 
 size_t nf_planar_elbo_workspace_bytes(int K, int D, int elem_size) {
     if (K < 1 || D < 1 || elem_size < 1) return 0;
-    if (D <= 4) {
+    if (nf::elbo_thread_per_sample(D)) {
         const size_t row = (size_t)K * (2 * D + 2) + 2;
         return row * (size_t)nf::max_grid_blocks() * (size_t)elem_size;
     }

@@ -290,6 +290,9 @@ __device__ __forceinline__ void elbo_tile(const T* __restrict__ eps, long long n
             if (k < K - 1) {
                 warp_reduce_multi<T, V>(vp, lane);
                 if (my_own) acc_w[(k + 1) * V + my_slot] += vp[0];
+#pragma unroll
+                for (int jx = 1; jx < WarpSlotTable<V>::KEEP; ++jx)      // V > 32 (D = 16): a second value per lane
+                    if (warp_slot_owner<V>(lane, jx)) acc_w[(k + 1) * V + warp_slot<V>(lane, jx)] += vp[jx];
             }
         };
         int k = K - 1;
@@ -304,6 +307,9 @@ __device__ __forceinline__ void elbo_tile(const T* __restrict__ eps, long long n
         for (int i = 0; i < V; ++i) vp[i] = vlast[i];
         warp_reduce_multi<T, V>(vp, lane);
         if (my_own) acc_w[my_slot] += vp[0];
+#pragma unroll
+        for (int jx = 1; jx < WarpSlotTable<V>::KEEP; ++jx)
+            if (warp_slot_owner<V>(lane, jx)) acc_w[warp_slot<V>(lane, jx)] += vp[jx];
     }
 #pragma unroll
     for (int j = 0; j < S; ++j) sum_q += (MASKED && !ok[j]) ? (T)0 : lq[j];
@@ -550,7 +556,9 @@ template <typename T, int D, int TGT>
 static int dispatch_bwd(bool bwd, const T* eps, long long N, int K, const T* w, const T* s, const T* b, const T* c,
                         const T* tp, int ntp, T epsv, T* partials, int max_blocks, int* nb, cudaStream_t st) {
     constexpr int NT = kElboThreads;
-    constexpr int SB = SamplesPerThread<T>::big, SM_ = SamplesPerThread<T>::mid, SS = SamplesPerThread<T>::small;
+    // D = 16 keeps 2 x 16 coordinates of z and of the gradient per sample in registers: two samples per thread at most
+    constexpr int SB = D <= 4 ? SamplesPerThread<T>::big : 2, SM_ = D <= 4 ? SamplesPerThread<T>::mid : (sizeof(T) == 4 ? 2 : 1),
+                  SS = D <= 4 ? SamplesPerThread<T>::small : 1;
 #define NF_GO(S_, ST_, NT_, BW_) \
     return launch_elbo<T, D, S_, ST_, NT_, TGT, BW_>(eps, N, K, w, s, b, c, tp, ntp, epsv, partials, max_blocks, nb, st)
     if (!bwd) {
@@ -677,8 +685,11 @@ static inline int max_grid_blocks() {
 }
 
 struct ElboRowLayout { int Vk, off_s, off_b; };
+// D <= 4 and D == 16 run one thread per sample (elbo_shared_kernel); other D share a sample among lanes
+static inline bool elbo_thread_per_sample(int D) { return D <= 4 || D == 16; }
+
 static inline ElboRowLayout elbo_row_layout(int D) {
-    if (D <= 4) return {2 * D + 2, D, 2 * D};
+    if (elbo_thread_per_sample(D)) return {2 * D + 2, D, 2 * D};
     const int Dp = (D + 3) & ~3;
     return {wide_vk(D), Dp, 2 * Dp};
 }
@@ -713,6 +724,7 @@ static int elbo_main(bool bwd, const T* eps, int64_t N, int D, int K, const T* w
         case 2: return dispatch_target<T, 2>(target_id, bwd, eps, N, K, w, s, b, c, tparams, ntp, epsv, partials, max_blocks, nrows, stream);
         case 3: return dispatch_target<T, 3>(target_id, bwd, eps, N, K, w, s, b, c, tparams, ntp, epsv, partials, max_blocks, nrows, stream);
         case 4: return dispatch_target<T, 4>(target_id, bwd, eps, N, K, w, s, b, c, tparams, ntp, epsv, partials, max_blocks, nrows, stream);
+        case 16: return dispatch_target<T, 16>(target_id, bwd, eps, N, K, w, s, b, c, tparams, ntp, epsv, partials, max_blocks, nrows, stream);
         default:
             if (target_id == NF_TARGET_GAUSSDIAG)
                 return dispatch_wide<T, NF_TARGET_GAUSSDIAG>(bwd, eps, N, D, K, w, s, b, c, tparams, ntp, epsv, partials, nrows, stream);
