@@ -286,8 +286,8 @@ def run_ours(args):
             'bound': 'mufu', 'achieved': per_gpu * MUFU_PER_SAMPLE / 1e9, 'peak': mufu_peak / 1e9, 'unit': 'G MUFU-op/s',
             'frac': fracs['mufu'],
             # dram__bytes_read.sum + dram__bytes_write.sum of one objective-kernel launch at this workload, from the
-            # committed `ncu --set full` capture (profiles/r01d_ncu_elbo_kernel.txt); algorithmic bytes: 8.39e6
-            'traffic': 8.457984e6 + 6.656e3,
+            # committed `ncu --set full` capture (profiles/r01e_ncu_elbo_kernel.txt); algorithmic bytes: 8.39e6
+            'traffic': 8.447488e6,
             'per_unit': {'flops': FLOPS_PER_SAMPLE, 'mufu': MUFU_PER_SAMPLE, 'bytes': BYTES_PER_SAMPLE},
             'peak_source': 'formula SMs*16*sm_max_mhz (SURVEY.md §8d; MEASURED_PEAKS.json has no MUFU figure); '
                            'sm_max_mhz and hbm_gbs %s' % ('of measured' if peaks else 'of fallback'),
