@@ -124,3 +124,74 @@ def test_amortised_flow_full_size_float32_vs_float64():
         out[dt] = [t.double().cpu().numpy() for t in (zK, logdet) + tuple(grads)]
     for x32, x64 in zip(out[torch.float32], out[torch.float64]):
         assert _rel(x32, x64) <= 2e-4
+
+
+# ---- matrix-product ("Gram") formulation of the wide-D free energy: csrc/nf_elbo_gram.cu ----
+def _gram_case(D, K, N, seed):
+    rs = np.random.RandomState(seed)
+    z0 = rs.randn(N, D)
+    sc = 1.0 / np.sqrt(D / 2)
+    params = np.concatenate([sc * 0.5 * rs.randn(2 * K * D), 0.3 * rs.randn(K)])
+    mu, ls = 0.2 * rs.randn(D), 0.3 * rs.randn(D) - 4.0 / D
+    return rs, z0, params, mu, ls
+
+
+@pytest.mark.parametrize('D,K,N,chunk', [(32, 5, 1500, None), (64, 7, 2000, None), (100, 16, 1100, None),
+                                         (256, 64, 1200, None), (64, 32, 3000, 512), (128, 9, 2500, 1024)])
+def test_gram_free_energy_matches_oracle(D, K, N, chunk, monkeypatch):
+    """N >= 1024, float32, D % 4 == 0, K <= 64 take the tensor-core path; ragged N, K that is not a multiple
+    of 4, and (through the chunk knob) several chunks with a short last one.  Same oracle and tolerance as the
+    direct wide-D kernel above; the direct kernel is run on the same inputs as a cross-check."""
+    from nfcore.objective import SharedFlowObjective
+    from oracle import planar_torch as pt
+    if chunk:
+        monkeypatch.setenv('NF_GRAM_CHUNK', str(chunk))
+    rs, z0, params, mu, ls = _gram_case(D, K, N, 11 * D + K)
+    tgt = lambda z: torch.exp(pt.log_mvn(z, mu, ls))
+    F_ref, g_ref = pt.script_value_and_grad(params, z0, tgt, 1e-7, K)
+    tol = 2e-4
+    obj = SharedFlowObjective(('gaussdiag', mu, ls), K, D, dtype='float32')
+    z0_dev = torch.tensor(z0, device=DEV)       # device samples go through nf_planar_elbo_fwd_bwd_f32
+    F, grad = obj.value_and_grad(params, z0_dev)
+    assert abs(F - F_ref) <= tol * max(1.0, abs(F_ref)), (F, F_ref)
+    assert _rel(grad, g_ref) <= tol, _rel(grad, g_ref)
+    assert abs(obj.value(params, z0_dev) - F_ref) <= tol * max(1.0, abs(F_ref))
+    monkeypatch.setenv('NF_NO_GRAM', '1')
+    F_d, grad_d = obj.value_and_grad(params, z0_dev)
+    assert abs(F - F_d) <= tol * max(1.0, abs(F_ref))
+    assert _rel(grad, grad_d) <= tol
+
+
+def test_gram_mixture_target_matches_oracle():
+    from nfcore.objective import SharedFlowObjective
+    from oracle import planar_torch as pt
+    D, K, N, G = 32, 6, 1300, 3
+    rs, z0, params, _, _ = _gram_case(D, K, N, 5)
+    pi = np.array([0.3, 0.45]); mmu = 0.3 * rs.randn(G, D); var = 0.8 + 0.4 * rs.rand(G, D)
+    sig = torch.tensor(np.array([np.diag(v) for v in var]))
+    tgt = lambda z: pt.prob_gm(z, torch.tensor(mmu), sig, torch.tensor(pi))
+    F_ref, g_ref = pt.script_value_and_grad(params, z0, tgt, 1e-7, K)
+    obj = SharedFlowObjective(('mixdiag', pi, mmu, var), K, D, dtype='float32')
+    F, grad = obj.value_and_grad(params, torch.tensor(z0, device=DEV))
+    assert abs(F - F_ref) <= 2e-4 * max(1.0, abs(F_ref)), (F, F_ref)
+    assert _rel(grad, g_ref) <= 2e-4, _rel(grad, g_ref)
+
+
+@pytest.mark.parametrize('D,N', [(64, 1 << 19), (256, 1 << 17)])
+def test_gram_full_size_agrees_with_direct_kernel(D, N, monkeypatch):
+    """BASELINE config 5 sizes (K = 64): the two formulations of the same sums, float32, on the same samples."""
+    from nfcore import ops
+    K = 64
+    torch.manual_seed(D)
+    eps = torch.randn(N, D, device=DEV)
+    sc = 0.5 / (D / 2) ** 0.5
+    w, s = sc * torch.randn(K, D, device=DEV), sc * torch.randn(K, D, device=DEV)
+    b, c = 0.3 * torch.randn(K, device=DEV), 0.3 * torch.randn(K, device=DEV)
+    tp = torch.cat([0.2 * torch.randn(D, device=DEV), 0.3 * torch.randn(D, device=DEV) - 4.0 / D])
+    got = [t.double().cpu().numpy() for t in ops.planar_elbo(eps, w, s, b, c, 'gaussdiag', tp)]
+    monkeypatch.setenv('NF_NO_GRAM', '1')
+    ref = [t.double().cpu().numpy() for t in ops.planar_elbo(eps, w, s, b, c, 'gaussdiag', tp)]
+    assert np.all(np.isfinite(got[0]))
+    assert np.abs(got[0] - ref[0]).max() <= 2e-4 * np.abs(ref[0]).max()
+    for a, r in zip(got[1:], ref[1:]):
+        assert _rel(a, r) <= 5e-4

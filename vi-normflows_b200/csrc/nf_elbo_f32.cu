@@ -2,6 +2,15 @@
 // that do not depend on the element type.
 #include "nf_elbo_impl.cuh"
 
+namespace nf {
+// nf_elbo_gram.cu: the matrix-product formulation for wide latent spaces (float32)
+bool gram_applicable(long long N, int D, int K, int target_id, int ntp);      // target_id < 0: any supported target
+size_t gram_workspace_bytes(long long N, int D, int K);
+int gram_elbo_f32(bool bwd, const float* eps, long long N, int D, int K, const float* w, const float* s, const float* b,
+                  const float* c, int target_id, const float* tp, int ntp, float epsv, float* out_F, float* g_w, float* g_s,
+                  float* g_b, float* g_c, void* workspace, cudaStream_t st);
+}  // namespace nf
+
 extern "C" {
 
 size_t nf_planar_elbo_workspace_bytes(int K, int D, int elem_size) {
@@ -15,10 +24,30 @@ size_t nf_planar_elbo_workspace_bytes(int K, int D, int elem_size) {
     return row * (size_t)((di.sms > 0 ? di.sms : 148) * nf::wide_blocks_per_sm(K, D, (size_t)elem_size) * nf::kWideWarps) * (size_t)elem_size;
 }
 
+size_t nf_planar_elbo_workspace_bytes_n(int64_t N, int K, int D, int elem_size) {
+    size_t need = nf_planar_elbo_workspace_bytes(K, D, elem_size);
+    if (need && elem_size == 4 && nf::gram_applicable(N, D, K, -1, 0)) {
+        const size_t g = nf::gram_workspace_bytes(N, D, K);
+        if (g > need) need = g;
+    }
+    return need;
+}
+
 int nf_planar_elbo_fwd_bwd_f32(const float* eps, int64_t N, int D, int K, const float* w, const float* s,
                                const float* b, const float* c, int target_id, const float* target_params,
                                int n_target_params, float log_eps, float* out_F, float* g_w, float* g_s,
                                float* g_b, float* g_c, void* workspace, size_t workspace_bytes, void* stream) {
+    // wide D with a workspace large enough for the intermediates of a chunk: matrix-product path
+    if (out_F && workspace && nf::gram_applicable(N, D, K, target_id, n_target_params) &&
+        workspace_bytes >= nf::gram_workspace_bytes(N, D, K) &&
+        ((reinterpret_cast<uintptr_t>(workspace) | reinterpret_cast<uintptr_t>(w) | reinterpret_cast<uintptr_t>(s)) & 15) == 0) {
+        const bool any_g = g_w || g_s || g_b || g_c, all_g = g_w && g_s && g_b && g_c;
+        if (any_g && !all_g) return NF_ERR_INVALID;
+        const int rc = nf::elbo_validate<float>(eps, N, D, K, w, s, b, c, target_id, target_params, n_target_params);
+        if (rc != NF_OK) return rc;
+        return nf::gram_elbo_f32(all_g, eps, N, D, K, w, s, b, c, target_id, target_params, n_target_params, log_eps, out_F,
+                                 g_w, g_s, g_b, g_c, workspace, (cudaStream_t)stream);
+    }
     return nf::elbo_entry<float>(eps, N, D, K, w, s, b, c, target_id, target_params, n_target_params, log_eps,
                                  out_F, g_w, g_s, g_b, g_c, workspace, workspace_bytes, stream);
 }

@@ -1,0 +1,506 @@
+// Shared-parameter free energy for wide latent spaces through matrix products ("Gram" path), sm_100a.
+//
+// get_data.py:104-109 moves z only inside span{s_j}:  z_k = z_0 + sum_{j<=k} s_j t_j.  With
+// M[k][j] = w_k.s_j every size-D operation of the layer chain and of its reverse pass becomes a
+// product with a K-column matrix, and what is sequential shrinks to K^2/2 scalar multiply-adds
+// per sample and direction (tests/test_gram_identity.py restates the algebra in NumPy):
+//
+//   A0 = z_0 W^T + b                       product 1   [N x D] x [D x K]
+//   a_k = A0[k] + sum_{j<k} M[k][j] t_j    forward recurrence, one thread per sample
+//   z_K = z_0 + T S                        product 2   [N x K] x [K x D]
+//   gz_K = dF/dz_K, log p, log q_0         target kernel (distributions.py:10-54)
+//   P = gz_K S^T                           product 3   [N x D] x [D x K]
+//   gz_k.s_k = P[k] + sum_{j>k} delta_j M[j][k]        reverse recurrence
+//   g_s = T^T gz_K + triu(T^T Delta,1) W   products 4, 6   (contraction over the samples)
+//   g_w = Delta^T z_0 + triu(T^T Delta,1)^T S          product 5
+//
+// The products run on the tensor cores (nf_gemm_tc.cu: tcgen05.mma kind::tf32, 3 passes for
+// float32 accuracy).  The direct kernel (nf_elbo_wide.cuh) spends 7 D multiply-adds per layer and
+// sample on the CUDA cores and, worse, has to add a [K][2D] gradient record per warp and layer
+// to global memory; here the gradient accumulators are output tiles of products 4-6.
+// Samples are processed in chunks so that the intermediates of a chunk stay close to the L2 size.
+// float32, D % 4 == 0, K <= 64, targets GAUSSDIAG / MIXDIAG (<= 16 components).
+#include <cstdio>
+#include <cstdlib>
+#include "nf_common.cuh"
+
+namespace nf {
+
+int tc_gemm_f32(const float* A, long long lda, const float* B, long long ldb, int M, int N, int K, float* C, long long ldc,
+                float* CT, long long ldct, const float* bias, int act, const float* mask_src, long long ldm, int mask,
+                cudaStream_t st, int splits = 1, float* split_ws = nullptr, bool accumulate = false);
+
+namespace gram {
+
+constexpr int kRecThreads = 128;
+constexpr int kMaxK = 64;
+constexpr int kMaxMix = 16;
+constexpr int kTgtRows = 32;         // rows per block of the target kernel
+constexpr int kTgtThreads = 256;
+
+static inline int pad_k(int K) { return K <= 16 ? 16 : (K <= 32 ? 32 : 64); }
+static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// chunk pitch (samples): about 4M elements of [Nc][D], a multiple of 128, no more than the job needs
+static inline long long chunk_samples(long long N, int D) {
+    long long nc = ((long long)4 << 20) / D;
+    if (const char* e = getenv("NF_GRAM_CHUNK")) { const long long v = atoll(e); if (v >= 128) nc = v; }
+    nc = (nc + 127) / 128 * 128;
+    const long long need = (N + 127) / 128 * 128;
+    return nc < need ? nc : need;
+}
+static inline int grad_splits(long long nc, int D) {
+    const int tiles_m = (D + 127) / 128;
+    long long s = (296 + tiles_m - 1) / tiles_m;          // about two CTAs per SM
+    const long long nkb = (nc + 31) / 32;
+    if (s > nkb / 4) s = nkb / 4;                          // at least four k-blocks per CTA
+    return (int)(s < 1 ? 1 : s);
+}
+
+struct Layout {
+    int KP; long long Nc; int splits;
+    size_t acc, M, Mt, ST, G4, G5, G6, part_ld, part_t, split4, split5, split6;   // offsets in floats
+    size_t AT, CT, DT, TT, Trow, Y, GZT, Z0T, total;
+};
+static Layout make_layout(long long N, int D, int K) {
+    Layout L{};
+    L.KP = pad_k(K);
+    L.Nc = chunk_samples(N, D);
+    L.splits = grad_splits(L.Nc, D);
+    size_t o = 0;
+    auto take = [&](size_t n) { const size_t at = o; o = align_up(o + n, 64); return at; };   // 256-byte aligned pieces
+    L.acc = take(3 + 2 * kMaxK);
+    L.M = take((size_t)L.KP * L.KP);
+    L.Mt = take((size_t)L.KP * L.KP);
+    L.ST = take((size_t)D * L.KP);
+    L.G4 = take((size_t)D * K);
+    L.G5 = take((size_t)D * K);
+    L.G6 = take((size_t)K * K);
+    L.part_ld = take((size_t)(L.Nc / kRecThreads));
+    L.part_t = take((size_t)2 * (L.Nc / kTgtRows));
+    L.split4 = take((size_t)L.splits * D * K);
+    L.split5 = take((size_t)L.splits * D * K);
+    L.split6 = take((size_t)L.splits * K * K);
+    L.AT = take((size_t)K * L.Nc);          // A0^T, later P^T
+    L.CT = take((size_t)K * L.Nc);          // per-sample d F / d c_k terms
+    L.DT = take((size_t)K * L.Nc);          // Delta^T
+    L.TT = take((size_t)K * L.Nc);          // T^T
+    L.Trow = take((size_t)L.Nc * L.KP);     // T, row per sample
+    L.Y = take((size_t)L.Nc * D);           // T S, later gz_K
+    L.GZT = take((size_t)D * L.Nc);
+    L.Z0T = take((size_t)D * L.Nc);
+    L.total = o;
+    return L;
+}
+
+// ------------------------------------------------------------------------------------------------
+// set-up: M = W S^T (both orientations, scaled for the exp2-based tanh, strictly triangular parts only),
+// S^T, and cleared running totals.  One block per layer.
+__global__ void prep_kernel(const float* __restrict__ w, const float* __restrict__ s, int K, int D, int KP,
+                            float* __restrict__ M, float* __restrict__ Mt, float* __restrict__ ST, float* __restrict__ acc) {
+    const int k = blockIdx.x;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+    if (k == 0)
+        for (int i = threadIdx.x; i < 3 + 2 * kMaxK; i += blockDim.x) acc[i] = 0.f;
+    for (int j = warp; j < KP; j += nw) {
+        float v = 0.f;
+        if (k < K && j < K && j != k) {
+            for (int d = lane; d < D; d += 32) v = fmaf(w[(size_t)k * D + d], s[(size_t)j * D + d], v);
+            v = warp_sum(v);
+        }
+        if (lane == 0) {
+            // forward uses column j of M below the diagonal: Mt[j][k], k > j, in units of the scaled tanh argument
+            Mt[(size_t)j * KP + k] = (k > j) ? v * Mth<float>::kArgScale : 0.f;
+            // reverse uses row k of M left of the diagonal: M[k][j], j < k
+            M[(size_t)k * KP + j] = (j < k) ? v : 0.f;
+        }
+    }
+    for (int d = threadIdx.x; d < D; d += blockDim.x) ST[(size_t)d * KP + k] = k < K ? s[(size_t)k * D + d] : 0.f;
+}
+
+// [rows][cols] (ld = cols) -> [cols][rows] (ld = ldo); 32 x 32 tiles, block (32, 8)
+__global__ void transpose_kernel(const float* __restrict__ in, int rows, int cols, float* __restrict__ out, long long ldo) {
+    __shared__ float tile[32][33];
+    const int r0 = blockIdx.y * 32, c0 = blockIdx.x * 32;
+    for (int i = threadIdx.y; i < 32; i += 8) {
+        const int r = r0 + i, c = c0 + threadIdx.x;
+        tile[i][threadIdx.x] = (r < rows && c < cols) ? in[(size_t)r * cols + c] : 0.f;
+    }
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += 8) {
+        const int c = c0 + i, r = r0 + threadIdx.x;
+        if (c < cols && r < rows) out[(size_t)c * ldo + r] = tile[threadIdx.x][i];
+    }
+}
+
+// block-wide sum in a fixed order (warp trees, then warp 0 over the warp results)
+template <int NT>
+__device__ __forceinline__ float block_sum(float v, float* red /* [NT/32] */) {
+    v = warp_sum(v);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    __syncthreads();
+    if (lane == 0) red[warp] = v;
+    __syncthreads();
+    float t = 0.f;
+    if (warp == 0) {
+        t = lane < NT / 32 ? red[lane] : 0.f;
+        t = warp_sum(t);
+    }
+    return t;      // valid on warp 0
+}
+
+// ------------------------------------------------------------------------------------------------
+// Forward recurrence.  One thread per sample; the K pre-activations live in registers and are turned
+// into t_j = tanh(a_j) in place, column j of M being added to the later ones as soon as t_j is known.
+// Mt rows are zero up to and including the diagonal, so whole float4 groups can be applied blindly.
+// Outputs: T^T (coalesced), T rows (operand of product 2), per-block sum of the log-det terms.
+template <int KP>
+__global__ void __launch_bounds__(kRecThreads)
+rec_fwd_kernel(const float* __restrict__ AT, long long ldn, int n_act, int K, const float* __restrict__ Mt,
+               const float* __restrict__ c, float epsv, float* __restrict__ TT, float* __restrict__ Trow,
+               float* __restrict__ part_ld) {
+    using M_ = Mth<float>;
+    __shared__ __align__(16) float sM[KP * KP];
+    __shared__ float sc[KP];
+    __shared__ float red[kRecThreads / 32];
+    for (int i = threadIdx.x; i < KP * KP; i += kRecThreads) sM[i] = Mt[i];
+    for (int i = threadIdx.x; i < KP; i += kRecThreads) sc[i] = i < K ? c[i] : 0.f;
+    __syncthreads();
+    const int n = blockIdx.x * kRecThreads + threadIdx.x;
+    const bool ok = n < n_act;
+    float a[KP];
+#pragma unroll
+    for (int k = 0; k < KP; ++k) a[k] = (ok && k < K) ? AT[(size_t)k * ldn + n] * M_::kArgScale : 0.f;
+    float prod = 1.f, ld = 0.f;
+#pragma unroll
+    for (int j = 0; j < KP; ++j) {
+        const float t = M_::tanh_pre(a[j]);
+        a[j] = t;
+        if (j < K) {
+            const float hp = fmaf(-t, t, 1.f);
+            prod *= epsv + fabsf(fmaf(hp, sc[j], 1.f));
+            if ((j & 3) == 3 || j == K - 1) { ld += M_::logp(prod); prod = 1.f; }
+            if (ok) TT[(size_t)j * ldn + n] = t;
+        }
+#pragma unroll
+        for (int k4 = (j + 1) / 4; k4 < KP / 4; ++k4) {
+            const float4 m = *reinterpret_cast<const float4*>(&sM[j * KP + 4 * k4]);
+            if (4 * k4 + 0 > j) a[4 * k4 + 0] = fmaf(m.x, t, a[4 * k4 + 0]);
+            if (4 * k4 + 1 > j) a[4 * k4 + 1] = fmaf(m.y, t, a[4 * k4 + 1]);
+            if (4 * k4 + 2 > j) a[4 * k4 + 2] = fmaf(m.z, t, a[4 * k4 + 2]);
+            if (4 * k4 + 3 > j) a[4 * k4 + 3] = fmaf(m.w, t, a[4 * k4 + 3]);
+        }
+    }
+    if (ok) {
+        float4* row = reinterpret_cast<float4*>(Trow + (size_t)n * KP);
+#pragma unroll
+        for (int k4 = 0; k4 < KP / 4; ++k4) row[k4] = make_float4(a[4 * k4], a[4 * k4 + 1], a[4 * k4 + 2], a[4 * k4 + 3]);
+    }
+    const float tot = block_sum<kRecThreads>(ok ? ld : 0.f, red);
+    if (threadIdx.x == 0) part_ld[blockIdx.x] = tot;
+}
+
+// Reverse recurrence.  p_k starts as (gz_K.s_k) and receives delta_j M[j][k] from the later layers.
+// Outputs: Delta^T and the per-sample d F / d c_k terms (both [K][Nc], summed along n afterwards).
+template <int KP>
+__global__ void __launch_bounds__(kRecThreads)
+rec_bwd_kernel(const float* __restrict__ PT, const float* __restrict__ TT, long long ldn, int n_act, int K,
+               const float* __restrict__ Mrow, const float* __restrict__ c, float epsv, float* __restrict__ DT,
+               float* __restrict__ CT) {
+    using M_ = Mth<float>;
+    __shared__ __align__(16) float sM[KP * KP];
+    __shared__ float sc[KP];
+    for (int i = threadIdx.x; i < KP * KP; i += kRecThreads) sM[i] = Mrow[i];
+    for (int i = threadIdx.x; i < KP; i += kRecThreads) sc[i] = i < K ? c[i] : 0.f;
+    __syncthreads();
+    const int n = blockIdx.x * kRecThreads + threadIdx.x;
+    if (n >= n_act) return;
+    float p[KP];
+#pragma unroll
+    for (int k = 0; k < KP; ++k) p[k] = k < K ? PT[(size_t)k * ldn + n] : 0.f;
+#pragma unroll
+    for (int k = KP - 1; k >= 0; --k) {
+        if (k < K) {
+            const float t = TT[(size_t)k * ldn + n];
+            const float ck = sc[k];
+            const float hp = fmaf(-t, t, 1.f);
+            const float x = fmaf(hp, ck, 1.f);
+            const float y = epsv + fabsf(x);
+            const float gx = M_::neg_copysign(M_::rcp(y), x);
+            CT[(size_t)k * ldn + n] = gx * hp;
+            const float gt = fmaf(-2.f * ck * gx, t, p[k]);
+            const float ga = gt * hp;
+            DT[(size_t)k * ldn + n] = ga;
+#pragma unroll
+            for (int i4 = 0; i4 < (k + 3) / 4; ++i4) {
+                const float4 m = *reinterpret_cast<const float4*>(&sM[k * KP + 4 * i4]);
+                if (4 * i4 + 0 < k) p[4 * i4 + 0] = fmaf(m.x, ga, p[4 * i4 + 0]);
+                if (4 * i4 + 1 < k) p[4 * i4 + 1] = fmaf(m.y, ga, p[4 * i4 + 1]);
+                if (4 * i4 + 2 < k) p[4 * i4 + 2] = fmaf(m.z, ga, p[4 * i4 + 2]);
+                if (4 * i4 + 3 < k) p[4 * i4 + 3] = fmaf(m.w, ga, p[4 * i4 + 3]);
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Target kernel: z_K = z_0 + Y, log p(z_K), log q_0(z_0) and gz_K = dF/dz_K = -d log p / dz_K.
+// A block owns 32 consecutive samples (8 warps x 4 rows); gz_K is written in place of Y (row form,
+// operand of product 3) and, through a shared-memory tile, transposed (operand of product 4).
+// Same density formulas as elbo_wide_kernel (distributions.py:10-54).
+template <int TGT, bool BWD>
+__global__ void __launch_bounds__(kTgtThreads)
+target_kernel(const float* __restrict__ z0, float* __restrict__ Y, int n_act, int D, long long ldn,
+              const float* __restrict__ tparams, int ntp, float epsv, float* __restrict__ GZT,
+              float* __restrict__ part /* [gridDim][2] : sum log q_0, sum log p */) {
+    using M_ = Mth<float>;
+    extern __shared__ float tile[];                 // [32][D + 1]
+    __shared__ float red[kTgtThreads / 32];
+    __shared__ float mixe[kTgtThreads / 32][kMaxMix];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int pitch = D + 1;
+    const float LOG2PI = 1.8378770664093453f;
+    const int n0 = blockIdx.x * kTgtRows;
+    float sum_q = 0.f, sum_p = 0.f;
+    float g_const = 0.f;
+    if (TGT == NF_TARGET_GAUSSDIAG) {
+        float ls = 0.f;
+        for (int d = lane; d < D; d += 32) ls += tparams[D + d];
+        ls = warp_sum(ls);
+        g_const = -0.5f * (D * LOG2PI + ls);
+    }
+    for (int r = warp; r < kTgtRows; r += kTgtThreads / 32) {
+        const int n = n0 + r;
+        if (n >= n_act) {
+            if (BWD) for (int d = lane; d < D; d += 32) tile[r * pitch + d] = 0.f;
+            continue;
+        }
+        const float* zr = z0 + (size_t)n * D;
+        float* yr = Y + (size_t)n * D;
+        float zz = 0.f;
+        for (int d = lane; d < D; d += 32) {
+            const float a = zr[d];
+            zz = fmaf(a, a, zz);
+            tile[r * pitch + d] = a + yr[d];
+        }
+        zz = warp_sum(zz);
+        sum_q += -0.5f * (D * LOG2PI + zz);
+        float lp;
+        if (TGT == NF_TARGET_GAUSSDIAG) {
+            float q = 0.f;
+            for (int d = lane; d < D; d += 32) {
+                const float df = tile[r * pitch + d] - tparams[d];
+                q = fmaf(df * M_::exp(-tparams[D + d]), df, q);
+            }
+            q = warp_sum(q);
+            const float dens = M_::exp(g_const - 0.5f * q);
+            const float den = epsv + dens;
+            lp = M_::logp(den);
+            if (BWD) {
+                const float rho = M_::div(dens, den);
+                for (int d = lane; d < D; d += 32) {
+                    const float g = rho * (tile[r * pitch + d] - tparams[d]) * M_::exp(-tparams[D + d]);
+                    tile[r * pitch + d] = g;
+                    yr[d] = g;
+                }
+            }
+        } else {   // MIXDIAG: [pi (G) | mu (G*D) | var (G*D)]
+            const int G = ntp / (1 + 2 * D);
+            float dens = 0.f;
+            for (int gc = 0; gc < G; ++gc) {
+                const float* mu = tparams + G + (size_t)gc * D;
+                const float* var = tparams + G + (size_t)G * D + (size_t)gc * D;
+                float q = 0.f, lsum = 0.f;
+                for (int d = lane; d < D; d += 32) {
+                    const float df = tile[r * pitch + d] - mu[d];
+                    q = fmaf(df, M_::div(df, var[d]), q);
+                    lsum += M_::logp(var[d]);
+                }
+                q = warp_sum(q);
+                lsum = warp_sum(lsum);
+                const float e = tparams[gc] * M_::exp(-0.5f * (D * LOG2PI + lsum + q));
+                dens += e;
+                if (lane == 0) mixe[warp][gc] = e;
+            }
+            const float den = epsv + dens;
+            lp = M_::logp(den);
+            if (BWD) {
+                __syncwarp();
+                const float inv = M_::div(1.f, den);
+                for (int d = lane; d < D; d += 32) {
+                    const float z = tile[r * pitch + d];
+                    float acc = 0.f;
+                    for (int gc = 0; gc < G; ++gc)
+                        acc = fmaf(mixe[warp][gc], M_::div(z - tparams[G + (size_t)gc * D + d], tparams[G + (size_t)G * D + (size_t)gc * D + d]), acc);
+                    const float g = acc * inv;
+                    tile[r * pitch + d] = g;
+                    yr[d] = g;
+                }
+                __syncwarp();
+            }
+        }
+        sum_p += lp;
+    }
+    // per-warp totals are identical on all lanes; add the eight warps in order
+    __syncthreads();
+    if (lane == 0) red[warp] = sum_q;
+    __syncthreads();
+    if (threadIdx.x == 0) { float t = 0.f; for (int i = 0; i < kTgtThreads / 32; ++i) t += red[i]; part[2 * blockIdx.x] = t; }
+    __syncthreads();
+    if (lane == 0) red[warp] = sum_p;
+    __syncthreads();
+    if (threadIdx.x == 0) { float t = 0.f; for (int i = 0; i < kTgtThreads / 32; ++i) t += red[i]; part[2 * blockIdx.x + 1] = t; }
+    if (BWD) {
+        // transposed copy: lane <-> sample, warps stride over the coordinates
+        const int n = n0 + lane;
+        if (n < n_act)
+            for (int d = warp; d < D; d += kTgtThreads / 32) GZT[(size_t)d * ldn + n] = tile[lane * pitch + d];
+    }
+}
+
+// Per chunk: running totals.  Blocks [0, K): sum_n Delta^T[k][n] -> g_b[k]; blocks [K, 2K): sum_n CT -> g_c;
+// block 2K: log-det, log q_0 and log p partial sums.  Fixed order, and chunks arrive in stream order.
+__global__ void __launch_bounds__(256)
+chunk_totals_kernel(const float* __restrict__ DT, const float* __restrict__ CT, long long ldn, int n_act, int K, int bwd,
+                    const float* __restrict__ part_ld, int n_ld, const float* __restrict__ part_t, int n_t,
+                    float* __restrict__ acc /* [ld, q0, p | g_b (kMaxK) | g_c (kMaxK)] */) {
+    __shared__ float red[8];
+    const int b = blockIdx.x;
+    if (b < 2 * K) {
+        if (!bwd) return;
+        const float* row = (b < K ? DT + (size_t)b * ldn : CT + (size_t)(b - K) * ldn);
+        float v = 0.f;
+        for (int n = threadIdx.x; n < n_act; n += 256) v += row[n];
+        const float t = block_sum<256>(v, red);
+        if (threadIdx.x == 0) acc[3 + (b < K ? b : kMaxK + (b - K))] += t;
+    } else {
+        float a = 0.f, q = 0.f, p = 0.f;
+        for (int i = threadIdx.x; i < n_ld; i += 256) a += part_ld[i];
+        for (int i = threadIdx.x; i < n_t; i += 256) { q += part_t[2 * i]; p += part_t[2 * i + 1]; }
+        const float ta = block_sum<256>(a, red);
+        const float tq = block_sum<256>(q, red);
+        const float tp = block_sum<256>(p, red);
+        if (threadIdx.x == 0) { acc[0] += ta; acc[1] += tq; acc[2] += tp; }
+    }
+}
+
+// g_s[k][d] = G4[d][k] + sum_{j>k} G6[k][j] w[j][d] ;  g_w[k][d] = G5[d][k] + sum_{j<k} G6[j][k] s[j][d]
+__global__ void finish_kernel(const float* __restrict__ acc, const float* __restrict__ G4, const float* __restrict__ G5,
+                              const float* __restrict__ G6, const float* __restrict__ w, const float* __restrict__ s,
+                              int K, int D, int bwd, float* __restrict__ out_F, float* __restrict__ g_w,
+                              float* __restrict__ g_s, float* __restrict__ g_b, float* __restrict__ g_c) {
+    const int k = blockIdx.x;
+    if (k == 0 && threadIdx.x == 0) {
+        const float sum_q = acc[1] - acc[0];
+        out_F[0] = sum_q - acc[2];
+        out_F[1] = sum_q;
+        out_F[2] = acc[2];
+    }
+    if (!bwd) return;
+    if (threadIdx.x == 0) { g_b[k] = acc[3 + k]; g_c[k] = acc[3 + kMaxK + k]; }
+    for (int d = threadIdx.x; d < D; d += blockDim.x) {
+        float gs = G4[(size_t)d * K + k], gw = G5[(size_t)d * K + k];
+        for (int j = k + 1; j < K; ++j) gs = fmaf(G6[(size_t)k * K + j], w[(size_t)j * D + d], gs);
+        for (int j = 0; j < k; ++j) gw = fmaf(G6[(size_t)j * K + k], s[(size_t)j * D + d], gw);
+        g_s[(size_t)k * D + d] = gs;
+        g_w[(size_t)k * D + d] = gw;
+    }
+}
+
+template <int TGT>
+static cudaError_t launch_target(bool bwd, const float* z0, float* Y, int n_act, int D, long long ldn, const float* tp,
+                                 int ntp, float epsv, float* GZT, float* part, cudaStream_t st) {
+    const size_t smem = (size_t)kTgtRows * (D + 1) * sizeof(float);
+    const int blocks = (n_act + kTgtRows - 1) / kTgtRows;
+    if (bwd) {
+        if (smem > 48 * 1024) cudaFuncSetAttribute(target_kernel<TGT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        target_kernel<TGT, true><<<blocks, kTgtThreads, smem, st>>>(z0, Y, n_act, D, ldn, tp, ntp, epsv, GZT, part);
+    } else {
+        if (smem > 48 * 1024) cudaFuncSetAttribute(target_kernel<TGT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        target_kernel<TGT, false><<<blocks, kTgtThreads, smem, st>>>(z0, Y, n_act, D, ldn, tp, ntp, epsv, GZT, part);
+    }
+    return cudaGetLastError();
+}
+
+template <int KP>
+static cudaError_t launch_rec(bool fwd, const Layout& L, float* ws, int n_act, int K, const float* c, float epsv, cudaStream_t st) {
+    const int blocks = (n_act + kRecThreads - 1) / kRecThreads;
+    if (fwd)
+        rec_fwd_kernel<KP><<<blocks, kRecThreads, 0, st>>>(ws + L.AT, L.Nc, n_act, K, ws + L.Mt, c, epsv, ws + L.TT, ws + L.Trow,
+                                                          ws + L.part_ld);
+    else
+        rec_bwd_kernel<KP><<<blocks, kRecThreads, 0, st>>>(ws + L.AT, ws + L.TT, L.Nc, n_act, K, ws + L.M, c, epsv, ws + L.DT, ws + L.CT);
+    return cudaGetLastError();
+}
+static cudaError_t launch_rec_any(bool fwd, const Layout& L, float* ws, int n_act, int K, const float* c, float epsv, cudaStream_t st) {
+    if (L.KP == 16) return launch_rec<16>(fwd, L, ws, n_act, K, c, epsv, st);
+    if (L.KP == 32) return launch_rec<32>(fwd, L, ws, n_act, K, c, epsv, st);
+    return launch_rec<64>(fwd, L, ws, n_act, K, c, epsv, st);
+}
+
+}  // namespace gram
+
+// ---- interface used by nf_elbo_f32.cu --------------------------------------------------------------
+bool gram_applicable(long long N, int D, int K, int target_id, int ntp) {
+    if (getenv("NF_NO_GRAM")) return false;
+    if (D < 32 || D > 4096 || (D % 4) != 0 || K < 1 || K > gram::kMaxK) return false;
+    long long min_n = 1024;
+    if (const char* e = getenv("NF_GRAM_MIN_N")) min_n = atoll(e);
+    if (N < min_n) return false;
+    if (target_id < 0 || target_id == NF_TARGET_GAUSSDIAG) return true;
+    if (target_id == NF_TARGET_MIXDIAG) return ntp / (1 + 2 * D) <= gram::kMaxMix;
+    return false;
+}
+
+size_t gram_workspace_bytes(long long N, int D, int K) { return gram::make_layout(N, D, K).total * sizeof(float); }
+
+int gram_elbo_f32(bool bwd, const float* eps, long long N, int D, int K, const float* w, const float* s, const float* b,
+                  const float* c, int target_id, const float* tp, int ntp, float epsv, float* out_F, float* g_w, float* g_s,
+                  float* g_b, float* g_c, void* workspace, cudaStream_t st) {
+    using namespace gram;
+    const Layout L = make_layout(N, D, K);
+    float* ws = reinterpret_cast<float*>(workspace);
+    const int KP = L.KP;
+    prep_kernel<<<KP, 256, 0, st>>>(w, s, K, D, KP, ws + L.M, ws + L.Mt, ws + L.ST, ws + L.acc);
+    NF_CUDA_OK(cudaGetLastError());
+    int rc;
+    bool first = true;
+    for (long long c0 = 0; c0 < N; c0 += L.Nc) {
+        const int n_act = (int)((N - c0 < L.Nc) ? (N - c0) : L.Nc);
+        const float* z0 = eps + (size_t)c0 * D;
+        // product 1: A0^T[k][n] = sum_d z0[n][d] w[k][d] + b[k]
+        if ((rc = tc_gemm_f32(z0, D, w, D, n_act, K, D, nullptr, 0, ws + L.AT, L.Nc, b, 0, nullptr, 0, 0, st)) != NF_OK) return rc;
+        NF_CUDA_OK(launch_rec_any(true, L, ws, n_act, K, c, epsv, st));
+        // product 2: Y[n][d] = sum_k T[n][k] S^T[d][k]
+        if ((rc = tc_gemm_f32(ws + L.Trow, KP, ws + L.ST, KP, n_act, D, K, ws + L.Y, D, nullptr, 0, nullptr, 0, nullptr, 0, 0, st)) != NF_OK)
+            return rc;
+        if (target_id == NF_TARGET_GAUSSDIAG)
+            NF_CUDA_OK(launch_target<NF_TARGET_GAUSSDIAG>(bwd, z0, ws + L.Y, n_act, D, L.Nc, tp, ntp, epsv, ws + L.GZT, ws + L.part_t, st));
+        else
+            NF_CUDA_OK(launch_target<NF_TARGET_MIXDIAG>(bwd, z0, ws + L.Y, n_act, D, L.Nc, tp, ntp, epsv, ws + L.GZT, ws + L.part_t, st));
+        if (bwd) {
+            // product 3: P^T[k][n] = sum_d gz[n][d] s[k][d]
+            if ((rc = tc_gemm_f32(ws + L.Y, D, s, D, n_act, K, D, nullptr, 0, ws + L.AT, L.Nc, nullptr, 0, nullptr, 0, 0, st)) != NF_OK) return rc;
+            NF_CUDA_OK(launch_rec_any(false, L, ws, n_act, K, c, epsv, st));
+            transpose_kernel<<<dim3((D + 31) / 32, (n_act + 31) / 32), dim3(32, 8), 0, st>>>(z0, n_act, D, ws + L.Z0T, L.Nc);
+            NF_CUDA_OK(cudaGetLastError());
+            // products 4-6 contract over the samples of the chunk (split across CTAs, fixed-order sums)
+            if ((rc = tc_gemm_f32(ws + L.GZT, L.Nc, ws + L.TT, L.Nc, D, K, n_act, ws + L.G4, K, nullptr, 0, nullptr, 0, nullptr, 0, 0, st,
+                                  L.splits, ws + L.split4, !first)) != NF_OK) return rc;
+            if ((rc = tc_gemm_f32(ws + L.Z0T, L.Nc, ws + L.DT, L.Nc, D, K, n_act, ws + L.G5, K, nullptr, 0, nullptr, 0, nullptr, 0, 0, st,
+                                  L.splits, ws + L.split5, !first)) != NF_OK) return rc;
+            if ((rc = tc_gemm_f32(ws + L.TT, L.Nc, ws + L.DT, L.Nc, K, K, n_act, ws + L.G6, K, nullptr, 0, nullptr, 0, nullptr, 0, 0, st,
+                                  L.splits, ws + L.split6, !first)) != NF_OK) return rc;
+        }
+        chunk_totals_kernel<<<2 * K + 1, 256, 0, st>>>(ws + L.DT, ws + L.CT, L.Nc, n_act, K, bwd ? 1 : 0, ws + L.part_ld,
+                                                      (n_act + kRecThreads - 1) / kRecThreads, ws + L.part_t,
+                                                      (n_act + kTgtRows - 1) / kTgtRows, ws + L.acc);
+        NF_CUDA_OK(cudaGetLastError());
+        first = false;
+    }
+    finish_kernel<<<K, 256, 0, st>>>(ws + L.acc, ws + L.G4, ws + L.G5, ws + L.G6, w, s, K, D, bwd ? 1 : 0, out_F, g_w, g_s, g_b, g_c);
+    NF_CUDA_OK(cudaGetLastError());
+    return NF_OK;
+}
+
+}  // namespace nf

@@ -340,19 +340,20 @@ static bool make_map(CUtensorMap* map, const float* base, long long rows, long l
 
 // C = epi(A B^T); returns NF_ERR_UNSUPPORTED when TMA cannot describe the operands (the caller then
 // uses the CUDA-core GEMM).  A: [M][K] ld lda, B: [N][K] ld ldb.
-__global__ void tc_splitk_reduce_kernel(const float* __restrict__ part, int nz, long long count, float* __restrict__ out) {
+__global__ void tc_splitk_reduce_kernel(const float* __restrict__ part, int nz, long long count, float* __restrict__ out, int accumulate) {
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x) {
         float s = 0.f;
         for (int z = 0; z < nz; ++z) s += part[(long long)z * count + i];      // fixed order
-        out[i] = s;
+        out[i] = accumulate ? out[i] + s : s;
     }
 }
 
 // splits > 1: the contraction is cut into `splits` ranges, each CTA layer writes a partial [M][N] tile set
-// into split_ws (splits*M*N floats) and a second kernel adds them in a fixed order (no bias/activation/C^T).
+// into split_ws (splits*M*N floats) and a second kernel adds them in a fixed order (no bias/activation/C^T);
+// with `accumulate` that sum is added to C instead of replacing it (split mode only).
 int tc_gemm_f32(const float* A, long long lda, const float* B, long long ldb, int M, int N, int K, float* C, long long ldc,
                 float* CT, long long ldct, const float* bias, int act, const float* mask_src, long long ldm, int mask,
-                cudaStream_t st, int splits = 1, float* split_ws = nullptr) {
+                cudaStream_t st, int splits = 1, float* split_ws = nullptr, bool accumulate = false) {
     if (M < 1 || N < 1 || K < 1) return NF_ERR_INVALID;
     if ((lda % 4) || (ldb % 4) || ((uintptr_t)A & 15) || ((uintptr_t)B & 15)) return NF_ERR_UNSUPPORTED;   // 16-byte strides
     CUtensorMap ma, mb;
@@ -361,9 +362,13 @@ int tc_gemm_f32(const float* A, long long lda, const float* B, long long ldb, in
     if (getenv("NF_GEMM_DBG") && !dbg_buf) cudaMallocManaged(&dbg_buf, 64);
     const int nkb_all = (K + tc::BK - 1) / tc::BK;
     if (splits > nkb_all) splits = nkb_all;
-    if (splits < 1 || !split_ws || bias || act || CT || mask || ldc != N) splits = 1;
+    if (splits < 1 || !split_ws || bias || act || CT || mask || ldc != N) {
+        if (accumulate) return NF_ERR_UNSUPPORTED;
+        splits = 1;
+    }
+    const bool via_ws = splits > 1 || accumulate;
     const int kbps = (nkb_all + splits - 1) / splits;
-    tc::Params p{M, N, K, splits > 1 ? split_ws : C, ldc, CT, ldct, bias, act, mask_src, ldm, mask, dbg_buf, kbps, (long long)M * N};
+    tc::Params p{M, N, K, via_ws ? split_ws : C, ldc, CT, ldct, bias, act, mask_src, ldm, mask, dbg_buf, kbps, (long long)M * N};
     const size_t smem = (size_t)tc::STAGES * tc::STAGE_BYTES + 1024;
     static bool attr_done = false;
     if (!attr_done) {
@@ -373,9 +378,10 @@ int tc_gemm_f32(const float* A, long long lda, const float* B, long long ldb, in
     dim3 grid((N + tc::BN - 1) / tc::BN, (M + tc::BM - 1) / tc::BM, splits);
     tc::gemm_tf32x3_kernel<<<grid, tc::THREADS, smem, st>>>(ma, mb, p);
     NF_CUDA_OK(cudaGetLastError());
-    if (splits > 1) {
+    if (via_ws) {
         const long long count = (long long)M * N;
-        tc_splitk_reduce_kernel<<<(int)((count + 255) / 256 < 1184 ? (count + 255) / 256 : 1184), 256, 0, st>>>(split_ws, splits, count, C);
+        tc_splitk_reduce_kernel<<<(int)((count + 255) / 256 < 1184 ? (count + 255) / 256 : 1184), 256, 0, st>>>(split_ws, splits, count, C,
+                                                                                                                accumulate ? 1 : 0);
         NF_CUDA_OK(cudaGetLastError());
     }
     if (dbg_buf) {

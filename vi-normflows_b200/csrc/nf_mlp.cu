@@ -16,7 +16,7 @@ namespace nf {
 // tensor-core GEMM (nf_gemm_tc.cu): C = epi(A B^T), both operands K-contiguous
 int tc_gemm_f32(const float* A, long long lda, const float* B, long long ldb, int M, int N, int K, float* C, long long ldc,
                 float* CT, long long ldct, const float* bias, int act, const float* mask_src, long long ldm, int mask,
-                cudaStream_t st, int splits = 1, float* split_ws = nullptr);
+                cudaStream_t st, int splits = 1, float* split_ws = nullptr, bool accumulate = false);
 
 enum { ACT_NONE = 0, ACT_RELU = 1, ACT_SIGMOID = 2, ACT_RBF = 3 };   // rbf: exp(-x^2) (nn_models.py:175)
 

@@ -34,6 +34,7 @@ PROTOTYPES = {
     'nf_built_for_sm': (c_int, []),
     'nf_check_device': (c_int, []),
     'nf_planar_elbo_workspace_bytes': (c_size_t, [c_int, c_int, c_int]),
+    'nf_planar_elbo_workspace_bytes_n': (c_size_t, [c_int64, c_int, c_int, c_int]),
     'nf_planar_elbo_fwd_bwd_f32': (c_int, _elbo_args(c_float)),
     'nf_planar_elbo_fwd_bwd_f64': (c_int, _elbo_args(c_double)),
     'nf_planar_elbo_fwd_bwd_noalloc_f32': (c_int, _elbo_args(c_float)[:17] + [c_void_p]),

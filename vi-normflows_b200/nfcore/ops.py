@@ -34,9 +34,9 @@ def require_cuda():
 _workspaces = {}
 
 
-def _workspace(K, D, dtype, device):
+def _workspace(K, D, dtype, device, N=0):
     lib = _lib.load()
-    nbytes = lib.nf_planar_elbo_workspace_bytes(K, D, _DT[dtype][1])
+    nbytes = lib.nf_planar_elbo_workspace_bytes_n(N, K, D, _DT[dtype][1])
     key = (device.index, torch.cuda.current_stream(device).cuda_stream)
     ws = _workspaces.get(key)
     if ws is None or ws.numel() < nbytes:
@@ -82,7 +82,7 @@ def planar_elbo(eps, w, s, b, c, target, target_params=None, log_eps=1e-7, backw
             g_w = g_s = g_b = g_c = None
     else:
         out_F, g_w, g_s, g_b, g_c = out
-    ws = _workspace(K, D, dtype, dev)
+    ws = _workspace(K, D, dtype, dev, N)
     fn = getattr(lib, 'nf_planar_elbo_fwd_bwd_' + sfx)
     with torch.cuda.device(dev):
         stream = torch.cuda.current_stream(dev).cuda_stream
