@@ -18,7 +18,7 @@
 // float32 accuracy).  The direct kernel (nf_elbo_wide.cuh) spends 7 D multiply-adds per layer and
 // sample on the CUDA cores and, worse, has to add a [K][2D] gradient record per warp and layer
 // to global memory; here the gradient accumulators are output tiles of products 4-6.
-// Samples are processed in chunks so that the intermediates of a chunk stay close to the L2 size.
+// Samples are processed in chunks of up to 32M/D (the workspace holds one chunk's intermediates).
 // float32, D % 4 == 0, K <= 64, targets GAUSSDIAG / MIXDIAG (<= 16 components).
 #include <cstdio>
 #include <cstdlib>
@@ -41,9 +41,10 @@ constexpr int kTgtThreads = 256;
 static inline int pad_k(int K) { return K <= 16 ? 16 : (K <= 32 ? 32 : 64); }
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
-// chunk pitch (samples): about 4M elements of [Nc][D], a multiple of 128, no more than the job needs
+// chunk pitch (samples): up to 32M elements of [Nc][D] (small chunks leave the GPU under-filled: every kernel of the
+// chain is a separate launch), a multiple of 128, no more than the job needs
 static inline long long chunk_samples(long long N, int D) {
-    long long nc = ((long long)4 << 20) / D;
+    long long nc = ((long long)32 << 20) / D;
     if (const char* e = getenv("NF_GRAM_CHUNK")) { const long long v = atoll(e); if (v >= 128) nc = v; }
     nc = (nc + 127) / 128 * 128;
     const long long need = (N + 127) / 128 * 128;
@@ -59,8 +60,8 @@ static inline int grad_splits(long long nc, int D) {
 
 struct Layout {
     int KP; long long Nc; int splits;
-    size_t acc, M, Mt, ST, G4, G5, G6, part_ld, part_t, split4, split5, split6;   // offsets in floats
-    size_t AT, CT, DT, TT, Trow, Y, GZT, Z0T, total;
+    size_t acc, M, Mt, ST, G4, G5, G6, part_ld, part_gc, part_t, split4, split5, split6;   // offsets in floats
+    size_t AT, DT, TT, Trow, Y, GZT, Z0T, total;
 };
 static Layout make_layout(long long N, int D, int K) {
     Layout L{};
@@ -75,16 +76,16 @@ static Layout make_layout(long long N, int D, int K) {
     L.ST = take((size_t)D * L.KP);
     L.G4 = take((size_t)D * K);
     L.G5 = take((size_t)D * K);
-    L.G6 = take((size_t)K * K);
+    L.G6 = take((size_t)(K + 1) * K);
     L.part_ld = take((size_t)(L.Nc / kRecThreads));
+    L.part_gc = take((size_t)(L.Nc / kRecThreads) * L.KP);
     L.part_t = take((size_t)2 * (L.Nc / kTgtRows));
     L.split4 = take((size_t)L.splits * D * K);
     L.split5 = take((size_t)L.splits * D * K);
-    L.split6 = take((size_t)L.splits * K * K);
+    L.split6 = take((size_t)L.splits * (K + 1) * K);
     L.AT = take((size_t)K * L.Nc);          // A0^T, later P^T
-    L.CT = take((size_t)K * L.Nc);          // per-sample d F / d c_k terms
     L.DT = take((size_t)K * L.Nc);          // Delta^T
-    L.TT = take((size_t)K * L.Nc);          // T^T
+    L.TT = take((size_t)(K + 1) * L.Nc);    // T^T and a row of ones
     L.Trow = take((size_t)L.Nc * L.KP);     // T, row per sample
     L.Y = take((size_t)L.Nc * D);           // T S, later gz_K
     L.GZT = take((size_t)D * L.Nc);
@@ -153,7 +154,12 @@ __device__ __forceinline__ float block_sum(float v, float* red /* [NT/32] */) {
 // Forward recurrence.  One thread per sample; the K pre-activations live in registers and are turned
 // into t_j = tanh(a_j) in place, column j of M being added to the later ones as soon as t_j is known.
 // Mt rows are zero up to and including the diagonal, so whole float4 groups can be applied blindly.
-// Outputs: T^T (coalesced), T rows (operand of product 2), per-block sum of the log-det terms.
+// The product-1 value of layer k is only needed at step k: it is fetched kPrefetch steps ahead, which
+// spreads the loads over the arithmetic instead of stalling every warp of a wave at its start.
+// Outputs: T^T (coalesced; row K is set to ones -- product 6 then also yields sum_n delta = g_b),
+// T rows (operand of product 2), per-block sum of the log-det terms.
+constexpr int kPrefetch = 12;
+
 template <int KP>
 __global__ void __launch_bounds__(kRecThreads)
 rec_fwd_kernel(const float* __restrict__ AT, long long ldn, int n_act, int K, const float* __restrict__ Mt,
@@ -168,19 +174,25 @@ rec_fwd_kernel(const float* __restrict__ AT, long long ldn, int n_act, int K, co
     __syncthreads();
     const int n = blockIdx.x * kRecThreads + threadIdx.x;
     const bool ok = n < n_act;
-    float a[KP];
+    const float* src = AT + (ok ? n : 0);
+    float* dst = TT + (ok ? n : 0);
+    float a[KP], in[KP];
 #pragma unroll
-    for (int k = 0; k < KP; ++k) a[k] = (ok && k < K) ? AT[(size_t)k * ldn + n] * M_::kArgScale : 0.f;
+    for (int k = 0; k < KP; ++k) a[k] = 0.f;
+#pragma unroll
+    for (int k = 0; k < kPrefetch && k < KP; ++k) in[k] = k < K ? src[(size_t)k * ldn] : 0.f;
     float prod = 1.f, ld = 0.f;
 #pragma unroll
     for (int j = 0; j < KP; ++j) {
-        const float t = M_::tanh_pre(a[j]);
+        if (j + kPrefetch < KP) in[j + kPrefetch] = (j + kPrefetch < K) ? src[(size_t)(j + kPrefetch) * ldn] : 0.f;
+        asm volatile("" ::: "memory");       // keep the fetch here: hoisted to the top it would pin K more registers
+        const float t = M_::tanh_pre(fmaf(in[j], M_::kArgScale, a[j]));
         a[j] = t;
         if (j < K) {
             const float hp = fmaf(-t, t, 1.f);
             prod *= epsv + fabsf(fmaf(hp, sc[j], 1.f));
             if ((j & 3) == 3 || j == K - 1) { ld += M_::logp(prod); prod = 1.f; }
-            if (ok) TT[(size_t)j * ldn + n] = t;
+            if (ok) dst[(size_t)j * ldn] = t;
         }
 #pragma unroll
         for (int k4 = (j + 1) / 4; k4 < KP / 4; ++k4) {
@@ -192,6 +204,7 @@ rec_fwd_kernel(const float* __restrict__ AT, long long ldn, int n_act, int K, co
         }
     }
     if (ok) {
+        dst[(size_t)K * ldn] = 1.f;
         float4* row = reinterpret_cast<float4*>(Trow + (size_t)n * KP);
 #pragma unroll
         for (int k4 = 0; k4 < KP / 4; ++k4) row[k4] = make_float4(a[4 * k4], a[4 * k4 + 1], a[4 * k4 + 2], a[4 * k4 + 3]);
@@ -201,181 +214,236 @@ rec_fwd_kernel(const float* __restrict__ AT, long long ldn, int n_act, int K, co
 }
 
 // Reverse recurrence.  p_k starts as (gz_K.s_k) and receives delta_j M[j][k] from the later layers.
-// Outputs: Delta^T and the per-sample d F / d c_k terms (both [K][Nc], summed along n afterwards).
+// Outputs: Delta^T ([K][Nc]) and per-block sums of the d F / d c_k terms (sixteen layers at a time through
+// the multi-value warp reduction, then across the four warps in order).
 template <int KP>
 __global__ void __launch_bounds__(kRecThreads)
 rec_bwd_kernel(const float* __restrict__ PT, const float* __restrict__ TT, long long ldn, int n_act, int K,
                const float* __restrict__ Mrow, const float* __restrict__ c, float epsv, float* __restrict__ DT,
-               float* __restrict__ CT) {
+               float* __restrict__ part_gc /* [gridDim][KP] */) {
     using M_ = Mth<float>;
     __shared__ __align__(16) float sM[KP * KP];
     __shared__ float sc[KP];
+    __shared__ float sgc[kRecThreads / 32][KP];
     for (int i = threadIdx.x; i < KP * KP; i += kRecThreads) sM[i] = Mrow[i];
     for (int i = threadIdx.x; i < KP; i += kRecThreads) sc[i] = i < K ? c[i] : 0.f;
     __syncthreads();
     const int n = blockIdx.x * kRecThreads + threadIdx.x;
-    if (n >= n_act) return;
-    float p[KP];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool ok = n < n_act;
+    const float* srcp = PT + (ok ? n : 0);
+    const float* srct = TT + (ok ? n : 0);
+    float* dst = DT + (ok ? n : 0);
+    float p[KP], pin[KP], tin[KP];
 #pragma unroll
-    for (int k = 0; k < KP; ++k) p[k] = k < K ? PT[(size_t)k * ldn + n] : 0.f;
+    for (int k = 0; k < KP; ++k) p[k] = 0.f;
+#pragma unroll
+    for (int i = 0; i < kPrefetch && i < KP; ++i) {
+        const int k = KP - 1 - i;
+        pin[k] = k < K ? srcp[(size_t)k * ldn] : 0.f;
+        tin[k] = k < K ? srct[(size_t)k * ldn] : 0.f;
+    }
+    float gcv[16];
 #pragma unroll
     for (int k = KP - 1; k >= 0; --k) {
-        if (k < K) {
-            const float t = TT[(size_t)k * ldn + n];
-            const float ck = sc[k];
-            const float hp = fmaf(-t, t, 1.f);
-            const float x = fmaf(hp, ck, 1.f);
-            const float y = epsv + fabsf(x);
-            const float gx = M_::neg_copysign(M_::rcp(y), x);
-            CT[(size_t)k * ldn + n] = gx * hp;
-            const float gt = fmaf(-2.f * ck * gx, t, p[k]);
-            const float ga = gt * hp;
-            DT[(size_t)k * ldn + n] = ga;
-#pragma unroll
-            for (int i4 = 0; i4 < (k + 3) / 4; ++i4) {
-                const float4 m = *reinterpret_cast<const float4*>(&sM[k * KP + 4 * i4]);
-                if (4 * i4 + 0 < k) p[4 * i4 + 0] = fmaf(m.x, ga, p[4 * i4 + 0]);
-                if (4 * i4 + 1 < k) p[4 * i4 + 1] = fmaf(m.y, ga, p[4 * i4 + 1]);
-                if (4 * i4 + 2 < k) p[4 * i4 + 2] = fmaf(m.z, ga, p[4 * i4 + 2]);
-                if (4 * i4 + 3 < k) p[4 * i4 + 3] = fmaf(m.w, ga, p[4 * i4 + 3]);
-            }
+        if (k - kPrefetch >= 0) {
+            pin[k - kPrefetch] = (k - kPrefetch < K) ? srcp[(size_t)(k - kPrefetch) * ldn] : 0.f;
+            tin[k - kPrefetch] = (k - kPrefetch < K) ? srct[(size_t)(k - kPrefetch) * ldn] : 0.f;
         }
+        asm volatile("" ::: "memory");       // keep the fetches here (see rec_fwd_kernel)
+        const float t = tin[k];
+        const float ck = sc[k];
+        const float hp = fmaf(-t, t, 1.f);
+        const float x = fmaf(hp, ck, 1.f);
+        const float y = epsv + fabsf(x);
+        float gx = M_::neg_copysign(M_::rcp(y), x);
+        gx = (ok && k < K) ? gx : 0.f;
+        gcv[k & 15] = gx * hp;
+        const float gt = fmaf(-2.f * ck * gx, t, p[k] + pin[k]);
+        const float ga = (ok && k < K) ? gt * hp : 0.f;
+        if (ok && k < K) dst[(size_t)k * ldn] = ga;
+#pragma unroll
+        for (int i4 = 0; i4 < (k + 3) / 4; ++i4) {
+            const float4 m = *reinterpret_cast<const float4*>(&sM[k * KP + 4 * i4]);
+            if (4 * i4 + 0 < k) p[4 * i4 + 0] = fmaf(m.x, ga, p[4 * i4 + 0]);
+            if (4 * i4 + 1 < k) p[4 * i4 + 1] = fmaf(m.y, ga, p[4 * i4 + 1]);
+            if (4 * i4 + 2 < k) p[4 * i4 + 2] = fmaf(m.z, ga, p[4 * i4 + 2]);
+            if (4 * i4 + 3 < k) p[4 * i4 + 3] = fmaf(m.w, ga, p[4 * i4 + 3]);
+        }
+        if ((k & 15) == 0) {        // layers k .. k+15 are complete: reduce them over the warp
+            warp_reduce_multi<float, 16>(gcv, lane);
+            if (warp_slot_owner<16>(lane)) sgc[warp][k + warp_slot<16>(lane)] = gcv[0];
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < KP) {
+        float t = 0.f;
+#pragma unroll
+        for (int w = 0; w < kRecThreads / 32; ++w) t += sgc[w][threadIdx.x];
+        part_gc[(size_t)blockIdx.x * KP + threadIdx.x] = t;
     }
 }
 
 // ------------------------------------------------------------------------------------------------
 // Target kernel: z_K = z_0 + Y, log p(z_K), log q_0(z_0) and gz_K = dF/dz_K = -d log p / dz_K.
-// A block owns 32 consecutive samples (8 warps x 4 rows); gz_K is written in place of Y (row form,
-// operand of product 3) and, through a shared-memory tile, transposed (operand of product 4).
+// A block owns 32 consecutive samples, i.e. one contiguous run of 32 D floats of z_0 and of Y: it is read
+// with float4 loads into two shared-memory tiles; eight lanes then share a row (four rows per warp at a
+// time, three shuffles per row sum).  gz_K replaces Y (row form, operand of product 3); gz_K^T and z_0^T
+// (operands of products 4 and 5) are written from the tiles, 32 consecutive samples per store.
 // Same density formulas as elbo_wide_kernel (distributions.py:10-54).
+__device__ __forceinline__ float sum8(float v) {
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    v += __shfl_xor_sync(0xffffffffu, v, 2);
+    v += __shfl_xor_sync(0xffffffffu, v, 4);
+    return v;
+}
+
+static inline int tgt_pitch(int D) { return D + 9; }     // odd: transposed reads conflict-free; 9: the four rows of a warp spread over the banks
+static inline size_t tgt_smem_bytes(int D, bool bwd) { return ((size_t)(bwd ? 2 : 1) * kTgtRows * tgt_pitch(D) + 2 * (size_t)D) * sizeof(float); }
+
 template <int TGT, bool BWD>
 __global__ void __launch_bounds__(kTgtThreads)
 target_kernel(const float* __restrict__ z0, float* __restrict__ Y, int n_act, int D, long long ldn,
-              const float* __restrict__ tparams, int ntp, float epsv, float* __restrict__ GZT,
+              const float* __restrict__ tparams, int ntp, float epsv, float* __restrict__ GZT, float* __restrict__ Z0T,
               float* __restrict__ part /* [gridDim][2] : sum log q_0, sum log p */) {
     using M_ = Mth<float>;
-    extern __shared__ float tile[];                 // [32][D + 1]
-    __shared__ float red[kTgtThreads / 32];
-    __shared__ float mixe[kTgtThreads / 32][kMaxMix];
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int pitch = D + 1;
+    extern __shared__ __align__(16) float smem[];
+    __shared__ float red[kTgtThreads / 32][2];
+    __shared__ float mixe[kTgtRows][kMaxMix];
+    const int pitch = D + 9;
+    float* tz = smem;                                  // z_K, then gz_K        [32][pitch]
+    float* t0 = BWD ? tz + kTgtRows * pitch : tz;      // z_0 (reverse pass only; forward recomputes nothing from it)
+    float* s_mu = smem + (BWD ? 2 : 1) * kTgtRows * pitch;
+    float* s_iv = s_mu + D;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const float LOG2PI = 1.8378770664093453f;
     const int n0 = blockIdx.x * kTgtRows;
-    float sum_q = 0.f, sum_p = 0.f;
+    const int rows = min(kTgtRows, n_act - n0);
     float g_const = 0.f;
     if (TGT == NF_TARGET_GAUSSDIAG) {
         float ls = 0.f;
+        for (int d = tid; d < D; d += kTgtThreads) { s_mu[d] = tparams[d]; s_iv[d] = M_::exp(-tparams[D + d]); }
         for (int d = lane; d < D; d += 32) ls += tparams[D + d];
-        ls = warp_sum(ls);
-        g_const = -0.5f * (D * LOG2PI + ls);
+        g_const = -0.5f * (D * LOG2PI + warp_sum(ls));
     }
-    for (int r = warp; r < kTgtRows; r += kTgtThreads / 32) {
-        const int n = n0 + r;
-        if (n >= n_act) {
-            if (BWD) for (int d = lane; d < D; d += 32) tile[r * pitch + d] = 0.f;
-            continue;
-        }
-        const float* zr = z0 + (size_t)n * D;
-        float* yr = Y + (size_t)n * D;
-        float zz = 0.f;
-        for (int d = lane; d < D; d += 32) {
-            const float a = zr[d];
-            zz = fmaf(a, a, zz);
-            tile[r * pitch + d] = a + yr[d];
-        }
-        zz = warp_sum(zz);
-        sum_q += -0.5f * (D * LOG2PI + zz);
-        float lp;
-        if (TGT == NF_TARGET_GAUSSDIAG) {
-            float q = 0.f;
-            for (int d = lane; d < D; d += 32) {
-                const float df = tile[r * pitch + d] - tparams[d];
-                q = fmaf(df * M_::exp(-tparams[D + d]), df, q);
-            }
-            q = warp_sum(q);
-            const float dens = M_::exp(g_const - 0.5f * q);
-            const float den = epsv + dens;
-            lp = M_::logp(den);
-            if (BWD) {
-                const float rho = M_::div(dens, den);
-                for (int d = lane; d < D; d += 32) {
-                    const float g = rho * (tile[r * pitch + d] - tparams[d]) * M_::exp(-tparams[D + d]);
-                    tile[r * pitch + d] = g;
-                    yr[d] = g;
-                }
-            }
-        } else {   // MIXDIAG: [pi (G) | mu (G*D) | var (G*D)]
-            const int G = ntp / (1 + 2 * D);
-            float dens = 0.f;
-            for (int gc = 0; gc < G; ++gc) {
-                const float* mu = tparams + G + (size_t)gc * D;
-                const float* var = tparams + G + (size_t)G * D + (size_t)gc * D;
-                float q = 0.f, lsum = 0.f;
-                for (int d = lane; d < D; d += 32) {
-                    const float df = tile[r * pitch + d] - mu[d];
-                    q = fmaf(df, M_::div(df, var[d]), q);
-                    lsum += M_::logp(var[d]);
-                }
-                q = warp_sum(q);
-                lsum = warp_sum(lsum);
-                const float e = tparams[gc] * M_::exp(-0.5f * (D * LOG2PI + lsum + q));
-                dens += e;
-                if (lane == 0) mixe[warp][gc] = e;
-            }
-            const float den = epsv + dens;
-            lp = M_::logp(den);
-            if (BWD) {
-                __syncwarp();
-                const float inv = M_::div(1.f, den);
-                for (int d = lane; d < D; d += 32) {
-                    const float z = tile[r * pitch + d];
-                    float acc = 0.f;
-                    for (int gc = 0; gc < G; ++gc)
-                        acc = fmaf(mixe[warp][gc], M_::div(z - tparams[G + (size_t)gc * D + d], tparams[G + (size_t)G * D + (size_t)gc * D + d]), acc);
-                    const float g = acc * inv;
-                    tile[r * pitch + d] = g;
-                    yr[d] = g;
-                }
-                __syncwarp();
-            }
-        }
-        sum_p += lp;
+    // ---- load: flat float4 run of rows * D floats ----
+    const float4* z4 = reinterpret_cast<const float4*>(z0 + (size_t)n0 * D);
+    const float4* y4 = reinterpret_cast<const float4*>(Y + (size_t)n0 * D);
+    const int nvec = rows * D / 4;
+    float zz_part = 0.f;        // only used by the forward-only instantiation
+    for (int v = tid; v < nvec; v += kTgtThreads) {
+        const float4 a = z4[v], b = y4[v];
+        const int r = (4 * v) / D, d = 4 * v - r * D;
+        float* q = tz + r * pitch + d;
+        q[0] = a.x + b.x; q[1] = a.y + b.y; q[2] = a.z + b.z; q[3] = a.w + b.w;
+        if (BWD) { float* q0 = t0 + r * pitch + d; q0[0] = a.x; q0[1] = a.y; q0[2] = a.z; q0[3] = a.w; }
+        else zz_part = fmaf(a.x, a.x, fmaf(a.y, a.y, fmaf(a.z, a.z, fmaf(a.w, a.w, zz_part))));
     }
-    // per-warp totals are identical on all lanes; add the eight warps in order
     __syncthreads();
-    if (lane == 0) red[warp] = sum_q;
-    __syncthreads();
-    if (threadIdx.x == 0) { float t = 0.f; for (int i = 0; i < kTgtThreads / 32; ++i) t += red[i]; part[2 * blockIdx.x] = t; }
-    __syncthreads();
-    if (lane == 0) red[warp] = sum_p;
-    __syncthreads();
-    if (threadIdx.x == 0) { float t = 0.f; for (int i = 0; i < kTgtThreads / 32; ++i) t += red[i]; part[2 * blockIdx.x + 1] = t; }
+    // ---- per row: eight lanes per row, rows 4*warp .. 4*warp+3 ----
+    const int r = 4 * warp + (lane >> 3), l = lane & 7;
+    const bool live = r < rows;
+    float* zr = tz + r * pitch;
+    float lq = 0.f, lp = 0.f;
     if (BWD) {
-        // transposed copy: lane <-> sample, warps stride over the coordinates
-        const int n = n0 + lane;
-        if (n < n_act)
-            for (int d = warp; d < D; d += kTgtThreads / 32) GZT[(size_t)d * ldn + n] = tile[lane * pitch + d];
+        float zz = 0.f;
+        if (live) for (int d = l; d < D; d += 8) { const float a = t0[r * pitch + d]; zz = fmaf(a, a, zz); }
+        zz = sum8(zz);
+        lq = live ? -0.5f * (D * LOG2PI + zz) : 0.f;
+    }
+    if (TGT == NF_TARGET_GAUSSDIAG) {
+        float q = 0.f;
+        if (live) for (int d = l; d < D; d += 8) { const float df = zr[d] - s_mu[d]; q = fmaf(df * s_iv[d], df, q); }
+        q = sum8(q);
+        const float dens = M_::exp(g_const - 0.5f * q);
+        const float den = epsv + dens;
+        lp = live ? M_::logp(den) : 0.f;
+        if (BWD) {
+            const float rho = M_::div(dens, den);
+            if (live) for (int d = l; d < D; d += 8) zr[d] = rho * (zr[d] - s_mu[d]) * s_iv[d];
+        }
+    } else {   // MIXDIAG: [pi (G) | mu (G*D) | var (G*D)]
+        const int G = ntp / (1 + 2 * D);
+        float dens = 0.f;
+        for (int gc = 0; gc < G; ++gc) {
+            const float* mu = tparams + G + (size_t)gc * D;
+            const float* var = tparams + G + (size_t)G * D + (size_t)gc * D;
+            float q = 0.f, lsum = 0.f;
+            if (live) for (int d = l; d < D; d += 8) {
+                const float df = zr[d] - mu[d];
+                q = fmaf(df, M_::div(df, var[d]), q);
+                lsum += M_::logp(var[d]);
+            }
+            q = sum8(q);
+            lsum = sum8(lsum);
+            const float e = tparams[gc] * M_::exp(-0.5f * (D * LOG2PI + lsum + q));
+            dens += e;
+            if (l == 0 && r < kTgtRows) mixe[r][gc] = e;
+        }
+        const float den = epsv + dens;
+        lp = live ? M_::logp(den) : 0.f;
+        if (BWD) {
+            __syncwarp();
+            const float inv = M_::div(1.f, den);
+            if (live) for (int d = l; d < D; d += 8) {
+                const float z = zr[d];
+                float acc = 0.f;
+                for (int gc = 0; gc < G; ++gc)
+                    acc = fmaf(mixe[r][gc], M_::div(z - tparams[G + (size_t)gc * D + d], tparams[G + (size_t)G * D + (size_t)gc * D + d]), acc);
+                zr[d] = acc * inv;
+            }
+        }
+    }
+    // block totals in a fixed order: lanes with l == 0 carry one row each
+    float vq = (l == 0) ? lq : 0.f, vp = (l == 0) ? lp : 0.f;
+    if (!BWD) vq = zz_part;
+    vq = warp_sum(vq);
+    vp = warp_sum(vp);
+    if (lane == 0) { red[warp][0] = vq; red[warp][1] = vp; }
+    __syncthreads();
+    if (tid == 0) {
+        float tq = 0.f, tp = 0.f;
+        for (int i = 0; i < kTgtThreads / 32; ++i) { tq += red[i][0]; tp += red[i][1]; }
+        if (!BWD) tq = -0.5f * (rows * (D * LOG2PI) + tq);
+        part[2 * blockIdx.x] = tq;
+        part[2 * blockIdx.x + 1] = tp;
+    }
+    if (BWD) {
+        // row form of gz_K, in place of Y
+        float4* o4 = reinterpret_cast<float4*>(Y + (size_t)n0 * D);
+        for (int v = tid; v < nvec; v += kTgtThreads) {
+            const int rr = (4 * v) / D, d = 4 * v - rr * D;
+            const float* q = tz + rr * pitch + d;
+            o4[v] = make_float4(q[0], q[1], q[2], q[3]);
+        }
+        // transposed copies: lane <-> sample, warps stride over the coordinates
+        if (lane < rows) {
+            float* gz_t = GZT + n0 + lane;
+            float* z0_t = Z0T + n0 + lane;
+            for (int d = warp; d < D; d += kTgtThreads / 32) {
+                gz_t[(size_t)d * ldn] = tz[lane * pitch + d];
+                z0_t[(size_t)d * ldn] = t0[lane * pitch + d];
+            }
+        }
     }
 }
 
-// Per chunk: running totals.  Blocks [0, K): sum_n Delta^T[k][n] -> g_b[k]; blocks [K, 2K): sum_n CT -> g_c;
-// block 2K: log-det, log q_0 and log p partial sums.  Fixed order, and chunks arrive in stream order.
+// Per chunk: running totals.  Blocks [0, K): column k of the per-block d F / d c_k sums; block K: log-det,
+// log q_0 and log p partial sums.  Fixed order, and chunks arrive in stream order.
 __global__ void __launch_bounds__(256)
-chunk_totals_kernel(const float* __restrict__ DT, const float* __restrict__ CT, long long ldn, int n_act, int K, int bwd,
-                    const float* __restrict__ part_ld, int n_ld, const float* __restrict__ part_t, int n_t,
-                    float* __restrict__ acc /* [ld, q0, p | g_b (kMaxK) | g_c (kMaxK)] */) {
+chunk_totals_kernel(const float* __restrict__ part_gc, int KP, int K, int bwd, const float* __restrict__ part_ld, int n_rec,
+                    const float* __restrict__ part_t, int n_t, float* __restrict__ acc /* [ld, q0, p | - | g_c (kMaxK)] */) {
     __shared__ float red[8];
     const int b = blockIdx.x;
-    if (b < 2 * K) {
+    if (b < K) {
         if (!bwd) return;
-        const float* row = (b < K ? DT + (size_t)b * ldn : CT + (size_t)(b - K) * ldn);
         float v = 0.f;
-        for (int n = threadIdx.x; n < n_act; n += 256) v += row[n];
+        for (int i = threadIdx.x; i < n_rec; i += 256) v += part_gc[(size_t)i * KP + b];
         const float t = block_sum<256>(v, red);
-        if (threadIdx.x == 0) acc[3 + (b < K ? b : kMaxK + (b - K))] += t;
+        if (threadIdx.x == 0) acc[3 + kMaxK + b] += t;
     } else {
         float a = 0.f, q = 0.f, p = 0.f;
-        for (int i = threadIdx.x; i < n_ld; i += 256) a += part_ld[i];
+        for (int i = threadIdx.x; i < n_rec; i += 256) a += part_ld[i];
         for (int i = threadIdx.x; i < n_t; i += 256) { q += part_t[2 * i]; p += part_t[2 * i + 1]; }
         const float ta = block_sum<256>(a, red);
         const float tq = block_sum<256>(q, red);
@@ -384,7 +452,8 @@ chunk_totals_kernel(const float* __restrict__ DT, const float* __restrict__ CT, 
     }
 }
 
-// g_s[k][d] = G4[d][k] + sum_{j>k} G6[k][j] w[j][d] ;  g_w[k][d] = G5[d][k] + sum_{j<k} G6[j][k] s[j][d]
+// g_s[k][d] = G4[d][k] + sum_{j>k} G6[k][j] w[j][d] ;  g_w[k][d] = G5[d][k] + sum_{j<k} G6[j][k] s[j][d] ;
+// g_b[k] = G6[K][k] (the row of ones appended to T^T)
 __global__ void finish_kernel(const float* __restrict__ acc, const float* __restrict__ G4, const float* __restrict__ G5,
                               const float* __restrict__ G6, const float* __restrict__ w, const float* __restrict__ s,
                               int K, int D, int bwd, float* __restrict__ out_F, float* __restrict__ g_w,
@@ -397,7 +466,7 @@ __global__ void finish_kernel(const float* __restrict__ acc, const float* __rest
         out_F[2] = acc[2];
     }
     if (!bwd) return;
-    if (threadIdx.x == 0) { g_b[k] = acc[3 + k]; g_c[k] = acc[3 + kMaxK + k]; }
+    if (threadIdx.x == 0) { g_b[k] = G6[(size_t)K * K + k]; g_c[k] = acc[3 + kMaxK + k]; }
     for (int d = threadIdx.x; d < D; d += blockDim.x) {
         float gs = G4[(size_t)d * K + k], gw = G5[(size_t)d * K + k];
         for (int j = k + 1; j < K; ++j) gs = fmaf(G6[(size_t)k * K + j], w[(size_t)j * D + d], gs);
@@ -409,15 +478,15 @@ __global__ void finish_kernel(const float* __restrict__ acc, const float* __rest
 
 template <int TGT>
 static cudaError_t launch_target(bool bwd, const float* z0, float* Y, int n_act, int D, long long ldn, const float* tp,
-                                 int ntp, float epsv, float* GZT, float* part, cudaStream_t st) {
-    const size_t smem = (size_t)kTgtRows * (D + 1) * sizeof(float);
+                                 int ntp, float epsv, float* GZT, float* Z0T, float* part, cudaStream_t st) {
+    const size_t smem = tgt_smem_bytes(D, bwd);
     const int blocks = (n_act + kTgtRows - 1) / kTgtRows;
     if (bwd) {
         if (smem > 48 * 1024) cudaFuncSetAttribute(target_kernel<TGT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        target_kernel<TGT, true><<<blocks, kTgtThreads, smem, st>>>(z0, Y, n_act, D, ldn, tp, ntp, epsv, GZT, part);
+        target_kernel<TGT, true><<<blocks, kTgtThreads, smem, st>>>(z0, Y, n_act, D, ldn, tp, ntp, epsv, GZT, Z0T, part);
     } else {
         if (smem > 48 * 1024) cudaFuncSetAttribute(target_kernel<TGT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        target_kernel<TGT, false><<<blocks, kTgtThreads, smem, st>>>(z0, Y, n_act, D, ldn, tp, ntp, epsv, GZT, part);
+        target_kernel<TGT, false><<<blocks, kTgtThreads, smem, st>>>(z0, Y, n_act, D, ldn, tp, ntp, epsv, GZT, Z0T, part);
     }
     return cudaGetLastError();
 }
@@ -429,7 +498,8 @@ static cudaError_t launch_rec(bool fwd, const Layout& L, float* ws, int n_act, i
         rec_fwd_kernel<KP><<<blocks, kRecThreads, 0, st>>>(ws + L.AT, L.Nc, n_act, K, ws + L.Mt, c, epsv, ws + L.TT, ws + L.Trow,
                                                           ws + L.part_ld);
     else
-        rec_bwd_kernel<KP><<<blocks, kRecThreads, 0, st>>>(ws + L.AT, ws + L.TT, L.Nc, n_act, K, ws + L.M, c, epsv, ws + L.DT, ws + L.CT);
+        rec_bwd_kernel<KP><<<blocks, kRecThreads, 0, st>>>(ws + L.AT, ws + L.TT, L.Nc, n_act, K, ws + L.M, c, epsv, ws + L.DT,
+                                                          ws + L.part_gc);
     return cudaGetLastError();
 }
 static cudaError_t launch_rec_any(bool fwd, const Layout& L, float* ws, int n_act, int K, const float* c, float epsv, cudaStream_t st) {
@@ -443,7 +513,7 @@ static cudaError_t launch_rec_any(bool fwd, const Layout& L, float* ws, int n_ac
 // ---- interface used by nf_elbo_f32.cu --------------------------------------------------------------
 bool gram_applicable(long long N, int D, int K, int target_id, int ntp) {
     if (getenv("NF_NO_GRAM")) return false;
-    if (D < 32 || D > 4096 || (D % 4) != 0 || K < 1 || K > gram::kMaxK) return false;
+    if (D < 32 || D > 512 || (D % 4) != 0 || K < 1 || K > gram::kMaxK) return false;
     long long min_n = 1024;
     if (const char* e = getenv("NF_GRAM_MIN_N")) min_n = atoll(e);
     if (N < min_n) return false;
@@ -475,26 +545,24 @@ int gram_elbo_f32(bool bwd, const float* eps, long long N, int D, int K, const f
         if ((rc = tc_gemm_f32(ws + L.Trow, KP, ws + L.ST, KP, n_act, D, K, ws + L.Y, D, nullptr, 0, nullptr, 0, nullptr, 0, 0, st)) != NF_OK)
             return rc;
         if (target_id == NF_TARGET_GAUSSDIAG)
-            NF_CUDA_OK(launch_target<NF_TARGET_GAUSSDIAG>(bwd, z0, ws + L.Y, n_act, D, L.Nc, tp, ntp, epsv, ws + L.GZT, ws + L.part_t, st));
+            NF_CUDA_OK(launch_target<NF_TARGET_GAUSSDIAG>(bwd, z0, ws + L.Y, n_act, D, L.Nc, tp, ntp, epsv, ws + L.GZT, ws + L.Z0T, ws + L.part_t, st));
         else
-            NF_CUDA_OK(launch_target<NF_TARGET_MIXDIAG>(bwd, z0, ws + L.Y, n_act, D, L.Nc, tp, ntp, epsv, ws + L.GZT, ws + L.part_t, st));
+            NF_CUDA_OK(launch_target<NF_TARGET_MIXDIAG>(bwd, z0, ws + L.Y, n_act, D, L.Nc, tp, ntp, epsv, ws + L.GZT, ws + L.Z0T, ws + L.part_t, st));
         if (bwd) {
             // product 3: P^T[k][n] = sum_d gz[n][d] s[k][d]
             if ((rc = tc_gemm_f32(ws + L.Y, D, s, D, n_act, K, D, nullptr, 0, ws + L.AT, L.Nc, nullptr, 0, nullptr, 0, 0, st)) != NF_OK) return rc;
             NF_CUDA_OK(launch_rec_any(false, L, ws, n_act, K, c, epsv, st));
-            transpose_kernel<<<dim3((D + 31) / 32, (n_act + 31) / 32), dim3(32, 8), 0, st>>>(z0, n_act, D, ws + L.Z0T, L.Nc);
-            NF_CUDA_OK(cudaGetLastError());
             // products 4-6 contract over the samples of the chunk (split across CTAs, fixed-order sums)
             if ((rc = tc_gemm_f32(ws + L.GZT, L.Nc, ws + L.TT, L.Nc, D, K, n_act, ws + L.G4, K, nullptr, 0, nullptr, 0, nullptr, 0, 0, st,
                                   L.splits, ws + L.split4, !first)) != NF_OK) return rc;
             if ((rc = tc_gemm_f32(ws + L.Z0T, L.Nc, ws + L.DT, L.Nc, D, K, n_act, ws + L.G5, K, nullptr, 0, nullptr, 0, nullptr, 0, 0, st,
                                   L.splits, ws + L.split5, !first)) != NF_OK) return rc;
-            if ((rc = tc_gemm_f32(ws + L.TT, L.Nc, ws + L.DT, L.Nc, K, K, n_act, ws + L.G6, K, nullptr, 0, nullptr, 0, nullptr, 0, 0, st,
+            if ((rc = tc_gemm_f32(ws + L.TT, L.Nc, ws + L.DT, L.Nc, K + 1, K, n_act, ws + L.G6, K, nullptr, 0, nullptr, 0, nullptr, 0, 0, st,
                                   L.splits, ws + L.split6, !first)) != NF_OK) return rc;
         }
-        chunk_totals_kernel<<<2 * K + 1, 256, 0, st>>>(ws + L.DT, ws + L.CT, L.Nc, n_act, K, bwd ? 1 : 0, ws + L.part_ld,
-                                                      (n_act + kRecThreads - 1) / kRecThreads, ws + L.part_t,
-                                                      (n_act + kTgtRows - 1) / kTgtRows, ws + L.acc);
+        chunk_totals_kernel<<<K + 1, 256, 0, st>>>(ws + L.part_gc, KP, K, bwd ? 1 : 0, ws + L.part_ld,
+                                                  (n_act + kRecThreads - 1) / kRecThreads, ws + L.part_t,
+                                                  (n_act + kTgtRows - 1) / kTgtRows, ws + L.acc);
         NF_CUDA_OK(cudaGetLastError());
         first = false;
     }

@@ -26,7 +26,7 @@ namespace nf {
 namespace tc {
 
 constexpr int BM = 128, BN = 64, BK = 32;          // tile (BK floats = 128 bytes = one swizzle row)
-constexpr int STAGES = 3;
+constexpr int MAX_STAGES = 3;                       // ring depth is a launch parameter (1..3): shallow rings let 2-4 CTAs share an SM
 constexpr int A_BYTES = BM * BK * 4, B_BYTES = BN * BK * 4;
 constexpr int STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;      // hi + lo of both operands
 constexpr int THREADS = 256;
@@ -89,15 +89,17 @@ struct Params {
     int act;                             // EPI_ACT_*
     const float* mask_src; long long ldm; int mask;     // multiply by act'(mask_src[m][n])
     long long* dbg;                      // optional phase timestamps of CTA (0,0) (bring-up aid), else null
+    int stages;                          // depth of the shared-memory ring
     int kb_per_split;                    // split-K: blockIdx.z owns k-blocks [z*kb_per_split, (z+1)*kb_per_split)
     long long split_stride;              // and writes its partial tile to C + z*split_stride
 };
 
-__global__ void __launch_bounds__(THREADS, 1)
+__global__ void __launch_bounds__(THREADS)
 gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, Params p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    __shared__ uint64_t full_bar[STAGES], split_bar[STAGES], empty_bar[STAGES], acc_bar;
+    __shared__ uint64_t full_bar[MAX_STAGES], split_bar[MAX_STAGES], empty_bar[MAX_STAGES], acc_bar;
+    const int STAGES = p.stages;
     __shared__ uint32_t tmem_base;
     __shared__ float sbias[BN];
 
@@ -340,11 +342,21 @@ static bool make_map(CUtensorMap* map, const float* base, long long rows, long l
 
 // C = epi(A B^T); returns NF_ERR_UNSUPPORTED when TMA cannot describe the operands (the caller then
 // uses the CUDA-core GEMM).  A: [M][K] ld lda, B: [N][K] ld ldb.
+// Block (32, 16): thread (x, y) adds slices y, y+16, ... of output element x in ascending order, then the
+// sixteen group sums are added in ascending order -- a fixed tree, with sixteen loads in flight per element.
 __global__ void tc_splitk_reduce_kernel(const float* __restrict__ part, int nz, long long count, float* __restrict__ out, int accumulate) {
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x) {
-        float s = 0.f;
-        for (int z = 0; z < nz; ++z) s += part[(long long)z * count + i];      // fixed order
-        out[i] = accumulate ? out[i] + s : s;
+    __shared__ float sm[16][33];
+    const long long i = (long long)blockIdx.x * 32 + threadIdx.x;
+    float s = 0.f;
+    if (i < count)
+        for (int z = threadIdx.y; z < nz; z += 16) s += part[(long long)z * count + i];
+    sm[threadIdx.y][threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.y == 0 && i < count) {
+        float t = 0.f;
+#pragma unroll
+        for (int y = 0; y < 16; ++y) t += sm[y][threadIdx.x];
+        out[i] = accumulate ? out[i] + t : t;
     }
 }
 
@@ -368,11 +380,17 @@ int tc_gemm_f32(const float* A, long long lda, const float* B, long long ldb, in
     }
     const bool via_ws = splits > 1 || accumulate;
     const int kbps = (nkb_all + splits - 1) / splits;
-    tc::Params p{M, N, K, via_ws ? split_ws : C, ldc, CT, ldct, bias, act, mask_src, ldm, mask, dbg_buf, kbps, (long long)M * N};
-    const size_t smem = (size_t)tc::STAGES * tc::STAGE_BYTES + 1024;
+    // Ring depth: short contractions are dominated by the per-tile prologue and epilogue, so they get a
+    // one-stage ring (49 KB) and four CTAs per SM that cover for one another; longer ones two stages and
+    // two CTAs per SM.  NF_GEMM_STAGES=1..3 overrides (tuning knob).
+    int stages = kbps <= 2 ? 1 : 2;
+    if (const char* e = getenv("NF_GEMM_STAGES")) { const int v = atoi(e); if (v >= 1 && v <= tc::MAX_STAGES) stages = v; }
+    tc::Params p{M, N, K, via_ws ? split_ws : C, ldc, CT, ldct, bias, act, mask_src, ldm, mask, dbg_buf, stages, kbps, (long long)M * N};
+    const size_t smem = (size_t)stages * tc::STAGE_BYTES + 1024;
     static bool attr_done = false;
     if (!attr_done) {
-        NF_CUDA_OK(cudaFuncSetAttribute(tc::gemm_tf32x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        NF_CUDA_OK(cudaFuncSetAttribute(tc::gemm_tf32x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)((size_t)tc::MAX_STAGES * tc::STAGE_BYTES + 1024)));
         attr_done = true;
     }
     dim3 grid((N + tc::BN - 1) / tc::BN, (M + tc::BM - 1) / tc::BM, splits);
@@ -380,8 +398,7 @@ int tc_gemm_f32(const float* A, long long lda, const float* B, long long ldb, in
     NF_CUDA_OK(cudaGetLastError());
     if (via_ws) {
         const long long count = (long long)M * N;
-        tc_splitk_reduce_kernel<<<(int)((count + 255) / 256 < 1184 ? (count + 255) / 256 : 1184), 256, 0, st>>>(split_ws, splits, count, C,
-                                                                                                                accumulate ? 1 : 0);
+        tc_splitk_reduce_kernel<<<(unsigned)((count + 31) / 32), dim3(32, 16), 0, st>>>(split_ws, splits, count, C, accumulate ? 1 : 0);
         NF_CUDA_OK(cudaGetLastError());
     }
     if (dbg_buf) {
