@@ -60,36 +60,35 @@ static inline int grad_splits(long long nc, int D) {
 
 struct Layout {
     int KP; long long Nc; int splits;
-    size_t acc, M, Mt, ST, G4, G5, G6, part_ld, part_gc, part_t, split4, split5, split6;   // offsets in floats
-    size_t AT, DT, TT, Trow, Y, GZT, Z0T, total;
+    size_t acc, M, Mt, ST, G4, G56, part_ld, part_g, part_t, split4, split56;   // offsets in floats
+    size_t AT, DT, TT, Z0T, Trow, Y, GZT, total;
 };
 static Layout make_layout(long long N, int D, int K) {
     Layout L{};
     L.KP = pad_k(K);
     L.Nc = chunk_samples(N, D);
     L.splits = grad_splits(L.Nc, D);
+    const size_t KP = (size_t)L.KP, Nc = (size_t)L.Nc;
     size_t o = 0;
     auto take = [&](size_t n) { const size_t at = o; o = align_up(o + n, 64); return at; };   // 256-byte aligned pieces
     L.acc = take(3 + 2 * kMaxK);
-    L.M = take((size_t)L.KP * L.KP);
-    L.Mt = take((size_t)L.KP * L.KP);
-    L.ST = take((size_t)D * L.KP);
-    L.G4 = take((size_t)D * K);
-    L.G5 = take((size_t)D * K);
-    L.G6 = take((size_t)(K + 1) * K);
-    L.part_ld = take((size_t)(L.Nc / kRecThreads));
-    L.part_gc = take((size_t)(L.Nc / kRecThreads) * L.KP);
-    L.part_t = take((size_t)2 * (L.Nc / kTgtRows));
+    L.M = take(KP * KP);
+    L.Mt = take(KP * KP);
+    L.ST = take((size_t)D * KP);
+    L.G4 = take((size_t)D * K);                 // gz_K^T T            [D][K]
+    L.G56 = take((KP + D) * K);                 // [T^T ; z_0^T] Delta [KP + D][K]
+    L.part_ld = take(Nc / kRecThreads);
+    L.part_g = take(Nc / kRecThreads * 2 * KP);
+    L.part_t = take(2 * (Nc / kTgtRows));
     L.split4 = take((size_t)L.splits * D * K);
-    L.split5 = take((size_t)L.splits * D * K);
-    L.split6 = take((size_t)L.splits * (K + 1) * K);
-    L.AT = take((size_t)K * L.Nc);          // A0^T, later P^T
-    L.DT = take((size_t)K * L.Nc);          // Delta^T
-    L.TT = take((size_t)(K + 1) * L.Nc);    // T^T and a row of ones
-    L.Trow = take((size_t)L.Nc * L.KP);     // T, row per sample
-    L.Y = take((size_t)L.Nc * D);           // T S, later gz_K
-    L.GZT = take((size_t)D * L.Nc);
-    L.Z0T = take((size_t)D * L.Nc);
+    L.split56 = take((size_t)L.splits * (KP + D) * K);
+    L.AT = take(KP * Nc);                       // A0^T, later P^T (rows K.. stay zero)
+    L.DT = take(KP * Nc);                       // Delta^T
+    L.TT = take((KP + D) * Nc);                 // T^T followed by z_0^T: one operand of products 5 and 6
+    L.Z0T = L.TT + KP * Nc;
+    L.Trow = take(Nc * KP);                     // T, row per sample
+    L.Y = take(Nc * D);                         // T S, later gz_K
+    L.GZT = take((size_t)D * Nc);
     L.total = o;
     return L;
 }
@@ -119,21 +118,6 @@ __global__ void prep_kernel(const float* __restrict__ w, const float* __restrict
     for (int d = threadIdx.x; d < D; d += blockDim.x) ST[(size_t)d * KP + k] = k < K ? s[(size_t)k * D + d] : 0.f;
 }
 
-// [rows][cols] (ld = cols) -> [cols][rows] (ld = ldo); 32 x 32 tiles, block (32, 8)
-__global__ void transpose_kernel(const float* __restrict__ in, int rows, int cols, float* __restrict__ out, long long ldo) {
-    __shared__ float tile[32][33];
-    const int r0 = blockIdx.y * 32, c0 = blockIdx.x * 32;
-    for (int i = threadIdx.y; i < 32; i += 8) {
-        const int r = r0 + i, c = c0 + threadIdx.x;
-        tile[i][threadIdx.x] = (r < rows && c < cols) ? in[(size_t)r * cols + c] : 0.f;
-    }
-    __syncthreads();
-    for (int i = threadIdx.y; i < 32; i += 8) {
-        const int c = c0 + i, r = r0 + threadIdx.x;
-        if (c < cols && r < rows) out[(size_t)c * ldo + r] = tile[threadIdx.x][i];
-    }
-}
-
 // block-wide sum in a fixed order (warp trees, then warp 0 over the warp results)
 template <int NT>
 __device__ __forceinline__ float block_sum(float v, float* red /* [NT/32] */) {
@@ -154,46 +138,48 @@ __device__ __forceinline__ float block_sum(float v, float* red /* [NT/32] */) {
 // Forward recurrence.  One thread per sample; the K pre-activations live in registers and are turned
 // into t_j = tanh(a_j) in place, column j of M being added to the later ones as soon as t_j is known.
 // Mt rows are zero up to and including the diagonal, so whole float4 groups can be applied blindly.
-// The product-1 value of layer k is only needed at step k: it is fetched kPrefetch steps ahead, which
-// spreads the loads over the arithmetic instead of stalling every warp of a wave at its start.
-// Outputs: T^T (coalesced; row K is set to ones -- product 6 then also yields sum_n delta = g_b),
-// T rows (operand of product 2), per-block sum of the log-det terms.
+// The loop body has no control flow that depends on K or on the sample index (padded layers have zero
+// rows everywhere and a unit log-det factor; samples past the end of the chunk compute on whatever the
+// buffers hold and are masked out of the sums), so the whole recurrence is one basic block the compiler
+// can schedule freely: the product-1 value of layer k is fetched a few steps before step k.
+// Outputs: T^T (coalesced), T rows (operand of product 2), per-block sum of the log-det terms.
 constexpr int kPrefetch = 12;
+#ifndef NF_REC_MIN_BLOCKS
+#define NF_REC_MIN_BLOCKS 4
+#endif
 
 template <int KP>
-__global__ void __launch_bounds__(kRecThreads)
+__global__ void __launch_bounds__(kRecThreads, NF_REC_MIN_BLOCKS)
 rec_fwd_kernel(const float* __restrict__ AT, long long ldn, int n_act, int K, const float* __restrict__ Mt,
                const float* __restrict__ c, float epsv, float* __restrict__ TT, float* __restrict__ Trow,
                float* __restrict__ part_ld) {
     using M_ = Mth<float>;
     __shared__ __align__(16) float sM[KP * KP];
-    __shared__ float sc[KP];
+    __shared__ float sc[KP], se[KP];
     __shared__ float red[kRecThreads / 32];
-    for (int i = threadIdx.x; i < KP * KP; i += kRecThreads) sM[i] = Mt[i];
-    for (int i = threadIdx.x; i < KP; i += kRecThreads) sc[i] = i < K ? c[i] : 0.f;
+    for (int i = threadIdx.x; i < KP * KP / 4; i += kRecThreads)
+        reinterpret_cast<float4*>(sM)[i] = reinterpret_cast<const float4*>(Mt)[i];
+    for (int i = threadIdx.x; i < KP; i += kRecThreads) { sc[i] = i < K ? c[i] : 0.f; se[i] = i < K ? epsv : 0.f; }
     __syncthreads();
-    const int n = blockIdx.x * kRecThreads + threadIdx.x;
+    const int n = blockIdx.x * kRecThreads + threadIdx.x;        // < Nc: the buffers are padded to whole blocks
     const bool ok = n < n_act;
-    const float* src = AT + (ok ? n : 0);
-    float* dst = TT + (ok ? n : 0);
+    const float* src = AT + n;
+    float* dst = TT + n;
     float a[KP], in[KP];
 #pragma unroll
     for (int k = 0; k < KP; ++k) a[k] = 0.f;
 #pragma unroll
-    for (int k = 0; k < kPrefetch && k < KP; ++k) in[k] = k < K ? src[(size_t)k * ldn] : 0.f;
+    for (int k = 0; k < kPrefetch && k < KP; ++k) in[k] = src[(size_t)k * ldn];
     float prod = 1.f, ld = 0.f;
 #pragma unroll
     for (int j = 0; j < KP; ++j) {
-        if (j + kPrefetch < KP) in[j + kPrefetch] = (j + kPrefetch < K) ? src[(size_t)(j + kPrefetch) * ldn] : 0.f;
-        asm volatile("" ::: "memory");       // keep the fetch here: hoisted to the top it would pin K more registers
+        if (j + kPrefetch < KP) in[j + kPrefetch] = src[(size_t)(j + kPrefetch) * ldn];
         const float t = M_::tanh_pre(fmaf(in[j], M_::kArgScale, a[j]));
         a[j] = t;
-        if (j < K) {
-            const float hp = fmaf(-t, t, 1.f);
-            prod *= epsv + fabsf(fmaf(hp, sc[j], 1.f));
-            if ((j & 3) == 3 || j == K - 1) { ld += M_::logp(prod); prod = 1.f; }
-            if (ok) dst[(size_t)j * ldn] = t;
-        }
+        const float hp = fmaf(-t, t, 1.f);
+        prod *= se[j] + fabsf(fmaf(hp, sc[j], 1.f));
+        if ((j & 3) == 3) { ld += M_::logp(prod); prod = 1.f; }
+        dst[(size_t)j * ldn] = t;
 #pragma unroll
         for (int k4 = (j + 1) / 4; k4 < KP / 4; ++k4) {
             const float4 m = *reinterpret_cast<const float4*>(&sM[j * KP + 4 * k4]);
@@ -203,84 +189,101 @@ rec_fwd_kernel(const float* __restrict__ AT, long long ldn, int n_act, int K, co
             if (4 * k4 + 3 > j) a[4 * k4 + 3] = fmaf(m.w, t, a[4 * k4 + 3]);
         }
     }
-    if (ok) {
-        dst[(size_t)K * ldn] = 1.f;
-        float4* row = reinterpret_cast<float4*>(Trow + (size_t)n * KP);
+    float4* row = reinterpret_cast<float4*>(Trow + (size_t)n * KP);
 #pragma unroll
-        for (int k4 = 0; k4 < KP / 4; ++k4) row[k4] = make_float4(a[4 * k4], a[4 * k4 + 1], a[4 * k4 + 2], a[4 * k4 + 3]);
-    }
+    for (int k4 = 0; k4 < KP / 4; ++k4) row[k4] = make_float4(a[4 * k4], a[4 * k4 + 1], a[4 * k4 + 2], a[4 * k4 + 3]);
     const float tot = block_sum<kRecThreads>(ok ? ld : 0.f, red);
     if (threadIdx.x == 0) part_ld[blockIdx.x] = tot;
 }
 
 // Reverse recurrence.  p_k starts as (gz_K.s_k) and receives delta_j M[j][k] from the later layers.
-// Outputs: Delta^T ([K][Nc]) and per-block sums of the d F / d c_k terms (sixteen layers at a time through
-// the multi-value warp reduction, then across the four warps in order).
+// Outputs: Delta^T ([KP][Nc]) and per-block sums over the samples of delta_k (= d F / d b_k) and of the
+// d F / d c_k terms: sixteen layers at a time through the multi-value warp reduction, then across the four
+// warps in order.  Branch-free body as in rec_fwd_kernel; the layers are peeled by template recursion
+// (a 64-trip `#pragma unroll` of this body is declined by the compiler, which would put p[] in local memory).
 template <int KP>
-__global__ void __launch_bounds__(kRecThreads)
-rec_bwd_kernel(const float* __restrict__ PT, const float* __restrict__ TT, long long ldn, int n_act, int K,
-               const float* __restrict__ Mrow, const float* __restrict__ c, float epsv, float* __restrict__ DT,
-               float* __restrict__ part_gc /* [gridDim][KP] */) {
-    using M_ = Mth<float>;
-    __shared__ __align__(16) float sM[KP * KP];
-    __shared__ float sc[KP];
-    __shared__ float sgc[kRecThreads / 32][KP];
-    for (int i = threadIdx.x; i < KP * KP; i += kRecThreads) sM[i] = Mrow[i];
-    for (int i = threadIdx.x; i < KP; i += kRecThreads) sc[i] = i < K ? c[i] : 0.f;
-    __syncthreads();
-    const int n = blockIdx.x * kRecThreads + threadIdx.x;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const bool ok = n < n_act;
-    const float* srcp = PT + (ok ? n : 0);
-    const float* srct = TT + (ok ? n : 0);
-    float* dst = DT + (ok ? n : 0);
-    float p[KP], pin[KP], tin[KP];
-#pragma unroll
-    for (int k = 0; k < KP; ++k) p[k] = 0.f;
-#pragma unroll
-    for (int i = 0; i < kPrefetch && i < KP; ++i) {
-        const int k = KP - 1 - i;
-        pin[k] = k < K ? srcp[(size_t)k * ldn] : 0.f;
-        tin[k] = k < K ? srct[(size_t)k * ldn] : 0.f;
-    }
-    float gcv[16];
-#pragma unroll
-    for (int k = KP - 1; k >= 0; --k) {
+struct BwdCtx {
+    const float* srcp; const float* srct; float* dst; long long ldn;
+    const float* sM; const float* sc; const float* se; const float* smask; float* sg;   // sg: this warp's [2 KP] record
+    bool ok; int lane;
+};
+
+template <int KP, int k>
+struct BwdLayer {
+    static __device__ __forceinline__ void run(const BwdCtx<KP>& x_, float (&p)[KP], float (&pin)[KP], float (&tin)[KP],
+                                               float (&gbv)[16], float (&gcv)[16]) {
+        using M_ = Mth<float>;
         if (k - kPrefetch >= 0) {
-            pin[k - kPrefetch] = (k - kPrefetch < K) ? srcp[(size_t)(k - kPrefetch) * ldn] : 0.f;
-            tin[k - kPrefetch] = (k - kPrefetch < K) ? srct[(size_t)(k - kPrefetch) * ldn] : 0.f;
+            pin[k - kPrefetch >= 0 ? k - kPrefetch : 0] = x_.srcp[(size_t)(k - kPrefetch) * x_.ldn];
+            tin[k - kPrefetch >= 0 ? k - kPrefetch : 0] = x_.srct[(size_t)(k - kPrefetch) * x_.ldn];
         }
-        asm volatile("" ::: "memory");       // keep the fetches here (see rec_fwd_kernel)
         const float t = tin[k];
-        const float ck = sc[k];
+        const float ck = x_.sc[k];
         const float hp = fmaf(-t, t, 1.f);
         const float x = fmaf(hp, ck, 1.f);
-        const float y = epsv + fabsf(x);
-        float gx = M_::neg_copysign(M_::rcp(y), x);
-        gx = (ok && k < K) ? gx : 0.f;
-        gcv[k & 15] = gx * hp;
+        const float y = x_.se[k] + fabsf(x);
+        const float gx = M_::neg_copysign(M_::rcp(y), x) * x_.smask[k];
         const float gt = fmaf(-2.f * ck * gx, t, p[k] + pin[k]);
-        const float ga = (ok && k < K) ? gt * hp : 0.f;
-        if (ok && k < K) dst[(size_t)k * ldn] = ga;
+        const float ga = gt * hp;
+        gcv[k & 15] = x_.ok ? gx * hp : 0.f;
+        gbv[k & 15] = x_.ok ? ga : 0.f;
+        x_.dst[(size_t)k * x_.ldn] = ga;
 #pragma unroll
         for (int i4 = 0; i4 < (k + 3) / 4; ++i4) {
-            const float4 m = *reinterpret_cast<const float4*>(&sM[k * KP + 4 * i4]);
+            const float4 m = *reinterpret_cast<const float4*>(&x_.sM[k * KP + 4 * i4]);
             if (4 * i4 + 0 < k) p[4 * i4 + 0] = fmaf(m.x, ga, p[4 * i4 + 0]);
             if (4 * i4 + 1 < k) p[4 * i4 + 1] = fmaf(m.y, ga, p[4 * i4 + 1]);
             if (4 * i4 + 2 < k) p[4 * i4 + 2] = fmaf(m.z, ga, p[4 * i4 + 2]);
             if (4 * i4 + 3 < k) p[4 * i4 + 3] = fmaf(m.w, ga, p[4 * i4 + 3]);
         }
         if ((k & 15) == 0) {        // layers k .. k+15 are complete: reduce them over the warp
-            warp_reduce_multi<float, 16>(gcv, lane);
-            if (warp_slot_owner<16>(lane)) sgc[warp][k + warp_slot<16>(lane)] = gcv[0];
+            warp_reduce_multi<float, 16>(gbv, x_.lane);
+            warp_reduce_multi<float, 16>(gcv, x_.lane);
+            if (warp_slot_owner<16>(x_.lane)) {
+                x_.sg[k + warp_slot<16>(x_.lane)] = gbv[0];
+                x_.sg[KP + k + warp_slot<16>(x_.lane)] = gcv[0];
+            }
         }
+        if constexpr (k > 0) BwdLayer<KP, k - 1>::run(x_, p, pin, tin, gbv, gcv);
+    }
+};
+
+template <int KP>
+__global__ void __launch_bounds__(kRecThreads, 3)
+rec_bwd_kernel(const float* __restrict__ PT, const float* __restrict__ TT, long long ldn, int n_act, int K,
+               const float* __restrict__ Mrow, const float* __restrict__ c, float epsv, float* __restrict__ DT,
+               float* __restrict__ part_g /* [gridDim][2][KP] : g_b | g_c */) {
+    __shared__ __align__(16) float sM[KP * KP];
+    __shared__ float sc[KP], se[KP], smask[KP];
+    __shared__ float sg[kRecThreads / 32][2 * KP];
+    for (int i = threadIdx.x; i < KP * KP / 4; i += kRecThreads)
+        reinterpret_cast<float4*>(sM)[i] = reinterpret_cast<const float4*>(Mrow)[i];
+    for (int i = threadIdx.x; i < KP; i += kRecThreads) {
+        sc[i] = i < K ? c[i] : 0.f; se[i] = i < K ? epsv : 0.f; smask[i] = i < K ? 1.f : 0.f;
     }
     __syncthreads();
-    if (threadIdx.x < KP) {
+    const int n = blockIdx.x * kRecThreads + threadIdx.x;
+    BwdCtx<KP> x_;
+    x_.srcp = PT + n; x_.srct = TT + n; x_.dst = DT + n; x_.ldn = ldn;
+    x_.sM = sM; x_.sc = sc; x_.se = se; x_.smask = smask; x_.sg = sg[threadIdx.x >> 5];
+    x_.ok = n < n_act; x_.lane = threadIdx.x & 31;
+    float p[KP], pin[KP], tin[KP];
+#pragma unroll
+    for (int k = 0; k < KP; ++k) p[k] = 0.f;
+#pragma unroll
+    for (int i = 0; i < kPrefetch && i < KP; ++i) {
+        const int k = KP - 1 - i;
+        pin[k] = x_.srcp[(size_t)k * ldn];
+        tin[k] = x_.srct[(size_t)k * ldn];
+    }
+    float gcv[16], gbv[16];
+    BwdLayer<KP, KP - 1>::run(x_, p, pin, tin, gbv, gcv);
+    __syncthreads();
+    if (threadIdx.x < 2 * KP) {
         float t = 0.f;
 #pragma unroll
-        for (int w = 0; w < kRecThreads / 32; ++w) t += sgc[w][threadIdx.x];
-        part_gc[(size_t)blockIdx.x * KP + threadIdx.x] = t;
+        for (int w = 0; w < kRecThreads / 32; ++w) t += sg[w][threadIdx.x];
+        part_g[(size_t)blockIdx.x * 2 * KP + threadIdx.x] = t;
     }
 }
 
@@ -428,19 +431,20 @@ target_kernel(const float* __restrict__ z0, float* __restrict__ Y, int n_act, in
     }
 }
 
-// Per chunk: running totals.  Blocks [0, K): column k of the per-block d F / d c_k sums; block K: log-det,
+// Per chunk: running totals.  Blocks [0, 2K): column sums of the per-block (g_b | g_c) records; block 2K: log-det,
 // log q_0 and log p partial sums.  Fixed order, and chunks arrive in stream order.
 __global__ void __launch_bounds__(256)
-chunk_totals_kernel(const float* __restrict__ part_gc, int KP, int K, int bwd, const float* __restrict__ part_ld, int n_rec,
-                    const float* __restrict__ part_t, int n_t, float* __restrict__ acc /* [ld, q0, p | - | g_c (kMaxK)] */) {
+chunk_totals_kernel(const float* __restrict__ part_g, int KP, int K, int bwd, const float* __restrict__ part_ld, int n_rec,
+                    const float* __restrict__ part_t, int n_t, float* __restrict__ acc /* [ld, q0, p | g_b (kMaxK) | g_c (kMaxK)] */) {
     __shared__ float red[8];
     const int b = blockIdx.x;
-    if (b < K) {
+    if (b < 2 * K) {
         if (!bwd) return;
+        const int col = b < K ? b : KP + (b - K);
         float v = 0.f;
-        for (int i = threadIdx.x; i < n_rec; i += 256) v += part_gc[(size_t)i * KP + b];
+        for (int i = threadIdx.x; i < n_rec; i += 256) v += part_g[(size_t)i * 2 * KP + col];
         const float t = block_sum<256>(v, red);
-        if (threadIdx.x == 0) acc[3 + kMaxK + b] += t;
+        if (threadIdx.x == 0) acc[3 + (b < K ? b : kMaxK + (b - K))] += t;
     } else {
         float a = 0.f, q = 0.f, p = 0.f;
         for (int i = threadIdx.x; i < n_rec; i += 256) a += part_ld[i];
@@ -452,28 +456,30 @@ chunk_totals_kernel(const float* __restrict__ part_gc, int KP, int K, int bwd, c
     }
 }
 
-// g_s[k][d] = G4[d][k] + sum_{j>k} G6[k][j] w[j][d] ;  g_w[k][d] = G5[d][k] + sum_{j<k} G6[j][k] s[j][d] ;
-// g_b[k] = G6[K][k] (the row of ones appended to T^T)
-__global__ void finish_kernel(const float* __restrict__ acc, const float* __restrict__ G4, const float* __restrict__ G5,
-                              const float* __restrict__ G6, const float* __restrict__ w, const float* __restrict__ s,
-                              int K, int D, int bwd, float* __restrict__ out_F, float* __restrict__ g_w,
-                              float* __restrict__ g_s, float* __restrict__ g_b, float* __restrict__ g_c) {
+// g_s[k][d] = G4[d][k] + sum_{j>k} G6[k][j] w[j][d] ;  g_w[k][d] = G5[d][k] + sum_{j<k} G6[j][k] s[j][d]
+// with G6 = rows [0, KP) and G5 = rows [KP, KP + D) of the stacked product; grid (K, ceil(D / 128)).
+__global__ void finish_kernel(const float* __restrict__ acc, const float* __restrict__ G4, const float* __restrict__ G56,
+                              const float* __restrict__ w, const float* __restrict__ s, int K, int KP, int D, int bwd,
+                              float* __restrict__ out_F, float* __restrict__ g_w, float* __restrict__ g_s,
+                              float* __restrict__ g_b, float* __restrict__ g_c) {
     const int k = blockIdx.x;
-    if (k == 0 && threadIdx.x == 0) {
+    if (k == 0 && blockIdx.y == 0 && threadIdx.x == 0) {
         const float sum_q = acc[1] - acc[0];
         out_F[0] = sum_q - acc[2];
         out_F[1] = sum_q;
         out_F[2] = acc[2];
     }
     if (!bwd) return;
-    if (threadIdx.x == 0) { g_b[k] = G6[(size_t)K * K + k]; g_c[k] = acc[3 + kMaxK + k]; }
-    for (int d = threadIdx.x; d < D; d += blockDim.x) {
-        float gs = G4[(size_t)d * K + k], gw = G5[(size_t)d * K + k];
-        for (int j = k + 1; j < K; ++j) gs = fmaf(G6[(size_t)k * K + j], w[(size_t)j * D + d], gs);
-        for (int j = 0; j < k; ++j) gw = fmaf(G6[(size_t)j * K + k], s[(size_t)j * D + d], gw);
-        g_s[(size_t)k * D + d] = gs;
-        g_w[(size_t)k * D + d] = gw;
-    }
+    if (blockIdx.y == 0 && threadIdx.x == 0) { g_b[k] = acc[3 + k]; g_c[k] = acc[3 + kMaxK + k]; }
+    const float* G6 = G56;
+    const float* G5 = G56 + (size_t)KP * K;
+    const int d = blockIdx.y * blockDim.x + threadIdx.x;
+    if (d >= D) return;
+    float gs = G4[(size_t)d * K + k], gw = G5[(size_t)d * K + k];
+    for (int j = k + 1; j < K; ++j) gs = fmaf(G6[(size_t)k * K + j], w[(size_t)j * D + d], gs);
+    for (int j = 0; j < k; ++j) gw = fmaf(G6[(size_t)j * K + k], s[(size_t)j * D + d], gw);
+    g_s[(size_t)k * D + d] = gs;
+    g_w[(size_t)k * D + d] = gw;
 }
 
 template <int TGT>
@@ -499,7 +505,7 @@ static cudaError_t launch_rec(bool fwd, const Layout& L, float* ws, int n_act, i
                                                           ws + L.part_ld);
     else
         rec_bwd_kernel<KP><<<blocks, kRecThreads, 0, st>>>(ws + L.AT, ws + L.TT, L.Nc, n_act, K, ws + L.M, c, epsv, ws + L.DT,
-                                                          ws + L.part_gc);
+                                                          ws + L.part_g);
     return cudaGetLastError();
 }
 static cudaError_t launch_rec_any(bool fwd, const Layout& L, float* ws, int n_act, int K, const float* c, float epsv, cudaStream_t st) {
@@ -533,6 +539,7 @@ int gram_elbo_f32(bool bwd, const float* eps, long long N, int D, int K, const f
     const int KP = L.KP;
     prep_kernel<<<KP, 256, 0, st>>>(w, s, K, D, KP, ws + L.M, ws + L.Mt, ws + L.ST, ws + L.acc);
     NF_CUDA_OK(cudaGetLastError());
+    if (KP > K) NF_CUDA_OK(cudaMemsetAsync(ws + L.AT + (size_t)K * L.Nc, 0, (size_t)(KP - K) * L.Nc * sizeof(float), st));
     int rc;
     bool first = true;
     for (long long c0 = 0; c0 < N; c0 += L.Nc) {
@@ -552,21 +559,21 @@ int gram_elbo_f32(bool bwd, const float* eps, long long N, int D, int K, const f
             // product 3: P^T[k][n] = sum_d gz[n][d] s[k][d]
             if ((rc = tc_gemm_f32(ws + L.Y, D, s, D, n_act, K, D, nullptr, 0, ws + L.AT, L.Nc, nullptr, 0, nullptr, 0, 0, st)) != NF_OK) return rc;
             NF_CUDA_OK(launch_rec_any(false, L, ws, n_act, K, c, epsv, st));
-            // products 4-6 contract over the samples of the chunk (split across CTAs, fixed-order sums)
+            // products 4-6 contract over the samples of the chunk (split across CTAs, fixed-order sums);
+            // 5 and 6 share the operand Delta^T and run as one product with [T^T ; z_0^T] stacked
             if ((rc = tc_gemm_f32(ws + L.GZT, L.Nc, ws + L.TT, L.Nc, D, K, n_act, ws + L.G4, K, nullptr, 0, nullptr, 0, nullptr, 0, 0, st,
                                   L.splits, ws + L.split4, !first)) != NF_OK) return rc;
-            if ((rc = tc_gemm_f32(ws + L.Z0T, L.Nc, ws + L.DT, L.Nc, D, K, n_act, ws + L.G5, K, nullptr, 0, nullptr, 0, nullptr, 0, 0, st,
-                                  L.splits, ws + L.split5, !first)) != NF_OK) return rc;
-            if ((rc = tc_gemm_f32(ws + L.TT, L.Nc, ws + L.DT, L.Nc, K + 1, K, n_act, ws + L.G6, K, nullptr, 0, nullptr, 0, nullptr, 0, 0, st,
-                                  L.splits, ws + L.split6, !first)) != NF_OK) return rc;
+            if ((rc = tc_gemm_f32(ws + L.TT, L.Nc, ws + L.DT, L.Nc, KP + D, K, n_act, ws + L.G56, K, nullptr, 0, nullptr, 0, nullptr, 0, 0, st,
+                                  L.splits, ws + L.split56, !first)) != NF_OK) return rc;
         }
-        chunk_totals_kernel<<<K + 1, 256, 0, st>>>(ws + L.part_gc, KP, K, bwd ? 1 : 0, ws + L.part_ld,
+        chunk_totals_kernel<<<2 * K + 1, 256, 0, st>>>(ws + L.part_g, KP, K, bwd ? 1 : 0, ws + L.part_ld,
                                                   (n_act + kRecThreads - 1) / kRecThreads, ws + L.part_t,
                                                   (n_act + kTgtRows - 1) / kTgtRows, ws + L.acc);
         NF_CUDA_OK(cudaGetLastError());
         first = false;
     }
-    finish_kernel<<<K, 256, 0, st>>>(ws + L.acc, ws + L.G4, ws + L.G5, ws + L.G6, w, s, K, D, bwd ? 1 : 0, out_F, g_w, g_s, g_b, g_c);
+    finish_kernel<<<dim3(K, (D + 127) / 128), 128, 0, st>>>(ws + L.acc, ws + L.G4, ws + L.G56, w, s, K, KP, D, bwd ? 1 : 0, out_F, g_w, g_s,
+                                                           g_b, g_c);
     NF_CUDA_OK(cudaGetLastError());
     return NF_OK;
 }
