@@ -140,41 +140,63 @@ __device__ __forceinline__ float block_sum(float v, float* red /* [NT/32] */) {
 // Mt rows are zero up to and including the diagonal, so whole float4 groups can be applied blindly.
 // The loop body has no control flow that depends on K or on the sample index (padded layers have zero
 // rows everywhere and a unit log-det factor; samples past the end of the chunk compute on whatever the
-// buffers hold and are masked out of the sums), so the whole recurrence is one basic block the compiler
-// can schedule freely: the product-1 value of layer k is fetched a few steps before step k.
+// buffers hold and are masked out of the sums), so the whole recurrence is one basic block.
+// The product-1 values of a thread (one per layer, needed at step k) are brought into a thread-private
+// column of shared memory by cp.async, sixteen layers per group, and waited for group by group: the
+// fetches cost no registers and overlap the arithmetic.
 // Outputs: T^T (coalesced), T rows (operand of product 2), per-block sum of the log-det terms.
-constexpr int kPrefetch = 12;
-#ifndef NF_REC_MIN_BLOCKS
-#define NF_REC_MIN_BLOCKS 4
-#endif
+__device__ __forceinline__ void cp_async4(float* smem_dst, const float* gsrc) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_le(int pending) {      // `pending` folds to a constant where this is used
+    if (pending <= 0) asm volatile("cp.async.wait_group 0;" ::: "memory");
+    else if (pending == 1) asm volatile("cp.async.wait_group 1;" ::: "memory");
+    else if (pending == 2) asm volatile("cp.async.wait_group 2;" ::: "memory");
+    else if (pending == 3) asm volatile("cp.async.wait_group 3;" ::: "memory");
+    else asm volatile("cp.async.wait_group 4;" ::: "memory");
+}
+
+template <int KP> constexpr size_t rec_fwd_smem() { return (size_t)(KP * KP + KP * kRecThreads) * sizeof(float); }
+template <int KP> constexpr size_t rec_bwd_smem() { return (size_t)(KP * KP + (KP < 32 ? KP : 32) * 2 * kRecThreads) * sizeof(float); }
 
 template <int KP>
-__global__ void __launch_bounds__(kRecThreads, NF_REC_MIN_BLOCKS)
+__global__ void __launch_bounds__(kRecThreads, 4)
 rec_fwd_kernel(const float* __restrict__ AT, long long ldn, int n_act, int K, const float* __restrict__ Mt,
                const float* __restrict__ c, float epsv, float* __restrict__ TT, float* __restrict__ Trow,
                float* __restrict__ part_ld) {
     using M_ = Mth<float>;
-    __shared__ __align__(16) float sM[KP * KP];
+    extern __shared__ __align__(16) float dyn[];
+    float* sM = dyn;                              // [KP][KP]
+    float* stage = dyn + KP * KP;                 // [KP][128]: column = thread
     __shared__ float sc[KP], se[KP];
     __shared__ float red[kRecThreads / 32];
-    for (int i = threadIdx.x; i < KP * KP / 4; i += kRecThreads)
-        reinterpret_cast<float4*>(sM)[i] = reinterpret_cast<const float4*>(Mt)[i];
-    for (int i = threadIdx.x; i < KP; i += kRecThreads) { sc[i] = i < K ? c[i] : 0.f; se[i] = i < K ? epsv : 0.f; }
-    __syncthreads();
+    constexpr int NG = KP / 16;
     const int n = blockIdx.x * kRecThreads + threadIdx.x;        // < Nc: the buffers are padded to whole blocks
     const bool ok = n < n_act;
     const float* src = AT + n;
     float* dst = TT + n;
-    float a[KP], in[KP];
+    for (int i = threadIdx.x; i < KP * KP / 4; i += kRecThreads) cp_async16(sM + 4 * i, Mt + 4 * i);
+#pragma unroll
+    for (int g = 0; g < NG; ++g) {
+#pragma unroll
+        for (int k = 16 * g; k < 16 * g + 16; ++k) cp_async4(stage + k * kRecThreads + threadIdx.x, src + (size_t)k * ldn);
+        cp_async_commit();                        // group g (group 0 also carries M)
+    }
+    for (int i = threadIdx.x; i < KP; i += kRecThreads) { sc[i] = i < K ? c[i] : 0.f; se[i] = i < K ? epsv : 0.f; }
+    cp_async_wait_le(NG - 1);
+    __syncthreads();                              // M, c and eps visible to all
+    float a[KP];
 #pragma unroll
     for (int k = 0; k < KP; ++k) a[k] = 0.f;
-#pragma unroll
-    for (int k = 0; k < kPrefetch && k < KP; ++k) in[k] = src[(size_t)k * ldn];
     float prod = 1.f, ld = 0.f;
 #pragma unroll
     for (int j = 0; j < KP; ++j) {
-        if (j + kPrefetch < KP) in[j + kPrefetch] = src[(size_t)(j + kPrefetch) * ldn];
-        const float t = M_::tanh_pre(fmaf(in[j], M_::kArgScale, a[j]));
+        if (j > 0 && (j & 15) == 0) cp_async_wait_le(NG - 1 - j / 16);
+        const float t = M_::tanh_pre(fmaf(stage[j * kRecThreads + threadIdx.x], M_::kArgScale, a[j]));
         a[j] = t;
         const float hp = fmaf(-t, t, 1.f);
         prod *= se[j] + fabsf(fmaf(hp, sc[j], 1.f));
@@ -201,29 +223,46 @@ rec_fwd_kernel(const float* __restrict__ AT, long long ldn, int n_act, int K, co
 // d F / d c_k terms: sixteen layers at a time through the multi-value warp reduction, then across the four
 // warps in order.  Branch-free body as in rec_fwd_kernel; the layers are peeled by template recursion
 // (a 64-trip `#pragma unroll` of this body is declined by the compiler, which would put p[] in local memory).
+// P^T and T^T arrive through cp.async in quarters of sixteen layers, two quarters resident (thread-private
+// columns again): when a quarter has been consumed its slot is refilled with the quarter after next.
 template <int KP>
 struct BwdCtx {
     const float* srcp; const float* srct; float* dst; long long ldn;
     const float* sM; const float* sc; const float* se; const float* smask; float* sg;   // sg: this warp's [2 KP] record
+    float* stage;          // [2 slots][16 layers][2 (P^T, T^T)][128], already offset by the thread index
     bool ok; int lane;
 };
 
+template <int KP>
+__device__ __forceinline__ void bwd_issue_quarter(const BwdCtx<KP>& x_, int q) {
+    float* slot = x_.stage + (q & 1) * 16 * 2 * kRecThreads;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const int k = 16 * q + i;
+        cp_async4(slot + (2 * i) * kRecThreads, x_.srcp + (size_t)k * x_.ldn);
+        cp_async4(slot + (2 * i + 1) * kRecThreads, x_.srct + (size_t)k * x_.ldn);
+    }
+    cp_async_commit();
+}
+
 template <int KP, int k>
 struct BwdLayer {
-    static __device__ __forceinline__ void run(const BwdCtx<KP>& x_, float (&p)[KP], float (&pin)[KP], float (&tin)[KP],
-                                               float (&gbv)[16], float (&gcv)[16]) {
+    static __device__ __forceinline__ void run(const BwdCtx<KP>& x_, float (&p)[KP], float (&gbv)[16], float (&gcv)[16]) {
         using M_ = Mth<float>;
-        if (k - kPrefetch >= 0) {
-            pin[k - kPrefetch >= 0 ? k - kPrefetch : 0] = x_.srcp[(size_t)(k - kPrefetch) * x_.ldn];
-            tin[k - kPrefetch >= 0 ? k - kPrefetch : 0] = x_.srct[(size_t)(k - kPrefetch) * x_.ldn];
+        constexpr int NQ = KP / 16, q = k / 16;
+        if ((k & 15) == 15) {                    // entering quarter q
+            if (q < NQ - 1 && q >= 1) bwd_issue_quarter<KP>(x_, q - 1);     // quarter q+1 is consumed: refill its slot
+            cp_async_wait_le(q >= 1 ? 1 : 0);
         }
-        const float t = tin[k];
+        const float* slot = x_.stage + (q & 1) * 16 * 2 * kRecThreads + 2 * (k & 15) * kRecThreads;
+        const float pin = slot[0];
+        const float t = slot[kRecThreads];
         const float ck = x_.sc[k];
         const float hp = fmaf(-t, t, 1.f);
         const float x = fmaf(hp, ck, 1.f);
         const float y = x_.se[k] + fabsf(x);
         const float gx = M_::neg_copysign(M_::rcp(y), x) * x_.smask[k];
-        const float gt = fmaf(-2.f * ck * gx, t, p[k] + pin[k]);
+        const float gt = fmaf(-2.f * ck * gx, t, p[k] + pin);
         const float ga = gt * hp;
         gcv[k & 15] = x_.ok ? gx * hp : 0.f;
         gbv[k & 15] = x_.ok ? ga : 0.f;
@@ -244,40 +283,39 @@ struct BwdLayer {
                 x_.sg[KP + k + warp_slot<16>(x_.lane)] = gcv[0];
             }
         }
-        if constexpr (k > 0) BwdLayer<KP, k - 1>::run(x_, p, pin, tin, gbv, gcv);
+        if constexpr (k > 0) BwdLayer<KP, k - 1>::run(x_, p, gbv, gcv);
     }
 };
 
 template <int KP>
-__global__ void __launch_bounds__(kRecThreads, 3)
+__global__ void __launch_bounds__(kRecThreads, 4)
 rec_bwd_kernel(const float* __restrict__ PT, const float* __restrict__ TT, long long ldn, int n_act, int K,
                const float* __restrict__ Mrow, const float* __restrict__ c, float epsv, float* __restrict__ DT,
                float* __restrict__ part_g /* [gridDim][2][KP] : g_b | g_c */) {
-    __shared__ __align__(16) float sM[KP * KP];
+    extern __shared__ __align__(16) float dyn[];
+    float* sM = dyn;                                // [KP][KP]
     __shared__ float sc[KP], se[KP], smask[KP];
     __shared__ float sg[kRecThreads / 32][2 * KP];
-    for (int i = threadIdx.x; i < KP * KP / 4; i += kRecThreads)
-        reinterpret_cast<float4*>(sM)[i] = reinterpret_cast<const float4*>(Mrow)[i];
-    for (int i = threadIdx.x; i < KP; i += kRecThreads) {
-        sc[i] = i < K ? c[i] : 0.f; se[i] = i < K ? epsv : 0.f; smask[i] = i < K ? 1.f : 0.f;
-    }
-    __syncthreads();
+    constexpr int NQ = KP / 16;
     const int n = blockIdx.x * kRecThreads + threadIdx.x;
     BwdCtx<KP> x_;
     x_.srcp = PT + n; x_.srct = TT + n; x_.dst = DT + n; x_.ldn = ldn;
     x_.sM = sM; x_.sc = sc; x_.se = se; x_.smask = smask; x_.sg = sg[threadIdx.x >> 5];
+    x_.stage = dyn + KP * KP + threadIdx.x;
     x_.ok = n < n_act; x_.lane = threadIdx.x & 31;
-    float p[KP], pin[KP], tin[KP];
+    for (int i = threadIdx.x; i < KP * KP / 4; i += kRecThreads) cp_async16(sM + 4 * i, Mrow + 4 * i);
+    bwd_issue_quarter<KP>(x_, NQ - 1);              // this group also carries M
+    if (NQ >= 2) bwd_issue_quarter<KP>(x_, NQ - 2);
+    for (int i = threadIdx.x; i < KP; i += kRecThreads) {
+        sc[i] = i < K ? c[i] : 0.f; se[i] = i < K ? epsv : 0.f; smask[i] = i < K ? 1.f : 0.f;
+    }
+    cp_async_wait_le(NQ >= 2 ? 1 : 0);
+    __syncthreads();
+    float p[KP];
 #pragma unroll
     for (int k = 0; k < KP; ++k) p[k] = 0.f;
-#pragma unroll
-    for (int i = 0; i < kPrefetch && i < KP; ++i) {
-        const int k = KP - 1 - i;
-        pin[k] = x_.srcp[(size_t)k * ldn];
-        tin[k] = x_.srct[(size_t)k * ldn];
-    }
     float gcv[16], gbv[16];
-    BwdLayer<KP, KP - 1>::run(x_, p, pin, tin, gbv, gcv);
+    BwdLayer<KP, KP - 1>::run(x_, p, gbv, gcv);
     __syncthreads();
     if (threadIdx.x < 2 * KP) {
         float t = 0.f;
@@ -290,9 +328,12 @@ rec_bwd_kernel(const float* __restrict__ PT, const float* __restrict__ TT, long 
 // ------------------------------------------------------------------------------------------------
 // Target kernel: z_K = z_0 + Y, log p(z_K), log q_0(z_0) and gz_K = dF/dz_K = -d log p / dz_K.
 // A block owns 32 consecutive samples, i.e. one contiguous run of 32 D floats of z_0 and of Y: it is read
-// with float4 loads into two shared-memory tiles; eight lanes then share a row (four rows per warp at a
-// time, three shuffles per row sum).  gz_K replaces Y (row form, operand of product 3); gz_K^T and z_0^T
-// (operands of products 4 and 5) are written from the tiles, 32 consecutive samples per store.
+// with float4 loads into two shared-memory tiles of float4; eight lanes then share a row (four rows per
+// warp at a time, three shuffles per row sum).  gz_K replaces Y (row form, operand of product 3); gz_K^T
+// and z_0^T (operands of products 4 and 5) are written from the tiles.
+// Tile layout: float4 number c of row r sits at slot r * (D/4) + (c + r % 8) mod (D/4).  With D % 32 == 0
+// every access pattern below is free of bank conflicts: consecutive float4 of a row (load, row phase, row
+// store), and in the transposed stores 8 samples x 4 coordinates per instruction (32-byte runs of samples).
 // Same density formulas as elbo_wide_kernel (distributions.py:10-54).
 __device__ __forceinline__ float sum8(float v) {
     v += __shfl_xor_sync(0xffffffffu, v, 1);
@@ -300,9 +341,14 @@ __device__ __forceinline__ float sum8(float v) {
     v += __shfl_xor_sync(0xffffffffu, v, 4);
     return v;
 }
+__device__ __forceinline__ int tile_slot(int r, int c, int NV) {
+    int x = c + (r & 7);
+    x = x >= NV ? x - NV : x;
+    return r * NV + x;
+}
+__device__ __forceinline__ float f4_get(const float4& v, int i) { return i == 0 ? v.x : (i == 1 ? v.y : (i == 2 ? v.z : v.w)); }
 
-static inline int tgt_pitch(int D) { return D + 9; }     // odd: transposed reads conflict-free; 9: the four rows of a warp spread over the banks
-static inline size_t tgt_smem_bytes(int D, bool bwd) { return ((size_t)(bwd ? 2 : 1) * kTgtRows * tgt_pitch(D) + 2 * (size_t)D) * sizeof(float); }
+static inline size_t tgt_smem_bytes(int D, bool bwd) { return ((size_t)(bwd ? 2 : 1) * kTgtRows * D + 2 * (size_t)D) * sizeof(float); }
 
 template <int TGT, bool BWD>
 __global__ void __launch_bounds__(kTgtThreads)
@@ -313,10 +359,10 @@ target_kernel(const float* __restrict__ z0, float* __restrict__ Y, int n_act, in
     extern __shared__ __align__(16) float smem[];
     __shared__ float red[kTgtThreads / 32][2];
     __shared__ float mixe[kTgtRows][kMaxMix];
-    const int pitch = D + 9;
-    float* tz = smem;                                  // z_K, then gz_K        [32][pitch]
-    float* t0 = BWD ? tz + kTgtRows * pitch : tz;      // z_0 (reverse pass only; forward recomputes nothing from it)
-    float* s_mu = smem + (BWD ? 2 : 1) * kTgtRows * pitch;
+    const int NV = D / 4;
+    float4* tz = reinterpret_cast<float4*>(smem);                    // z_K, then gz_K
+    float4* t0 = BWD ? tz + kTgtRows * NV : tz;                      // z_0 (reverse pass only)
+    float* s_mu = smem + (BWD ? 2 : 1) * kTgtRows * D;
     float* s_iv = s_mu + D;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const float LOG2PI = 1.8378770664093453f;
@@ -329,41 +375,53 @@ target_kernel(const float* __restrict__ z0, float* __restrict__ Y, int n_act, in
         for (int d = lane; d < D; d += 32) ls += tparams[D + d];
         g_const = -0.5f * (D * LOG2PI + warp_sum(ls));
     }
-    // ---- load: flat float4 run of rows * D floats ----
+    // ---- load: one flat run of rows * D floats ----
     const float4* z4 = reinterpret_cast<const float4*>(z0 + (size_t)n0 * D);
     const float4* y4 = reinterpret_cast<const float4*>(Y + (size_t)n0 * D);
-    const int nvec = rows * D / 4;
+    const int nvec = rows * NV;
     float zz_part = 0.f;        // only used by the forward-only instantiation
     for (int v = tid; v < nvec; v += kTgtThreads) {
         const float4 a = z4[v], b = y4[v];
-        const int r = (4 * v) / D, d = 4 * v - r * D;
-        float* q = tz + r * pitch + d;
-        q[0] = a.x + b.x; q[1] = a.y + b.y; q[2] = a.z + b.z; q[3] = a.w + b.w;
-        if (BWD) { float* q0 = t0 + r * pitch + d; q0[0] = a.x; q0[1] = a.y; q0[2] = a.z; q0[3] = a.w; }
+        const int rr = v / NV, c = v - rr * NV;
+        const int at = tile_slot(rr, c, NV);
+        tz[at] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+        if (BWD) t0[at] = a;
         else zz_part = fmaf(a.x, a.x, fmaf(a.y, a.y, fmaf(a.z, a.z, fmaf(a.w, a.w, zz_part))));
     }
     __syncthreads();
     // ---- per row: eight lanes per row, rows 4*warp .. 4*warp+3 ----
     const int r = 4 * warp + (lane >> 3), l = lane & 7;
     const bool live = r < rows;
-    float* zr = tz + r * pitch;
     float lq = 0.f, lp = 0.f;
     if (BWD) {
         float zz = 0.f;
-        if (live) for (int d = l; d < D; d += 8) { const float a = t0[r * pitch + d]; zz = fmaf(a, a, zz); }
+        if (live) for (int c = l; c < NV; c += 8) {
+            const float4 a = t0[tile_slot(r, c, NV)];
+            zz = fmaf(a.x, a.x, fmaf(a.y, a.y, fmaf(a.z, a.z, fmaf(a.w, a.w, zz))));
+        }
         zz = sum8(zz);
         lq = live ? -0.5f * (D * LOG2PI + zz) : 0.f;
     }
     if (TGT == NF_TARGET_GAUSSDIAG) {
+        const float4* mu4 = reinterpret_cast<const float4*>(s_mu);
+        const float4* iv4 = reinterpret_cast<const float4*>(s_iv);
         float q = 0.f;
-        if (live) for (int d = l; d < D; d += 8) { const float df = zr[d] - s_mu[d]; q = fmaf(df * s_iv[d], df, q); }
+        if (live) for (int c = l; c < NV; c += 8) {
+            const float4 z = tz[tile_slot(r, c, NV)], m = mu4[c], iv = iv4[c];
+            const float dx = z.x - m.x, dy = z.y - m.y, dz = z.z - m.z, dw = z.w - m.w;
+            q = fmaf(dx * iv.x, dx, fmaf(dy * iv.y, dy, fmaf(dz * iv.z, dz, fmaf(dw * iv.w, dw, q))));
+        }
         q = sum8(q);
         const float dens = M_::exp(g_const - 0.5f * q);
         const float den = epsv + dens;
         lp = live ? M_::logp(den) : 0.f;
         if (BWD) {
             const float rho = M_::div(dens, den);
-            if (live) for (int d = l; d < D; d += 8) zr[d] = rho * (zr[d] - s_mu[d]) * s_iv[d];
+            if (live) for (int c = l; c < NV; c += 8) {
+                const int at = tile_slot(r, c, NV);
+                const float4 z = tz[at], m = mu4[c], iv = iv4[c];
+                tz[at] = make_float4(rho * (z.x - m.x) * iv.x, rho * (z.y - m.y) * iv.y, rho * (z.z - m.z) * iv.z, rho * (z.w - m.w) * iv.w);
+            }
         }
     } else {   // MIXDIAG: [pi (G) | mu (G*D) | var (G*D)]
         const int G = ntp / (1 + 2 * D);
@@ -372,28 +430,40 @@ target_kernel(const float* __restrict__ z0, float* __restrict__ Y, int n_act, in
             const float* mu = tparams + G + (size_t)gc * D;
             const float* var = tparams + G + (size_t)G * D + (size_t)gc * D;
             float q = 0.f, lsum = 0.f;
-            if (live) for (int d = l; d < D; d += 8) {
-                const float df = zr[d] - mu[d];
-                q = fmaf(df, M_::div(df, var[d]), q);
-                lsum += M_::logp(var[d]);
+            if (live) for (int c = l; c < NV; c += 8) {
+                const float4 z = tz[tile_slot(r, c, NV)];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const int d = 4 * c + e;
+                    const float df = f4_get(z, e) - mu[d];
+                    q = fmaf(df, M_::div(df, var[d]), q);
+                    lsum += M_::logp(var[d]);
+                }
             }
             q = sum8(q);
             lsum = sum8(lsum);
             const float e = tparams[gc] * M_::exp(-0.5f * (D * LOG2PI + lsum + q));
             dens += e;
-            if (l == 0 && r < kTgtRows) mixe[r][gc] = e;
+            if (l == 0) mixe[r][gc] = e;
         }
         const float den = epsv + dens;
         lp = live ? M_::logp(den) : 0.f;
         if (BWD) {
             __syncwarp();
             const float inv = M_::div(1.f, den);
-            if (live) for (int d = l; d < D; d += 8) {
-                const float z = zr[d];
-                float acc = 0.f;
-                for (int gc = 0; gc < G; ++gc)
-                    acc = fmaf(mixe[r][gc], M_::div(z - tparams[G + (size_t)gc * D + d], tparams[G + (size_t)G * D + (size_t)gc * D + d]), acc);
-                zr[d] = acc * inv;
+            if (live) for (int c = l; c < NV; c += 8) {
+                const int at = tile_slot(r, c, NV);
+                const float4 z = tz[at];
+                float g[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const int d = 4 * c + e;
+                    float acc = 0.f;
+                    for (int gc = 0; gc < G; ++gc)
+                        acc = fmaf(mixe[r][gc], M_::div(f4_get(z, e) - tparams[G + (size_t)gc * D + d], tparams[G + (size_t)G * D + (size_t)gc * D + d]), acc);
+                    g[e] = acc * inv;
+                }
+                tz[at] = make_float4(g[0], g[1], g[2], g[3]);
             }
         }
     }
@@ -415,17 +485,21 @@ target_kernel(const float* __restrict__ z0, float* __restrict__ Y, int n_act, in
         // row form of gz_K, in place of Y
         float4* o4 = reinterpret_cast<float4*>(Y + (size_t)n0 * D);
         for (int v = tid; v < nvec; v += kTgtThreads) {
-            const int rr = (4 * v) / D, d = 4 * v - rr * D;
-            const float* q = tz + rr * pitch + d;
-            o4[v] = make_float4(q[0], q[1], q[2], q[3]);
+            const int rr = v / NV, c = v - rr * NV;
+            o4[v] = tz[tile_slot(rr, c, NV)];
         }
-        // transposed copies: lane <-> sample, warps stride over the coordinates
-        if (lane < rows) {
-            float* gz_t = GZT + n0 + lane;
-            float* z0_t = Z0T + n0 + lane;
-            for (int d = warp; d < D; d += kTgtThreads / 32) {
-                gz_t[(size_t)d * ldn] = tz[lane * pitch + d];
-                z0_t[(size_t)d * ldn] = t0[lane * pitch + d];
+        // transposed copies: per instruction 8 samples (lane % 8) x 4 coordinates (lane / 8) of one float4 column
+        const int s8 = lane & 7, dd = lane >> 3;
+        for (int c = warp; c < NV; c += kTgtThreads / 32) {
+            const size_t orow = (size_t)(4 * c + dd) * ldn + n0;
+#pragma unroll
+            for (int j = 0; j < kTgtRows / 8; ++j) {
+                const int rr = 8 * j + s8;
+                if (rr < rows) {
+                    const int at = tile_slot(rr, c, NV);
+                    GZT[orow + rr] = reinterpret_cast<const float*>(tz + at)[dd];
+                    Z0T[orow + rr] = reinterpret_cast<const float*>(t0 + at)[dd];
+                }
             }
         }
     }
@@ -500,12 +574,18 @@ static cudaError_t launch_target(bool bwd, const float* z0, float* Y, int n_act,
 template <int KP>
 static cudaError_t launch_rec(bool fwd, const Layout& L, float* ws, int n_act, int K, const float* c, float epsv, cudaStream_t st) {
     const int blocks = (n_act + kRecThreads - 1) / kRecThreads;
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaFuncSetAttribute(rec_fwd_kernel<KP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rec_fwd_smem<KP>());
+        cudaFuncSetAttribute(rec_bwd_kernel<KP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rec_bwd_smem<KP>());
+        attr_done = true;
+    }
     if (fwd)
-        rec_fwd_kernel<KP><<<blocks, kRecThreads, 0, st>>>(ws + L.AT, L.Nc, n_act, K, ws + L.Mt, c, epsv, ws + L.TT, ws + L.Trow,
-                                                          ws + L.part_ld);
+        rec_fwd_kernel<KP><<<blocks, kRecThreads, rec_fwd_smem<KP>(), st>>>(ws + L.AT, L.Nc, n_act, K, ws + L.Mt, c, epsv, ws + L.TT,
+                                                                           ws + L.Trow, ws + L.part_ld);
     else
-        rec_bwd_kernel<KP><<<blocks, kRecThreads, 0, st>>>(ws + L.AT, ws + L.TT, L.Nc, n_act, K, ws + L.M, c, epsv, ws + L.DT,
-                                                          ws + L.part_g);
+        rec_bwd_kernel<KP><<<blocks, kRecThreads, rec_bwd_smem<KP>(), st>>>(ws + L.AT, ws + L.TT, L.Nc, n_act, K, ws + L.M, c, epsv,
+                                                                           ws + L.DT, ws + L.part_g);
     return cudaGetLastError();
 }
 static cudaError_t launch_rec_any(bool fwd, const Layout& L, float* ws, int n_act, int K, const float* c, float epsv, cudaStream_t st) {
