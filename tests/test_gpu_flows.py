@@ -139,11 +139,12 @@ def _gram_case(D, K, N, seed):
 @pytest.mark.parametrize('D,K,N,chunk', [(32, 5, 1500, None), (64, 7, 2000, None), (100, 16, 1100, None),
                                          (256, 64, 1200, None), (64, 32, 3000, 512), (128, 9, 2500, 1024)])
 def test_gram_free_energy_matches_oracle(D, K, N, chunk, monkeypatch):
-    """N >= 1024, float32, D % 4 == 0, K <= 64 take the tensor-core path; ragged N, K that is not a multiple
+    """float32, D % 4 == 0, K <= 64 can take the tensor-core path (forced here); ragged N, K that is not a multiple
     of 4, and (through the chunk knob) several chunks with a short last one.  Same oracle and tolerance as the
     direct wide-D kernel above; the direct kernel is run on the same inputs as a cross-check."""
     from nfcore.objective import SharedFlowObjective
     from oracle import planar_torch as pt
+    monkeypatch.setenv('NF_GRAM', '1')          # small shapes would otherwise be routed to the direct kernel
     if chunk:
         monkeypatch.setenv('NF_GRAM_CHUNK', str(chunk))
     rs, z0, params, mu, ls = _gram_case(D, K, N, 11 * D + K)
@@ -156,15 +157,17 @@ def test_gram_free_energy_matches_oracle(D, K, N, chunk, monkeypatch):
     assert abs(F - F_ref) <= tol * max(1.0, abs(F_ref)), (F, F_ref)
     assert _rel(grad, g_ref) <= tol, _rel(grad, g_ref)
     assert abs(obj.value(params, z0_dev) - F_ref) <= tol * max(1.0, abs(F_ref))
+    monkeypatch.delenv('NF_GRAM')
     monkeypatch.setenv('NF_NO_GRAM', '1')
     F_d, grad_d = obj.value_and_grad(params, z0_dev)
     assert abs(F - F_d) <= tol * max(1.0, abs(F_ref))
     assert _rel(grad, grad_d) <= tol
 
 
-def test_gram_mixture_target_matches_oracle():
+def test_gram_mixture_target_matches_oracle(monkeypatch):
     from nfcore.objective import SharedFlowObjective
     from oracle import planar_torch as pt
+    monkeypatch.setenv('NF_GRAM', '1')
     D, K, N, G = 32, 6, 1300, 3
     rs, z0, params, _, _ = _gram_case(D, K, N, 5)
     pi = np.array([0.3, 0.45]); mmu = 0.3 * rs.randn(G, D); var = 0.8 + 0.4 * rs.rand(G, D)

@@ -597,15 +597,22 @@ static cudaError_t launch_rec_any(bool fwd, const Layout& L, float* ws, int n_ac
 }  // namespace gram
 
 // ---- interface used by nf_elbo_f32.cu --------------------------------------------------------------
+// Shapes the path supports, and among those the ones where it is expected to win.  Cost models fitted on a B200
+// (profiles/r01f_gram_crossover.txt), in microseconds: the direct kernel spends ~0.94 ns per (sample, layer,
+// coordinate), growing with D beyond 128 where its per-warp gradient records fall out of L2; this path has ~100 us
+// of fixed launch cost, ~18 ns per (sample, coordinate) in the products and the target kernel, and ~0.14 ns per
+// (sample, layer^2) in the recurrences.  NF_GRAM=1 forces this path where it is supported, NF_NO_GRAM=1 forbids it.
 bool gram_applicable(long long N, int D, int K, int target_id, int ntp) {
     if (getenv("NF_NO_GRAM")) return false;
-    if (D < 32 || D > 512 || (D % 4) != 0 || K < 1 || K > gram::kMaxK) return false;
-    long long min_n = 1024;
-    if (const char* e = getenv("NF_GRAM_MIN_N")) min_n = atoll(e);
-    if (N < min_n) return false;
-    if (target_id < 0 || target_id == NF_TARGET_GAUSSDIAG) return true;
-    if (target_id == NF_TARGET_MIXDIAG) return ntp / (1 + 2 * D) <= gram::kMaxMix;
-    return false;
+    if (D < 32 || D > 512 || (D % 4) != 0 || K < 1 || K > gram::kMaxK || N < 1) return false;
+    if (target_id == NF_TARGET_MIXDIAG) { if (ntp / (1 + 2 * D) > gram::kMaxMix) return false; }
+    else if (target_id >= 0 && target_id != NF_TARGET_GAUSSDIAG) return false;
+    if (const char* e = getenv("NF_GRAM")) { if (atoi(e) != 0) return true; }
+    if (N < 1024) return false;
+    const double n = (double)N;
+    const double t_direct = n * K * D * 0.94e-3 * (D > 115 ? D / 115.0 : 1.0) * 1e-3;
+    const double t_gram = 100.0 + n * (18e-3 * D + 0.143e-3 * K * K) * 1e-3;
+    return t_gram < t_direct;
 }
 
 size_t gram_workspace_bytes(long long N, int D, int K) { return gram::make_layout(N, D, K).total * sizeof(float); }
