@@ -146,6 +146,9 @@ int nf_session_elbo_host_f64(nf_session* s, const double* eps_host, int64_t N, c
  * D <= 4 or the wide-D targets, script semantics.  Asynchronous on `stream`.
  * ------------------------------------------------------------------------- */
 size_t nf_script_train_workspace_bytes(int K, int D, int elem_size);
+/* The same with room for the matrix-product path of nf_planar_elbo_workspace_bytes_n (N samples per iteration):
+ * nf_script_train_f32 given at least this much evaluates wide-D objectives through it. */
+size_t nf_script_train_workspace_bytes_n(int64_t N, int K, int D, int elem_size);
 int nf_script_train_f32(const float* eps_all, int64_t n_iters, int64_t N, int D, int K, float* params, int target_id,
                         const float* target_params, int n_target_params, float log_eps, int optimizer,
                         float step_size, float h1, float h2, float h3, float* opt_state, float* trace_F,

@@ -2,15 +2,6 @@
 // that do not depend on the element type.
 #include "nf_elbo_impl.cuh"
 
-namespace nf {
-// nf_elbo_gram.cu: the matrix-product formulation for wide latent spaces (float32)
-bool gram_applicable(long long N, int D, int K, int target_id, int ntp);      // target_id < 0: any supported target
-size_t gram_workspace_bytes(long long N, int D, int K);
-int gram_elbo_f32(bool bwd, const float* eps, long long N, int D, int K, const float* w, const float* s, const float* b,
-                  const float* c, int target_id, const float* tp, int ntp, float epsv, float* out_F, float* g_w, float* g_s,
-                  float* g_b, float* g_c, void* workspace, cudaStream_t st);
-}  // namespace nf
-
 extern "C" {
 
 size_t nf_planar_elbo_workspace_bytes(int K, int D, int elem_size) {
@@ -76,6 +67,13 @@ size_t nf_script_train_workspace_bytes(int K, int D, int elem_size) {
     const size_t nlc = (size_t)2 * K * D + 2 * K, nres = 3 + nlc;
     const size_t head = ((nlc + nres) * (size_t)elem_size + 255) & ~(size_t)255;
     return head + nf_planar_elbo_workspace_bytes(K, D, elem_size);
+}
+
+size_t nf_script_train_workspace_bytes_n(int64_t N, int K, int D, int elem_size) {
+    if (K < 1 || D < 1 || elem_size < 1) return 0;
+    const size_t nlc = (size_t)2 * K * D + 2 * K, nres = 3 + nlc;
+    const size_t head = ((nlc + nres) * (size_t)elem_size + 255) & ~(size_t)255;
+    return head + nf_planar_elbo_workspace_bytes_n(N, K, D, elem_size);
 }
 
 }  // extern "C"

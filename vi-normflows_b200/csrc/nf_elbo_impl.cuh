@@ -973,6 +973,13 @@ script_step_kernel(T* __restrict__ params /*[2KD+K]*/, T* __restrict__ lc /*w|s|
     }
 }
 
+// nf_elbo_gram.cu: the matrix-product formulation for wide latent spaces (float32 only)
+bool gram_applicable(long long N, int D, int K, int target_id, int ntp);      // target_id < 0: any supported target
+size_t gram_workspace_bytes(long long N, int D, int K);
+int gram_elbo_f32(bool bwd, const float* eps, long long N, int D, int K, const float* w, const float* s, const float* b,
+                  const float* c, int target_id, const float* tp, int ntp, float epsv, float* out_F, float* g_w, float* g_s,
+                  float* g_b, float* g_c, void* workspace, cudaStream_t st);
+
 template <typename T>
 static int script_train(const T* eps_all, int64_t n_iters, int64_t N, int D, int K, T* params, int target_id,
                         const T* tparams, int ntp, T epsv, int optimizer, T step, T h1, T h2, T h3, T* state,
@@ -990,6 +997,10 @@ static int script_train(const T* eps_all, int64_t n_iters, int64_t N, int D, int
     const T *w = lc, *s = lc + K * D, *b = lc + 2 * K * D, *c = lc + 2 * K * D + K;
     int rc = elbo_validate<T>(eps_all, N, D, K, w, s, b, c, target_id, tparams, ntp);
     if (rc != NF_OK) return rc;
+    // wide D, float32, and a workspace sized by nf_script_train_workspace_bytes_n: matrix-product path per iteration
+    bool use_gram = false;
+    if constexpr (sizeof(T) == 4)
+        use_gram = gram_applicable(N, D, K, target_id, ntp) && workspace_bytes >= head + gram_workspace_bytes(N, D, K);
     // optimiser state: rmsprop starts its running average at ones (autograd 1.3), the others at zero
     NF_CUDA_OK(cudaMemsetAsync(state, 0, 2 * P * sizeof(T), st));
     if (optimizer == OPT_RMSPROP) {
@@ -1003,6 +1014,13 @@ static int script_train(const T* eps_all, int64_t n_iters, int64_t N, int D, int
         NF_CUDA_OK(launch_pdl(script_step_kernel<T>, dim3(1), dim3(256), 0, st, params, lc, (const T*)res, state, K, D,
                               (long long)N, it > 0 ? 1 : 0, (long long)it, optimizer, step, h1, h2, h3, trace_F, 0));
         if (it == n_iters) break;
+        if (use_gram) {
+            if constexpr (sizeof(T) == 4)
+                rc = gram_elbo_f32(true, eps_all + (size_t)it * N * D, N, D, K, w, s, b, c, target_id, tparams, ntp, epsv, res, res + 3,
+                                   res + 3 + K * D, res + 3 + 2 * K * D, res + 3 + 2 * K * D + K, rows, st);
+            if (rc != NF_OK) return rc;
+            continue;
+        }
         int nb = 0;
         rc = elbo_main<T>(true, eps_all + (size_t)it * N * D, N, D, K, w, s, b, c, target_id, tparams, ntp, epsv, rows, &nb, st);
         if (rc != NF_OK) return rc;

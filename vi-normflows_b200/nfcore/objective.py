@@ -296,7 +296,7 @@ class SharedFlowObjective:
         p_dev = torch.as_tensor(np.asarray(params, dtype=np.float64).astype(self.np_dtype)).to(dev)
         state = torch.empty(2 * P, dtype=self.dtype, device=dev)
         trace = torch.empty(max(n_iters, 1), dtype=self.dtype, device=dev)
-        nws = lib.nf_script_train_workspace_bytes(K, D, self.np_dtype.itemsize)
+        nws = lib.nf_script_train_workspace_bytes_n(N, K, D, self.np_dtype.itemsize)
         ws = torch.empty(nws, dtype=torch.uint8, device=dev)
         fn = lib.nf_script_train_f32 if self.np_dtype == np.float32 else lib.nf_script_train_f64
         creal = ctypes.c_float if self.np_dtype == np.float32 else ctypes.c_double
