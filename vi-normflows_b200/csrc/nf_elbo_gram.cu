@@ -200,7 +200,7 @@ rec_fwd_kernel(const float* __restrict__ AT, long long ldn, int n_act, int K, co
         a[j] = t;
         const float hp = fmaf(-t, t, 1.f);
         prod *= se[j] + fabsf(fmaf(hp, sc[j], 1.f));
-        if ((j & 3) == 3) { ld += M_::logp(prod); prod = 1.f; }
+        if ((j & 3) == 3) { ld += M_::flog(prod); prod = 1.f; }      // MUFU.LG2, as in the direct kernels
         dst[(size_t)j * ldn] = t;
 #pragma unroll
         for (int k4 = (j + 1) / 4; k4 < KP / 4; ++k4) {

@@ -31,7 +31,8 @@ constexpr int A_BYTES = BM * BK * 4, B_BYTES = BN * BK * 4;
 constexpr int STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;      // hi + lo of both operands
 constexpr int THREADS = 256;
 constexpr int SPLIT_THREADS = 192;                  // warps 2-7 split; warps 4-7 also run the epilogue
-constexpr int TMEM_COLS = 64;
+constexpr int ACC_COLS = 64;                        // accumulator; with the A operand in tensor memory each stage adds 64 (hi | lo)
+constexpr int STAGE_BYTES_TS = A_BYTES + 2 * B_BYTES;   // A raw | B hi | B lo
 
 enum { EPI_ACT_NONE = 0, EPI_ACT_RELU = 1, EPI_ACT_SIGMOID = 2 };
 enum { EPI_MASK_NONE = 0, EPI_MASK_RELU = 1, EPI_MASK_SIGMOID = 2 };   // multiply by act'(saved output)
@@ -77,6 +78,19 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint6
         "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc),
         "r"((uint32_t)accumulate) : "memory");
 }
+// A operand from tensor memory (128 lanes = rows, 8 columns = the k-slice), B from shared memory
+__device__ __forceinline__ void umma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, bool accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc),
+        "r"((uint32_t)accumulate) : "memory");
+}
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+        "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]), "r"(r[10]),
+        "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]) : "memory");
+}
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
@@ -94,12 +108,18 @@ struct Params {
     long long split_stride;              // and writes its partial tile to C + z*split_stride
 };
 
+template <bool ATMEM>
 __global__ void __launch_bounds__(THREADS)
 gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, Params p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     __shared__ uint64_t full_bar[MAX_STAGES], split_bar[MAX_STAGES], empty_bar[MAX_STAGES], acc_bar;
     const int STAGES = p.stages;
+    // ATMEM: the hi/lo halves of A are written to tensor memory by the four warps that own its lanes, and the
+    // MMAs read A from there -- A then crosses shared memory twice (TMA in, split read) instead of six times.
+    constexpr int STAGE_BYTES_ = ATMEM ? STAGE_BYTES_TS : STAGE_BYTES;
+    constexpr int B_OFF = ATMEM ? A_BYTES : 2 * A_BYTES;
+    const uint32_t tmem_cols = ATMEM ? (STAGES == 1 ? 128u : 256u) : 64u;
     __shared__ uint32_t tmem_base;
     __shared__ float sbias[BN];
 
@@ -126,7 +146,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
         sbias[i] = (p.bias && n0 + i < p.N) ? p.bias[n0 + i] : 0.f;
     }
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base)), "r"(TMEM_COLS) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base)), "r"(tmem_cols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -141,10 +161,10 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
             for (int kb = 0; kb < nkb; ++kb) {
                 const int s = kb % STAGES, it = kb / STAGES;
                 if (it > 0) mbar_wait(&empty_bar[s], (it - 1) & 1);
-                uint8_t* st = smem + (size_t)s * STAGE_BYTES;
+                uint8_t* st = smem + (size_t)s * STAGE_BYTES_;
                 mbar_expect_tx(&full_bar[s], A_BYTES + B_BYTES);
                 tma_load_2d(st, &map_a, (kb0 + kb) * BK, m0, &full_bar[s]);                  // A hi slot (raw data)
-                tma_load_2d(st + 2 * A_BYTES, &map_b, (kb0 + kb) * BK, n0, &full_bar[s]);    // B hi slot (raw data)
+                tma_load_2d(st + B_OFF, &map_b, (kb0 + kb) * BK, n0, &full_bar[s]);          // B hi slot (raw data)
             }
         }
     } else if (warp == 1) {
@@ -157,16 +177,23 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
             mbar_wait(&split_bar[s], it & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             if (lane == 0) {
-                const uint32_t a_hi = smem_u32(smem + (size_t)s * STAGE_BYTES);
+                const uint32_t a_hi = smem_u32(smem + (size_t)s * STAGE_BYTES_);
                 const uint32_t a_lo = a_hi + A_BYTES;
-                const uint32_t b_hi = a_hi + 2 * A_BYTES;
+                const uint32_t b_hi = a_hi + B_OFF;
                 const uint32_t b_lo = b_hi + B_BYTES;
+                const uint32_t ta_hi = tmem_d + ACC_COLS + (uint32_t)s * 64u, ta_lo = ta_hi + 32u;
 #pragma unroll
                 for (int k = 0; k < BK / 8; ++k) {
                     const uint32_t off = k * 32;       // 8 tf32 = 32 bytes along K inside the swizzle row
-                    umma_tf32(tmem_d, umma_desc(a_hi + off), umma_desc(b_hi + off), idesc, (kb | k) != 0);
-                    umma_tf32(tmem_d, umma_desc(a_lo + off), umma_desc(b_hi + off), idesc, true);
-                    umma_tf32(tmem_d, umma_desc(a_hi + off), umma_desc(b_lo + off), idesc, true);
+                    if (ATMEM) {
+                        umma_tf32_ts(tmem_d, ta_hi + 8u * k, umma_desc(b_hi + off), idesc, (kb | k) != 0);
+                        umma_tf32_ts(tmem_d, ta_lo + 8u * k, umma_desc(b_hi + off), idesc, true);
+                        umma_tf32_ts(tmem_d, ta_hi + 8u * k, umma_desc(b_lo + off), idesc, true);
+                    } else {
+                        umma_tf32(tmem_d, umma_desc(a_hi + off), umma_desc(b_hi + off), idesc, (kb | k) != 0);
+                        umma_tf32(tmem_d, umma_desc(a_lo + off), umma_desc(b_hi + off), idesc, true);
+                        umma_tf32(tmem_d, umma_desc(a_hi + off), umma_desc(b_lo + off), idesc, true);
+                    }
                 }
                 if (dbg && kb == 0) p.dbg[4] = clock64();
                 umma_commit(&empty_bar[s]);                 // stage reusable once these MMAs have read it
@@ -180,7 +207,49 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
         for (int kb = 0; kb < nkb; ++kb) {
             const int s = kb % STAGES, it = kb / STAGES;
             mbar_wait(&full_bar[s], it & 1);
-            uint8_t* st = smem + (size_t)s * STAGE_BYTES;
+            uint8_t* st = smem + (size_t)s * STAGE_BYTES_;
+            if (ATMEM) {
+                if (warp < 4) {
+                    // warps 2, 3: B in shared memory, hi in place, lo behind it
+#pragma unroll 4
+                    for (int i = t; i < B_BYTES / 16; i += 64) {
+                        uint8_t* hi = st + B_OFF + (size_t)i * 16;
+                        float4 v = *reinterpret_cast<float4*>(hi);
+                        float4 h, l;
+                        h.x = __uint_as_float(__float_as_uint(v.x) & 0xFFFFE000u); l.x = v.x - h.x;
+                        h.y = __uint_as_float(__float_as_uint(v.y) & 0xFFFFE000u); l.y = v.y - h.y;
+                        h.z = __uint_as_float(__float_as_uint(v.z) & 0xFFFFE000u); l.z = v.z - h.z;
+                        h.w = __uint_as_float(__float_as_uint(v.w) & 0xFFFFE000u); l.w = v.w - h.w;
+                        *reinterpret_cast<float4*>(hi) = h;
+                        *reinterpret_cast<float4*>(hi + B_BYTES) = l;
+                    }
+                } else {
+                    // warps 4-7: row (32 q + lane) of A, 32 k-values, from the swizzled tile into tensor memory:
+                    // columns [0, 32) of the stage hold hi, [32, 64) lo.  16-byte chunk j of row r sits at chunk j ^ (r % 8).
+                    const int q = warp - 4, row = 32 * q + lane;
+                    const uint8_t* rp = st + (size_t)row * 128;
+                    const uint32_t ta = tmem_base + ((uint32_t)(32 * q) << 16) + ACC_COLS + (uint32_t)s * 64u;
+#pragma unroll
+                    for (int h2 = 0; h2 < 2; ++h2) {
+                        uint32_t hi[16], lo[16];
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const float4 v = *reinterpret_cast<const float4*>(rp + 16 * ((4 * h2 + j) ^ (row & 7)));
+                            const float x[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                const uint32_t hb = __float_as_uint(x[e]) & 0xFFFFE000u;
+                                hi[4 * j + e] = hb;
+                                lo[4 * j + e] = __float_as_uint(x[e] - __uint_as_float(hb));
+                            }
+                        }
+                        tmem_st16(ta + 16u * h2, hi);
+                        tmem_st16(ta + 32u + 16u * h2, lo);
+                    }
+                    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+                    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                }
+            } else {
             // A: hi in place at [0, A_BYTES), lo at [A_BYTES, 2 A_BYTES); B likewise after 2 A_BYTES
 #pragma unroll 4
             for (int i = t; i < (A_BYTES + B_BYTES) / 16; i += SPLIT_THREADS) {
@@ -195,6 +264,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
                 h.w = __uint_as_float(__float_as_uint(v.w) & 0xFFFFE000u); l.w = v.w - h.w;
                 *reinterpret_cast<float4*>(hi) = h;
                 *reinterpret_cast<float4*>(lo) = l;
+            }
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy writes -> visible to UMMA
             mbar_arrive(&split_bar[s]);
@@ -295,7 +365,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
     __syncthreads();
     if (dbg && threadIdx.x == 0) p.dbg[7] = clock64();
     if (warp == 1)
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(TMEM_COLS) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(tmem_cols) : "memory");
 }
 
 static PFN_cuTensorMapEncodeTiled get_encoder() {
@@ -380,21 +450,29 @@ int tc_gemm_f32(const float* A, long long lda, const float* B, long long ldb, in
     }
     const bool via_ws = splits > 1 || accumulate;
     const int kbps = (nkb_all + splits - 1) / splits;
-    // Ring depth: short contractions are dominated by the per-tile prologue and epilogue, so they get a
-    // one-stage ring (49 KB) and four CTAs per SM that cover for one another; longer ones two stages and
-    // two CTAs per SM.  NF_GEMM_STAGES=1..3 overrides (tuning knob).
-    int stages = kbps <= 2 ? 1 : 2;
+    // A through tensor memory (default) or split in shared memory (NF_GEMM_ATMEM=0, the first version of this kernel).
+    // Ring depth: short contractions are dominated by the per-tile prologue and epilogue, so they get a one-stage
+    // ring and four CTAs per SM that cover for one another; longer ones a deeper ring and two CTAs per SM
+    // (tensor-memory path: 3 stages, 256 columns per CTA; shared-memory path: 2 stages).  NF_GEMM_STAGES=1..3 overrides.
+    static const bool atmem = []() { const char* e = getenv("NF_GEMM_ATMEM"); return !(e && atoi(e) == 0); }();
+    int stages = kbps <= 2 ? 1 : (atmem ? 3 : 2);
     if (const char* e = getenv("NF_GEMM_STAGES")) { const int v = atoi(e); if (v >= 1 && v <= tc::MAX_STAGES) stages = v; }
     tc::Params p{M, N, K, via_ws ? split_ws : C, ldc, CT, ldct, bias, act, mask_src, ldm, mask, dbg_buf, stages, kbps, (long long)M * N};
-    const size_t smem = (size_t)stages * tc::STAGE_BYTES + 1024;
+    constexpr size_t kSlab = 4 * 32 * 65 * sizeof(float);       // the epilogue parks the accumulator in the ring's memory
+    size_t ring = (size_t)stages * (atmem ? tc::STAGE_BYTES_TS : tc::STAGE_BYTES);
+    if (ring < kSlab) ring = kSlab;
+    const size_t smem = ring + 1024;
     static bool attr_done = false;
     if (!attr_done) {
-        NF_CUDA_OK(cudaFuncSetAttribute(tc::gemm_tf32x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        NF_CUDA_OK(cudaFuncSetAttribute(tc::gemm_tf32x3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)((size_t)tc::MAX_STAGES * tc::STAGE_BYTES + 1024)));
+        NF_CUDA_OK(cudaFuncSetAttribute(tc::gemm_tf32x3_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)((size_t)tc::MAX_STAGES * tc::STAGE_BYTES_TS + 1024)));
         attr_done = true;
     }
     dim3 grid((N + tc::BN - 1) / tc::BN, (M + tc::BM - 1) / tc::BM, splits);
-    tc::gemm_tf32x3_kernel<<<grid, tc::THREADS, smem, st>>>(ma, mb, p);
+    if (atmem) tc::gemm_tf32x3_kernel<true><<<grid, tc::THREADS, smem, st>>>(ma, mb, p);
+    else tc::gemm_tf32x3_kernel<false><<<grid, tc::THREADS, smem, st>>>(ma, mb, p);
     NF_CUDA_OK(cudaGetLastError());
     if (via_ws) {
         const long long count = (long long)M * N;
