@@ -371,7 +371,7 @@ target_kernel(const float* __restrict__ z0, float* __restrict__ Y, int n_act, in
     float g_const = 0.f;
     if (TGT == NF_TARGET_GAUSSDIAG) {
         float ls = 0.f;
-        for (int d = tid; d < D; d += kTgtThreads) { s_mu[d] = tparams[d]; s_iv[d] = M_::exp(-tparams[D + d]); }
+        for (int d = tid; d < D; d += kTgtThreads) { s_mu[d] = tparams[d]; s_iv[d] = M_::fexp(-tparams[D + d]); }
         for (int d = lane; d < D; d += 32) ls += tparams[D + d];
         g_const = -0.5f * (D * LOG2PI + warp_sum(ls));
     }
@@ -380,13 +380,19 @@ target_kernel(const float* __restrict__ z0, float* __restrict__ Y, int n_act, in
     const float4* y4 = reinterpret_cast<const float4*>(Y + (size_t)n0 * D);
     const int nvec = rows * NV;
     float zz_part = 0.f;        // only used by the forward-only instantiation
-    for (int v = tid; v < nvec; v += kTgtThreads) {
-        const float4 a = z4[v], b = y4[v];
-        const int rr = v / NV, c = v - rr * NV;
-        const int at = tile_slot(rr, c, NV);
-        tz[at] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
-        if (BWD) t0[at] = a;
-        else zz_part = fmaf(a.x, a.x, fmaf(a.y, a.y, fmaf(a.z, a.z, fmaf(a.w, a.w, zz_part))));
+    // (row, column) of float4 number v = tid + 256 i, advanced without divisions inside the loop
+    const int step_r = kTgtThreads / NV, step_c = kTgtThreads - step_r * NV;
+    {
+        int rr = tid / NV, c = tid - rr * NV;
+        for (int v = tid; v < nvec; v += kTgtThreads) {
+            const float4 a = z4[v], b = y4[v];
+            const int at = tile_slot(rr, c, NV);
+            tz[at] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+            if (BWD) t0[at] = a;
+            else zz_part = fmaf(a.x, a.x, fmaf(a.y, a.y, fmaf(a.z, a.z, fmaf(a.w, a.w, zz_part))));
+            rr += step_r; c += step_c;
+            if (c >= NV) { c -= NV; ++rr; }
+        }
     }
     __syncthreads();
     // ---- per row: eight lanes per row, rows 4*warp .. 4*warp+3 ----
@@ -412,9 +418,9 @@ target_kernel(const float* __restrict__ z0, float* __restrict__ Y, int n_act, in
             q = fmaf(dx * iv.x, dx, fmaf(dy * iv.y, dy, fmaf(dz * iv.z, dz, fmaf(dw * iv.w, dw, q))));
         }
         q = sum8(q);
-        const float dens = M_::exp(g_const - 0.5f * q);
+        const float dens = M_::fexp(g_const - 0.5f * q);       // MUFU-based exp / log: once per sample, rel. error ~1e-6
         const float den = epsv + dens;
-        lp = live ? M_::logp(den) : 0.f;
+        lp = live ? M_::flog(den) : 0.f;
         if (BWD) {
             const float rho = M_::div(dens, den);
             if (live) for (int c = l; c < NV; c += 8) {
@@ -484,23 +490,34 @@ target_kernel(const float* __restrict__ z0, float* __restrict__ Y, int n_act, in
     if (BWD) {
         // row form of gz_K, in place of Y
         float4* o4 = reinterpret_cast<float4*>(Y + (size_t)n0 * D);
-        for (int v = tid; v < nvec; v += kTgtThreads) {
-            const int rr = v / NV, c = v - rr * NV;
-            o4[v] = tz[tile_slot(rr, c, NV)];
+        {
+            int rr = tid / NV, c = tid - rr * NV;
+            for (int v = tid; v < nvec; v += kTgtThreads) {
+                o4[v] = tz[tile_slot(rr, c, NV)];
+                rr += step_r; c += step_c;
+                if (c >= NV) { c -= NV; ++rr; }
+            }
         }
         // transposed copies: per instruction 8 samples (lane % 8) x 4 coordinates (lane / 8) of one float4 column
         const int s8 = lane & 7, dd = lane >> 3;
+        float* gcol = GZT + (size_t)(4 * warp + dd) * ldn + n0 + s8;       // column c = warp, coordinate 4c + dd, sample n0 + s8
+        float* zcol = Z0T + (size_t)(4 * warp + dd) * ldn + n0 + s8;
+        const size_t cstride = (size_t)4 * (kTgtThreads / 32) * ldn;
+        const float* tzf = reinterpret_cast<const float*>(tz) + dd;
+        const float* t0f = reinterpret_cast<const float*>(t0) + dd;
         for (int c = warp; c < NV; c += kTgtThreads / 32) {
-            const size_t orow = (size_t)(4 * c + dd) * ldn + n0;
+            // rows s8, s8 + 8, ... share r % 8 = s8, hence one slot offset inside the row
+            int x = c + s8;
+            x = x >= NV ? x - NV : x;
+            const int at0 = 4 * (s8 * NV + x);
 #pragma unroll
             for (int j = 0; j < kTgtRows / 8; ++j) {
-                const int rr = 8 * j + s8;
-                if (rr < rows) {
-                    const int at = tile_slot(rr, c, NV);
-                    GZT[orow + rr] = reinterpret_cast<const float*>(tz + at)[dd];
-                    Z0T[orow + rr] = reinterpret_cast<const float*>(t0 + at)[dd];
+                if (8 * j + s8 < rows) {
+                    gcol[8 * j] = tzf[at0 + 32 * j * NV];
+                    zcol[8 * j] = t0f[at0 + 32 * j * NV];
                 }
             }
+            gcol += cstride; zcol += cstride;
         }
     }
 }
