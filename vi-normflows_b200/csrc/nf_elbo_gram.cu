@@ -30,6 +30,10 @@ int tc_gemm_f32(const float* A, long long lda, const float* B, long long ldb, in
                 float* CT, long long ldct, const float* bias, int act, const float* mask_src, long long ldm, int mask,
                 cudaStream_t st, int splits = 1, float* split_ws = nullptr, bool accumulate = false);
 
+int tc_gemm_stacked_f32(const float* A, long long lda, int M1, const float* A2, long long lda2, int M2, const float* B, long long ldb,
+                        int N, int K, float* C, long long ldc, float* CT, long long ldct, const float* bias, int act,
+                        const float* mask_src, long long ldm, int mask, cudaStream_t st, int splits, float* split_ws, bool accumulate);
+
 namespace gram {
 
 constexpr int kRecThreads = 128;
@@ -61,8 +65,9 @@ static inline int grad_splits(long long nc, int D) {
 struct Layout {
     int KP; long long Nc; int splits;
     size_t acc, M, Mt, ST, G4, G56, part_ld, part_g, part_t, split4, split56;   // offsets in floats
-    size_t AT, DT, TT, Z0T, Trow, Y, GZT, total;
+    size_t AT, DT, TT, Trow, Y, total;
 };
+constexpr int kG5Row = 128;      // row of the stacked product 5/6 result where the z_0^T Delta block starts (tile-aligned)
 static Layout make_layout(long long N, int D, int K) {
     Layout L{};
     L.KP = pad_k(K);
@@ -75,20 +80,18 @@ static Layout make_layout(long long N, int D, int K) {
     L.M = take(KP * KP);
     L.Mt = take(KP * KP);
     L.ST = take((size_t)D * KP);
-    L.G4 = take((size_t)D * K);                 // gz_K^T T            [D][K]
-    L.G56 = take((KP + D) * K);                 // [T^T ; z_0^T] Delta [KP + D][K]
+    L.G4 = take((size_t)D * K);                 // gz_K^T T             [D][K]
+    L.G56 = take((size_t)(kG5Row + D) * K);     // [T^T ; 0 ; z_0^T] Delta: rows [0, KP) and [128, 128 + D)
     L.part_ld = take(Nc / kRecThreads);
     L.part_g = take(Nc / kRecThreads * 2 * KP);
     L.part_t = take(2 * (Nc / kTgtRows));
     L.split4 = take((size_t)L.splits * D * K);
-    L.split56 = take((size_t)L.splits * (KP + D) * K);
+    L.split56 = take((size_t)L.splits * (kG5Row + D) * K);
     L.AT = take(KP * Nc);                       // A0^T, later P^T (rows K.. stay zero)
     L.DT = take(KP * Nc);                       // Delta^T
-    L.TT = take((KP + D) * Nc);                 // T^T followed by z_0^T: one operand of products 5 and 6
-    L.Z0T = L.TT + KP * Nc;
+    L.TT = take(KP * Nc);                       // T^T
     L.Trow = take(Nc * KP);                     // T, row per sample
     L.Y = take(Nc * D);                         // T S, later gz_K
-    L.GZT = take((size_t)D * Nc);
     L.total = o;
     return L;
 }
@@ -326,14 +329,10 @@ rec_bwd_kernel(const float* __restrict__ PT, const float* __restrict__ TT, long 
 }
 
 // ------------------------------------------------------------------------------------------------
-// Target kernel: z_K = z_0 + Y, log p(z_K), log q_0(z_0) and gz_K = dF/dz_K = -d log p / dz_K.
-// A block owns 32 consecutive samples, i.e. one contiguous run of 32 D floats of z_0 and of Y: it is read
-// with float4 loads into two shared-memory tiles of float4; eight lanes then share a row (four rows per
-// warp at a time, three shuffles per row sum).  gz_K replaces Y (row form, operand of product 3); gz_K^T
-// and z_0^T (operands of products 4 and 5) are written from the tiles.
-// Tile layout: float4 number c of row r sits at slot r * (D/4) + (c + r % 8) mod (D/4).  With D % 32 == 0
-// every access pattern below is free of bank conflicts: consecutive float4 of a row (load, row phase, row
-// store), and in the transposed stores 8 samples x 4 coordinates per instruction (32-byte runs of samples).
+// Target kernel: z_K = z_0 + Y, log p(z_K), log q_0(z_0) and gz_K = dF/dz_K = -d log p / dz_K, which replaces Y in
+// place (rows: operand of product 3 as it is, and -- read sample-major by the product kernel -- of product 4).
+// Eight lanes share a sample (four samples per warp, 32 per block); a lane keeps its float4 slices of z_K in
+// registers between the row sums and the gradient, so every byte is read once and written once, in 128-byte runs.
 // Same density formulas as elbo_wide_kernel (distributions.py:10-54).
 __device__ __forceinline__ float sum8(float v) {
     v += __shfl_xor_sync(0xffffffffu, v, 1);
@@ -341,81 +340,66 @@ __device__ __forceinline__ float sum8(float v) {
     v += __shfl_xor_sync(0xffffffffu, v, 4);
     return v;
 }
-__device__ __forceinline__ int tile_slot(int r, int c, int NV) {
-    int x = c + (r & 7);
-    x = x >= NV ? x - NV : x;
-    return r * NV + x;
-}
 __device__ __forceinline__ float f4_get(const float4& v, int i) { return i == 0 ? v.x : (i == 1 ? v.y : (i == 2 ? v.z : v.w)); }
 
-static inline size_t tgt_smem_bytes(int D, bool bwd) { return ((size_t)(bwd ? 2 : 1) * kTgtRows * D + 2 * (size_t)D) * sizeof(float); }
 
-template <int TGT, bool BWD>
+static inline size_t tgt_smem_bytes(int D) { return 2 * (size_t)D * sizeof(float); }
+
+template <int TGT, bool BWD, int kTgtMaxVec /* float4 slices per lane: D <= 32 kTgtMaxVec */>
 __global__ void __launch_bounds__(kTgtThreads)
-target_kernel(const float* __restrict__ z0, float* __restrict__ Y, int n_act, int D, long long ldn,
-              const float* __restrict__ tparams, int ntp, float epsv, float* __restrict__ GZT, float* __restrict__ Z0T,
-              float* __restrict__ part /* [gridDim][2] : sum log q_0, sum log p */) {
+target_kernel(const float* __restrict__ z0, float* __restrict__ Y, int n_act, int D, const float* __restrict__ tparams, int ntp,
+              float epsv, float* __restrict__ part /* [gridDim][2] : sum log q_0, sum log p */) {
     using M_ = Mth<float>;
     extern __shared__ __align__(16) float smem[];
     __shared__ float red[kTgtThreads / 32][2];
     __shared__ float mixe[kTgtRows][kMaxMix];
     const int NV = D / 4;
-    float4* tz = reinterpret_cast<float4*>(smem);                    // z_K, then gz_K
-    float4* t0 = BWD ? tz + kTgtRows * NV : tz;                      // z_0 (reverse pass only)
-    float* s_mu = smem + (BWD ? 2 : 1) * kTgtRows * D;
-    float* s_iv = s_mu + D;
+    float* s_mu = smem;
+    float* s_iv = smem + D;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const float LOG2PI = 1.8378770664093453f;
-    const int n0 = blockIdx.x * kTgtRows;
-    const int rows = min(kTgtRows, n_act - n0);
     float g_const = 0.f;
     if (TGT == NF_TARGET_GAUSSDIAG) {
         float ls = 0.f;
         for (int d = tid; d < D; d += kTgtThreads) { s_mu[d] = tparams[d]; s_iv[d] = M_::fexp(-tparams[D + d]); }
         for (int d = lane; d < D; d += 32) ls += tparams[D + d];
         g_const = -0.5f * (D * LOG2PI + warp_sum(ls));
+        __syncthreads();
     }
-    // ---- load: one flat run of rows * D floats ----
-    const float4* z4 = reinterpret_cast<const float4*>(z0 + (size_t)n0 * D);
-    const float4* y4 = reinterpret_cast<const float4*>(Y + (size_t)n0 * D);
-    const int nvec = rows * NV;
-    float zz_part = 0.f;        // only used by the forward-only instantiation
-    // (row, column) of float4 number v = tid + 256 i, advanced without divisions inside the loop
-    const int step_r = kTgtThreads / NV, step_c = kTgtThreads - step_r * NV;
-    {
-        int rr = tid / NV, c = tid - rr * NV;
-        for (int v = tid; v < nvec; v += kTgtThreads) {
-            const float4 a = z4[v], b = y4[v];
-            const int at = tile_slot(rr, c, NV);
-            tz[at] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
-            if (BWD) t0[at] = a;
-            else zz_part = fmaf(a.x, a.x, fmaf(a.y, a.y, fmaf(a.z, a.z, fmaf(a.w, a.w, zz_part))));
-            rr += step_r; c += step_c;
-            if (c >= NV) { c -= NV; ++rr; }
-        }
-    }
-    __syncthreads();
-    // ---- per row: eight lanes per row, rows 4*warp .. 4*warp+3 ----
-    const int r = 4 * warp + (lane >> 3), l = lane & 7;
-    const bool live = r < rows;
-    float lq = 0.f, lp = 0.f;
-    if (BWD) {
-        float zz = 0.f;
-        if (live) for (int c = l; c < NV; c += 8) {
-            const float4 a = t0[tile_slot(r, c, NV)];
+    const int rl = 4 * warp + (lane >> 3), l = lane & 7;       // row inside the block, lane inside the row
+    const int n = blockIdx.x * kTgtRows + rl;
+    const bool live = n < n_act;
+    const float4* z4 = reinterpret_cast<const float4*>(z0 + (size_t)(live ? n : 0) * D);
+    float4* y4 = reinterpret_cast<float4*>(Y + (size_t)(live ? n : 0) * D);
+    float4 z[kTgtMaxVec];
+    float zz = 0.f;
+#pragma unroll
+    for (int i = 0; i < kTgtMaxVec; ++i) {
+        const int c = l + 8 * i;
+        if (c < NV && live) {
+            const float4 a = z4[c], b = y4[c];
             zz = fmaf(a.x, a.x, fmaf(a.y, a.y, fmaf(a.z, a.z, fmaf(a.w, a.w, zz))));
+            z[i] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+        } else {
+            z[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
-        zz = sum8(zz);
-        lq = live ? -0.5f * (D * LOG2PI + zz) : 0.f;
     }
+    zz = sum8(zz);
+    const float lq = live ? -0.5f * (D * LOG2PI + zz) : 0.f;
+    float lp = 0.f;
     if (TGT == NF_TARGET_GAUSSDIAG) {
         const float4* mu4 = reinterpret_cast<const float4*>(s_mu);
         const float4* iv4 = reinterpret_cast<const float4*>(s_iv);
         float q = 0.f;
-        if (live) for (int c = l; c < NV; c += 8) {
-            const float4 z = tz[tile_slot(r, c, NV)], m = mu4[c], iv = iv4[c];
-            const float dx = z.x - m.x, dy = z.y - m.y, dz = z.z - m.z, dw = z.w - m.w;
-            q = fmaf(dx * iv.x, dx, fmaf(dy * iv.y, dy, fmaf(dz * iv.z, dz, fmaf(dw * iv.w, dw, q))));
+#pragma unroll
+        for (int i = 0; i < kTgtMaxVec; ++i) {
+            const int c = l + 8 * i;
+            if (c < NV) {
+                const float4 m = mu4[c], iv = iv4[c];
+                const float dx = z[i].x - m.x, dy = z[i].y - m.y, dz = z[i].z - m.z, dw = z[i].w - m.w;
+                q = fmaf(dx * iv.x, dx, fmaf(dy * iv.y, dy, fmaf(dz * iv.z, dz, fmaf(dw * iv.w, dw, q))));
+                z[i] = make_float4(dx * iv.x, dy * iv.y, dz * iv.z, dw * iv.w);      // (z - mu) / var, scaled by rho below
+            }
         }
         q = sum8(q);
         const float dens = M_::fexp(g_const - 0.5f * q);       // MUFU-based exp / log: once per sample, rel. error ~1e-6
@@ -423,10 +407,10 @@ target_kernel(const float* __restrict__ z0, float* __restrict__ Y, int n_act, in
         lp = live ? M_::flog(den) : 0.f;
         if (BWD) {
             const float rho = M_::div(dens, den);
-            if (live) for (int c = l; c < NV; c += 8) {
-                const int at = tile_slot(r, c, NV);
-                const float4 z = tz[at], m = mu4[c], iv = iv4[c];
-                tz[at] = make_float4(rho * (z.x - m.x) * iv.x, rho * (z.y - m.y) * iv.y, rho * (z.z - m.z) * iv.z, rho * (z.w - m.w) * iv.w);
+#pragma unroll
+            for (int i = 0; i < kTgtMaxVec; ++i) {
+                const int c = l + 8 * i;
+                if (c < NV && live) y4[c] = make_float4(rho * z[i].x, rho * z[i].y, rho * z[i].z, rho * z[i].w);
             }
         }
     } else {   // MIXDIAG: [pi (G) | mu (G*D) | var (G*D)]
@@ -436,46 +420,50 @@ target_kernel(const float* __restrict__ z0, float* __restrict__ Y, int n_act, in
             const float* mu = tparams + G + (size_t)gc * D;
             const float* var = tparams + G + (size_t)G * D + (size_t)gc * D;
             float q = 0.f, lsum = 0.f;
-            if (live) for (int c = l; c < NV; c += 8) {
-                const float4 z = tz[tile_slot(r, c, NV)];
 #pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    const int d = 4 * c + e;
-                    const float df = f4_get(z, e) - mu[d];
-                    q = fmaf(df, M_::div(df, var[d]), q);
-                    lsum += M_::logp(var[d]);
+            for (int i = 0; i < kTgtMaxVec; ++i) {
+                const int c = l + 8 * i;
+                if (c < NV) {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const int d = 4 * c + e;
+                        const float df = f4_get(z[i], e) - mu[d];
+                        q = fmaf(df, M_::div(df, var[d]), q);
+                        lsum += M_::logp(var[d]);
+                    }
                 }
             }
             q = sum8(q);
             lsum = sum8(lsum);
             const float e = tparams[gc] * M_::exp(-0.5f * (D * LOG2PI + lsum + q));
             dens += e;
-            if (l == 0) mixe[r][gc] = e;
+            if (l == 0) mixe[rl][gc] = e;
         }
         const float den = epsv + dens;
         lp = live ? M_::logp(den) : 0.f;
         if (BWD) {
             __syncwarp();
             const float inv = M_::div(1.f, den);
-            if (live) for (int c = l; c < NV; c += 8) {
-                const int at = tile_slot(r, c, NV);
-                const float4 z = tz[at];
-                float g[4];
 #pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    const int d = 4 * c + e;
-                    float acc = 0.f;
-                    for (int gc = 0; gc < G; ++gc)
-                        acc = fmaf(mixe[r][gc], M_::div(f4_get(z, e) - tparams[G + (size_t)gc * D + d], tparams[G + (size_t)G * D + (size_t)gc * D + d]), acc);
-                    g[e] = acc * inv;
+            for (int i = 0; i < kTgtMaxVec; ++i) {
+                const int c = l + 8 * i;
+                if (c < NV && live) {
+                    float g[4];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const int d = 4 * c + e;
+                        float acc = 0.f;
+                        for (int gc = 0; gc < G; ++gc)
+                            acc = fmaf(mixe[rl][gc], M_::div(f4_get(z[i], e) - tparams[G + (size_t)gc * D + d], tparams[G + (size_t)G * D + (size_t)gc * D + d]), acc);
+                        g[e] = acc * inv;
+                    }
+                    y4[c] = make_float4(g[0], g[1], g[2], g[3]);
                 }
-                tz[at] = make_float4(g[0], g[1], g[2], g[3]);
             }
         }
     }
     // block totals in a fixed order: lanes with l == 0 carry one row each
     float vq = (l == 0) ? lq : 0.f, vp = (l == 0) ? lp : 0.f;
-    if (!BWD) vq = zz_part;
     vq = warp_sum(vq);
     vp = warp_sum(vp);
     if (lane == 0) { red[warp][0] = vq; red[warp][1] = vp; }
@@ -483,42 +471,8 @@ target_kernel(const float* __restrict__ z0, float* __restrict__ Y, int n_act, in
     if (tid == 0) {
         float tq = 0.f, tp = 0.f;
         for (int i = 0; i < kTgtThreads / 32; ++i) { tq += red[i][0]; tp += red[i][1]; }
-        if (!BWD) tq = -0.5f * (rows * (D * LOG2PI) + tq);
         part[2 * blockIdx.x] = tq;
         part[2 * blockIdx.x + 1] = tp;
-    }
-    if (BWD) {
-        // row form of gz_K, in place of Y
-        float4* o4 = reinterpret_cast<float4*>(Y + (size_t)n0 * D);
-        {
-            int rr = tid / NV, c = tid - rr * NV;
-            for (int v = tid; v < nvec; v += kTgtThreads) {
-                o4[v] = tz[tile_slot(rr, c, NV)];
-                rr += step_r; c += step_c;
-                if (c >= NV) { c -= NV; ++rr; }
-            }
-        }
-        // transposed copies: per instruction 8 samples (lane % 8) x 4 coordinates (lane / 8) of one float4 column
-        const int s8 = lane & 7, dd = lane >> 3;
-        float* gcol = GZT + (size_t)(4 * warp + dd) * ldn + n0 + s8;       // column c = warp, coordinate 4c + dd, sample n0 + s8
-        float* zcol = Z0T + (size_t)(4 * warp + dd) * ldn + n0 + s8;
-        const size_t cstride = (size_t)4 * (kTgtThreads / 32) * ldn;
-        const float* tzf = reinterpret_cast<const float*>(tz) + dd;
-        const float* t0f = reinterpret_cast<const float*>(t0) + dd;
-        for (int c = warp; c < NV; c += kTgtThreads / 32) {
-            // rows s8, s8 + 8, ... share r % 8 = s8, hence one slot offset inside the row
-            int x = c + s8;
-            x = x >= NV ? x - NV : x;
-            const int at0 = 4 * (s8 * NV + x);
-#pragma unroll
-            for (int j = 0; j < kTgtRows / 8; ++j) {
-                if (8 * j + s8 < rows) {
-                    gcol[8 * j] = tzf[at0 + 32 * j * NV];
-                    zcol[8 * j] = t0f[at0 + 32 * j * NV];
-                }
-            }
-            gcol += cstride; zcol += cstride;
-        }
     }
 }
 
@@ -548,7 +502,7 @@ chunk_totals_kernel(const float* __restrict__ part_g, int KP, int K, int bwd, co
 }
 
 // g_s[k][d] = G4[d][k] + sum_{j>k} G6[k][j] w[j][d] ;  g_w[k][d] = G5[d][k] + sum_{j<k} G6[j][k] s[j][d]
-// with G6 = rows [0, KP) and G5 = rows [KP, KP + D) of the stacked product; grid (K, ceil(D / 128)).
+// with G6 = rows [0, KP) and G5 = rows [128, 128 + D) of the stacked product; grid (K, ceil(D / 128)).
 __global__ void finish_kernel(const float* __restrict__ acc, const float* __restrict__ G4, const float* __restrict__ G56,
                               const float* __restrict__ w, const float* __restrict__ s, int K, int KP, int D, int bwd,
                               float* __restrict__ out_F, float* __restrict__ g_w, float* __restrict__ g_s,
@@ -563,7 +517,7 @@ __global__ void finish_kernel(const float* __restrict__ acc, const float* __rest
     if (!bwd) return;
     if (blockIdx.y == 0 && threadIdx.x == 0) { g_b[k] = acc[3 + k]; g_c[k] = acc[3 + kMaxK + k]; }
     const float* G6 = G56;
-    const float* G5 = G56 + (size_t)KP * K;
+    const float* G5 = G56 + (size_t)kG5Row * K;
     const int d = blockIdx.y * blockDim.x + threadIdx.x;
     if (d >= D) return;
     float gs = G4[(size_t)d * K + k], gw = G5[(size_t)d * K + k];
@@ -573,19 +527,22 @@ __global__ void finish_kernel(const float* __restrict__ acc, const float* __rest
     g_w[(size_t)k * D + d] = gw;
 }
 
-template <int TGT>
-static cudaError_t launch_target(bool bwd, const float* z0, float* Y, int n_act, int D, long long ldn, const float* tp,
-                                 int ntp, float epsv, float* GZT, float* Z0T, float* part, cudaStream_t st) {
-    const size_t smem = tgt_smem_bytes(D, bwd);
+template <int TGT, int VEC>
+static cudaError_t launch_target_v(bool bwd, const float* z0, float* Y, int n_act, int D, const float* tp, int ntp, float epsv,
+                                   float* part, cudaStream_t st) {
+    const size_t smem = tgt_smem_bytes(D);
     const int blocks = (n_act + kTgtRows - 1) / kTgtRows;
-    if (bwd) {
-        if (smem > 48 * 1024) cudaFuncSetAttribute(target_kernel<TGT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        target_kernel<TGT, true><<<blocks, kTgtThreads, smem, st>>>(z0, Y, n_act, D, ldn, tp, ntp, epsv, GZT, Z0T, part);
-    } else {
-        if (smem > 48 * 1024) cudaFuncSetAttribute(target_kernel<TGT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        target_kernel<TGT, false><<<blocks, kTgtThreads, smem, st>>>(z0, Y, n_act, D, ldn, tp, ntp, epsv, GZT, Z0T, part);
-    }
+    if (bwd) target_kernel<TGT, true, VEC><<<blocks, kTgtThreads, smem, st>>>(z0, Y, n_act, D, tp, ntp, epsv, part);
+    else target_kernel<TGT, false, VEC><<<blocks, kTgtThreads, smem, st>>>(z0, Y, n_act, D, tp, ntp, epsv, part);
     return cudaGetLastError();
+}
+template <int TGT>
+static cudaError_t launch_target(bool bwd, const float* z0, float* Y, int n_act, int D, const float* tp, int ntp, float epsv,
+                                 float* part, cudaStream_t st) {
+    if (D <= 64) return launch_target_v<TGT, 2>(bwd, z0, Y, n_act, D, tp, ntp, epsv, part, st);
+    if (D <= 128) return launch_target_v<TGT, 4>(bwd, z0, Y, n_act, D, tp, ntp, epsv, part, st);
+    if (D <= 256) return launch_target_v<TGT, 8>(bwd, z0, Y, n_act, D, tp, ntp, epsv, part, st);
+    return launch_target_v<TGT, 16>(bwd, z0, Y, n_act, D, tp, ntp, epsv, part, st);
 }
 
 template <int KP>
@@ -656,19 +613,20 @@ int gram_elbo_f32(bool bwd, const float* eps, long long N, int D, int K, const f
         if ((rc = tc_gemm_f32(ws + L.Trow, KP, ws + L.ST, KP, n_act, D, K, ws + L.Y, D, nullptr, 0, nullptr, 0, nullptr, 0, 0, st)) != NF_OK)
             return rc;
         if (target_id == NF_TARGET_GAUSSDIAG)
-            NF_CUDA_OK(launch_target<NF_TARGET_GAUSSDIAG>(bwd, z0, ws + L.Y, n_act, D, L.Nc, tp, ntp, epsv, ws + L.GZT, ws + L.Z0T, ws + L.part_t, st));
+            NF_CUDA_OK(launch_target<NF_TARGET_GAUSSDIAG>(bwd, z0, ws + L.Y, n_act, D, tp, ntp, epsv, ws + L.part_t, st));
         else
-            NF_CUDA_OK(launch_target<NF_TARGET_MIXDIAG>(bwd, z0, ws + L.Y, n_act, D, L.Nc, tp, ntp, epsv, ws + L.GZT, ws + L.Z0T, ws + L.part_t, st));
+            NF_CUDA_OK(launch_target<NF_TARGET_MIXDIAG>(bwd, z0, ws + L.Y, n_act, D, tp, ntp, epsv, ws + L.part_t, st));
         if (bwd) {
             // product 3: P^T[k][n] = sum_d gz[n][d] s[k][d]
             if ((rc = tc_gemm_f32(ws + L.Y, D, s, D, n_act, K, D, nullptr, 0, ws + L.AT, L.Nc, nullptr, 0, nullptr, 0, 0, st)) != NF_OK) return rc;
             NF_CUDA_OK(launch_rec_any(false, L, ws, n_act, K, c, epsv, st));
-            // products 4-6 contract over the samples of the chunk (split across CTAs, fixed-order sums);
-            // 5 and 6 share the operand Delta^T and run as one product with [T^T ; z_0^T] stacked
-            if ((rc = tc_gemm_f32(ws + L.GZT, L.Nc, ws + L.TT, L.Nc, D, K, n_act, ws + L.G4, K, nullptr, 0, nullptr, 0, nullptr, 0, 0, st,
-                                  L.splits, ws + L.split4, !first)) != NF_OK) return rc;
-            if ((rc = tc_gemm_f32(ws + L.TT, L.Nc, ws + L.DT, L.Nc, KP + D, K, n_act, ws + L.G56, K, nullptr, 0, nullptr, 0, nullptr, 0, 0, st,
-                                  L.splits, ws + L.split56, !first)) != NF_OK) return rc;
+            // products 4-6 contract over the samples of the chunk (split across CTAs, fixed-order sums).  gz_K and z_0 are
+            // read as they lie in memory, sample-major; 5 and 6 share Delta^T and run as one product whose row blocks
+            // are T^T (rows [0, KP)) and z_0 (rows [128, 128 + D))
+            if ((rc = tc_gemm_stacked_f32(nullptr, 0, 0, ws + L.Y, D, D, ws + L.TT, L.Nc, K, n_act, ws + L.G4, K, nullptr, 0, nullptr, 0,
+                                          nullptr, 0, 0, st, L.splits, ws + L.split4, !first)) != NF_OK) return rc;
+            if ((rc = tc_gemm_stacked_f32(ws + L.TT, L.Nc, KP, z0, D, D, ws + L.DT, L.Nc, K, n_act, ws + L.G56, K, nullptr, 0, nullptr, 0,
+                                          nullptr, 0, 0, st, L.splits, ws + L.split56, !first)) != NF_OK) return rc;
         }
         chunk_totals_kernel<<<2 * K + 1, 256, 0, st>>>(ws + L.part_g, KP, K, bwd ? 1 : 0, ws + L.part_ld,
                                                   (n_act + kRecThreads - 1) / kRecThreads, ws + L.part_t,

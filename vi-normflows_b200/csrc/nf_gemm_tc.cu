@@ -104,13 +104,15 @@ struct Params {
     const float* mask_src; long long ldm; int mask;     // multiply by act'(mask_src[m][n])
     long long* dbg;                      // optional phase timestamps of CTA (0,0) (bring-up aid), else null
     int stages;                          // depth of the shared-memory ring
+    int m_split;                         // output rows >= m_split (a multiple of BM) take A from the second, sample-major operand
     int kb_per_split;                    // split-K: blockIdx.z owns k-blocks [z*kb_per_split, (z+1)*kb_per_split)
     long long split_stride;              // and writes its partial tile to C + z*split_stride
 };
 
 template <bool ATMEM>
 __global__ void __launch_bounds__(THREADS)
-gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, Params p) {
+gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                   const __grid_constant__ CUtensorMap map_a2, Params p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     __shared__ uint64_t full_bar[MAX_STAGES], split_bar[MAX_STAGES], empty_bar[MAX_STAGES], acc_bar;
@@ -163,6 +165,11 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
                 if (it > 0) mbar_wait(&empty_bar[s], (it - 1) & 1);
                 uint8_t* st = smem + (size_t)s * STAGE_BYTES_;
                 mbar_expect_tx(&full_bar[s], A_BYTES + B_BYTES);
+                if (ATMEM && m0 >= p.m_split) {
+                    // A2 is stored [k][m] (contraction index outermost): four 32 x 32 boxes, one per 32 output rows
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) tma_load_2d(st + q * 4096, &map_a2, m0 - p.m_split + 32 * q, (kb0 + kb) * BK, &full_bar[s]);
+                } else
                 tma_load_2d(st, &map_a, (kb0 + kb) * BK, m0, &full_bar[s]);                  // A hi slot (raw data)
                 tma_load_2d(st + B_OFF, &map_b, (kb0 + kb) * BK, n0, &full_bar[s]);          // B hi slot (raw data)
             }
@@ -228,20 +235,28 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
                     // columns [0, 32) of the stage hold hi, [32, 64) lo.  16-byte chunk j of row r sits at chunk j ^ (r % 8).
                     const int q = warp - 4, row = 32 * q + lane;
                     const uint8_t* rp = st + (size_t)row * 128;
+                    const float* cp = reinterpret_cast<const float*>(st + q * 4096) + lane;     // sample-major box of this warp: [k][32 rows]
+                    const bool km = m0 >= p.m_split;
                     const uint32_t ta = tmem_base + ((uint32_t)(32 * q) << 16) + ACC_COLS + (uint32_t)s * 64u;
 #pragma unroll
                     for (int h2 = 0; h2 < 2; ++h2) {
                         uint32_t hi[16], lo[16];
+                        float x[16];
+                        if (km) {
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            const float4 v = *reinterpret_cast<const float4*>(rp + 16 * ((4 * h2 + j) ^ (row & 7)));
-                            const float x[4] = {v.x, v.y, v.z, v.w};
+                            for (int e = 0; e < 16; ++e) x[e] = cp[(16 * h2 + e) * 32];
+                        } else {
 #pragma unroll
-                            for (int e = 0; e < 4; ++e) {
-                                const uint32_t hb = __float_as_uint(x[e]) & 0xFFFFE000u;
-                                hi[4 * j + e] = hb;
-                                lo[4 * j + e] = __float_as_uint(x[e] - __uint_as_float(hb));
+                            for (int j = 0; j < 4; ++j) {
+                                const float4 v = *reinterpret_cast<const float4*>(rp + 16 * ((4 * h2 + j) ^ (row & 7)));
+                                x[4 * j] = v.x; x[4 * j + 1] = v.y; x[4 * j + 2] = v.z; x[4 * j + 3] = v.w;
                             }
+                        }
+#pragma unroll
+                        for (int e = 0; e < 16; ++e) {
+                            const uint32_t hb = __float_as_uint(x[e]) & 0xFFFFE000u;
+                            hi[e] = hb;
+                            lo[e] = __float_as_uint(x[e] - __uint_as_float(hb));
                         }
                         tmem_st16(ta + 16u * h2, hi);
                         tmem_st16(ta + 32u + 16u * h2, lo);
@@ -382,15 +397,15 @@ static PFN_cuTensorMapEncodeTiled get_encoder() {
 // row-major [rows][cols] float matrix with leading dimension ld (elements); box = box_rows x 32 columns.
 // Encoding a map costs several microseconds on the host; the MLP re-uses the same buffers step after
 // step (the framework's caching allocator hands the same addresses back), so maps are memoised.
-struct MapKey { const float* base; long long rows, cols, ld; int box_rows; };
-static bool make_map(CUtensorMap* map, const float* base, long long rows, long long cols, long long ld, int box_rows) {
+struct MapKey { const float* base; long long rows, cols, ld; int box_rows; bool swz; };
+static bool make_map(CUtensorMap* map, const float* base, long long rows, long long cols, long long ld, int box_rows, bool swz = true) {
     constexpr int kCache = 128;
     static thread_local MapKey keys[kCache];
     static thread_local CUtensorMap vals[kCache];
     static thread_local int used = 0, next = 0;
     for (int i = 0; i < used; ++i) {
         const MapKey& k = keys[i];
-        if (k.base == base && k.rows == rows && k.cols == cols && k.ld == ld && k.box_rows == box_rows) { *map = vals[i]; return true; }
+        if (k.base == base && k.rows == rows && k.cols == cols && k.ld == ld && k.box_rows == box_rows && k.swz == swz) { *map = vals[i]; return true; }
     }
     PFN_cuTensorMapEncodeTiled enc = get_encoder();
     if (!enc) return false;
@@ -399,11 +414,11 @@ static bool make_map(CUtensorMap* map, const float* base, long long rows, long l
     cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
     cuuint32_t estr[2] = {1, 1};
     if (enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstride, box, estr,
-            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, swz ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
         return false;
     const int slot = used < kCache ? used++ : (next++ % kCache);
-    keys[slot] = MapKey{base, rows, cols, ld, box_rows};
+    keys[slot] = MapKey{base, rows, cols, ld, box_rows, swz};
     vals[slot] = *map;
     return true;
 }
@@ -433,13 +448,26 @@ __global__ void tc_splitk_reduce_kernel(const float* __restrict__ part, int nz, 
 // splits > 1: the contraction is cut into `splits` ranges, each CTA layer writes a partial [M][N] tile set
 // into split_ws (splits*M*N floats) and a second kernel adds them in a fixed order (no bias/activation/C^T);
 // with `accumulate` that sum is added to C instead of replacing it (split mode only).
-int tc_gemm_f32(const float* A, long long lda, const float* B, long long ldb, int M, int N, int K, float* C, long long ldc,
-                float* CT, long long ldct, const float* bias, int act, const float* mask_src, long long ldm, int mask,
-                cudaStream_t st, int splits = 1, float* split_ws = nullptr, bool accumulate = false) {
-    if (M < 1 || N < 1 || K < 1) return NF_ERR_INVALID;
-    if ((lda % 4) || (ldb % 4) || ((uintptr_t)A & 15) || ((uintptr_t)B & 15)) return NF_ERR_UNSUPPORTED;   // 16-byte strides
-    CUtensorMap ma, mb;
-    if (!tc::make_map(&ma, A, M, K, lda, tc::BM) || !tc::make_map(&mb, B, N, K, ldb, tc::BN)) return NF_ERR_UNSUPPORTED;
+// General form: output rows [0, M1) take A1 ([M1][K], K contiguous); when A2 != nullptr, rows [m_split, m_split + M2) with
+// m_split = M1 rounded up to 128 take A2, stored sample-major: A2[k][m] ([K][M2], ld lda2) -- the layout in which the
+// free-energy chain holds z_0 and gz_K -- and rows [M1, m_split) of C are zero padding.  C has m_split + M2 rows then.
+int tc_gemm_stacked_f32(const float* A, long long lda, int M1, const float* A2, long long lda2, int M2, const float* B, long long ldb,
+                        int N, int K, float* C, long long ldc, float* CT, long long ldct, const float* bias, int act,
+                        const float* mask_src, long long ldm, int mask, cudaStream_t st, int splits, float* split_ws, bool accumulate) {
+    if (M1 < 0 || M2 < 0 || (M1 < 1 && M2 < 1) || N < 1 || K < 1) return NF_ERR_INVALID;
+    if ((ldb % 4) || ((uintptr_t)B & 15)) return NF_ERR_UNSUPPORTED;                                   // 16-byte strides
+    if (M1 > 0 && ((lda % 4) || ((uintptr_t)A & 15))) return NF_ERR_UNSUPPORTED;
+    if (M2 > 0 && (!A2 || (lda2 % 4) || ((uintptr_t)A2 & 15))) return NF_ERR_UNSUPPORTED;
+    static const bool atmem = []() { const char* e = getenv("NF_GEMM_ATMEM"); return !(e && atoi(e) == 0); }();
+    if (M2 > 0 && !atmem) return NF_ERR_UNSUPPORTED;          // the sample-major operand needs the tensor-memory path
+    const int m_split = M2 > 0 ? (M1 + tc::BM - 1) / tc::BM * tc::BM : (1 << 30);
+    const int M = M2 > 0 ? m_split + M2 : M1;
+    CUtensorMap ma, mb, ma2;
+    if (M1 > 0) { if (!tc::make_map(&ma, A, M1, K, lda, tc::BM)) return NF_ERR_UNSUPPORTED; }
+    if (!tc::make_map(&mb, B, N, K, ldb, tc::BN)) return NF_ERR_UNSUPPORTED;
+    if (M2 > 0) { if (!tc::make_map(&ma2, A2, K, M2, lda2, 32, false)) return NF_ERR_UNSUPPORTED; }
+    else ma2 = mb;
+    if (M1 < 1) ma = mb;
     static long long* dbg_buf = nullptr;
     if (getenv("NF_GEMM_DBG") && !dbg_buf) cudaMallocManaged(&dbg_buf, 64);
     const int nkb_all = (K + tc::BK - 1) / tc::BK;
@@ -454,10 +482,9 @@ int tc_gemm_f32(const float* A, long long lda, const float* B, long long ldb, in
     // Ring depth: short contractions are dominated by the per-tile prologue and epilogue, so they get a one-stage
     // ring and four CTAs per SM that cover for one another; longer ones a deeper ring and two CTAs per SM
     // (tensor-memory path: 3 stages, 256 columns per CTA; shared-memory path: 2 stages).  NF_GEMM_STAGES=1..3 overrides.
-    static const bool atmem = []() { const char* e = getenv("NF_GEMM_ATMEM"); return !(e && atoi(e) == 0); }();
     int stages = kbps <= 2 ? 1 : (atmem ? 3 : 2);
     if (const char* e = getenv("NF_GEMM_STAGES")) { const int v = atoi(e); if (v >= 1 && v <= tc::MAX_STAGES) stages = v; }
-    tc::Params p{M, N, K, via_ws ? split_ws : C, ldc, CT, ldct, bias, act, mask_src, ldm, mask, dbg_buf, stages, kbps, (long long)M * N};
+    tc::Params p{M, N, K, via_ws ? split_ws : C, ldc, CT, ldct, bias, act, mask_src, ldm, mask, dbg_buf, stages, m_split, kbps, (long long)M * N};
     constexpr size_t kSlab = 4 * 32 * 65 * sizeof(float);       // the epilogue parks the accumulator in the ring's memory
     size_t ring = (size_t)stages * (atmem ? tc::STAGE_BYTES_TS : tc::STAGE_BYTES);
     if (ring < kSlab) ring = kSlab;
@@ -471,8 +498,8 @@ int tc_gemm_f32(const float* A, long long lda, const float* B, long long ldb, in
         attr_done = true;
     }
     dim3 grid((N + tc::BN - 1) / tc::BN, (M + tc::BM - 1) / tc::BM, splits);
-    if (atmem) tc::gemm_tf32x3_kernel<true><<<grid, tc::THREADS, smem, st>>>(ma, mb, p);
-    else tc::gemm_tf32x3_kernel<false><<<grid, tc::THREADS, smem, st>>>(ma, mb, p);
+    if (atmem) tc::gemm_tf32x3_kernel<true><<<grid, tc::THREADS, smem, st>>>(ma, mb, ma2, p);
+    else tc::gemm_tf32x3_kernel<false><<<grid, tc::THREADS, smem, st>>>(ma, mb, ma2, p);
     NF_CUDA_OK(cudaGetLastError());
     if (via_ws) {
         const long long count = (long long)M * N;
@@ -485,6 +512,13 @@ int tc_gemm_f32(const float* A, long long lda, const float* B, long long ldb, in
                 dbg_buf[1] - dbg_buf[0], dbg_buf[2] - dbg_buf[5], dbg_buf[3] - dbg_buf[2], dbg_buf[6] - dbg_buf[3]);
     }
     return NF_OK;
+}
+
+int tc_gemm_f32(const float* A, long long lda, const float* B, long long ldb, int M, int N, int K, float* C, long long ldc,
+                float* CT, long long ldct, const float* bias, int act, const float* mask_src, long long ldm, int mask,
+                cudaStream_t st, int splits = 1, float* split_ws = nullptr, bool accumulate = false) {
+    return tc_gemm_stacked_f32(A, lda, M, nullptr, 0, 0, B, ldb, N, K, C, ldc, CT, ldct, bias, act, mask_src, ldm, mask, st, splits,
+                               split_ws, accumulate);
 }
 
 }  // namespace nf
