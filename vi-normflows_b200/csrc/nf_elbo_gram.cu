@@ -65,9 +65,9 @@ static inline int grad_splits(long long nc, int D) {
 struct Layout {
     int KP; long long Nc; int splits;
     size_t acc, M, Mt, ST, G4, G56, part_ld, part_g, part_t, split4, split56;   // offsets in floats
-    size_t AT, DT, TT, Trow, Y, total;
+    size_t AT, DT, TT, Y, total;
 };
-constexpr int kG5Row = 128;      // row of the stacked product 5/6 result where the z_0^T Delta block starts (tile-aligned)
+constexpr int kG5Row = 64;       // row of the stacked product 5/6 result where the z_0^T Delta block starts (KP <= 64 rounded up to 64)
 static Layout make_layout(long long N, int D, int K) {
     Layout L{};
     L.KP = pad_k(K);
@@ -81,7 +81,7 @@ static Layout make_layout(long long N, int D, int K) {
     L.Mt = take(KP * KP);
     L.ST = take((size_t)D * KP);
     L.G4 = take((size_t)D * K);                 // gz_K^T T             [D][K]
-    L.G56 = take((size_t)(kG5Row + D) * K);     // [T^T ; 0 ; z_0^T] Delta: rows [0, KP) and [128, 128 + D)
+    L.G56 = take((size_t)(kG5Row + D) * K);     // [T^T ; 0 ; z_0^T] Delta: rows [0, KP) and [64, 64 + D)
     L.part_ld = take(Nc / kRecThreads);
     L.part_g = take(Nc / kRecThreads * 2 * KP);
     L.part_t = take(2 * (Nc / kTgtRows));
@@ -90,7 +90,6 @@ static Layout make_layout(long long N, int D, int K) {
     L.AT = take(KP * Nc);                       // A0^T, later P^T (rows K.. stay zero)
     L.DT = take(KP * Nc);                       // Delta^T
     L.TT = take(KP * Nc);                       // T^T
-    L.Trow = take(Nc * KP);                     // T, row per sample
     L.Y = take(Nc * D);                         // T S, later gz_K
     L.total = o;
     return L;
@@ -147,7 +146,7 @@ __device__ __forceinline__ float block_sum(float v, float* red /* [NT/32] */) {
 // The product-1 values of a thread (one per layer, needed at step k) are brought into a thread-private
 // column of shared memory by cp.async, sixteen layers per group, and waited for group by group: the
 // fetches cost no registers and overlap the arithmetic.
-// Outputs: T^T (coalesced), T rows (operand of product 2), per-block sum of the log-det terms.
+// Outputs: T^T ([KP][Nc], coalesced; operand of products 2, 4 and 6), per-block sum of the log-det terms.
 __device__ __forceinline__ void cp_async4(float* smem_dst, const float* gsrc) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
 }
@@ -169,8 +168,7 @@ template <int KP> constexpr size_t rec_bwd_smem() { return (size_t)(KP * KP + (K
 template <int KP>
 __global__ void __launch_bounds__(kRecThreads, 4)
 rec_fwd_kernel(const float* __restrict__ AT, long long ldn, int n_act, int K, const float* __restrict__ Mt,
-               const float* __restrict__ c, float epsv, float* __restrict__ TT, float* __restrict__ Trow,
-               float* __restrict__ part_ld) {
+               const float* __restrict__ c, float epsv, float* __restrict__ TT, float* __restrict__ part_ld) {
     using M_ = Mth<float>;
     extern __shared__ __align__(16) float dyn[];
     float* sM = dyn;                              // [KP][KP]
@@ -200,7 +198,6 @@ rec_fwd_kernel(const float* __restrict__ AT, long long ldn, int n_act, int K, co
     for (int j = 0; j < KP; ++j) {
         if (j > 0 && (j & 15) == 0) cp_async_wait_le(NG - 1 - j / 16);
         const float t = M_::tanh_pre(fmaf(stage[j * kRecThreads + threadIdx.x], M_::kArgScale, a[j]));
-        a[j] = t;
         const float hp = fmaf(-t, t, 1.f);
         prod *= se[j] + fabsf(fmaf(hp, sc[j], 1.f));
         if ((j & 3) == 3) { ld += M_::flog(prod); prod = 1.f; }      // MUFU.LG2, as in the direct kernels
@@ -214,9 +211,6 @@ rec_fwd_kernel(const float* __restrict__ AT, long long ldn, int n_act, int K, co
             if (4 * k4 + 3 > j) a[4 * k4 + 3] = fmaf(m.w, t, a[4 * k4 + 3]);
         }
     }
-    float4* row = reinterpret_cast<float4*>(Trow + (size_t)n * KP);
-#pragma unroll
-    for (int k4 = 0; k4 < KP / 4; ++k4) row[k4] = make_float4(a[4 * k4], a[4 * k4 + 1], a[4 * k4 + 2], a[4 * k4 + 3]);
     const float tot = block_sum<kRecThreads>(ok ? ld : 0.f, red);
     if (threadIdx.x == 0) part_ld[blockIdx.x] = tot;
 }
@@ -502,7 +496,7 @@ chunk_totals_kernel(const float* __restrict__ part_g, int KP, int K, int bwd, co
 }
 
 // g_s[k][d] = G4[d][k] + sum_{j>k} G6[k][j] w[j][d] ;  g_w[k][d] = G5[d][k] + sum_{j<k} G6[j][k] s[j][d]
-// with G6 = rows [0, KP) and G5 = rows [128, 128 + D) of the stacked product; grid (K, ceil(D / 128)).
+// with G6 = rows [0, KP) and G5 = rows [64, 64 + D) of the stacked product; grid (K, ceil(D / 128)).
 __global__ void finish_kernel(const float* __restrict__ acc, const float* __restrict__ G4, const float* __restrict__ G56,
                               const float* __restrict__ w, const float* __restrict__ s, int K, int KP, int D, int bwd,
                               float* __restrict__ out_F, float* __restrict__ g_w, float* __restrict__ g_s,
@@ -556,7 +550,7 @@ static cudaError_t launch_rec(bool fwd, const Layout& L, float* ws, int n_act, i
     }
     if (fwd)
         rec_fwd_kernel<KP><<<blocks, kRecThreads, rec_fwd_smem<KP>(), st>>>(ws + L.AT, L.Nc, n_act, K, ws + L.Mt, c, epsv, ws + L.TT,
-                                                                           ws + L.Trow, ws + L.part_ld);
+                                                                           ws + L.part_ld);
     else
         rec_bwd_kernel<KP><<<blocks, kRecThreads, rec_bwd_smem<KP>(), st>>>(ws + L.AT, ws + L.TT, L.Nc, n_act, K, ws + L.M, c, epsv,
                                                                            ws + L.DT, ws + L.part_g);
@@ -574,7 +568,7 @@ static cudaError_t launch_rec_any(bool fwd, const Layout& L, float* ws, int n_ac
 // Shapes the path supports, and among those the ones where it is expected to win.  Cost models fitted on a B200
 // (profiles/r01f_gram_crossover.txt), in microseconds: the direct kernel spends ~0.94 ns per (sample, layer,
 // coordinate), growing with D beyond 128 where its per-warp gradient records fall out of L2; this path has ~100 us
-// of fixed launch cost, ~18 ns per (sample, coordinate) in the products and the target kernel, and ~0.14 ns per
+// of fixed launch cost, ~11.5 ns per (sample, coordinate) in the products and the target kernel, and ~0.14 ns per
 // (sample, layer^2) in the recurrences.  NF_GRAM=1 forces this path where it is supported, NF_NO_GRAM=1 forbids it.
 bool gram_applicable(long long N, int D, int K, int target_id, int ntp) {
     if (getenv("NF_NO_GRAM")) return false;
@@ -585,7 +579,7 @@ bool gram_applicable(long long N, int D, int K, int target_id, int ntp) {
     if (N < 1024) return false;
     const double n = (double)N;
     const double t_direct = n * K * D * 0.94e-3 * (D > 115 ? D / 115.0 : 1.0) * 1e-3;
-    const double t_gram = 100.0 + n * (18e-3 * D + 0.143e-3 * K * K) * 1e-3;
+    const double t_gram = 100.0 + n * (11.5e-3 * D + 0.143e-3 * K * K) * 1e-3;
     return t_gram < t_direct;
 }
 
@@ -609,9 +603,9 @@ int gram_elbo_f32(bool bwd, const float* eps, long long N, int D, int K, const f
         // product 1: A0^T[k][n] = sum_d z0[n][d] w[k][d] + b[k]
         if ((rc = tc_gemm_f32(z0, D, w, D, n_act, K, D, nullptr, 0, ws + L.AT, L.Nc, b, 0, nullptr, 0, 0, st)) != NF_OK) return rc;
         NF_CUDA_OK(launch_rec_any(true, L, ws, n_act, K, c, epsv, st));
-        // product 2: Y[n][d] = sum_k T[n][k] S^T[d][k]
-        if ((rc = tc_gemm_f32(ws + L.Trow, KP, ws + L.ST, KP, n_act, D, K, ws + L.Y, D, nullptr, 0, nullptr, 0, nullptr, 0, 0, st)) != NF_OK)
-            return rc;
+        // product 2: Y[n][d] = sum_k T^T[k][n] S^T[d][k]   (T is read layer-major, as the recurrence wrote it)
+        if ((rc = tc_gemm_stacked_f32(nullptr, 0, 0, ws + L.TT, L.Nc, n_act, ws + L.ST, KP, D, K, ws + L.Y, D, nullptr, 0, nullptr, 0,
+                                      nullptr, 0, 0, st, 1, nullptr, false)) != NF_OK) return rc;
         if (target_id == NF_TARGET_GAUSSDIAG)
             NF_CUDA_OK(launch_target<NF_TARGET_GAUSSDIAG>(bwd, z0, ws + L.Y, n_act, D, tp, ntp, epsv, ws + L.part_t, st));
         else
@@ -622,7 +616,7 @@ int gram_elbo_f32(bool bwd, const float* eps, long long N, int D, int K, const f
             NF_CUDA_OK(launch_rec_any(false, L, ws, n_act, K, c, epsv, st));
             // products 4-6 contract over the samples of the chunk (split across CTAs, fixed-order sums).  gz_K and z_0 are
             // read as they lie in memory, sample-major; 5 and 6 share Delta^T and run as one product whose row blocks
-            // are T^T (rows [0, KP)) and z_0 (rows [128, 128 + D))
+            // are T^T (rows [0, KP)) and z_0 (rows [64, 64 + D))
             if ((rc = tc_gemm_stacked_f32(nullptr, 0, 0, ws + L.Y, D, D, ws + L.TT, L.Nc, K, n_act, ws + L.G4, K, nullptr, 0, nullptr, 0,
                                           nullptr, 0, 0, st, L.splits, ws + L.split4, !first)) != NF_OK) return rc;
             if ((rc = tc_gemm_stacked_f32(ws + L.TT, L.Nc, KP, z0, D, D, ws + L.DT, L.Nc, K, n_act, ws + L.G56, K, nullptr, 0, nullptr, 0,

@@ -104,7 +104,7 @@ struct Params {
     const float* mask_src; long long ldm; int mask;     // multiply by act'(mask_src[m][n])
     long long* dbg;                      // optional phase timestamps of CTA (0,0) (bring-up aid), else null
     int stages;                          // depth of the shared-memory ring
-    int m_split;                         // output rows >= m_split (a multiple of BM) take A from the second, sample-major operand
+    int m_split;                         // output rows >= m_split (a multiple of 64) take A from the second, sample-major operand
     int kb_per_split;                    // split-K: blockIdx.z owns k-blocks [z*kb_per_split, (z+1)*kb_per_split)
     long long split_stride;              // and writes its partial tile to C + z*split_stride
 };
@@ -112,7 +112,7 @@ struct Params {
 template <bool ATMEM>
 __global__ void __launch_bounds__(THREADS)
 gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                   const __grid_constant__ CUtensorMap map_a2, Params p) {
+                   const __grid_constant__ CUtensorMap map_a2, const __grid_constant__ CUtensorMap map_a_half, Params p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     __shared__ uint64_t full_bar[MAX_STAGES], split_bar[MAX_STAGES], empty_bar[MAX_STAGES], acc_bar;
@@ -165,10 +165,13 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
                 if (it > 0) mbar_wait(&empty_bar[s], (it - 1) & 1);
                 uint8_t* st = smem + (size_t)s * STAGE_BYTES_;
                 mbar_expect_tx(&full_bar[s], A_BYTES + B_BYTES);
-                if (ATMEM && m0 >= p.m_split) {
-                    // A2 is stored [k][m] (contraction index outermost): four 32 x 32 boxes, one per 32 output rows
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) tma_load_2d(st + q * 4096, &map_a2, m0 - p.m_split + 32 * q, (kb0 + kb) * BK, &full_bar[s]);
+                const int a1_rows = p.m_split - m0;       // rows of this tile that come from A1: >= 128 all, 64 half, <= 0 none
+                if (ATMEM && a1_rows < BM) {
+                    // A2 is stored [k][m] (contraction index outermost): 32 x 32 boxes, one per 32 output rows; a boundary
+                    // tile takes its first 64 rows from A1 through a 64-row box
+                    if (a1_rows > 0) tma_load_2d(st, &map_a_half, (kb0 + kb) * BK, m0, &full_bar[s]);
+                    for (int q = a1_rows > 0 ? 2 : 0; q < 4; ++q)
+                        tma_load_2d(st + q * 4096, &map_a2, m0 + 32 * q - p.m_split, (kb0 + kb) * BK, &full_bar[s]);
                 } else
                 tma_load_2d(st, &map_a, (kb0 + kb) * BK, m0, &full_bar[s]);                  // A hi slot (raw data)
                 tma_load_2d(st + B_OFF, &map_b, (kb0 + kb) * BK, n0, &full_bar[s]);          // B hi slot (raw data)
@@ -236,7 +239,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
                     const int q = warp - 4, row = 32 * q + lane;
                     const uint8_t* rp = st + (size_t)row * 128;
                     const float* cp = reinterpret_cast<const float*>(st + q * 4096) + lane;     // sample-major box of this warp: [k][32 rows]
-                    const bool km = m0 >= p.m_split;
+                    const bool km = m0 + 32 * q >= p.m_split;
                     const uint32_t ta = tmem_base + ((uint32_t)(32 * q) << 16) + ACC_COLS + (uint32_t)s * 64u;
 #pragma unroll
                     for (int h2 = 0; h2 < 2; ++h2) {
@@ -449,7 +452,7 @@ __global__ void tc_splitk_reduce_kernel(const float* __restrict__ part, int nz, 
 // into split_ws (splits*M*N floats) and a second kernel adds them in a fixed order (no bias/activation/C^T);
 // with `accumulate` that sum is added to C instead of replacing it (split mode only).
 // General form: output rows [0, M1) take A1 ([M1][K], K contiguous); when A2 != nullptr, rows [m_split, m_split + M2) with
-// m_split = M1 rounded up to 128 take A2, stored sample-major: A2[k][m] ([K][M2], ld lda2) -- the layout in which the
+// m_split = M1 rounded up to 64 take A2, stored sample-major: A2[k][m] ([K][M2], ld lda2) -- the layout in which the
 // free-energy chain holds z_0 and gz_K -- and rows [M1, m_split) of C are zero padding.  C has m_split + M2 rows then.
 int tc_gemm_stacked_f32(const float* A, long long lda, int M1, const float* A2, long long lda2, int M2, const float* B, long long ldb,
                         int N, int K, float* C, long long ldc, float* CT, long long ldct, const float* bias, int act,
@@ -460,14 +463,16 @@ int tc_gemm_stacked_f32(const float* A, long long lda, int M1, const float* A2, 
     if (M2 > 0 && (!A2 || (lda2 % 4) || ((uintptr_t)A2 & 15))) return NF_ERR_UNSUPPORTED;
     static const bool atmem = []() { const char* e = getenv("NF_GEMM_ATMEM"); return !(e && atoi(e) == 0); }();
     if (M2 > 0 && !atmem) return NF_ERR_UNSUPPORTED;          // the sample-major operand needs the tensor-memory path
-    const int m_split = M2 > 0 ? (M1 + tc::BM - 1) / tc::BM * tc::BM : (1 << 30);
+    const int m_split = M2 > 0 ? (M1 + 63) / 64 * 64 : (1 << 30);
     const int M = M2 > 0 ? m_split + M2 : M1;
-    CUtensorMap ma, mb, ma2;
+    CUtensorMap ma, mb, ma2, mah;
     if (M1 > 0) { if (!tc::make_map(&ma, A, M1, K, lda, tc::BM)) return NF_ERR_UNSUPPORTED; }
     if (!tc::make_map(&mb, B, N, K, ldb, tc::BN)) return NF_ERR_UNSUPPORTED;
     if (M2 > 0) { if (!tc::make_map(&ma2, A2, K, M2, lda2, 32, false)) return NF_ERR_UNSUPPORTED; }
     else ma2 = mb;
     if (M1 < 1) ma = mb;
+    if (M2 > 0 && (m_split % tc::BM) != 0) { if (!tc::make_map(&mah, A, M1, K, lda, 64)) return NF_ERR_UNSUPPORTED; }
+    else mah = mb;
     static long long* dbg_buf = nullptr;
     if (getenv("NF_GEMM_DBG") && !dbg_buf) cudaMallocManaged(&dbg_buf, 64);
     const int nkb_all = (K + tc::BK - 1) / tc::BK;
@@ -498,8 +503,8 @@ int tc_gemm_stacked_f32(const float* A, long long lda, int M1, const float* A2, 
         attr_done = true;
     }
     dim3 grid((N + tc::BN - 1) / tc::BN, (M + tc::BM - 1) / tc::BM, splits);
-    if (atmem) tc::gemm_tf32x3_kernel<true><<<grid, tc::THREADS, smem, st>>>(ma, mb, ma2, p);
-    else tc::gemm_tf32x3_kernel<false><<<grid, tc::THREADS, smem, st>>>(ma, mb, ma2, p);
+    if (atmem) tc::gemm_tf32x3_kernel<true><<<grid, tc::THREADS, smem, st>>>(ma, mb, ma2, mah, p);
+    else tc::gemm_tf32x3_kernel<false><<<grid, tc::THREADS, smem, st>>>(ma, mb, ma2, mah, p);
     NF_CUDA_OK(cudaGetLastError());
     if (via_ws) {
         const long long count = (long long)M * N;
