@@ -43,8 +43,9 @@ def shared_case(name, K, D, N, target, tname, tparams=None, steps=50, dtype=torc
     dt = timed(lambda i: ops.planar_elbo(eps[i % nbuf], *a, tname, tp, out=out), steps)
     roof, fl, mu = roofline(K, D, target)
     v = N / dt
-    print('%-34s K=%-3d D=%-4d N=2^%-2d %9.1f us/step %10.3e samples/s  roofline %.3e  frac %.3f' %
-          (name, K, D, N.bit_length() - 1, dt * 1e6, v, roof, v / roof), flush=True)
+    note = '  [matrix-product path; the bound shown is the CUDA-core bound of the direct algorithm]' if (D >= 32 and dtype == torch.float32) else ''
+    print('%-34s K=%-3d D=%-4d N=2^%-2d %9.1f us/step %10.3e samples/s  roofline %.3e  frac %.3f%s' %
+          (name, K, D, N.bit_length() - 1, dt * 1e6, v, roof, v / roof, note), flush=True)
     return {'case': name, 'K': K, 'D': D, 'N': N, 'us_per_step': dt * 1e6, 'samples_per_s': v, 'roofline': roof, 'frac': v / roof}
 
 
@@ -77,7 +78,7 @@ def main():
     res.append(shared_case('C3 mixture', 32, 2, 1 << 24, 'mix', 'mixdiag', mix, steps=10))
     # C5 (single-GPU slice of the sweep)
     res.append(shared_case('C5 U1', 64, 2, 1 << 23, 'u', 'p1', steps=10))
-    for D, N in ((16, 1 << 21), (64, 1 << 19), (256, 1 << 17)):
+    for D, N in ((16, 1 << 21), (64, 1 << 19), (128, 1 << 18), (256, 1 << 17), (512, 1 << 16)):
         rs = np.random.RandomState(5)
         tp = np.concatenate([rs.uniform(-1, 1, D), rs.uniform(-1, 1, D)])
         res.append(shared_case('C5 gaussdiag', 64, D, N if not quick else N >> 2, 'gauss', 'gaussdiag', tp, steps=5))
