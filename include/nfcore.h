@@ -264,8 +264,9 @@ int nf_bernoulli_ll_f64(const double* x, const double* p, int64_t count, double 
 
 /* Tensor-core GEMM used by the MLP entry points above, exposed for testing and reuse:
  *   C[m][n] = act( sum_k A[m][k] B[n][k] + bias[n] ),  A: [M][K] (lda), B: [N][K] (ldb), float32.
- * TMA tile loads, tcgen05.mma kind::tf32 with an in-shared-memory hi/lo split of both operands
- * (three MMAs per k-step) so that results stay at float32 accuracy; accumulator in TMEM.
+ * TMA tile loads, tcgen05.mma kind::tf32; both operands are split into hi/lo halves on the fly (B in shared
+ * memory, A into tensor memory by the warps that own its lanes) and every k-step issues three MMAs, so that
+ * results stay at float32 accuracy; accumulator in TMEM.
  * C (ldc) and/or its transpose CT[n][m] (ldct) are written; act: 0 none, 1 relu, 2 sigmoid.
  * lda, ldb must be multiples of 4 and A, B 16-byte aligned, else NF_ERR_UNSUPPORTED.
  * (The reference's counterpart is the np.matmul chain of nn_models.py:59-84.) */

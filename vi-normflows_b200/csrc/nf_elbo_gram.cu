@@ -46,12 +46,12 @@ static inline int pad_k(int K) { return K <= 16 ? 16 : (K <= 32 ? 32 : 64); }
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // chunk pitch (samples): up to 32M elements of [Nc][D] (small chunks leave the GPU under-filled: every kernel of the
-// chain is a separate launch), a multiple of 128, no more than the job needs
+// chain is a separate launch), a multiple of 256, no more than the job needs
 static inline long long chunk_samples(long long N, int D) {
     long long nc = ((long long)32 << 20) / D;
     if (const char* e = getenv("NF_GRAM_CHUNK")) { const long long v = atoll(e); if (v >= 128) nc = v; }
-    nc = (nc + 127) / 128 * 128;
-    const long long need = (N + 127) / 128 * 128;
+    nc = (nc + 255) / 256 * 256;          // whole blocks of the recurrence kernels (2 x 128 samples)
+    const long long need = (N + 255) / 256 * 256;
     return nc < need ? nc : need;
 }
 static inline int grad_splits(long long nc, int D) {
@@ -162,56 +162,92 @@ __device__ __forceinline__ void cp_async_wait_le(int pending) {      // `pending
     else asm volatile("cp.async.wait_group 4;" ::: "memory");
 }
 
-template <int KP> constexpr size_t rec_fwd_smem() { return (size_t)(KP * KP + KP * kRecThreads) * sizeof(float); }
-template <int KP> constexpr size_t rec_bwd_smem() { return (size_t)(KP * KP + (KP < 32 ? KP : 32) * 2 * kRecThreads) * sizeof(float); }
+// S samples per thread (columns tid, tid + 128, ... of the block) share every M value fetched from shared memory.
+// S = 2 halves the broadcast LDS.128 traffic but was measured slower on B200 (D=256: 539 vs 504 us per call, D=64:
+// 830 vs 765): at 219-255 registers only 8 warps fit an SM, and the recurrences are latency-bound, not LSU-bound.
+constexpr int kRecS = 1;
+template <int KP, int S> constexpr size_t rec_fwd_smem() { return (size_t)(KP * KP + KP * S * kRecThreads) * sizeof(float); }
+template <int KP, int S> constexpr size_t rec_bwd_smem() { return (size_t)(KP * KP + (KP < 32 ? KP : 32) * 2 * S * kRecThreads) * sizeof(float); }
 
-template <int KP>
-__global__ void __launch_bounds__(kRecThreads, 4)
+template <int KP, int S>
+struct FwdCtx {
+    const float* stage;    // [KP][S * 128], already offset by the thread index
+    const float* sM; const float* sc; const float* se;
+    float* dst; long long ldn;
+};
+
+// one layer of the forward recurrence; the layers are peeled by template recursion so that a[][] stays in registers
+template <int KP, int S, int j>
+struct FwdLayer {
+    static __device__ __forceinline__ void run(const FwdCtx<KP, S>& x_, float (&a)[S][KP], float (&prod)[S], float (&ld)[S]) {
+        using M_ = Mth<float>;
+        constexpr int NG = KP / 16, W = S * kRecThreads;
+        if (j > 0 && (j & 15) == 0) cp_async_wait_le(NG - 1 - j / 16);
+        float t[S];
+#pragma unroll
+        for (int u = 0; u < S; ++u) {
+            t[u] = M_::tanh_pre(fmaf(x_.stage[j * W + u * kRecThreads], M_::kArgScale, a[u][j]));
+            const float hp = fmaf(-t[u], t[u], 1.f);
+            prod[u] *= x_.se[j] + fabsf(fmaf(hp, x_.sc[j], 1.f));
+            if ((j & 3) == 3) { ld[u] += M_::flog(prod[u]); prod[u] = 1.f; }      // MUFU.LG2, as in the direct kernels
+            x_.dst[(size_t)j * x_.ldn + u * kRecThreads] = t[u];
+        }
+#pragma unroll
+        for (int k4 = (j + 1) / 4; k4 < KP / 4; ++k4) {
+            const float4 m = *reinterpret_cast<const float4*>(&x_.sM[j * KP + 4 * k4]);
+#pragma unroll
+            for (int u = 0; u < S; ++u) {
+                if (4 * k4 + 0 > j) a[u][4 * k4 + 0] = fmaf(m.x, t[u], a[u][4 * k4 + 0]);
+                if (4 * k4 + 1 > j) a[u][4 * k4 + 1] = fmaf(m.y, t[u], a[u][4 * k4 + 1]);
+                if (4 * k4 + 2 > j) a[u][4 * k4 + 2] = fmaf(m.z, t[u], a[u][4 * k4 + 2]);
+                if (4 * k4 + 3 > j) a[u][4 * k4 + 3] = fmaf(m.w, t[u], a[u][4 * k4 + 3]);
+            }
+        }
+        if constexpr (j + 1 < KP) FwdLayer<KP, S, j + 1>::run(x_, a, prod, ld);
+    }
+};
+
+template <int KP, int S>
+__global__ void __launch_bounds__(kRecThreads, S == 1 ? 4 : 2)
 rec_fwd_kernel(const float* __restrict__ AT, long long ldn, int n_act, int K, const float* __restrict__ Mt,
                const float* __restrict__ c, float epsv, float* __restrict__ TT, float* __restrict__ part_ld) {
-    using M_ = Mth<float>;
+    constexpr int W = S * kRecThreads;            // samples per block
     extern __shared__ __align__(16) float dyn[];
     float* sM = dyn;                              // [KP][KP]
-    float* stage = dyn + KP * KP;                 // [KP][128]: column = thread
+    float* stage = dyn + KP * KP;                 // [KP][W]: column = sample inside the block
     __shared__ float sc[KP], se[KP];
     __shared__ float red[kRecThreads / 32];
     constexpr int NG = KP / 16;
-    const int n = blockIdx.x * kRecThreads + threadIdx.x;        // < Nc: the buffers are padded to whole blocks
-    const bool ok = n < n_act;
+    const int n = blockIdx.x * W + threadIdx.x;   // first sample of this thread; all < Nc: the buffers are padded to whole blocks
     const float* src = AT + n;
-    float* dst = TT + n;
     for (int i = threadIdx.x; i < KP * KP / 4; i += kRecThreads) cp_async16(sM + 4 * i, Mt + 4 * i);
 #pragma unroll
     for (int g = 0; g < NG; ++g) {
 #pragma unroll
-        for (int k = 16 * g; k < 16 * g + 16; ++k) cp_async4(stage + k * kRecThreads + threadIdx.x, src + (size_t)k * ldn);
+        for (int k = 16 * g; k < 16 * g + 16; ++k)
+#pragma unroll
+            for (int u = 0; u < S; ++u)
+                cp_async4(stage + k * W + u * kRecThreads + threadIdx.x, src + (size_t)k * ldn + u * kRecThreads);
         cp_async_commit();                        // group g (group 0 also carries M)
     }
     for (int i = threadIdx.x; i < KP; i += kRecThreads) { sc[i] = i < K ? c[i] : 0.f; se[i] = i < K ? epsv : 0.f; }
     cp_async_wait_le(NG - 1);
     __syncthreads();                              // M, c and eps visible to all
-    float a[KP];
+    FwdCtx<KP, S> x_;
+    x_.stage = stage + threadIdx.x; x_.sM = sM; x_.sc = sc; x_.se = se; x_.dst = TT + n; x_.ldn = ldn;
+    float a[S][KP];
+    float prod[S], ld[S];
 #pragma unroll
-    for (int k = 0; k < KP; ++k) a[k] = 0.f;
-    float prod = 1.f, ld = 0.f;
+    for (int u = 0; u < S; ++u) {
+        prod[u] = 1.f; ld[u] = 0.f;
 #pragma unroll
-    for (int j = 0; j < KP; ++j) {
-        if (j > 0 && (j & 15) == 0) cp_async_wait_le(NG - 1 - j / 16);
-        const float t = M_::tanh_pre(fmaf(stage[j * kRecThreads + threadIdx.x], M_::kArgScale, a[j]));
-        const float hp = fmaf(-t, t, 1.f);
-        prod *= se[j] + fabsf(fmaf(hp, sc[j], 1.f));
-        if ((j & 3) == 3) { ld += M_::flog(prod); prod = 1.f; }      // MUFU.LG2, as in the direct kernels
-        dst[(size_t)j * ldn] = t;
-#pragma unroll
-        for (int k4 = (j + 1) / 4; k4 < KP / 4; ++k4) {
-            const float4 m = *reinterpret_cast<const float4*>(&sM[j * KP + 4 * k4]);
-            if (4 * k4 + 0 > j) a[4 * k4 + 0] = fmaf(m.x, t, a[4 * k4 + 0]);
-            if (4 * k4 + 1 > j) a[4 * k4 + 1] = fmaf(m.y, t, a[4 * k4 + 1]);
-            if (4 * k4 + 2 > j) a[4 * k4 + 2] = fmaf(m.z, t, a[4 * k4 + 2]);
-            if (4 * k4 + 3 > j) a[4 * k4 + 3] = fmaf(m.w, t, a[4 * k4 + 3]);
-        }
+        for (int k = 0; k < KP; ++k) a[u][k] = 0.f;
     }
-    const float tot = block_sum<kRecThreads>(ok ? ld : 0.f, red);
+    FwdLayer<KP, S, 0>::run(x_, a, prod, ld);
+    float mine = 0.f;
+#pragma unroll
+    for (int u = 0; u < S; ++u) mine += (n + u * kRecThreads < n_act) ? ld[u] : 0.f;
+    const float tot = block_sum<kRecThreads>(mine, red);
     if (threadIdx.x == 0) part_ld[blockIdx.x] = tot;
 }
 
@@ -222,55 +258,69 @@ rec_fwd_kernel(const float* __restrict__ AT, long long ldn, int n_act, int K, co
 // (a 64-trip `#pragma unroll` of this body is declined by the compiler, which would put p[] in local memory).
 // P^T and T^T arrive through cp.async in quarters of sixteen layers, two quarters resident (thread-private
 // columns again): when a quarter has been consumed its slot is refilled with the quarter after next.
-template <int KP>
+template <int KP, int S>
 struct BwdCtx {
     const float* srcp; const float* srct; float* dst; long long ldn;
     const float* sM; const float* sc; const float* se; const float* smask; float* sg;   // sg: this warp's [2 KP] record
-    float* stage;          // [2 slots][16 layers][2 (P^T, T^T)][128], already offset by the thread index
-    bool ok; int lane;
+    float* stage;          // [2 slots][16 layers][2 (P^T, T^T)][S * 128], already offset by the thread index
+    bool ok[S]; int lane;
 };
 
-template <int KP>
-__device__ __forceinline__ void bwd_issue_quarter(const BwdCtx<KP>& x_, int q) {
-    float* slot = x_.stage + (q & 1) * 16 * 2 * kRecThreads;
+template <int KP, int S>
+__device__ __forceinline__ void bwd_issue_quarter(const BwdCtx<KP, S>& x_, int q) {
+    constexpr int W = S * kRecThreads;
+    float* slot = x_.stage + (q & 1) * 16 * 2 * W;
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
         const int k = 16 * q + i;
-        cp_async4(slot + (2 * i) * kRecThreads, x_.srcp + (size_t)k * x_.ldn);
-        cp_async4(slot + (2 * i + 1) * kRecThreads, x_.srct + (size_t)k * x_.ldn);
+#pragma unroll
+        for (int u = 0; u < S; ++u) {
+            cp_async4(slot + (2 * i) * W + u * kRecThreads, x_.srcp + (size_t)k * x_.ldn + u * kRecThreads);
+            cp_async4(slot + (2 * i + 1) * W + u * kRecThreads, x_.srct + (size_t)k * x_.ldn + u * kRecThreads);
+        }
     }
     cp_async_commit();
 }
 
-template <int KP, int k>
+template <int KP, int S, int k>
 struct BwdLayer {
-    static __device__ __forceinline__ void run(const BwdCtx<KP>& x_, float (&p)[KP], float (&gbv)[16], float (&gcv)[16]) {
+    static __device__ __forceinline__ void run(const BwdCtx<KP, S>& x_, float (&p)[S][KP], float (&gbv)[16], float (&gcv)[16]) {
         using M_ = Mth<float>;
-        constexpr int NQ = KP / 16, q = k / 16;
+        constexpr int NQ = KP / 16, q = k / 16, W = S * kRecThreads;
         if ((k & 15) == 15) {                    // entering quarter q
-            if (q < NQ - 1 && q >= 1) bwd_issue_quarter<KP>(x_, q - 1);     // quarter q+1 is consumed: refill its slot
+            if (q < NQ - 1 && q >= 1) bwd_issue_quarter<KP, S>(x_, q - 1);     // quarter q+1 is consumed: refill its slot
             cp_async_wait_le(q >= 1 ? 1 : 0);
         }
-        const float* slot = x_.stage + (q & 1) * 16 * 2 * kRecThreads + 2 * (k & 15) * kRecThreads;
-        const float pin = slot[0];
-        const float t = slot[kRecThreads];
+        const float* slot = x_.stage + (q & 1) * 16 * 2 * W + 2 * (k & 15) * W;
         const float ck = x_.sc[k];
-        const float hp = fmaf(-t, t, 1.f);
-        const float x = fmaf(hp, ck, 1.f);
-        const float y = x_.se[k] + fabsf(x);
-        const float gx = M_::neg_copysign(M_::rcp(y), x) * x_.smask[k];
-        const float gt = fmaf(-2.f * ck * gx, t, p[k] + pin);
-        const float ga = gt * hp;
-        gcv[k & 15] = x_.ok ? gx * hp : 0.f;
-        gbv[k & 15] = x_.ok ? ga : 0.f;
-        x_.dst[(size_t)k * x_.ldn] = ga;
+        float ga[S];
+        float sum_b = 0.f, sum_c = 0.f;
+#pragma unroll
+        for (int u = 0; u < S; ++u) {
+            const float pin = slot[u * kRecThreads];
+            const float t = slot[W + u * kRecThreads];
+            const float hp = fmaf(-t, t, 1.f);
+            const float x = fmaf(hp, ck, 1.f);
+            const float y = x_.se[k] + fabsf(x);
+            const float gx = M_::neg_copysign(M_::rcp(y), x) * x_.smask[k];
+            const float gt = fmaf(-2.f * ck * gx, t, p[u][k] + pin);
+            ga[u] = gt * hp;
+            sum_c += x_.ok[u] ? gx * hp : 0.f;
+            sum_b += x_.ok[u] ? ga[u] : 0.f;
+            x_.dst[(size_t)k * x_.ldn + u * kRecThreads] = ga[u];
+        }
+        gcv[k & 15] = sum_c;
+        gbv[k & 15] = sum_b;
 #pragma unroll
         for (int i4 = 0; i4 < (k + 3) / 4; ++i4) {
             const float4 m = *reinterpret_cast<const float4*>(&x_.sM[k * KP + 4 * i4]);
-            if (4 * i4 + 0 < k) p[4 * i4 + 0] = fmaf(m.x, ga, p[4 * i4 + 0]);
-            if (4 * i4 + 1 < k) p[4 * i4 + 1] = fmaf(m.y, ga, p[4 * i4 + 1]);
-            if (4 * i4 + 2 < k) p[4 * i4 + 2] = fmaf(m.z, ga, p[4 * i4 + 2]);
-            if (4 * i4 + 3 < k) p[4 * i4 + 3] = fmaf(m.w, ga, p[4 * i4 + 3]);
+#pragma unroll
+            for (int u = 0; u < S; ++u) {
+                if (4 * i4 + 0 < k) p[u][4 * i4 + 0] = fmaf(m.x, ga[u], p[u][4 * i4 + 0]);
+                if (4 * i4 + 1 < k) p[u][4 * i4 + 1] = fmaf(m.y, ga[u], p[u][4 * i4 + 1]);
+                if (4 * i4 + 2 < k) p[u][4 * i4 + 2] = fmaf(m.z, ga[u], p[u][4 * i4 + 2]);
+                if (4 * i4 + 3 < k) p[u][4 * i4 + 3] = fmaf(m.w, ga[u], p[u][4 * i4 + 3]);
+            }
         }
         if ((k & 15) == 0) {        // layers k .. k+15 are complete: reduce them over the warp
             warp_reduce_multi<float, 16>(gbv, x_.lane);
@@ -280,12 +330,12 @@ struct BwdLayer {
                 x_.sg[KP + k + warp_slot<16>(x_.lane)] = gcv[0];
             }
         }
-        if constexpr (k > 0) BwdLayer<KP, k - 1>::run(x_, p, gbv, gcv);
+        if constexpr (k > 0) BwdLayer<KP, S, k - 1>::run(x_, p, gbv, gcv);
     }
 };
 
-template <int KP>
-__global__ void __launch_bounds__(kRecThreads, 4)
+template <int KP, int S>
+__global__ void __launch_bounds__(kRecThreads, S == 1 ? 4 : 2)
 rec_bwd_kernel(const float* __restrict__ PT, const float* __restrict__ TT, long long ldn, int n_act, int K,
                const float* __restrict__ Mrow, const float* __restrict__ c, float epsv, float* __restrict__ DT,
                float* __restrict__ part_g /* [gridDim][2][KP] : g_b | g_c */) {
@@ -294,25 +344,29 @@ rec_bwd_kernel(const float* __restrict__ PT, const float* __restrict__ TT, long 
     __shared__ float sc[KP], se[KP], smask[KP];
     __shared__ float sg[kRecThreads / 32][2 * KP];
     constexpr int NQ = KP / 16;
-    const int n = blockIdx.x * kRecThreads + threadIdx.x;
-    BwdCtx<KP> x_;
+    const int n = blockIdx.x * S * kRecThreads + threadIdx.x;
+    BwdCtx<KP, S> x_;
     x_.srcp = PT + n; x_.srct = TT + n; x_.dst = DT + n; x_.ldn = ldn;
     x_.sM = sM; x_.sc = sc; x_.se = se; x_.smask = smask; x_.sg = sg[threadIdx.x >> 5];
     x_.stage = dyn + KP * KP + threadIdx.x;
-    x_.ok = n < n_act; x_.lane = threadIdx.x & 31;
+#pragma unroll
+    for (int u = 0; u < S; ++u) x_.ok[u] = n + u * kRecThreads < n_act;
+    x_.lane = threadIdx.x & 31;
     for (int i = threadIdx.x; i < KP * KP / 4; i += kRecThreads) cp_async16(sM + 4 * i, Mrow + 4 * i);
-    bwd_issue_quarter<KP>(x_, NQ - 1);              // this group also carries M
-    if (NQ >= 2) bwd_issue_quarter<KP>(x_, NQ - 2);
+    bwd_issue_quarter<KP, S>(x_, NQ - 1);           // this group also carries M
+    if (NQ >= 2) bwd_issue_quarter<KP, S>(x_, NQ - 2);
     for (int i = threadIdx.x; i < KP; i += kRecThreads) {
         sc[i] = i < K ? c[i] : 0.f; se[i] = i < K ? epsv : 0.f; smask[i] = i < K ? 1.f : 0.f;
     }
     cp_async_wait_le(NQ >= 2 ? 1 : 0);
     __syncthreads();
-    float p[KP];
+    float p[S][KP];
 #pragma unroll
-    for (int k = 0; k < KP; ++k) p[k] = 0.f;
+    for (int u = 0; u < S; ++u)
+#pragma unroll
+        for (int k = 0; k < KP; ++k) p[u][k] = 0.f;
     float gcv[16], gbv[16];
-    BwdLayer<KP, KP - 1>::run(x_, p, gbv, gcv);
+    BwdLayer<KP, S, KP - 1>::run(x_, p, gbv, gcv);
     __syncthreads();
     if (threadIdx.x < 2 * KP) {
         float t = 0.f;
@@ -541,19 +595,23 @@ static cudaError_t launch_target(bool bwd, const float* z0, float* Y, int n_act,
 
 template <int KP>
 static cudaError_t launch_rec(bool fwd, const Layout& L, float* ws, int n_act, int K, const float* c, float epsv, cudaStream_t st) {
-    const int blocks = (n_act + kRecThreads - 1) / kRecThreads;
-    static bool attr_done = false;
+    constexpr int S = kRecS;
+    const int blocks = (n_act + S * kRecThreads - 1) / (S * kRecThreads);
+    static bool attr_done_dev[64] = {};           // the attribute is per device
+    int dev_id = 0;
+    cudaGetDevice(&dev_id);
+    bool& attr_done = attr_done_dev[dev_id & 63];
     if (!attr_done) {
-        cudaFuncSetAttribute(rec_fwd_kernel<KP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rec_fwd_smem<KP>());
-        cudaFuncSetAttribute(rec_bwd_kernel<KP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rec_bwd_smem<KP>());
+        cudaFuncSetAttribute(rec_fwd_kernel<KP, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rec_fwd_smem<KP, S>());
+        cudaFuncSetAttribute(rec_bwd_kernel<KP, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rec_bwd_smem<KP, S>());
         attr_done = true;
     }
     if (fwd)
-        rec_fwd_kernel<KP><<<blocks, kRecThreads, rec_fwd_smem<KP>(), st>>>(ws + L.AT, L.Nc, n_act, K, ws + L.Mt, c, epsv, ws + L.TT,
-                                                                           ws + L.part_ld);
+        rec_fwd_kernel<KP, S><<<blocks, kRecThreads, rec_fwd_smem<KP, S>(), st>>>(ws + L.AT, L.Nc, n_act, K, ws + L.Mt, c, epsv, ws + L.TT,
+                                                                                 ws + L.part_ld);
     else
-        rec_bwd_kernel<KP><<<blocks, kRecThreads, rec_bwd_smem<KP>(), st>>>(ws + L.AT, ws + L.TT, L.Nc, n_act, K, ws + L.M, c, epsv,
-                                                                           ws + L.DT, ws + L.part_g);
+        rec_bwd_kernel<KP, S><<<blocks, kRecThreads, rec_bwd_smem<KP, S>(), st>>>(ws + L.AT, ws + L.TT, L.Nc, n_act, K, ws + L.M, c, epsv,
+                                                                                 ws + L.DT, ws + L.part_g);
     return cudaGetLastError();
 }
 static cudaError_t launch_rec_any(bool fwd, const Layout& L, float* ws, int n_act, int K, const float* c, float epsv, cudaStream_t st) {
@@ -623,7 +681,7 @@ int gram_elbo_f32(bool bwd, const float* eps, long long N, int D, int K, const f
                                           nullptr, 0, 0, st, L.splits, ws + L.split56, !first)) != NF_OK) return rc;
         }
         chunk_totals_kernel<<<2 * K + 1, 256, 0, st>>>(ws + L.part_g, KP, K, bwd ? 1 : 0, ws + L.part_ld,
-                                                  (n_act + kRecThreads - 1) / kRecThreads, ws + L.part_t,
+                                                  (n_act + kRecS * kRecThreads - 1) / (kRecS * kRecThreads), ws + L.part_t,
                                                   (n_act + kTgtRows - 1) / kTgtRows, ws + L.acc);
         NF_CUDA_OK(cudaGetLastError());
         first = false;

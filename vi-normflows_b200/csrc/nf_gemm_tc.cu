@@ -494,7 +494,10 @@ int tc_gemm_stacked_f32(const float* A, long long lda, int M1, const float* A2, 
     size_t ring = (size_t)stages * (atmem ? tc::STAGE_BYTES_TS : tc::STAGE_BYTES);
     if (ring < kSlab) ring = kSlab;
     const size_t smem = ring + 1024;
-    static bool attr_done = false;
+    static bool attr_done_dev[64] = {};           // the attribute is per device
+    int dev_id = 0;
+    NF_CUDA_OK(cudaGetDevice(&dev_id));
+    bool& attr_done = attr_done_dev[dev_id & 63];
     if (!attr_done) {
         NF_CUDA_OK(cudaFuncSetAttribute(tc::gemm_tf32x3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)((size_t)tc::MAX_STAGES * tc::STAGE_BYTES + 1024)));
