@@ -36,7 +36,15 @@ int tc_gemm_stacked_f32(const float* A, long long lda, int M1, const float* A2, 
 
 namespace gram {
 
-constexpr int kRecThreads = 128;
+#ifndef NF_REC_THREADS
+#define NF_REC_THREADS 128
+#endif
+// Recurrence kernels: 128-thread blocks, four per SM.  Their bodies are ~4000 instructions of straight-line code (the
+// running values sit in registers, so nothing can be rolled) and instruction fetch is their largest stall reason; one
+// 512-thread block per SM whose warps re-align every sixteenth layer (to share fetched lines) was measured slower
+// (D=64, N=2^19: forward 127 vs 118 us, reverse 165 vs 146 us).  -DNF_REC_THREADS=512 rebuilds that variant.
+constexpr int kRecThreads = NF_REC_THREADS;
+constexpr int kRecBlocksPerSM = 512 / NF_REC_THREADS;
 constexpr int kMaxK = 64;
 constexpr int kMaxMix = 16;
 constexpr int kTgtRows = 32;         // rows per block of the target kernel
@@ -46,12 +54,13 @@ static inline int pad_k(int K) { return K <= 16 ? 16 : (K <= 32 ? 32 : 64); }
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // chunk pitch (samples): up to 32M elements of [Nc][D] (small chunks leave the GPU under-filled: every kernel of the
-// chain is a separate launch), a multiple of 256, no more than the job needs
+// chain is a separate launch), a multiple of 512, no more than the job needs
 static inline long long chunk_samples(long long N, int D) {
     long long nc = ((long long)32 << 20) / D;
     if (const char* e = getenv("NF_GRAM_CHUNK")) { const long long v = atoll(e); if (v >= 128) nc = v; }
-    nc = (nc + 255) / 256 * 256;          // whole blocks of the recurrence kernels (2 x 128 samples)
-    const long long need = (N + 255) / 256 * 256;
+    constexpr long long kBlk = 512;       // whole blocks of the recurrence kernels
+    nc = (nc + kBlk - 1) / kBlk * kBlk;
+    const long long need = (N + kBlk - 1) / kBlk * kBlk;
     return nc < need ? nc : need;
 }
 static inline int grad_splits(long long nc, int D) {
@@ -182,7 +191,7 @@ struct FwdLayer {
     static __device__ __forceinline__ void run(const FwdCtx<KP, S>& x_, float (&a)[S][KP], float (&prod)[S], float (&ld)[S]) {
         using M_ = Mth<float>;
         constexpr int NG = KP / 16, W = S * kRecThreads;
-        if (j > 0 && (j & 15) == 0) cp_async_wait_le(NG - 1 - j / 16);
+        if (j > 0 && (j & 15) == 0) { cp_async_wait_le(NG - 1 - j / 16); if (kRecThreads > 128) __syncthreads(); }
         float t[S];
 #pragma unroll
         for (int u = 0; u < S; ++u) {
@@ -208,7 +217,7 @@ struct FwdLayer {
 };
 
 template <int KP, int S>
-__global__ void __launch_bounds__(kRecThreads, S == 1 ? 4 : 2)
+__global__ void __launch_bounds__(kRecThreads, S == 1 ? kRecBlocksPerSM : 1)
 rec_fwd_kernel(const float* __restrict__ AT, long long ldn, int n_act, int K, const float* __restrict__ Mt,
                const float* __restrict__ c, float epsv, float* __restrict__ TT, float* __restrict__ part_ld) {
     constexpr int W = S * kRecThreads;            // samples per block
@@ -290,6 +299,7 @@ struct BwdLayer {
         if ((k & 15) == 15) {                    // entering quarter q
             if (q < NQ - 1 && q >= 1) bwd_issue_quarter<KP, S>(x_, q - 1);     // quarter q+1 is consumed: refill its slot
             cp_async_wait_le(q >= 1 ? 1 : 0);
+            if (kRecThreads > 128 && q < NQ - 1) __syncthreads();     // large-block variant: keep the warps in step
         }
         const float* slot = x_.stage + (q & 1) * 16 * 2 * W + 2 * (k & 15) * W;
         const float ck = x_.sc[k];
@@ -335,7 +345,7 @@ struct BwdLayer {
 };
 
 template <int KP, int S>
-__global__ void __launch_bounds__(kRecThreads, S == 1 ? 4 : 2)
+__global__ void __launch_bounds__(kRecThreads, S == 1 ? kRecBlocksPerSM : 1)
 rec_bwd_kernel(const float* __restrict__ PT, const float* __restrict__ TT, long long ldn, int n_act, int K,
                const float* __restrict__ Mrow, const float* __restrict__ c, float epsv, float* __restrict__ DT,
                float* __restrict__ part_g /* [gridDim][2][KP] : g_b | g_c */) {
