@@ -220,3 +220,28 @@ def test_device_training_loop_wide_matrix_product_vs_direct(monkeypatch):
     tgt = lambda z: torch.exp(pt.log_mvn(z, mu, ls))
     F0, _ = pt.script_value_and_grad(params, eps_all[0], tgt, 1e-7, K)
     assert abs(tr_g[0] - F0) <= 2e-4 * max(1.0, abs(F0))
+
+
+@pytest.mark.parametrize('D,K,N,chunk', [(64, 7, 3000, None), (128, 16, 5200, 512)])
+def test_gram_host_samples_session_matches_oracle(D, K, N, chunk, monkeypatch):
+    """NumPy samples go through the host-buffer session (nf_session_elbo_host_f32), which for wide D feeds the
+    matrix-product path piece by piece while the next piece uploads; with the chunk knob: eleven pieces, more than
+    the session has events.  Against the oracle, and against the same session forced onto the direct kernel."""
+    from nfcore.objective import SharedFlowObjective
+    from oracle import planar_torch as pt
+    monkeypatch.setenv('NF_GRAM', '1')
+    if chunk:
+        monkeypatch.setenv('NF_GRAM_CHUNK', str(chunk))
+    rs, z0, params, mu, ls = _gram_case(D, K, N, 17 * D + K)
+    tgt = lambda z: torch.exp(pt.log_mvn(z, mu, ls))
+    F_ref, g_ref = pt.script_value_and_grad(params, z0, tgt, 1e-7, K)
+    obj = SharedFlowObjective(('gaussdiag', mu, ls), K, D, dtype='float32')
+    F, grad = obj.value_and_grad(params, z0)
+    assert abs(F - F_ref) <= 2e-4 * max(1.0, abs(F_ref)), (F, F_ref)
+    assert _rel(grad, g_ref) <= 2e-4, _rel(grad, g_ref)
+    assert abs(obj.value(params, z0) - F_ref) <= 2e-4 * max(1.0, abs(F_ref))
+    monkeypatch.delenv('NF_GRAM')
+    monkeypatch.setenv('NF_NO_GRAM', '1')
+    F_d, grad_d = obj.value_and_grad(params, z0)
+    assert abs(F - F_d) <= 2e-4 * max(1.0, abs(F_ref))
+    assert _rel(grad, grad_d) <= 2e-4

@@ -653,53 +653,83 @@ bool gram_applicable(long long N, int D, int K, int target_id, int ntp) {
 
 size_t gram_workspace_bytes(long long N, int D, int K) { return gram::make_layout(N, D, K).total * sizeof(float); }
 
-int gram_elbo_f32(bool bwd, const float* eps, long long N, int D, int K, const float* w, const float* s, const float* b,
-                  const float* c, int target_id, const float* tp, int ntp, float epsv, float* out_F, float* g_w, float* g_s,
-                  float* g_b, float* g_c, void* workspace, cudaStream_t st) {
+// The evaluation in three parts, so that a caller that receives its samples piecewise (the host-buffer session, which
+// overlaps the upload of one piece with the arithmetic on the previous one) can feed pieces of at most gram_chunk_pitch()
+// samples: begin (layer products, cleared totals), one call per piece (running totals and gradient products accumulate),
+// end (results).  `layout_n` is the sample count the workspace was sized for; it fixes the layout.
+long long gram_chunk_pitch(long long layout_n, int D, int K) { return gram::make_layout(layout_n, D, K).Nc; }
+
+int gram_begin(long long layout_n, int D, int K, const float* w, const float* s, void* workspace, cudaStream_t st) {
     using namespace gram;
-    const Layout L = make_layout(N, D, K);
+    const Layout L = make_layout(layout_n, D, K);
     float* ws = reinterpret_cast<float*>(workspace);
     const int KP = L.KP;
     prep_kernel<<<KP, 256, 0, st>>>(w, s, K, D, KP, ws + L.M, ws + L.Mt, ws + L.ST, ws + L.acc);
     NF_CUDA_OK(cudaGetLastError());
     if (KP > K) NF_CUDA_OK(cudaMemsetAsync(ws + L.AT + (size_t)K * L.Nc, 0, (size_t)(KP - K) * L.Nc * sizeof(float), st));
+    return NF_OK;
+}
+
+int gram_piece(bool bwd, bool first, const float* z0, int n_act, long long layout_n, int D, int K, const float* w, const float* s,
+               const float* b, const float* c, int target_id, const float* tp, int ntp, float epsv, void* workspace, cudaStream_t st) {
+    using namespace gram;
+    const Layout L = make_layout(layout_n, D, K);
+    if (n_act < 1 || n_act > L.Nc) return NF_ERR_INVALID;
+    float* ws = reinterpret_cast<float*>(workspace);
+    const int KP = L.KP;
     int rc;
-    bool first = true;
-    for (long long c0 = 0; c0 < N; c0 += L.Nc) {
-        const int n_act = (int)((N - c0 < L.Nc) ? (N - c0) : L.Nc);
-        const float* z0 = eps + (size_t)c0 * D;
-        // product 1: A0^T[k][n] = sum_d z0[n][d] w[k][d] + b[k]
-        if ((rc = tc_gemm_f32(z0, D, w, D, n_act, K, D, nullptr, 0, ws + L.AT, L.Nc, b, 0, nullptr, 0, 0, st)) != NF_OK) return rc;
-        NF_CUDA_OK(launch_rec_any(true, L, ws, n_act, K, c, epsv, st));
-        // product 2: Y[n][d] = sum_k T^T[k][n] S^T[d][k]   (T is read layer-major, as the recurrence wrote it)
-        if ((rc = tc_gemm_stacked_f32(nullptr, 0, 0, ws + L.TT, L.Nc, n_act, ws + L.ST, KP, D, K, ws + L.Y, D, nullptr, 0, nullptr, 0,
-                                      nullptr, 0, 0, st, 1, nullptr, false)) != NF_OK) return rc;
-        if (target_id == NF_TARGET_GAUSSDIAG)
-            NF_CUDA_OK(launch_target<NF_TARGET_GAUSSDIAG>(bwd, z0, ws + L.Y, n_act, D, tp, ntp, epsv, ws + L.part_t, st));
-        else
-            NF_CUDA_OK(launch_target<NF_TARGET_MIXDIAG>(bwd, z0, ws + L.Y, n_act, D, tp, ntp, epsv, ws + L.part_t, st));
-        if (bwd) {
-            // product 3: P^T[k][n] = sum_d gz[n][d] s[k][d]
-            if ((rc = tc_gemm_f32(ws + L.Y, D, s, D, n_act, K, D, nullptr, 0, ws + L.AT, L.Nc, nullptr, 0, nullptr, 0, 0, st)) != NF_OK) return rc;
-            NF_CUDA_OK(launch_rec_any(false, L, ws, n_act, K, c, epsv, st));
-            // products 4-6 contract over the samples of the chunk (split across CTAs, fixed-order sums).  gz_K and z_0 are
-            // read as they lie in memory, sample-major; 5 and 6 share Delta^T and run as one product whose row blocks
-            // are T^T (rows [0, KP)) and z_0 (rows [64, 64 + D))
-            if ((rc = tc_gemm_stacked_f32(nullptr, 0, 0, ws + L.Y, D, D, ws + L.TT, L.Nc, K, n_act, ws + L.G4, K, nullptr, 0, nullptr, 0,
-                                          nullptr, 0, 0, st, L.splits, ws + L.split4, !first)) != NF_OK) return rc;
-            if ((rc = tc_gemm_stacked_f32(ws + L.TT, L.Nc, KP, z0, D, D, ws + L.DT, L.Nc, K, n_act, ws + L.G56, K, nullptr, 0, nullptr, 0,
-                                          nullptr, 0, 0, st, L.splits, ws + L.split56, !first)) != NF_OK) return rc;
-        }
-        chunk_totals_kernel<<<2 * K + 1, 256, 0, st>>>(ws + L.part_g, KP, K, bwd ? 1 : 0, ws + L.part_ld,
-                                                  (n_act + kRecS * kRecThreads - 1) / (kRecS * kRecThreads), ws + L.part_t,
-                                                  (n_act + kTgtRows - 1) / kTgtRows, ws + L.acc);
-        NF_CUDA_OK(cudaGetLastError());
-        first = false;
+    // product 1: A0^T[k][n] = sum_d z0[n][d] w[k][d] + b[k]
+    if ((rc = tc_gemm_f32(z0, D, w, D, n_act, K, D, nullptr, 0, ws + L.AT, L.Nc, b, 0, nullptr, 0, 0, st)) != NF_OK) return rc;
+    NF_CUDA_OK(launch_rec_any(true, L, ws, n_act, K, c, epsv, st));
+    // product 2: Y[n][d] = sum_k T^T[k][n] S^T[d][k]   (T is read layer-major, as the recurrence wrote it)
+    if ((rc = tc_gemm_stacked_f32(nullptr, 0, 0, ws + L.TT, L.Nc, n_act, ws + L.ST, KP, D, K, ws + L.Y, D, nullptr, 0, nullptr, 0,
+                                  nullptr, 0, 0, st, 1, nullptr, false)) != NF_OK) return rc;
+    if (target_id == NF_TARGET_GAUSSDIAG)
+        NF_CUDA_OK(launch_target<NF_TARGET_GAUSSDIAG>(bwd, z0, ws + L.Y, n_act, D, tp, ntp, epsv, ws + L.part_t, st));
+    else
+        NF_CUDA_OK(launch_target<NF_TARGET_MIXDIAG>(bwd, z0, ws + L.Y, n_act, D, tp, ntp, epsv, ws + L.part_t, st));
+    if (bwd) {
+        // product 3: P^T[k][n] = sum_d gz[n][d] s[k][d]
+        if ((rc = tc_gemm_f32(ws + L.Y, D, s, D, n_act, K, D, nullptr, 0, ws + L.AT, L.Nc, nullptr, 0, nullptr, 0, 0, st)) != NF_OK) return rc;
+        NF_CUDA_OK(launch_rec_any(false, L, ws, n_act, K, c, epsv, st));
+        // products 4-6 contract over the samples of the piece (split across CTAs, fixed-order sums).  gz_K and z_0 are
+        // read as they lie in memory, sample-major; 5 and 6 share Delta^T and run as one product whose row blocks
+        // are T^T (rows [0, KP)) and z_0 (rows [64, 64 + D))
+        if ((rc = tc_gemm_stacked_f32(nullptr, 0, 0, ws + L.Y, D, D, ws + L.TT, L.Nc, K, n_act, ws + L.G4, K, nullptr, 0, nullptr, 0,
+                                      nullptr, 0, 0, st, L.splits, ws + L.split4, !first)) != NF_OK) return rc;
+        if ((rc = tc_gemm_stacked_f32(ws + L.TT, L.Nc, KP, z0, D, D, ws + L.DT, L.Nc, K, n_act, ws + L.G56, K, nullptr, 0, nullptr, 0,
+                                      nullptr, 0, 0, st, L.splits, ws + L.split56, !first)) != NF_OK) return rc;
     }
-    finish_kernel<<<dim3(K, (D + 127) / 128), 128, 0, st>>>(ws + L.acc, ws + L.G4, ws + L.G56, w, s, K, KP, D, bwd ? 1 : 0, out_F, g_w, g_s,
-                                                           g_b, g_c);
+    chunk_totals_kernel<<<2 * K + 1, 256, 0, st>>>(ws + L.part_g, KP, K, bwd ? 1 : 0, ws + L.part_ld,
+                                              (n_act + kRecS * kRecThreads - 1) / (kRecS * kRecThreads), ws + L.part_t,
+                                              (n_act + kTgtRows - 1) / kTgtRows, ws + L.acc);
     NF_CUDA_OK(cudaGetLastError());
     return NF_OK;
+}
+
+int gram_end(bool bwd, long long layout_n, int D, int K, const float* w, const float* s, float* out_F, float* g_w, float* g_s,
+             float* g_b, float* g_c, void* workspace, cudaStream_t st) {
+    using namespace gram;
+    const Layout L = make_layout(layout_n, D, K);
+    float* ws = reinterpret_cast<float*>(workspace);
+    finish_kernel<<<dim3(K, (D + 127) / 128), 128, 0, st>>>(ws + L.acc, ws + L.G4, ws + L.G56, w, s, K, L.KP, D, bwd ? 1 : 0, out_F, g_w,
+                                                           g_s, g_b, g_c);
+    NF_CUDA_OK(cudaGetLastError());
+    return NF_OK;
+}
+
+int gram_elbo_f32(bool bwd, const float* eps, long long N, int D, int K, const float* w, const float* s, const float* b,
+                  const float* c, int target_id, const float* tp, int ntp, float epsv, float* out_F, float* g_w, float* g_s,
+                  float* g_b, float* g_c, void* workspace, cudaStream_t st) {
+    const long long pitch = gram_chunk_pitch(N, D, K);
+    int rc = gram_begin(N, D, K, w, s, workspace, st);
+    if (rc != NF_OK) return rc;
+    for (long long c0 = 0; c0 < N; c0 += pitch) {
+        const int n_act = (int)((N - c0 < pitch) ? (N - c0) : pitch);
+        rc = gram_piece(bwd, c0 == 0, eps + (size_t)c0 * D, n_act, N, D, K, w, s, b, c, target_id, tp, ntp, epsv, workspace, st);
+        if (rc != NF_OK) return rc;
+    }
+    return gram_end(bwd, N, D, K, w, s, out_F, g_w, g_s, g_b, g_c, workspace, st);
 }
 
 }  // namespace nf

@@ -769,6 +769,19 @@ static int elbo_entry(const T* eps, int64_t N, int D, int K, const T* w, const T
 // in NumPy).  A session owns the device-side staging for that call shape: the samples are sent in
 // chunks on a copy stream while the compute stream runs the objective kernel on the chunks that
 // have landed; all chunks write partial-sum rows into one workspace and a single row kernel sums them.
+// nf_elbo_gram.cu: the matrix-product formulation for wide latent spaces (float32 only)
+bool gram_applicable(long long N, int D, int K, int target_id, int ntp);      // target_id < 0: any supported target
+size_t gram_workspace_bytes(long long N, int D, int K);
+int gram_elbo_f32(bool bwd, const float* eps, long long N, int D, int K, const float* w, const float* s, const float* b,
+                  const float* c, int target_id, const float* tp, int ntp, float epsv, float* out_F, float* g_w, float* g_s,
+                  float* g_b, float* g_c, void* workspace, cudaStream_t st);
+long long gram_chunk_pitch(long long layout_n, int D, int K);
+int gram_begin(long long layout_n, int D, int K, const float* w, const float* s, void* workspace, cudaStream_t st);
+int gram_piece(bool bwd, bool first, const float* z0, int n_act, long long layout_n, int D, int K, const float* w, const float* s,
+               const float* b, const float* c, int target_id, const float* tp, int ntp, float epsv, void* workspace, cudaStream_t st);
+int gram_end(bool bwd, long long layout_n, int D, int K, const float* w, const float* s, float* out_F, float* g_w, float* g_s,
+             float* g_b, float* g_c, void* workspace, cudaStream_t st);
+
 constexpr int kSessionMaxChunks = 8;
 constexpr int64_t kSessionChunkSamples = 1 << 18;
 
@@ -782,6 +795,8 @@ struct Session {
     void *lc_pin = nullptr, *out_pin = nullptr;
     size_t ws_chunk_bytes = 0, tp_cap = 0;
     int n_out = 0;
+    void* gram_ws = nullptr;          // float32, wide D: workspace of the matrix-product path, sized for gram_layout_n samples
+    long long gram_layout_n = 0;
 };
 
 static inline void session_free(Session* S) {
@@ -791,7 +806,7 @@ static inline void session_free(Session* S) {
     for (auto& e : S->ev) if (e) cudaEventDestroy(e);
     if (S->s_copy) cudaStreamDestroy(S->s_copy);
     if (S->s_comp) cudaStreamDestroy(S->s_comp);
-    cudaFree(S->eps_dev); cudaFree(S->lc_dev); cudaFree(S->tp_dev); cudaFree(S->out_dev); cudaFree(S->ws_dev);
+    cudaFree(S->eps_dev); cudaFree(S->lc_dev); cudaFree(S->tp_dev); cudaFree(S->out_dev); cudaFree(S->ws_dev); cudaFree(S->gram_ws);
     cudaFreeHost(S->lc_pin); cudaFreeHost(S->out_pin);
     delete S;
 }
@@ -816,6 +831,9 @@ static inline int session_create(Session** out, int64_t max_samples, int D, int 
     ok(cudaMalloc(&S->tp_dev, S->tp_cap * S->elem));
     ok(cudaMalloc(&S->out_dev, (size_t)S->n_out * S->elem));
     ok(cudaMalloc(&S->ws_dev, S->ws_chunk_bytes * kSessionMaxChunks));
+    S->gram_layout_n = max_samples < kSessionChunkSamples ? max_samples : kSessionChunkSamples;
+    if (elem_size == 4 && gram_applicable(1 << 30, D, K, -1, 0))        // shape supported (the per-call cost model decides later)
+        ok(cudaMalloc(&S->gram_ws, gram_workspace_bytes(S->gram_layout_n, D, K)));
     ok(cudaMallocHost(&S->lc_pin, (size_t)(2 * K * D + 2 * K + S->tp_cap) * S->elem));
     ok(cudaMallocHost(&S->out_pin, (size_t)S->n_out * S->elem));
     if (e != cudaSuccess) { nf_set_last_cuda_error(e); session_free(S); return NF_ERR_CUDA; }
@@ -842,6 +860,36 @@ static int session_elbo_host(Session* S, const T* eps_host, int64_t N, const T* 
     T* eps = reinterpret_cast<T*>(S->eps_dev);
     int rc = elbo_validate<T>(eps, N, D, K, w, s, b, c, target_id, ntp > 0 ? tp : nullptr, ntp);
     if (rc != NF_OK) return rc;
+    if constexpr (sizeof(T) == 4) {
+        if (S->gram_ws && N > 0 && gram_applicable(N, D, K, target_id, ntp)) {
+            // wide D: pieces of at most one chunk pitch, each uploaded on the copy stream while the previous one is worked on
+            const long long pitch = gram_chunk_pitch(S->gram_layout_n, D, K);
+            int64_t pieces = (N + pitch - 1) / pitch;
+            if (pieces < 4 && N >= 4 * 4096) pieces = 4;                       // a few pieces even when one would do, for the overlap
+            const int64_t per = ((N + pieces - 1) / pieces + 511) & ~(int64_t)511;
+            T* out = reinterpret_cast<T*>(S->out_dev);
+            rc = gram_begin(S->gram_layout_n, D, K, w, s, S->gram_ws, S->s_comp);
+            if (rc != NF_OK) return rc;
+            int i = 0;
+            for (int64_t lo = 0; lo < N; lo += per, ++i) {
+                const int64_t n = (N - lo < per) ? N - lo : per;
+                NF_CUDA_OK(cudaMemcpyAsync(eps + lo * D, eps_host + lo * D, (size_t)n * D * sizeof(T), cudaMemcpyHostToDevice, S->s_copy));
+                NF_CUDA_OK(cudaEventRecord(S->ev[i % kSessionMaxChunks], S->s_copy));
+                NF_CUDA_OK(cudaStreamWaitEvent(S->s_comp, S->ev[i % kSessionMaxChunks], 0));
+                rc = gram_piece(backward != 0, i == 0, eps + lo * D, (int)n, S->gram_layout_n, D, K, w, s, b, c, target_id,
+                                ntp > 0 ? tp : nullptr, ntp, epsv, S->gram_ws, S->s_comp);
+                if (rc != NF_OK) return rc;
+            }
+            rc = gram_end(backward != 0, S->gram_layout_n, D, K, w, s, out, out + 3, out + 3 + K * D, out + 3 + 2 * K * D,
+                          out + 3 + 2 * K * D + K, S->gram_ws, S->s_comp);
+            if (rc != NF_OK) return rc;
+            NF_CUDA_OK(cudaMemcpyAsync(S->out_pin, out, (size_t)S->n_out * sizeof(T), cudaMemcpyDeviceToHost, S->s_comp));
+            NF_CUDA_OK(cudaStreamSynchronize(S->s_comp));
+            const T* op = reinterpret_cast<const T*>(S->out_pin);
+            for (int j = 0; j < S->n_out; ++j) out_host[j] = op[j];
+            return NF_OK;
+        }
+    }
     int nch = (int)((N + kSessionChunkSamples - 1) / kSessionChunkSamples);
     if (nch < 1) nch = 1;
     if (nch > kSessionMaxChunks) nch = kSessionMaxChunks;
@@ -972,13 +1020,6 @@ script_step_kernel(T* __restrict__ params /*[2KD+K]*/, T* __restrict__ lc /*w|s|
         lc[2 * K * D + K + k] = paper ? ws : wu;
     }
 }
-
-// nf_elbo_gram.cu: the matrix-product formulation for wide latent spaces (float32 only)
-bool gram_applicable(long long N, int D, int K, int target_id, int ntp);      // target_id < 0: any supported target
-size_t gram_workspace_bytes(long long N, int D, int K);
-int gram_elbo_f32(bool bwd, const float* eps, long long N, int D, int K, const float* w, const float* s, const float* b,
-                  const float* c, int target_id, const float* tp, int ntp, float epsv, float* out_F, float* g_w, float* g_s,
-                  float* g_b, float* g_c, void* workspace, cudaStream_t st);
 
 template <typename T>
 static int script_train(const T* eps_all, int64_t n_iters, int64_t N, int D, int K, T* params, int target_id,
