@@ -134,6 +134,11 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
     const int nkb = max(0, min(p.kb_per_split, nkb_all - kb0));
     if (p.C) p.C += (long long)blockIdx.z * p.split_stride;
 
+    if (threadIdx.x == 32) {       // descriptor fetch off the critical path of the first loads
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a2) : "memory");
+    }
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(&full_bar[s], 1);
@@ -217,6 +222,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
         for (int kb = 0; kb < nkb; ++kb) {
             const int s = kb % STAGES, it = kb / STAGES;
             mbar_wait(&full_bar[s], it & 1);
+            if (dbg && kb == 0 && t == 64) p.dbg[8] = clock64();
             uint8_t* st = smem + (size_t)s * STAGE_BYTES_;
             if (ATMEM) {
                 if (warp < 4) {
@@ -286,6 +292,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy writes -> visible to UMMA
             mbar_arrive(&split_bar[s]);
+            if (dbg && kb == 0 && t == 64) p.dbg[9] = clock64();
         }
         // epilogue: warp q = warp - 4 owns TMEM lanes 32q .. 32q+31 = rows m0 + 32q + lane
         if (warp >= 4) {
@@ -474,7 +481,7 @@ int tc_gemm_stacked_f32(const float* A, long long lda, int M1, const float* A2, 
     if (M2 > 0 && (m_split % tc::BM) != 0) { if (!tc::make_map(&mah, A, M1, K, lda, 64)) return NF_ERR_UNSUPPORTED; }
     else mah = mb;
     static long long* dbg_buf = nullptr;
-    if (getenv("NF_GEMM_DBG") && !dbg_buf) cudaMallocManaged(&dbg_buf, 64);
+    if (getenv("NF_GEMM_DBG") && !dbg_buf) cudaMallocManaged(&dbg_buf, 128);
     const int nkb_all = (K + tc::BK - 1) / tc::BK;
     if (splits > nkb_all) splits = nkb_all;
     if (splits < 1 || !split_ws || bias || act || CT || mask || ldc != N) {
@@ -516,8 +523,9 @@ int tc_gemm_stacked_f32(const float* A, long long lda, int M1, const float* A2, 
     }
     if (dbg_buf) {
         cudaStreamSynchronize(st);
-        fprintf(stderr, "[gemm dbg] M=%d N=%d K=%d setup=%lld | epilogue: tmem->smem %lld, C rows %lld, CT %lld clk\n", M, N, K,
-                dbg_buf[1] - dbg_buf[0], dbg_buf[2] - dbg_buf[5], dbg_buf[3] - dbg_buf[2], dbg_buf[6] - dbg_buf[3]);
+        fprintf(stderr, "[gemm dbg] M=%d N=%d K=%d stages=%d kb/cta=%d setup=%lld tile-landed=%lld split=%lld first-mma=%lld rest-of-k=%lld | epilogue: tmem->smem %lld, C rows %lld, CT %lld | total %lld clk\n",
+                M, N, K, stages, kbps, dbg_buf[1] - dbg_buf[0], dbg_buf[8] - dbg_buf[1], dbg_buf[9] - dbg_buf[8], dbg_buf[4] - dbg_buf[1], dbg_buf[5] - dbg_buf[4], dbg_buf[2] - dbg_buf[5],
+                dbg_buf[3] - dbg_buf[2], dbg_buf[6] - dbg_buf[3], dbg_buf[7] - dbg_buf[0]);
     }
     return NF_OK;
 }
