@@ -20,6 +20,7 @@
 // to global memory; here the gradient accumulators are output tiles of products 4-6.
 // Samples are processed in chunks of up to 32M/D (the workspace holds one chunk's intermediates).
 // float32, D % 4 == 0, K <= 64, targets GAUSSDIAG / MIXDIAG (<= 16 components).
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include "nf_common.cuh"
@@ -633,21 +634,31 @@ static cudaError_t launch_rec_any(bool fwd, const Layout& L, float* ws, int n_ac
 }  // namespace gram
 
 // ---- interface used by nf_elbo_f32.cu --------------------------------------------------------------
-// Shapes the path supports, and among those the ones where it is expected to win.  Cost models fitted on a B200
-// (profiles/r01f_gram_crossover.txt), in microseconds: the direct kernel spends ~0.94 ns per (sample, layer,
-// coordinate), growing with D beyond 128 where its per-warp gradient records fall out of L2; this path has ~100 us
-// of fixed launch cost, ~11.5 ns per (sample, coordinate) in the products and the target kernel, and ~0.14 ns per
-// (sample, layer^2) in the recurrences.  NF_GRAM=1 forces this path where it is supported, NF_NO_GRAM=1 forbids it.
+// Shapes the path supports, and among those the ones where it is expected to win.  Both cost models (microseconds) were
+// fitted on a B200 over D = 32..256, K = 16..64, N = 2^10..2^19 (profiles/r01h_gram_crossover.txt):
+//   this path     a floor of ~(78 + 0.45 K) us for its chain of launches, then
+//                 per sample max(0.67 ns, 11.5 ps D) in the products and the target kernel + 0.143 ps K^2 in the recurrences;
+//   direct kernel one under-filled wave costs T0 = 10 + K (0.35 + 0.0078 D) us (at least 29), beyond it
+//                 0.79 ps per (sample, layer, coordinate), growing as (D/64)^0.65 above D = 64 where the per-warp
+//                 gradient records spill out of L2 (1.05 ps at D <= 32, where few lanes share a sample).
+// NF_GRAM=1 forces this path where it is supported, NF_NO_GRAM=1 forbids it.
 bool gram_applicable(long long N, int D, int K, int target_id, int ntp) {
     if (getenv("NF_NO_GRAM")) return false;
     if (D < 32 || D > 512 || (D % 4) != 0 || K < 1 || K > gram::kMaxK || N < 1) return false;
     if (target_id == NF_TARGET_MIXDIAG) { if (ntp / (1 + 2 * D) > gram::kMaxMix) return false; }
     else if (target_id >= 0 && target_id != NF_TARGET_GAUSSDIAG) return false;
     if (const char* e = getenv("NF_GRAM")) { if (atoi(e) != 0) return true; }
-    if (N < 1024) return false;
+    if (N < 512) return false;
     const double n = (double)N;
-    const double t_direct = n * K * D * 0.94e-3 * (D > 115 ? D / 115.0 : 1.0) * 1e-3;
-    const double t_gram = 100.0 + n * (11.5e-3 * D + 0.143e-3 * K * K) * 1e-3;
+    const double floor_g = 78.0 + 0.45 * K;
+    const double per_d = 11.5e-6 * D > 0.67e-3 ? 11.5e-6 * D : 0.67e-3;
+    const double lin_g = floor_g - 30.0 + n * (per_d + 0.143e-6 * K * K);
+    const double t_gram = lin_g > floor_g ? lin_g : floor_g;
+    double t0 = 10.0 + K * (0.35 + 0.0078 * D);
+    if (t0 < 29.0) t0 = 29.0;
+    const double cd = D <= 32 ? 1.05e-6 : 0.79e-6 * (D <= 64 ? 1.0 : pow(D / 64.0, 0.65));
+    const double lin_d = 0.6 * t0 + n * K * D * cd;
+    const double t_direct = lin_d > t0 ? lin_d : t0;
     return t_gram < t_direct;
 }
 
