@@ -85,9 +85,10 @@ int nf_check_device(void);
  * ------------------------------------------------------------------------- */
 size_t nf_planar_elbo_workspace_bytes(int K, int D, int elem_size);
 /* Workspace that also lets a call over N samples take the fastest path the library has for the shape:
- * for float32 and 32 <= D (D % 4 == 0), K <= 64, N >= 1024 and the GAUSSDIAG / MIXDIAG targets that is the
- * matrix-product formulation (csrc/nf_elbo_gram.cu), which keeps the intermediates of a chunk of samples
- * (about 4K + 3D floats per sample, chunks of up to 32M/D samples) in the workspace.  Never smaller than
+ * for float32, 32 <= D <= 512 (D % 4 == 0), K <= 64 and the GAUSSDIAG / MIXDIAG targets that can be the
+ * matrix-product formulation (csrc/nf_elbo_gram.cu; the library picks it where its fitted cost model says it wins,
+ * roughly from 2^15 samples at D = 64 down to 2^10 at D = 256), which keeps the intermediates of a chunk of
+ * samples (about 3 * 64 + D floats per sample, chunks of up to 32M/D samples) in the workspace.  Never smaller than
  * nf_planar_elbo_workspace_bytes(); a call given less than this runs the direct kernel.  Same quantity
  * (get_data.py:97-115), same outputs.  No counterpart in the reference (NumPy allocates as it goes). */
 size_t nf_planar_elbo_workspace_bytes_n(int64_t N, int K, int D, int elem_size);
