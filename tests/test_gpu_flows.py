@@ -137,7 +137,7 @@ def _gram_case(D, K, N, seed):
 
 
 @pytest.mark.parametrize('D,K,N,chunk', [(32, 5, 1500, None), (64, 7, 2000, None), (100, 16, 1100, None),
-                                         (256, 64, 1200, None), (64, 32, 3000, 512), (128, 9, 2500, 1024), (512, 33, 1050, None)])
+                                         (256, 64, 1200, None), (64, 32, 3000, 512), (128, 9, 2500, 1024), (512, 33, 1050, None), (32, 1, 700, None), (64, 2, 513, None)])
 def test_gram_free_energy_matches_oracle(D, K, N, chunk, monkeypatch):
     """float32, D % 4 == 0, K <= 64 can take the tensor-core path (forced here); ragged N, K that is not a multiple
     of 4, and (through the chunk knob) several chunks with a short last one.  Same oracle and tolerance as the
