@@ -159,6 +159,16 @@ int nf_script_train_f64(const double* eps_all, int64_t n_iters, int64_t N, int D
                         double step_size, double h1, double h2, double h3, double* opt_state, double* trace_F,
                         void* workspace, size_t workspace_bytes, void* stream);
 
+/* Host-side parameter algebra of the shared-parameter path (float64, K*D numbers, no GPU involved).
+ * get_data.py:106-108 derives the step vector u_hat and the log-det coefficient w.u from the raw (w, u) inside
+ * the objective; the entry points above take them as inputs (s, c) and return gradients with respect to them.
+ *   nf_script_constants_host : params [W | U | B] (get_data.py:74-78 layout) -> lc [w | s | b | c]
+ *   nf_script_chain_host     : g [g_w | g_s | g_b | g_c] -> dparams [dW | dU | dB] = scale * d/d(params)
+ * semantics 0: script (get_data.py:106-108: ||w|| not squared, c = w.u); 1: paper (Rezende & Mohamed eq. 10-12). */
+int nf_script_constants_host(const double* params, int K, int D, int semantics, double* lc);
+int nf_script_chain_host(const double* params, const double* g, int K, int D, int semantics, double scale,
+                         double* dparams);
+
 /* nf_planar_elbo_fwd_bwd_f32 for callers that must not allocate device memory.  It has no
  * counterpart in the reference (which never touches a GPU); it exists for host programs
  * whose device memory was all handed out at start-up, or for which cudaMalloc/cudaFree --

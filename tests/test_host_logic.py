@@ -93,3 +93,29 @@ def test_resolve_target():
         resolve_target(lambda z: z, 2)
     with pytest.raises(nfcore.NFError):
         resolve_target('p1', 3)
+
+
+@pytest.mark.parametrize('semantics', ['script', 'paper'])
+@pytest.mark.parametrize('K,D', [(1, 1), (8, 2), (5, 40)])
+def test_c_host_algebra_matches_numpy_algebra(semantics, K, D):
+    """nf_script_constants_host / nf_script_chain_host (plain C in libnfcore, no GPU needed) against the NumPy
+    statement of the same map and chain rule in nfcore/semantics.py (which the oracle tests pin to get_data.py:106-108)."""
+    import ctypes
+    from nfcore import _lib, semantics as sem
+    lib = _lib.load()
+    rs = np.random.RandomState(K * 100 + D)
+    W, U, B = rs.randn(K, D), rs.randn(K, D), rs.randn(K)
+    p = sem.pack(W, U, B)
+    sid = sem.SEMANTICS.index(semantics)
+    lc = np.empty(2 * K * D + 2 * K)
+    assert lib.nf_script_constants_host(ctypes.c_void_p(p.ctypes.data), K, D, sid, ctypes.c_void_p(lc.ctypes.data)) == 0
+    S, c = sem.forward(W, U, semantics)
+    np.testing.assert_allclose(lc, np.concatenate([W.ravel(), S.ravel(), B, c]), rtol=1e-13, atol=1e-14)
+    g = rs.randn(2 * K * D + 2 * K)
+    out = np.empty(2 * K * D + K)
+    assert lib.nf_script_chain_host(ctypes.c_void_p(p.ctypes.data), ctypes.c_void_p(g.ctypes.data), K, D, sid,
+                                    ctypes.c_double(0.25), ctypes.c_void_p(out.ctypes.data)) == 0
+    dW, dU, dB = sem.backward(W, U, g[:K * D].reshape(K, D), g[K * D:2 * K * D].reshape(K, D), g[2 * K * D:2 * K * D + K],
+                              g[2 * K * D + K:], semantics)
+    np.testing.assert_allclose(out, 0.25 * sem.pack(dW, dU, dB), rtol=1e-12, atol=1e-13)
+    assert lib.nf_script_constants_host(None, K, D, sid, ctypes.c_void_p(lc.ctypes.data)) != 0

@@ -33,6 +33,8 @@ PROTOTYPES = {
     'nf_version': (c_int, []),
     'nf_built_for_sm': (c_int, []),
     'nf_check_device': (c_int, []),
+    'nf_script_constants_host': (c_int, [c_void_p, c_int, c_int, c_int, c_void_p]),
+    'nf_script_chain_host': (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, ctypes.c_double, c_void_p]),
     'nf_planar_elbo_workspace_bytes': (c_size_t, [c_int, c_int, c_int]),
     'nf_planar_elbo_workspace_bytes_n': (c_size_t, [c_int64, c_int, c_int, c_int]),
     'nf_planar_elbo_fwd_bwd_f32': (c_int, _elbo_args(c_float)),

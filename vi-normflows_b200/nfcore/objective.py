@@ -120,10 +120,32 @@ class SharedFlowObjective:
         except Exception:
             pass
 
+    # -- host-side parameter algebra (libnfcore, plain C: the NumPy version costs ~85 us per call) ----
+    def _constants(self, params):
+        """[W | U | B] float64 -> ([w | s | b | c] float64, the contiguous float64 parameter vector)."""
+        lib = _lib.load()
+        p = np.ascontiguousarray(params, dtype=np.float64).ravel()
+        if p.size != 2 * self.K * self.D + self.K:
+            raise NFError('params must have 2*K*D + K = %d entries, got %d' % (2 * self.K * self.D + self.K, p.size))
+        lc = np.empty(self.n_lc, dtype=np.float64)
+        _lib.check(lib.nf_script_constants_host(ctypes.c_void_p(p.ctypes.data), self.K, self.D,
+                                                sem.SEMANTICS.index(self.semantics), ctypes.c_void_p(lc.ctypes.data)))
+        return lc, p
+
+    def _chain(self, p, res, n):
+        """res = [F parts (3) | g_w | g_s | g_b | g_c] float64 -> d(sum F)/d[W | U | B] / n."""
+        lib = _lib.load()
+        g = np.ascontiguousarray(res[3:], dtype=np.float64)
+        out = np.empty(p.size, dtype=np.float64)
+        _lib.check(lib.nf_script_chain_host(ctypes.c_void_p(p.ctypes.data), ctypes.c_void_p(g.ctypes.data), self.K, self.D,
+                                            sem.SEMANTICS.index(self.semantics), ctypes.c_double(1.0 / n),
+                                            ctypes.c_void_p(out.ctypes.data)))
+        return out
+
     # -- host-buffer path: nf_session_elbo_host_* (chunked H2D overlapped with the kernels) ----
     def _host_eval(self, params, z0, backward):
         """z0 in host memory (NumPy array or CPU torch tensor, pinned or not) -> float64 result vector
-        [F parts (3) | g_w | g_s | g_b | g_c] (sums) and (W, U)."""
+        [F parts (3) | g_w | g_s | g_b | g_c] (sums), N and the float64 parameter vector."""
         lib = _lib.load()
         if isinstance(z0, torch.Tensor):
             if z0.dtype != self.dtype or not z0.is_contiguous():
@@ -146,9 +168,8 @@ class SharedFlowObjective:
             with torch.cuda.device(self.device):
                 _lib.check(lib.nf_session_create(ctypes.byref(h), cap, D, K, self.np_dtype.itemsize))
             self._session, self._session_cap = h, cap
-        W, U, B = sem.unpack(np.asarray(params, dtype=np.float64), K, D)
-        S, c = sem.forward(W, U, self.semantics)
-        lc = np.concatenate([W.ravel(), S.ravel(), B, c]).astype(self.np_dtype)
+        lc64, p64 = self._constants(params)
+        lc = lc64.astype(self.np_dtype)
         out = np.empty(3 + self.n_lc, dtype=self.np_dtype)
         tp = self._tparams_host
         fn = lib.nf_session_elbo_host_f32 if self.np_dtype == np.float32 else lib.nf_session_elbo_host_f64
@@ -158,7 +179,7 @@ class SharedFlowObjective:
                 creal(self.log_eps), 1 if backward else 0, ctypes.c_void_p(out.ctypes.data))
         _lib.check(rc)
         self.launches += 2
-        return out.astype(np.float64), N, W, U
+        return out.astype(np.float64), N, p64
 
     def _is_host(self, z0):
         return self.group is None and not (isinstance(z0, torch.Tensor) and z0.is_cuda)
@@ -198,13 +219,8 @@ class SharedFlowObjective:
     # -- evaluation ----------------------------------------------------------------------
     def _launch(self, params, eps_dev, backward):
         K, D = self.K, self.D
-        W, U, B = sem.unpack(np.asarray(params, dtype=np.float64), K, D)
-        S, c = sem.forward(W, U, self.semantics)
-        host = self._lc_host.numpy()
-        host[:K * D] = W.ravel()
-        host[K * D:2 * K * D] = S.ravel()
-        host[2 * K * D:2 * K * D + K] = B
-        host[2 * K * D + K:] = c
+        lc64, p64 = self._constants(params)
+        self._lc_host.numpy()[:] = lc64
         self._lc.copy_(self._lc_host, non_blocking=True)
         lc = self._lc
         w = lc[:K * D].view(K, D)
@@ -216,7 +232,7 @@ class SharedFlowObjective:
                r[3 + 2 * K * D:3 + 2 * K * D + K], r[3 + 2 * K * D + K:]) if backward else (r[:3], None, None, None, None)
         ops.planar_elbo(eps_dev, w, s, b, cc, self.target_name, self.tparams, self.log_eps, backward, out)
         self.launches += 2
-        return W, U
+        return p64
 
     def _fetch(self, n_local):
         """all-reduce (when sharded) + D2H of [F parts | grads]; returns float64 array and global N."""
@@ -236,22 +252,16 @@ class SharedFlowObjective:
 
     def value_and_grad(self, params, z0):
         if self._is_host(z0):
-            res, n, W, U = self._host_eval(params, z0, True)
+            res, n, p64 = self._host_eval(params, z0, True)
         else:
             eps_dev = self.stage_samples(z0)
-            W, U = self._launch(params, eps_dev, True)
+            p64 = self._launch(params, eps_dev, True)
             res, n = self._fetch(eps_dev.shape[0])
-        K, D = self.K, self.D
-        g_w = res[3:3 + K * D].reshape(K, D)
-        g_s = res[3 + K * D:3 + 2 * K * D].reshape(K, D)
-        g_b = res[3 + 2 * K * D:3 + 2 * K * D + K]
-        g_c = res[3 + 2 * K * D + K:]
-        dW, dU, dB = sem.backward(W, U, g_w, g_s, g_b, g_c, self.semantics)
-        return res[0] / n, sem.pack(dW, dU, dB) / n
+        return res[0] / n, self._chain(p64, res, n)
 
     def value(self, params, z0):
         if self._is_host(z0):
-            res, n, _, _ = self._host_eval(params, z0, False)
+            res, n, _ = self._host_eval(params, z0, False)
             return res[0] / max(n, 1)
         eps_dev = self.stage_samples(z0)
         self._launch(params, eps_dev, False)
@@ -261,7 +271,7 @@ class SharedFlowObjective:
     def metrics(self, params, z0):
         """(mean log q_K, mean log p) -- get_data.py:80-95 ``other_metrics``."""
         if self._is_host(z0):
-            res, n, _, _ = self._host_eval(params, z0, False)
+            res, n, _ = self._host_eval(params, z0, False)
             return res[1] / max(n, 1), res[2] / max(n, 1)
         eps_dev = self.stage_samples(z0)
         self._launch(params, eps_dev, False)
