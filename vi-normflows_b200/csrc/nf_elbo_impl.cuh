@@ -890,7 +890,13 @@ static int session_elbo_host(Session* S, const T* eps_host, int64_t N, const T* 
             return NF_OK;
         }
     }
-    int nch = (int)((N + kSessionChunkSamples - 1) / kSessionChunkSamples);
+    // upload granularity: NF_SESSION_CHUNK=<samples> overrides (tuning knob, read once)
+    static const int64_t chunk_samples = []() {
+        const char* e = getenv("NF_SESSION_CHUNK");
+        const long long v = e ? atoll(e) : 0;
+        return (int64_t)(v >= 1024 ? v : kSessionChunkSamples);
+    }();
+    int nch = (int)((N + chunk_samples - 1) / chunk_samples);
     if (nch < 1) nch = 1;
     if (nch > kSessionMaxChunks) nch = kSessionMaxChunks;
     int64_t per = ((N + nch - 1) / nch + 1023) & ~(int64_t)1023;       // keeps every chunk 16-byte aligned
