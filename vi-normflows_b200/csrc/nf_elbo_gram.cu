@@ -107,14 +107,16 @@ static Layout make_layout(long long N, int D, int K) {
 
 // ------------------------------------------------------------------------------------------------
 // set-up: M = W S^T (both orientations, scaled for the exp2-based tanh, strictly triangular parts only),
-// S^T, and cleared running totals.  One block per layer.
+// S^T, and cleared running totals.  Grid (KP, KP / 8), 256 threads: block (k, y) owns the eight products
+// w_k . s_j, j = 8 y .. 8 y + 7, one per warp.
 __global__ void prep_kernel(const float* __restrict__ w, const float* __restrict__ s, int K, int D, int KP,
                             float* __restrict__ M, float* __restrict__ Mt, float* __restrict__ ST, float* __restrict__ acc) {
     const int k = blockIdx.x;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
-    if (k == 0)
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (k == 0 && blockIdx.y == 0)
         for (int i = threadIdx.x; i < 3 + 2 * kMaxK; i += blockDim.x) acc[i] = 0.f;
-    for (int j = warp; j < KP; j += nw) {
+    const int j = blockIdx.y * 8 + warp;
+    if (j < KP) {
         float v = 0.f;
         if (k < K && j < K && j != k) {
             for (int d = lane; d < D; d += 32) v = fmaf(w[(size_t)k * D + d], s[(size_t)j * D + d], v);
@@ -127,7 +129,8 @@ __global__ void prep_kernel(const float* __restrict__ w, const float* __restrict
             M[(size_t)k * KP + j] = (j < k) ? v : 0.f;
         }
     }
-    for (int d = threadIdx.x; d < D; d += blockDim.x) ST[(size_t)d * KP + k] = k < K ? s[(size_t)k * D + d] : 0.f;
+    if (blockIdx.y == 0)
+        for (int d = threadIdx.x; d < D; d += blockDim.x) ST[(size_t)d * KP + k] = k < K ? s[(size_t)k * D + d] : 0.f;
 }
 
 // block-wide sum in a fixed order (warp trees, then warp 0 over the warp results)
@@ -675,7 +678,7 @@ int gram_begin(long long layout_n, int D, int K, const float* w, const float* s,
     const Layout L = make_layout(layout_n, D, K);
     float* ws = reinterpret_cast<float*>(workspace);
     const int KP = L.KP;
-    prep_kernel<<<KP, 256, 0, st>>>(w, s, K, D, KP, ws + L.M, ws + L.Mt, ws + L.ST, ws + L.acc);
+    prep_kernel<<<dim3(KP, KP / 8), 256, 0, st>>>(w, s, K, D, KP, ws + L.M, ws + L.Mt, ws + L.ST, ws + L.acc);
     NF_CUDA_OK(cudaGetLastError());
     if (KP > K) NF_CUDA_OK(cudaMemsetAsync(ws + L.AT + (size_t)K * L.Nc, 0, (size_t)(KP - K) * L.Nc * sizeof(float), st));
     return NF_OK;
