@@ -141,10 +141,18 @@ int nf_session_elbo_host_f64(nf_session* s, const double* eps_host, int64_t N, c
  *               `gradient(params, t)`, get_data.py:100-101)
  *   params    : [W (K*D) | U (K*D) | B (K)], updated in place (get_data.py:74-78 layout)
  *   optimizer : 0 sgd (h1 = mass), 1 rmsprop (h1 = gamma, h2 = eps), 2 adam (h1 = b1, h2 = b2, h3 = eps)
- *   opt_state : 2*(2KD+K) elements of scratch for the optimiser (initialised by the call)
+ *   first_iter: global index of the first iteration of this call (0 for a fresh run).  Adam's bias correction
+ *               uses first_iter + t + 1, as autograd 1.3 does for iteration index first_iter + t.
+ *   resume    : 0: the call initialises opt_state (zeros; rmsprop's running average starts at ones, autograd 1.3);
+ *               != 0: opt_state is taken as a previous call left it, so that a run cut into several calls (the
+ *               callback cadence of get_data.py:128-138) follows exactly the trajectory of a single call
+ *   eps_stride: elements between the slices of consecutive iterations (0: N*D).  Slices are read with 16-byte
+ *               vector loads: eps_stride * elem_size must be a multiple of 16 when n_iters > 1 (NF_ERR_INVALID
+ *               otherwise) -- pad the slices
+ *   opt_state : 2*(2KD+K) elements kept by the caller between calls
  *   trace_F   : [n_iters] free energy seen by each gradient evaluation, or NULL
  *   workspace : nf_script_train_workspace_bytes(K, D, elem_size)
- * D <= 4 or the wide-D targets, script semantics.  Asynchronous on `stream`.
+ * D <= 4 or the wide-D targets, script semantics.  Asynchronous on `stream`: nothing in the call synchronises.
  * ------------------------------------------------------------------------- */
 size_t nf_script_train_workspace_bytes(int K, int D, int elem_size);
 /* The same with room for the matrix-product path of nf_planar_elbo_workspace_bytes_n (N samples per iteration):
@@ -152,12 +160,12 @@ size_t nf_script_train_workspace_bytes(int K, int D, int elem_size);
 size_t nf_script_train_workspace_bytes_n(int64_t N, int K, int D, int elem_size);
 int nf_script_train_f32(const float* eps_all, int64_t n_iters, int64_t N, int D, int K, float* params, int target_id,
                         const float* target_params, int n_target_params, float log_eps, int optimizer,
-                        float step_size, float h1, float h2, float h3, float* opt_state, float* trace_F,
-                        void* workspace, size_t workspace_bytes, void* stream);
+                        float step_size, float h1, float h2, float h3, int64_t first_iter, int resume, int64_t eps_stride,
+                        float* opt_state, float* trace_F, void* workspace, size_t workspace_bytes, void* stream);
 int nf_script_train_f64(const double* eps_all, int64_t n_iters, int64_t N, int D, int K, double* params, int target_id,
                         const double* target_params, int n_target_params, double log_eps, int optimizer,
-                        double step_size, double h1, double h2, double h3, double* opt_state, double* trace_F,
-                        void* workspace, size_t workspace_bytes, void* stream);
+                        double step_size, double h1, double h2, double h3, int64_t first_iter, int resume, int64_t eps_stride,
+                        double* opt_state, double* trace_F, void* workspace, size_t workspace_bytes, void* stream);
 
 /* Host-side parameter algebra of the shared-parameter path (float64, K*D numbers, no GPU involved).
  * get_data.py:106-108 derives the step vector u_hat and the log-det coefficient w.u from the raw (w, u) inside

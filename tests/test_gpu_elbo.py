@@ -251,3 +251,69 @@ def test_gradient_create_draws_like_the_reference():
     assert abs(mq - float(lq.mean())) <= 1e-10 * abs(float(lq.mean())) and abs(mp - float(lp.mean())) <= 1e-10 * max(1, abs(float(lp.mean())))
     W, U, B = unpack_params(params)
     assert W.shape == (K, D) and U.shape == (K, D) and B.shape == (K,)
+
+
+def _reference_optimise(optimizer, target_fn, num_samples, num_iter, lr, K, D=2):
+    """get_data.py:119-142 line for line, with the oracle's gradient in place of grad(variational_objective): the loop of
+    autograd.misc.optimizers, one global-RNG draw per gradient, the callback's two draws at t % 100 == 0 and its two
+    draws at the last iteration (the values it prints are not needed, the draws are)."""
+    from autograd.misc import optimizers
+    from oracle import planar_torch as pt
+
+    def draw():
+        return np.random.multivariate_normal(np.zeros(D), np.eye(D), num_samples)
+
+    def gradient(x, t):
+        return pt.script_value_and_grad(x, draw(), target_fn, 1e-7, K)[1]
+
+    def callback(x, t, g):
+        if t % 100 == 0:
+            draw(); draw()
+        if (t + 1) % num_iter == 0:
+            draw(); draw()
+    init = np.concatenate([0.1 * np.ones(K * D), 0.1 * np.ones(K * D), 0.1 * np.ones(K)])
+    return getattr(optimizers, optimizer)(gradient, init, callback, num_iter, lr)
+
+
+@pytest.mark.parametrize('optimizer', ['rmsprop', 'adam', 'sgd'])
+@pytest.mark.parametrize('num_samples,num_iter', [(100, 250), (101, 201), (100, 101)])
+def test_optimise_follows_the_reference_trajectory(optimizer, num_samples, num_iter):
+    """normflows.objectives.optimise cuts the run where the reference's callback prints (every 100 iterations and at
+    the end) and runs the stretches in between on the device.  The optimiser state and the iteration count carry over
+    from one stretch to the next, so the parameters after num_iter iterations are those of the reference's single
+    rmsprop / adam / sgd loop on the same seed (get_data.py:140).  Odd sample counts exercise the padded sample
+    slices, num_iter % 100 == 1 the single-iteration last stretch."""
+    from normflows import objectives
+    from oracle import planar_torch as pt
+    K = 4
+    np.random.seed(17)
+    x_ref = _reference_optimise(optimizer, pt.p1, num_samples, num_iter, 5e-4, K)
+    np.random.seed(17)
+    x = objectives.optimise('p1', num_samples, num_iter, 5e-4, K, optimizer=optimizer, dtype='float64', verbose=False)
+    err = np.abs(x - x_ref).max()
+    assert err <= 1e-8 * max(1.0, np.abs(x_ref).max()), err
+    assert np.abs(x_ref - 0.1).max() > 1e-3
+
+
+def test_training_loop_resume_equals_one_call():
+    """nf_script_train_*: a run cut into calls (resume != 0, first_iter = iterations done) is bitwise the run of one
+    call, in float32 and float64, for every optimiser; a fresh call after a resumed one starts from fresh state."""
+    from nfcore.objective import SharedFlowObjective
+    K, D, N, T = 8, 2, 128, 60
+    rs = np.random.RandomState(4)
+    eps_all = rs.randn(T, N, D)
+    init = np.concatenate([0.1 + 0.02 * rs.randn(2 * K * D), 0.1 * np.ones(K)])
+    for dtype in ('float64', 'float32'):
+        for optimizer in ('adam', 'rmsprop', 'sgd'):
+            obj = SharedFlowObjective('p2', K, D, dtype=dtype)
+            x_one, tr_one = obj.train(init, eps_all, optimizer=optimizer, step_size=1e-3)
+            x, st, traces = init, None, []
+            for lo, hi in ((0, 1), (1, 25), (25, 26), (26, 60)):
+                x, tr = obj.train(x, eps_all[lo:hi], optimizer=optimizer, step_size=1e-3, state=st)
+                st = obj.train_state
+                traces.append(tr)
+            assert st['iters'] == T
+            assert np.array_equal(x, x_one), (dtype, optimizer, np.abs(x - x_one).max())
+            assert np.array_equal(np.concatenate(traces), tr_one)
+            x_again, _ = obj.train(init, eps_all, optimizer=optimizer, step_size=1e-3)
+            assert np.array_equal(x_again, x_one)

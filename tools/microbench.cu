@@ -15,6 +15,9 @@ __global__ void __launch_bounds__(1024) k(float* out, long long* cyc, float seed
 #pragma unroll
     for (int i = 0; i < UNROLL; ++i) { a[i] = seed + threadIdx.x * 1e-3f + i; p[i] = make_float2(a[i], a[i] + 1.f); }
     const float m = 0.999f + seed * 1e-6f, c = 1e-3f * seed;
+    unsigned long long mm, cc;
+    asm volatile("mov.b64 %0, {%1, %2};" : "=l"(mm) : "f"(m), "f"(m * 0.9999f));
+    asm volatile("mov.b64 %0, {%1, %2};" : "=l"(cc) : "f"(c), "f"(c * 1.0001f));
     __shared__ float sh[1024];
     sh[threadIdx.x] = seed;
     __syncthreads();
@@ -25,7 +28,7 @@ __global__ void __launch_bounds__(1024) k(float* out, long long* cyc, float seed
             if (OP == 0) a[i] = fmaf(a[i], m, c);
             if (OP == 1) asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(*(unsigned long long*)&p[i]) : "l"(*(const unsigned long long*)&p[(i + 1) % UNROLL]), "l"(*(const unsigned long long*)&p[(i + 2) % UNROLL]));
             if (OP == 2) asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(a[i]));
-            if (OP == 3) asm volatile("rcp.approx.ftz.f32 %0, %0;" : "+f"(a[i]));
+            if (OP == 3) { asm volatile("rcp.approx.ftz.f32 %0, %0;" : "+f"(a[i])); a[i] += c; }   // FADD keeps ptxas from folding rcp(rcp(x))
             if (OP == 4) asm volatile("lg2.approx.ftz.f32 %0, %0;" : "+f"(a[i]));
             if (OP == 5) { a[i] = fmaf(a[i], m, c); a[i] = fmaf(a[i], m, c); a[i] = fmaf(a[i], m, c); a[i] = fmaf(a[i], m, c);
                            a[i] = fmaf(a[i], m, c); a[i] = fmaf(a[i], m, c); a[i] = fmaf(a[i], m, c);
@@ -36,6 +39,19 @@ __global__ void __launch_bounds__(1024) k(float* out, long long* cyc, float seed
             if (OP == 9) { a[i] = fmaf(a[i], m, c); a[i] = fmaf(a[i], m, c); a[i] = fmaf(a[i], m, c);
                            asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(a[i])); }     // 3 FFMA : 1 MUFU
             if (OP == 10) a[i] = (a[i] > 0.5f) ? a[(i + 1) % UNROLL] : m;                 // FSETP+SEL (alu pipe)
+            // packed-pair variants: which operand patterns reach one instruction per two clocks per scheduler
+            if (OP == 11) asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(*(unsigned long long*)&p[i]) : "l"(mm), "l"(cc));   // invariant multiplier and addend
+            if (OP == 12) asm volatile("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(*(unsigned long long*)&p[i]) : "l"(mm), "l"(cc));   // accumulate form
+            if (OP == 13) asm volatile("mul.rn.f32x2 %0, %0, %1;" : "+l"(*(unsigned long long*)&p[i]) : "l"(mm));
+            if (OP == 14) asm volatile("add.rn.f32x2 %0, %0, %1;" : "+l"(*(unsigned long long*)&p[i]) : "l"(cc));
+            if (OP == 15) { asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(*(unsigned long long*)&p[i]) : "l"(mm), "l"(cc)); a[i] = fmaf(a[i], m, c); }  // 1 FFMA2 + 1 FFMA
+            if (OP == 16) { asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(*(unsigned long long*)&p[i]) : "l"(mm), "l"(cc));
+                            asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(*(unsigned long long*)&p[i]) : "l"(mm), "l"(cc));
+                            asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(*(unsigned long long*)&p[i]) : "l"(mm), "l"(cc));
+                            asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(a[i])); }     // 3 FFMA2 : 1 MUFU
+            if (OP == 17) asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(*(unsigned long long*)&p[i]) : "l"(*(const unsigned long long*)&p[(i + 1) % UNROLL]), "l"(cc));  // two varying sources
+            if (OP == 18) { asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(*(unsigned long long*)&p[i]) : "l"(mm), "l"(cc));
+                            a[i] = (a[i] > 0.5f) ? a[(i + 1) % UNROLL] : m; }   // 1 FFMA2 + FSETP + SEL (alu pipe)
         }
     }
     long long t1 = clock64();
@@ -86,6 +102,14 @@ int main() {
         run<6>("SHFL.BFLY", 1, threads);
         run<7>("LDS", 1, threads);
         run<10>("FSETP+SEL", 2, threads);
+        run<11>("FFMA2 d=d*M+C (invariant M,C)", 1, threads);
+        run<12>("FFMA2 d=M*C+d (accumulate)", 1, threads);
+        run<13>("FMUL2 d=d*M", 1, threads);
+        run<14>("FADD2 d=d+C", 1, threads);
+        run<15>("1 FFMA2 + 1 FFMA", 2, threads);
+        run<16>("3 FFMA2 + 1 MUFU.EX2", 4, threads);
+        run<17>("FFMA2 d=d*p+C (two varying)", 1, threads);
+        run<18>("1 FFMA2 + FSETP + SEL", 3, threads);
     }
     return 0;
 }

@@ -8,11 +8,12 @@ size_t nf_planar_elbo_workspace_bytes(int K, int D, int elem_size) {
     if (K < 1 || D < 1 || elem_size < 1) return 0;
     if (nf::elbo_thread_per_sample(D)) {
         const size_t row = (size_t)K * (2 * D + 2) + 2;
-        return row * (size_t)nf::max_grid_blocks() * (size_t)elem_size;
+        return row * (size_t)nf::max_grid_blocks() * (size_t)elem_size + nf::kSyncHeaderBytes;
     }
     const size_t row = (size_t)K * nf::wide_vk(D) + 2;      // one row per warp of the wide kernel
     const nf::DevInfo di = nf::dev_info();
-    return row * (size_t)((di.sms > 0 ? di.sms : 148) * nf::wide_blocks_per_sm(K, D, (size_t)elem_size) * nf::kWideWarps) * (size_t)elem_size;
+    return row * (size_t)((di.sms > 0 ? di.sms : 148) * nf::wide_blocks_per_sm(K, D, (size_t)elem_size) * nf::kWideWarps) * (size_t)elem_size +
+           nf::kSyncHeaderBytes;
 }
 
 size_t nf_planar_elbo_workspace_bytes_n(int64_t N, int K, int D, int elem_size) {
@@ -57,9 +58,11 @@ int nf_session_elbo_host_f32(nf_session* s, const float* eps_host, int64_t N, co
 
 int nf_script_train_f32(const float* eps_all, int64_t n_iters, int64_t N, int D, int K, float* params, int target_id,
                         const float* target_params, int n_target_params, float log_eps, int optimizer, float step_size, float h1,
-                        float h2, float h3, float* opt_state, float* trace_F, void* workspace, size_t workspace_bytes, void* stream) {
+                        float h2, float h3, int64_t first_iter, int resume, int64_t eps_stride, float* opt_state, float* trace_F,
+                        void* workspace, size_t workspace_bytes, void* stream) {
     return nf::script_train<float>(eps_all, n_iters, N, D, K, params, target_id, target_params, n_target_params, log_eps, optimizer,
-                                step_size, h1, h2, h3, opt_state, trace_F, workspace, workspace_bytes, stream);
+                                step_size, h1, h2, h3, first_iter, resume, eps_stride, opt_state, trace_F, workspace,
+                                workspace_bytes, stream);
 }
 
 size_t nf_script_train_workspace_bytes(int K, int D, int elem_size) {
@@ -107,7 +110,6 @@ namespace nf {
 
 static __device__ __align__(256) unsigned char g_noalloc_scratch[NF_NOALLOC_SCRATCH_BYTES];
 
-constexpr int kMaxDevices = 64;
 static void* g_noalloc_ptr[kMaxDevices];          // device address of the array, per device ordinal
 static bool g_noalloc_ready[kMaxDevices];
 static std::mutex g_noalloc_mutex;

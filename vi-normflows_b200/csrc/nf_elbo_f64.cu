@@ -20,9 +20,11 @@ int nf_session_elbo_host_f64(nf_session* s, const double* eps_host, int64_t N, c
 
 int nf_script_train_f64(const double* eps_all, int64_t n_iters, int64_t N, int D, int K, double* params, int target_id,
                         const double* target_params, int n_target_params, double log_eps, int optimizer, double step_size, double h1,
-                        double h2, double h3, double* opt_state, double* trace_F, void* workspace, size_t workspace_bytes, void* stream) {
+                        double h2, double h3, int64_t first_iter, int resume, int64_t eps_stride, double* opt_state, double* trace_F,
+                        void* workspace, size_t workspace_bytes, void* stream) {
     return nf::script_train<double>(eps_all, n_iters, N, D, K, params, target_id, target_params, n_target_params, log_eps, optimizer,
-                                step_size, h1, h2, h3, opt_state, trace_F, workspace, workspace_bytes, stream);
+                                step_size, h1, h2, h3, first_iter, resume, eps_stride, opt_state, trace_F, workspace,
+                                workspace_bytes, stream);
 }
 
 }  // extern "C"

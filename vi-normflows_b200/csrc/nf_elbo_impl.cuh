@@ -28,12 +28,13 @@
 #include "nf_common.cuh"
 #include "nf_targets.cuh"
 #include "nf_elbo_wide.cuh"
+#include "nf_launch.cuh"
+#include "nf_elbo_pair.cuh"
 
 namespace nf {
 
 constexpr int kElboThreads = 64;
 constexpr int kMaxBlocksPerSM = 16;
-constexpr int kLogEvery = 4;          // layers per MUFU.LG2 (product of 4 factors >= eps^4 = 1e-28: no underflow)
 
 // ---- tensor memory as a per-thread activation stash ---------------------------------------
 // TMEM (256 KB per SM, 128 lanes x 512 32-bit columns) is otherwise idle in this kernel.  A
@@ -471,36 +472,6 @@ __global__ void elbo_finalize_kernel(const T* __restrict__ partials, int nrows, 
     }
 }
 
-// Launch with the programmatic-stream-serialization attribute: the kernel's launch latency and prologue
-// overlap the tail of its predecessor; the kernel itself waits (griddepcontrol.wait) before touching memory.
-template <typename... KArgs, typename... Args>
-static inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
-    return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
-}
-
-struct DevInfo { int sms; int ok; };
-static inline DevInfo dev_info() {
-    static thread_local int cached_dev = -1;
-    static thread_local DevInfo info = {0, 0};
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess) return {0, 0};
-    if (dev != cached_dev) {
-        int sms = 0, major = 0;
-        if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return {0, 0};
-        if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess) return {0, 0};
-        info.sms = sms;
-        info.ok = (major == 10);
-        cached_dev = dev;
-    }
-    return info;
-}
-
 template <typename T, int D, int S, int ST, int NT, int TGT, bool BWD>
 static int launch_elbo(const T* eps, long long N, int K, const T* w, const T* s, const T* b, const T* c,
                        const T* tparams, int ntp, T epsv, T* partials, int max_blocks, int* nblocks_out,
@@ -548,6 +519,13 @@ static int launch_elbo(const T* eps, long long N, int K, const T* w, const T* s,
     *nblocks_out = (int)grid;
     return NF_OK;
 }
+
+// ---- packed-pair kernel (nf_elbo_pair.cuh, built in its own translation units): float32, D <= 2, K <= 64 ----
+bool pair_applicable(size_t elem, bool bwd, long long N, int D, int K);
+// rows only (sync == NULL: `*nb` rows of partial sums for elbo_finish) or the whole call in one launch
+int pair_elbo(int tgt, const float* eps, long long N, int D, int K, const float* w, const float* s, const float* b,
+              const float* c, const float* tp, int ntp, float epsv, float* partials, pr::SyncHeader* sync,
+              float* out_F, float* g_w, float* g_s, float* g_b, float* g_c, int* nb, cudaStream_t st);
 
 template <typename T> struct SamplesPerThread { static constexpr int big = 8, mid = 4, small = 2; };
 template <> struct SamplesPerThread<double> { static constexpr int big = 4, mid = 2, small = 1; };
@@ -719,6 +697,11 @@ template <typename T>
 static int elbo_main(bool bwd, const T* eps, int64_t N, int D, int K, const T* w, const T* s, const T* b, const T* c,
                      int target_id, const T* tparams, int ntp, T epsv, T* partials, int* nrows, cudaStream_t stream) {
     const int max_blocks = max_grid_blocks();
+    if constexpr (sizeof(T) == 4) {
+        if (pair_applicable(sizeof(T), bwd, N, D, K))
+            return pair_elbo(target_id, eps, N, D, K, w, s, b, c, tparams, ntp, epsv, partials, nullptr, nullptr, nullptr, nullptr,
+                             nullptr, nullptr, nrows, stream);
+    }
     switch (D) {
         case 1: return dispatch_target<T, 1>(target_id, bwd, eps, N, K, w, s, b, c, tparams, ntp, epsv, partials, max_blocks, nrows, stream);
         case 2: return dispatch_target<T, 2>(target_id, bwd, eps, N, K, w, s, b, c, tparams, ntp, epsv, partials, max_blocks, nrows, stream);
@@ -745,6 +728,25 @@ static int elbo_finish(bool bwd, const T* partials, int nrows, int D, int K, T* 
     return NF_OK;
 }
 
+// objective + fixed-order sum into the caller's outputs.  `partials` is a workspace of nf_planar_elbo_workspace_bytes():
+// its last kSyncHeaderBytes hold the ticket of the single-launch kernel.
+template <typename T>
+static int elbo_fused(bool bwd, const T* eps, int64_t N, int D, int K, const T* w, const T* s, const T* b, const T* c,
+                      int target_id, const T* tparams, int ntp, T epsv, T* out_F, T* g_w, T* g_s, T* g_b, T* g_c, T* partials,
+                      cudaStream_t stream) {
+    int nb = 0;
+    if constexpr (sizeof(T) == 4) {
+        if (pair_applicable(sizeof(T), bwd, N, D, K)) {
+            unsigned char* base = reinterpret_cast<unsigned char*>(partials);
+            pr::SyncHeader* sync = reinterpret_cast<pr::SyncHeader*>(base + nf_planar_elbo_workspace_bytes(K, D, 4) - kSyncHeaderBytes);
+            return pair_elbo(target_id, eps, N, D, K, w, s, b, c, tparams, ntp, epsv, partials, sync, out_F, g_w, g_s, g_b, g_c, &nb, stream);
+        }
+    }
+    int rc = elbo_main<T>(bwd, eps, N, D, K, w, s, b, c, target_id, tparams, ntp, epsv, partials, &nb, stream);
+    if (rc != NF_OK) return rc;
+    return elbo_finish<T>(bwd, partials, nb, D, K, out_F, g_w, g_s, g_b, g_c, stream);
+}
+
 template <typename T>
 static int elbo_entry(const T* eps, int64_t N, int D, int K, const T* w, const T* s, const T* b, const T* c,
                       int target_id, const T* tparams, int ntp, T epsv, T* out_F, T* g_w, T* g_s, T* g_b, T* g_c,
@@ -758,10 +760,7 @@ static int elbo_entry(const T* eps, int64_t N, int D, int K, const T* w, const T
     if (rc != NF_OK) return rc;
     if (workspace_bytes < nf_planar_elbo_workspace_bytes(K, D, (int)sizeof(T))) return NF_ERR_WORKSPACE;
     T* partials = reinterpret_cast<T*>(workspace);
-    int nb = 0;
-    rc = elbo_main<T>(all_g, eps, N, D, K, w, s, b, c, target_id, tparams, ntp, epsv, partials, &nb, stream);
-    if (rc != NF_OK) return rc;
-    return elbo_finish<T>(all_g, partials, nb, D, K, out_F, g_w, g_s, g_b, g_c, stream);
+    return elbo_fused<T>(all_g, eps, N, D, K, w, s, b, c, target_id, tparams, ntp, epsv, out_F, g_w, g_s, g_b, g_c, partials, stream);
 }
 
 // ---- host-buffer session: H2D of the samples overlapped with the objective kernel -------------
@@ -939,7 +938,7 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 script_step_kernel(T* __restrict__ params /*[2KD+K]*/, T* __restrict__ lc /*w|s|b|c*/, const T* __restrict__ res /*[3+2KD+2K]*/,
                    T* __restrict__ state /*[2P]*/, int K, int D, long long n_samples, int apply_update, long long iter,
-                   int optimizer, T step, T h1, T h2, T h3, T* __restrict__ trace_F, int paper) {
+                   long long trace_idx, int optimizer, T step, T h1, T h2, T h3, T* __restrict__ trace_F, int paper) {
     asm volatile("griddepcontrol.wait;" ::: "memory");
     const int P = 2 * K * D + K;
     T* W = params;
@@ -1008,7 +1007,7 @@ script_step_kernel(T* __restrict__ params /*[2KD+K]*/, T* __restrict__ lc /*w|s|
         }
     }
     __syncthreads();
-    if (apply_update && trace_F && threadIdx.x == 0) trace_F[iter - 1] = res[0] / (T)n_samples;
+    if (apply_update && trace_F && threadIdx.x == 0) trace_F[trace_idx] = res[0] / (T)n_samples;
     // constants for the next objective evaluation
     for (int k = threadIdx.x; k < K; k += blockDim.x) {
         T wu = 0, n2 = 0;
@@ -1027,12 +1026,29 @@ script_step_kernel(T* __restrict__ params /*[2KD+K]*/, T* __restrict__ lc /*w|s|
     }
 }
 
+// optimiser state at the start of a run: zeros, except rmsprop's running average (ones, autograd 1.3)
+template <typename T>
+__global__ void script_state_init_kernel(T* __restrict__ state, int P, int optimizer) {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 2 * P; i += gridDim.x * blockDim.x)
+        state[i] = (optimizer == OPT_RMSPROP && i < P) ? (T)1 : (T)0;
+}
+
+// `first_iter` is the global index of the first iteration of this call (Adam's bias correction uses
+// first_iter + local index + 1); `resume` != 0 keeps `state` as the previous call left it, so that a run cut
+// into several calls follows the trajectory of one call; `eps_stride` is the distance in elements between
+// the sample slices of consecutive iterations (0: N*D).
 template <typename T>
 static int script_train(const T* eps_all, int64_t n_iters, int64_t N, int D, int K, T* params, int target_id,
-                        const T* tparams, int ntp, T epsv, int optimizer, T step, T h1, T h2, T h3, T* state,
-                        T* trace_F, void* workspace, size_t workspace_bytes, void* stream_) {
+                        const T* tparams, int ntp, T epsv, int optimizer, T step, T h1, T h2, T h3, int64_t first_iter,
+                        int resume, int64_t eps_stride, T* state, T* trace_F, void* workspace, size_t workspace_bytes,
+                        void* stream_) {
     cudaStream_t st = (cudaStream_t)stream_;
-    if (n_iters < 0 || N < 1 || !params || !state || !workspace || optimizer < 0 || optimizer > 2) return NF_ERR_INVALID;
+    if (n_iters < 0 || N < 1 || !params || !state || !workspace || optimizer < 0 || optimizer > 2 || first_iter < 0) return NF_ERR_INVALID;
+    if (eps_stride == 0) eps_stride = N * D;
+    if (eps_stride < N * D) return NF_ERR_INVALID;
+    // every iteration's slice is read with 16-byte vector loads (load_samples)
+    if (n_iters > 1 && ((size_t)eps_stride * sizeof(T)) % 16 != 0) return NF_ERR_INVALID;
     const size_t P = (size_t)2 * K * D + K, nlc = (size_t)2 * K * D + 2 * K, nres = 3 + nlc;
     // workspace: [lc | res | pad to 256 B | rows]
     const size_t head = ((nlc + nres) * sizeof(T) + 255) & ~(size_t)255;
@@ -1048,30 +1064,24 @@ static int script_train(const T* eps_all, int64_t n_iters, int64_t N, int D, int
     bool use_gram = false;
     if constexpr (sizeof(T) == 4)
         use_gram = gram_applicable(N, D, K, target_id, ntp) && workspace_bytes >= head + gram_workspace_bytes(N, D, K);
-    // optimiser state: rmsprop starts its running average at ones (autograd 1.3), the others at zero
-    NF_CUDA_OK(cudaMemsetAsync(state, 0, 2 * P * sizeof(T), st));
-    if (optimizer == OPT_RMSPROP) {
-        // fill with ones through the update kernel's first pass would complicate it: use a small fill
-        std::vector<T> ones(P, (T)1);
-        NF_CUDA_OK(cudaMemcpyAsync(state, ones.data(), P * sizeof(T), cudaMemcpyHostToDevice, st));
-        NF_CUDA_OK(cudaStreamSynchronize(st));
-    }
+    if (!resume)
+        NF_CUDA_OK(launch_pdl(script_state_init_kernel<T>, dim3(8), dim3(256), 0, st, state, (int)P, optimizer));
     for (int64_t it = 0; it <= n_iters; ++it) {
         // apply update of iteration it-1 (if any), then prepare constants for iteration it
         NF_CUDA_OK(launch_pdl(script_step_kernel<T>, dim3(1), dim3(256), 0, st, params, lc, (const T*)res, state, K, D,
-                              (long long)N, it > 0 ? 1 : 0, (long long)it, optimizer, step, h1, h2, h3, trace_F, 0));
+                              (long long)N, it > 0 ? 1 : 0, (long long)(first_iter + it), (long long)(it - 1), optimizer, step,
+                              h1, h2, h3, trace_F, 0));
         if (it == n_iters) break;
+        const T* eps_it = eps_all + (size_t)it * (size_t)eps_stride;
         if (use_gram) {
             if constexpr (sizeof(T) == 4)
-                rc = gram_elbo_f32(true, eps_all + (size_t)it * N * D, N, D, K, w, s, b, c, target_id, tparams, ntp, epsv, res, res + 3,
+                rc = gram_elbo_f32(true, eps_it, N, D, K, w, s, b, c, target_id, tparams, ntp, epsv, res, res + 3,
                                    res + 3 + K * D, res + 3 + 2 * K * D, res + 3 + 2 * K * D + K, rows, st);
             if (rc != NF_OK) return rc;
             continue;
         }
-        int nb = 0;
-        rc = elbo_main<T>(true, eps_all + (size_t)it * N * D, N, D, K, w, s, b, c, target_id, tparams, ntp, epsv, rows, &nb, st);
-        if (rc != NF_OK) return rc;
-        rc = elbo_finish<T>(true, rows, nb, D, K, res, res + 3, res + 3 + K * D, res + 3 + 2 * K * D, res + 3 + 2 * K * D + K, st);
+        rc = elbo_fused<T>(true, eps_it, N, D, K, w, s, b, c, target_id, tparams, ntp, epsv, res, res + 3, res + 3 + K * D,
+                           res + 3 + 2 * K * D, res + 3 + 2 * K * D + K, rows, st);
         if (rc != NF_OK) return rc;
     }
     return NF_OK;

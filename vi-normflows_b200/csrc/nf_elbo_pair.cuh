@@ -1,0 +1,502 @@
+// Packed-pair variant of the shared-parameter free-energy kernel (float32, D <= 2, K <= 64).
+//
+// Same arithmetic as elbo_shared_kernel (nf_elbo_impl.cuh; get_data.py:97-115), laid out for the
+// instruction-issue limit that kernel runs into: every thread carries its samples as PAIRS in 64-bit
+// registers and all per-layer multiply-adds are fma/mul/add.f32x2 (SASS FFMA2/FMUL2/FADD2: two results
+// per issued instruction, one instruction per two clocks per scheduler when at most two operands are
+// sample data -- tools/microbench.cu).  Only the transcendentals (MUFU ex2/rcp/lg2) and the two sign
+// manipulations stay scalar.  Signs are arranged so that no packed negation is needed:
+//     nhp = t*t - 1 (= -h'),  x = nhp*(-c) + 1,  ngx = copysign(1/(eps+|x|), x) (= -d(-log y)/dx),
+//     g_c += ngx*nhp,  ngt = ngx*(-2c)*t + gz.(-s) (= -g_t),  g_a = ngt*nhp.
+// Structure:
+//   * one persistent block per SM; warp w of the grid owns the w-th slice of every round of samples.
+//     The samples are dealt in rounds of SMAX per thread plus one shorter round, so that every warp of
+//     the grid does the same amount of work for any N (no tail wave);
+//   * tanh history: the first ST samples of a thread in tensor memory (tcgen05.st/ld, fetched one layer
+//     ahead), the rest in shared memory as 64-bit pairs;
+//   * the 2D+2 gradient partials of a layer are reduced across the warp one layer behind the arithmetic
+//     (halving butterfly) into a per-warp shared-memory table; the block writes one row of sums;
+//   * the last block to finish (ticket in the workspace header) adds the rows in a fixed order and writes
+//     the caller's outputs: one launch per call, bitwise reproducible for a fixed grid.
+#pragma once
+#include "nf_common.cuh"
+#include "nf_launch.cuh"
+#include "nf_targets.cuh"
+
+namespace nf {
+namespace pr {
+
+typedef unsigned long long u64;
+
+__device__ __forceinline__ u64 pk(float lo, float hi) { u64 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void upk(u64 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ u64 fma2(u64 a, u64 b, u64 c) { u64 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
+__device__ __forceinline__ u64 mul2(u64 a, u64 b) { u64 d; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+__device__ __forceinline__ u64 add2(u64 a, u64 b) { u64 d; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+// (|r| with the sign of x) in one LOP3: (r & 0x7fffffff) | (x & 0x80000000)
+__device__ __forceinline__ float copysign_bits(float r, float x) {
+    unsigned o;
+    asm("lop3.b32 %0, %1, 0x80000000, %2, 0xb8;" : "=r"(o) : "r"(__float_as_uint(r)), "r"(__float_as_uint(x)));
+    return __uint_as_float(o);
+}
+
+template <int N> struct Tm;
+template <> struct Tm<2> {
+    static __device__ __forceinline__ void st(uint32_t a, const float* r) {
+        asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1, %2};" ::"r"(a), "r"(__float_as_uint(r[0])), "r"(__float_as_uint(r[1])) : "memory");
+    }
+    static __device__ __forceinline__ void ld(uint32_t a, float* r) {
+        uint32_t v0, v1;
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0, %1}, [%2];" : "=r"(v0), "=r"(v1) : "r"(a) : "memory");
+        r[0] = __uint_as_float(v0); r[1] = __uint_as_float(v1);
+    }
+};
+template <> struct Tm<4> {
+    static __device__ __forceinline__ void st(uint32_t a, const float* r) {
+        asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(__float_as_uint(r[0])),
+                     "r"(__float_as_uint(r[1])), "r"(__float_as_uint(r[2])), "r"(__float_as_uint(r[3])) : "memory");
+    }
+    static __device__ __forceinline__ void ld(uint32_t a, float* r) {
+        uint32_t v0, v1, v2, v3;
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v0), "=r"(v1), "=r"(v2), "=r"(v3) : "r"(a) : "memory");
+        r[0] = __uint_as_float(v0); r[1] = __uint_as_float(v1); r[2] = __uint_as_float(v2); r[3] = __uint_as_float(v3);
+    }
+};
+template <> struct Tm<8> {
+    static __device__ __forceinline__ void st(uint32_t a, const float* r) {
+        asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(a),
+                     "r"(__float_as_uint(r[0])), "r"(__float_as_uint(r[1])), "r"(__float_as_uint(r[2])), "r"(__float_as_uint(r[3])),
+                     "r"(__float_as_uint(r[4])), "r"(__float_as_uint(r[5])), "r"(__float_as_uint(r[6])), "r"(__float_as_uint(r[7])) : "memory");
+    }
+    static __device__ __forceinline__ void ld(uint32_t a, float* r) {
+        uint32_t v[8];
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                     : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]) : "r"(a) : "memory");
+#pragma unroll
+        for (int i = 0; i < 8; ++i) r[i] = __uint_as_float(v[i]);
+    }
+};
+__device__ __forceinline__ void tm_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tm_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__host__ __device__ constexpr int tm_columns(int n) { int c = 32; while (c < n) c <<= 1; return c; }
+
+// per-layer constant records in shared memory, every value duplicated into both halves of a pair
+//   forward : w[D]*kappa | b*kappa | s[D]            (2D+1 pairs, padded to an even count)
+//   backward: -s[D] | -c | -2c | w[D]                (2D+2 pairs)
+template <int D> __host__ __device__ constexpr int recf_pairs() { return (2 * D + 2) & ~1; }
+template <int D> __host__ __device__ constexpr int recb_pairs() { return 2 * D + 2; }
+
+struct Smem {
+    int lcf, lcb, tp, acc, hist, total;      // offsets in floats
+    __host__ __device__ Smem(int K, int D, int ssp /*pairs per thread kept in shared memory*/, int ntp_s, int nthreads) {
+        const int V = 2 * D + 2;
+        const int rf = 2 * ((2 * D + 2) & ~1), rb = 2 * (2 * D + 2);
+        lcf = 0;
+        lcb = lcf + K * rf;
+        tp = lcb + K * rb;
+        acc = (tp + ntp_s + 3) & ~3;
+        hist = (acc + (nthreads / 32) * K * V + 3) & ~3;
+        total = hist + 2 * K * ssp * nthreads;
+    }
+};
+
+// workspace header of the single-launch mode (16 bytes): a cookie that tells an initialised ticket counter from
+// whatever the caller's memory held, and the ticket counter itself (zero between launches)
+struct SyncHeader { u64 cookie; unsigned counter; unsigned pad; };
+constexpr u64 kCookieBusy = 0x6e66636f72655f42ull;       // "nfcore_B": a block is clearing the counter
+__host__ __device__ inline u64 cookie_for(const void* p) { return 0x6e66636f72653032ull ^ (u64)(uintptr_t)p; }
+
+// One round of one warp: S samples per thread (S/2 pairs) through all K layers and back.
+template <int D, int S, int SMAX, int ST, int NT, int TGT, bool MASKED>
+__device__ __forceinline__ void pair_tile(const float* __restrict__ eps, long long n0, long long N, int K,
+                                          const float* __restrict__ lcf, const float* __restrict__ lcb,
+                                          const float* __restrict__ tp, int ntp, float epsv,
+                                          u64* __restrict__ hist_t, uint32_t taddr, float* __restrict__ acc_w, int lane,
+                                          int my_slot, bool my_own, float& sum_q, float& sum_p) {
+    using M = Mth<float>;
+    constexpr int V = 2 * D + 2;
+    constexpr int P = S / 2;                        // pairs this round
+    constexpr int STP = ST / 2;                     // pairs per thread that tensor memory can hold
+    constexpr int PT = P < STP ? P : STP;           // pairs of this round whose history goes to tensor memory
+    constexpr int SSP = (SMAX - ST) / 2;            // shared-memory pair slots per thread and layer
+    constexpr int RF = 2 * recf_pairs<D>(), RB = 2 * recb_pairs<D>();
+    static_assert(S % 2 == 0 && S <= SMAX && P - PT <= SSP, "round size");
+    const float LOG2PI = 1.8378770664093453f;
+    const u64 one2 = pk(1.0f, 1.0f), mone2 = pk(-1.0f, -1.0f), mtwo2 = pk(-2.0f, -2.0f);
+    const u64 nln2 = pk(-0.6931471805599453f, -0.6931471805599453f);
+
+    u64 z[P][D], gz[P][D], lq[P], prod[P], ep[MASKED ? P : 1];
+    bool ok[S];
+    {
+        float zs[S][D];
+        if (!MASKED) {
+            constexpr int E = S * D;
+            float buf[E];
+            const float* src = eps + n0 * D;
+            if ((E * 4) % 16 == 0) {
+                const int4* p = reinterpret_cast<const int4*>(src);
+                int4* q = reinterpret_cast<int4*>(buf);
+#pragma unroll
+                for (int i = 0; i < E / 4; ++i) q[i] = __ldg(p + i);
+            } else {
+                const int2* p = reinterpret_cast<const int2*>(src);
+                int2* q = reinterpret_cast<int2*>(buf);
+#pragma unroll
+                for (int i = 0; i < E / 2; ++i) q[i] = __ldg(p + i);
+            }
+#pragma unroll
+            for (int j = 0; j < S; ++j) {
+                ok[j] = true;
+#pragma unroll
+                for (int d = 0; d < D; ++d) zs[j][d] = buf[j * D + d];
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < S; ++j) {
+                ok[j] = n0 + j < N;
+#pragma unroll
+                for (int d = 0; d < D; ++d) zs[j][d] = ok[j] ? eps[(n0 + j) * D + d] : 0.5f;
+            }
+        }
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            float q0 = 0.f, q1 = 0.f;
+#pragma unroll
+            for (int d = 0; d < D; ++d) {
+                q0 = fmaf(zs[2 * p][d], zs[2 * p][d], q0);
+                q1 = fmaf(zs[2 * p + 1][d], zs[2 * p + 1][d], q1);
+                z[p][d] = pk(zs[2 * p][d], zs[2 * p + 1][d]);
+            }
+            lq[p] = pk(-0.5f * (D * LOG2PI + q0), -0.5f * (D * LOG2PI + q1));      // get_data.py:111, first term
+            prod[p] = one2;
+            // a sample past N gets eps = +inf: y = inf, 1/y = 0, so every gradient contribution of the layer chain
+            // vanishes without a per-layer select (its log q and log p are dropped by selects at the end)
+            if (MASKED) ep[p] = pk(ok[2 * p] ? epsv : __int_as_float(0x7f800000), ok[2 * p + 1] ? epsv : __int_as_float(0x7f800000));
+        }
+        if (!MASKED) ep[0] = pk(epsv, epsv);
+    }
+    // ---- forward over the K layers (get_data.py:104-109); the log-det is left to the reverse sweep ----
+    for (int k = 0; k < K; ++k) {
+        u64 rf[RF / 2];
+        {
+            const ulonglong2* src = reinterpret_cast<const ulonglong2*>(lcf + k * RF);
+#pragma unroll
+            for (int i = 0; i < RF / 4; ++i) { const ulonglong2 v = src[i]; rf[2 * i] = v.x; rf[2 * i + 1] = v.y; }
+        }
+        float tt[2 * (PT > 0 ? PT : 1)];
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            u64 a = rf[D];
+#pragma unroll
+            for (int d = 0; d < D; ++d) a = fma2(rf[d], z[p][d], a);
+            float a0, a1;
+            upk(a, a0, a1);
+            const u64 den = add2(pk(M::ex2(a0), M::ex2(a1)), one2);
+            float d0, d1;
+            upk(den, d0, d1);
+            const u64 t = fma2(pk(M::rcp(d0), M::rcp(d1)), mtwo2, one2);         // tanh = 1 - 2/(1+e^{2a})
+#pragma unroll
+            for (int d = 0; d < D; ++d) z[p][d] = fma2(rf[D + 1 + d], t, z[p][d]);
+            if (p < PT) upk(t, tt[2 * p], tt[2 * p + 1]);
+            else hist_t[(k * SSP + (p - PT)) * NT] = t;
+        }
+        if (PT > 0) Tm<2 * (PT > 0 ? PT : 1)>::st(taddr + k * ST, tt);
+    }
+    if (PT > 0) tm_wait_st();
+    // ---- target: log(eps + target(z_K)) and the reverse seed gz = -d log p / dz ----
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+        float za[D], zb[D], ga[D], gb[D], lpa, lpb;
+#pragma unroll
+        for (int d = 0; d < D; ++d) upk(z[p][d], za[d], zb[d]);
+        Target<float, D, TGT, true>::eval(za, tp, ntp, epsv, lpa, ga);
+        Target<float, D, TGT, true>::eval(zb, tp, ntp, epsv, lpb, gb);
+        if (MASKED) {
+            sum_p += (ok[2 * p] ? lpa : 0.f) + (ok[2 * p + 1] ? lpb : 0.f);
+#pragma unroll
+            for (int d = 0; d < D; ++d) gz[p][d] = pk(ok[2 * p] ? ga[d] : 0.f, ok[2 * p + 1] ? gb[d] : 0.f);
+        } else {
+            sum_p += lpa + lpb;
+#pragma unroll
+            for (int d = 0; d < D; ++d) gz[p][d] = pk(ga[d], gb[d]);
+        }
+    }
+    // ---- reverse sweep: restores z, accumulates log|det| and the gradient partials ----
+    // Layer k+1's partials are merged (pair halves added) at the end of its iteration and reduced across the warp
+    // inside iteration k, next to arithmetic they do not depend on.  History held in tensor memory is fetched one
+    // layer ahead; the loop is unrolled by two so that the prefetch buffers alternate instead of being copied.
+    constexpr int NTV = 2 * (PT > 0 ? PT : 1);
+    float ta[NTV], tb[NTV], vp[V];
+#pragma unroll
+    for (int i = 0; i < V; ++i) vp[i] = 0.f;
+    if (PT > 0) Tm<NTV>::ld(taddr + (K - 1) * ST, ta);
+    auto layer = [&](int k, float (&tc)[NTV], float (&tn)[NTV]) {
+        if (PT > 0) {
+            tm_wait_ld();
+            if (k > 0) Tm<NTV>::ld(taddr + (k - 1) * ST, tn);
+        }
+        u64 rb[RB / 2];
+        {
+            const ulonglong2* src = reinterpret_cast<const ulonglong2*>(lcb + k * RB);
+#pragma unroll
+            for (int i = 0; i < RB / 4; ++i) { const ulonglong2 v = src[i]; rb[2 * i] = v.x; rb[2 * i + 1] = v.y; }
+        }
+        const u64 nc = rb[D], c2 = rb[D + 1];
+        u64 v[V];                                   // the first pair starts the per-layer sums (no zero fill)
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            const u64 t = (p < PT) ? pk(tc[p < PT ? 2 * p : 0], tc[p < PT ? 2 * p + 1 : 0]) : hist_t[(k * SSP + (p - PT)) * NT];
+#pragma unroll
+            for (int d = 0; d < D; ++d) z[p][d] = fma2(rb[d], t, z[p][d]);        // z_{k-1} = z_k - s_k t_k
+            const u64 nhp = fma2(t, t, mone2);                                     // -(1 - t^2)
+            const u64 x = fma2(nhp, nc, one2);                                     // 1 + h' c
+            float x0, x1;
+            upk(x, x0, x1);
+            const u64 y = add2(pk(fabsf(x0), fabsf(x1)), ep[MASKED ? p : 0]);
+            prod[p] = mul2(prod[p], y);
+            float y0, y1;
+            upk(y, y0, y1);
+            const u64 ngx = pk(copysign_bits(M::rcp(y0), x0), copysign_bits(M::rcp(y1), x1));     // sign(x)/(eps+|x|)
+            v[2 * D + 1] = (p == 0) ? mul2(ngx, nhp) : fma2(ngx, nhp, v[2 * D + 1]);       // g_c
+            u64 ngt = mul2(mul2(ngx, c2), t);                                      // -(d/dt of the log-det term)
+#pragma unroll
+            for (int d = 0; d < D; ++d) {
+                v[D + d] = (p == 0) ? mul2(gz[p][d], t) : fma2(gz[p][d], t, v[D + d]);     // g_s
+                ngt = fma2(gz[p][d], rb[d], ngt);
+            }
+            const u64 ga = mul2(ngt, nhp);
+            v[2 * D] = (p == 0) ? ga : add2(v[2 * D], ga);                         // g_b
+#pragma unroll
+            for (int d = 0; d < D; ++d) {
+                v[d] = (p == 0) ? mul2(ga, z[p][d]) : fma2(ga, z[p][d], v[d]);     // g_w (direct)
+                gz[p][d] = fma2(ga, rb[D + 2 + d], gz[p][d]);
+            }
+        }
+        if ((k % kLogEvery) == 0) {
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                float p0, p1;
+                upk(prod[p], p0, p1);
+                lq[p] = fma2(pk(M::lg2(p0), M::lg2(p1)), nln2, lq[p]);
+                prod[p] = one2;
+            }
+        }
+        // cross-lane reduction of layer k+1's partials
+        if (k < K - 1) {
+            warp_reduce_multi<float, V>(vp, lane);
+            if (my_own) acc_w[(k + 1) * V + my_slot] += vp[0];
+        }
+#pragma unroll
+        for (int i = 0; i < V; ++i) { float a, b; upk(v[i], a, b); vp[i] = a + b; }
+    };
+    int k = K - 1;
+    for (; k >= 1; k -= 2) {
+        layer(k, ta, tb);
+        layer(k - 1, tb, ta);
+    }
+    if (k == 0) layer(0, ta, tb);
+    warp_reduce_multi<float, V>(vp, lane);
+    if (my_own) acc_w[my_slot] += vp[0];
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+        float a, b;
+        upk(lq[p], a, b);
+        sum_q += ((MASKED && !ok[2 * p]) ? 0.f : a) + ((MASKED && !ok[2 * p + 1]) ? 0.f : b);
+    }
+}
+
+template <int D, int NW, int SMAX, int ST, int TGT>
+__global__ void __launch_bounds__(NW * 32, 1)
+elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float* __restrict__ w,
+                 const float* __restrict__ s, const float* __restrict__ b, const float* __restrict__ c,
+                 const float* __restrict__ tparams, int ntp, float epsv, float* __restrict__ partials /*[gridDim.x][K*V+2]*/,
+                 SyncHeader* __restrict__ sync /* NULL: rows only, the caller sums them */, float* __restrict__ out_F,
+                 float* __restrict__ g_w, float* __restrict__ g_s, float* __restrict__ g_b, float* __restrict__ g_c) {
+    using M = Mth<float>;
+    constexpr int NT = NW * 32;
+    constexpr int V = 2 * D + 2;
+    constexpr int RF = 2 * recf_pairs<D>(), RB = 2 * recb_pairs<D>();
+    constexpr int SSP = (SMAX - ST) / 2;
+    static_assert(NW % 4 == 0 && SMAX % 2 == 0 && ST % 2 == 0 && ST <= SMAX && (ST == 0 || ST == 2 || ST == 4 || ST == 8), "configuration");
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float* sm = reinterpret_cast<float*>(smem_raw);
+    const int ntp_s = target_smem_count(TGT, D, ntp);
+    const Smem L(K, D, SSP, ntp_s, NT);
+    float* lcf = sm + L.lcf;
+    float* lcb = sm + L.lcb;
+    float* tp = sm + L.tp;
+    float* acc = sm + L.acc;                                      // [NW][K][V]
+    u64* hist = reinterpret_cast<u64*>(sm + L.hist);              // [K][SSP][NT] pairs
+    __shared__ uint32_t tmem_base_smem;
+    __shared__ float red[2 * NW];
+    __shared__ int s_last;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tmem_cols = tm_columns((NW / 4) * ST * K);
+    if (ST > 0 && warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                         (uint32_t)__cvta_generic_to_shared(&tmem_base_smem)), "r"(tmem_cols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    // programmatic dependent launch: nothing written by earlier work on the stream is touched before this returns
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+
+    if (sync && tid == NT - 1) {
+        // first use of this workspace (or its header was overwritten): exactly one block clears the ticket counter
+        const u64 good = cookie_for(sync);
+        volatile u64* ck = &sync->cookie;
+        u64 seen = *ck;
+        if (seen != good) {
+            if (seen != kCookieBusy && atomicCAS(&sync->cookie, seen, kCookieBusy) == seen) {
+                sync->counter = 0;
+                __threadfence();
+                atomicExch(&sync->cookie, good);
+            }
+            while (*ck != good) { }
+            __threadfence();
+        }
+    }
+
+    for (int k = tid; k < K; k += NT) {
+        const float kap = M::kArgScale;
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            const float wv = w[k * D + d], sv = s[k * D + d];
+            lcf[k * RF + 2 * d] = lcf[k * RF + 2 * d + 1] = wv * kap;
+            lcf[k * RF + 2 * (D + 1 + d)] = lcf[k * RF + 2 * (D + 1 + d) + 1] = sv;
+            lcb[k * RB + 2 * d] = lcb[k * RB + 2 * d + 1] = -sv;
+            lcb[k * RB + 2 * (D + 2 + d)] = lcb[k * RB + 2 * (D + 2 + d) + 1] = wv;
+        }
+        lcf[k * RF + 2 * D] = lcf[k * RF + 2 * D + 1] = b[k] * kap;
+        if (RF > 2 * (2 * D + 1)) lcf[k * RF + 2 * (2 * D + 1)] = lcf[k * RF + 2 * (2 * D + 1) + 1] = 0.f;
+        lcb[k * RB + 2 * D] = lcb[k * RB + 2 * D + 1] = -c[k];
+        lcb[k * RB + 2 * (D + 1)] = lcb[k * RB + 2 * (D + 1) + 1] = -2.f * c[k];
+    }
+    target_prepare<float>(TGT, D, tparams, ntp, tp);
+    for (int i = tid; i < NW * K * V; i += NT) acc[i] = 0.f;
+    if (ST > 0) asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    uint32_t taddr = 0;
+    if (ST > 0) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        taddr = tmem_base_smem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((warp >> 2) * ST * K);
+    }
+    const int my_slot = warp_slot<V>(lane);
+    const bool my_own = warp_slot_owner<V>(lane);
+    float* acc_w = acc + warp * K * V;
+    u64* hist_t = hist + tid;
+
+    float sum_q = 0.f, sum_p = 0.f;
+    // rounds: every thread of the grid takes SMAX samples per full round and `srem` in the last one
+    const long long T = (long long)gridDim.x * NT;
+    const long long per = ((N + T - 1) / T + 1) & ~1LL;                 // samples per thread, rounded up to a pair
+    const long long nfull = per / SMAX;
+    const int srem = (int)(per - nfull * SMAX);
+    const long long gw = (long long)blockIdx.x * NW + warp;
+    for (long long r = 0; r < nfull; ++r) {
+        const long long start = r * T * SMAX + gw * 32 * SMAX;
+        if (start >= N) break;
+        const long long n0 = start + (long long)lane * SMAX;
+        if (start + 32 * SMAX <= N)
+            pair_tile<D, SMAX, SMAX, ST, NT, TGT, false>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, my_slot, my_own, sum_q, sum_p);
+        else
+            pair_tile<D, SMAX, SMAX, ST, NT, TGT, true>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, my_slot, my_own, sum_q, sum_p);
+    }
+    if (srem > 0) {
+        const long long start = nfull * T * SMAX + gw * 32 * srem;
+        const long long n0 = start + (long long)lane * srem;
+        if (start < N) {
+            const bool full = start + 32LL * srem <= N;
+#define NF_PR_REM(S_)                                                                                                        \
+    if (SMAX > S_ && srem == S_) {                                                                                           \
+        if (full) pair_tile<D, (S_ < SMAX ? S_ : 2), SMAX, ST, NT, TGT, false>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, my_slot, my_own, sum_q, sum_p); \
+        else pair_tile<D, (S_ < SMAX ? S_ : 2), SMAX, ST, NT, TGT, true>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, my_slot, my_own, sum_q, sum_p);      \
+    }
+            NF_PR_REM(2)
+            NF_PR_REM(4)
+            NF_PR_REM(6)
+#undef NF_PR_REM
+        }
+    }
+
+    // ---- block row ----
+    sum_q = warp_sum(sum_q);
+    sum_p = warp_sum(sum_p);
+    if (lane == 0) { red[warp] = sum_q; red[NW + warp] = sum_p; }
+    __syncthreads();
+    const int row = K * V + 2;
+    float* out = partials + (size_t)blockIdx.x * row;
+    for (int i = tid; i < K * V; i += NT) {
+        float a = 0.f;
+#pragma unroll
+        for (int wi = 0; wi < NW; ++wi) a += acc[wi * K * V + i];
+        out[i] = a;
+    }
+    if (tid == 0) {
+        float q = 0.f, p = 0.f;
+#pragma unroll
+        for (int wi = 0; wi < NW; ++wi) { q += red[wi]; p += red[NW + wi]; }
+        out[K * V] = q;
+        out[K * V + 1] = p;
+    }
+    if (ST > 0) asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    if (sync) {
+        // the last block to arrive adds all rows in row order and scatters them into the caller's arrays
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) s_last = (atomicAdd(&sync->counter, 1u) == gridDim.x - 1) ? 1 : 0;
+        __syncthreads();
+        if (s_last) {
+            __threadfence();
+            const int nrows = gridDim.x;
+            float* stage = acc;                                   // reuse: [groups][row]
+            const int groups = (NT / row) > 0 ? ((NT / row) < 4 ? (NT / row) : 4) : 1;
+            for (int base = 0; base < row; base += NT) {          // row > NT: several passes, one group
+                const int g = (groups > 1) ? tid / row : 0;
+                const int i = (groups > 1) ? tid - g * row : base + tid;
+                float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+                if (i < row && g < groups) {
+                    const int r0 = (nrows * g) / groups, r1 = (nrows * (g + 1)) / groups;
+                    int r = r0;
+                    for (; r + 4 <= r1; r += 4) {
+                        a0 += __ldcg(partials + (size_t)r * row + i);
+                        a1 += __ldcg(partials + (size_t)(r + 1) * row + i);
+                        a2 += __ldcg(partials + (size_t)(r + 2) * row + i);
+                        a3 += __ldcg(partials + (size_t)(r + 3) * row + i);
+                    }
+                    for (; r < r1; ++r) a0 += __ldcg(partials + (size_t)r * row + i);
+                    stage[g * row + i] = (a0 + a1) + (a2 + a3);
+                }
+                if (groups > 1) break;
+            }
+            __syncthreads();
+            for (int i = tid; i < row; i += NT) {
+                float a = stage[i];
+                for (int g = 1; g < groups; ++g) a += stage[g * row + i];
+                if (i >= K * V) {
+                    out_F[1 + (i - K * V)] = a;
+                    stage[i] = a;
+                } else if (g_w) {
+                    const int k = i / V, j = i - k * V;
+                    if (j < D) g_w[k * D + j] = a;
+                    else if (j < 2 * D) g_s[k * D + (j - D)] = a;
+                    else if (j == 2 * D) g_b[k] = a;
+                    else g_c[k] = a;
+                }
+            }
+            __syncthreads();
+            if (tid == 0) {
+                out_F[0] = stage[K * V] - stage[K * V + 1];
+                sync->counter = 0;
+            }
+        }
+    }
+    if (ST > 0) {
+        __syncthreads();
+        if (warp == 0)
+            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base_smem), "r"(tmem_cols) : "memory");
+    }
+}
+
+}  // namespace pr
+}  // namespace nf

@@ -42,8 +42,8 @@ PROTOTYPES = {
     'nf_planar_elbo_fwd_bwd_noalloc_f32': (c_int, _elbo_args(c_float)[:17] + [c_void_p]),
     'nf_script_train_workspace_bytes': (c_size_t, [c_int, c_int, c_int]),
     'nf_script_train_workspace_bytes_n': (c_size_t, [c_int64, c_int, c_int, c_int]),
-    'nf_script_train_f32': (c_int, [c_void_p, c_int64, c_int64, c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_float, c_int] + [c_float] * 4 + [c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
-    'nf_script_train_f64': (c_int, [c_void_p, c_int64, c_int64, c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_double, c_int] + [c_double] * 4 + [c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    'nf_script_train_f32': (c_int, [c_void_p, c_int64, c_int64, c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_float, c_int] + [c_float] * 4 + [c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    'nf_script_train_f64': (c_int, [c_void_p, c_int64, c_int64, c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_double, c_int] + [c_double] * 4 + [c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     'nf_session_create': (c_int, [ctypes.POINTER(c_void_p), c_int64, c_int, c_int, c_int]),
     'nf_session_destroy': (None, [c_void_p]),
     'nf_session_elbo_host_f32': (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int, c_void_p, c_int, c_float, c_int, c_void_p]),

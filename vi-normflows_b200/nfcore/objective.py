@@ -284,11 +284,14 @@ class SharedFlowObjective:
             'rmsprop': (1, lambda h: (h.get('gamma', 0.9), h.get('eps', 1e-8), 0.0)),
             'adam': (2, lambda h: (h.get('b1', 0.9), h.get('b2', 0.999), h.get('eps', 1e-8)))}
 
-    def train(self, params, eps_all, optimizer='adam', step_size=1e-3, **hyper):
+    def train(self, params, eps_all, optimizer='adam', step_size=1e-3, state=None, **hyper):
         """Run len(eps_all) optimiser iterations without leaving the GPU.
 
         eps_all: (n_iters, N, D) samples, slice t being the draw of iteration t.  Update rules and defaults
         are autograd 1.3's (autograd.misc.optimizers).  Returns (final params float64, trace of F per iteration).
+        After the call ``self.train_state`` describes the optimiser (its running averages and the number of
+        iterations done); passing it back as ``state`` continues the same run -- a run cut into several calls
+        follows the trajectory of one call (the reference keeps one optimiser for all iterations, get_data.py:140).
         Script semantics only; not available with a process group."""
         if self.group is not None or self.semantics != 'script':
             raise NFError('train(): single-process, script semantics only')
@@ -302,9 +305,23 @@ class SharedFlowObjective:
         dev = self.device
         code, hp = self._OPT[optimizer]
         h1, h2, h3 = hp(hyper)
+        # the kernels read every iteration's slice with 16-byte vector loads: pad the slices to a multiple of 16 bytes
+        per16 = 16 // self.np_dtype.itemsize
+        stride = -(-(N * D) // per16) * per16
+        if stride != N * D and n_iters > 1:
+            padded = np.zeros((n_iters, stride), dtype=self.np_dtype)
+            padded[:, :N * D] = eps_all.reshape(n_iters, N * D)
+            eps_all = padded
+        else:
+            stride = N * D
         eps_dev = torch.as_tensor(eps_all).to(dev)
         p_dev = torch.as_tensor(np.asarray(params, dtype=np.float64).astype(self.np_dtype)).to(dev)
-        state = torch.empty(2 * P, dtype=self.dtype, device=dev)
+        if state is not None:
+            if state['optimizer'] != optimizer or state['opt'].numel() != 2 * P or state['opt'].dtype != self.dtype:
+                raise NFError('train(): `state` belongs to a different optimiser or problem')
+            opt, first_iter, resume = state['opt'], int(state['iters']), 1
+        else:
+            opt, first_iter, resume = torch.empty(2 * P, dtype=self.dtype, device=dev), 0, 0
         trace = torch.empty(max(n_iters, 1), dtype=self.dtype, device=dev)
         nws = lib.nf_script_train_workspace_bytes_n(N, K, D, self.np_dtype.itemsize)
         ws = torch.empty(nws, dtype=torch.uint8, device=dev)
@@ -315,7 +332,9 @@ class SharedFlowObjective:
             st = torch.cuda.current_stream(dev).cuda_stream
             rc = fn(vp(eps_dev), n_iters, N, D, K, vp(p_dev), ops.TARGET_IDS[self.target_name], vp(self.tparams),
                     0 if self.tparams is None else self.tparams.numel(), creal(self.log_eps), code, creal(step_size),
-                    creal(h1), creal(h2), creal(h3), vp(state), vp(trace), vp(ws), nws, ctypes.c_void_p(st))
+                    creal(h1), creal(h2), creal(h3), first_iter, resume, stride, vp(opt), vp(trace), vp(ws), nws,
+                    ctypes.c_void_p(st))
         _lib.check(rc)
         self.launches += 3 * n_iters + 1
+        self.train_state = {'opt': opt, 'iters': first_iter + n_iters, 'optimizer': optimizer}
         return p_dev.double().cpu().numpy(), trace[:n_iters].double().cpu().numpy()

@@ -65,35 +65,34 @@ def optimise(func, num_samples, num_iter, lr, K, dim_z=2, optimizer='rmsprop', e
     def draw():
         return np.random.multivariate_normal(np.zeros(dim_z), np.eye(dim_z), num_samples)
 
-    t = 0
-    while t < num_iter:
-        # iterations [t, end) run on the device; iteration t is the only one of the chunk whose callback prints
-        end = min(num_iter, (t // 100 + 1) * 100)
-        z_first = draw()                                     # gradient(params, t)
+    # Iterations run on the device in runs that end where the reference's callback has to print: the callback of
+    # iteration t (get_data.py:128-138) sees the parameters BEFORE update t and draws after gradient(params, t)
+    # has drawn, so a run covers iterations [t0, t1) where t1 is the next iteration whose callback prints.  One
+    # optimiser state serves all runs (rmsprop(gradient, init_params, callback, num_iter, lr) keeps one, :140).
+    def prints(t):
+        return t % 100 == 0 or (t + 1) % num_iter == 0
+
+    state = None
+    pending = []                 # draws of iterations whose update has not been applied yet
+    for t in range(num_iter):
+        if prints(t) and pending:
+            x, _ = obj.train(x, np.stack(pending), optimizer=optimizer, step_size=lr, state=state)
+            state, pending = obj.train_state, []
+        pending.append(draw())                               # gradient(params, t)
         if t % 100 == 0:                                     # callback :129-132 (objective, then other_metrics)
             z_obj, z_met = draw(), draw()
             if verbose:
                 energy = obj.value(x, z_obj)
                 joint, entropy = obj.metrics(x, z_met)
                 print("Iteration {}; Energy: {}; Joint: {}; Entropy: {}".format(t, energy, joint, entropy))
-        last_in_chunk = end == num_iter
-        n_mid = end - t - 1 - (1 if last_in_chunk and end - t > 1 else 0)
-        zs = [z_first] + [draw() for _ in range(max(n_mid, 0))]
-        x, _ = obj.train(x, np.stack(zs), optimizer=optimizer, step_size=lr)
-        t += len(zs)
-        if last_in_chunk:
-            if t < num_iter:                                 # the final iteration: its draws come before the final metrics
-                z_last = draw()
-            else:
-                z_last = None
-            z_met, z_obj = draw(), draw()                    # callback :133-138 (other_metrics, then objective)
+        if (t + 1) % num_iter == 0:                          # callback :133-138 (other_metrics, then objective)
+            z_met, z_obj = draw(), draw()
             if verbose:
                 print("\nFINAL METRICS\n")
                 joint, entropy = obj.metrics(x, z_met)
                 print("Free energy: ", obj.value(x, z_obj))
                 print("Joint: ", joint)
                 print("Entropy: ", entropy)
-            if z_last is not None:
-                x, _ = obj.train(x, z_last[None], optimizer=optimizer, step_size=lr)
-                t += 1
+    if pending:
+        x, _ = obj.train(x, np.stack(pending), optimizer=optimizer, step_size=lr, state=state)
     return x
