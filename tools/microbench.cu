@@ -52,6 +52,15 @@ __global__ void __launch_bounds__(1024) k(float* out, long long* cyc, float seed
             if (OP == 17) asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(*(unsigned long long*)&p[i]) : "l"(*(const unsigned long long*)&p[(i + 1) % UNROLL]), "l"(cc));  // two varying sources
             if (OP == 18) { asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(*(unsigned long long*)&p[i]) : "l"(mm), "l"(cc));
                             a[i] = (a[i] > 0.5f) ? a[(i + 1) % UNROLL] : m; }   // 1 FFMA2 + FSETP + SEL (alu pipe)
+            // does a packed instruction hold the issue port for its two pipe cycles?  (2 FFMA2 + 1 LOP3: 4 clocks if not, 5 if so)
+            if (OP == 19) { asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(*(unsigned long long*)&p[i]) : "l"(mm), "l"(cc));
+                            asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(*(unsigned long long*)&p[(i + 4) % UNROLL]) : "l"(mm), "l"(cc));
+                            asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(*(unsigned*)&a[i]) : "r"(*(const unsigned*)&m), "r"(*(const unsigned*)&c)); }
+            if (OP == 20) { asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(*(unsigned long long*)&p[i]) : "l"(mm), "l"(cc));
+                            asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(*(unsigned*)&a[i]) : "r"(*(const unsigned*)&m), "r"(*(const unsigned*)&c)); }
+            if (OP == 21) asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(*(unsigned*)&a[i]) : "r"(*(const unsigned*)&m), "r"(*(const unsigned*)&c));
+            if (OP == 22) asm volatile("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(*(unsigned long long*)&p[i]) : "l"(*(const unsigned long long*)&p[(i + 1) % UNROLL]), "l"(*(const unsigned long long*)&p[(i + 3) % UNROLL]));  // accumulate, three varying
+            if (OP == 23) { a[i] = fmaf(a[i], m, c); asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(*(unsigned*)&p[i].x) : "r"(*(const unsigned*)&m), "r"(*(const unsigned*)&c)); }  // FFMA + LOP3
         }
     }
     long long t1 = clock64();
@@ -110,6 +119,11 @@ int main() {
         run<16>("3 FFMA2 + 1 MUFU.EX2", 4, threads);
         run<17>("FFMA2 d=d*p+C (two varying)", 1, threads);
         run<18>("1 FFMA2 + FSETP + SEL", 3, threads);
+        run<19>("2 FFMA2 + 1 LOP3", 3, threads);
+        run<20>("1 FFMA2 + 1 LOP3", 2, threads);
+        run<21>("LOP3", 1, threads);
+        run<22>("FFMA2 d=a*b+d (three varying)", 1, threads);
+        run<23>("1 FFMA + 1 LOP3", 2, threads);
     }
     return 0;
 }

@@ -14,8 +14,10 @@
 //     the grid does the same amount of work for any N (no tail wave);
 //   * tanh history: the first ST samples of a thread in tensor memory (tcgen05.st/ld, fetched one layer
 //     ahead), the rest in shared memory as 64-bit pairs;
-//   * the 2D+2 gradient partials of a layer are reduced across the warp one layer behind the arithmetic
-//     (halving butterfly) into a per-warp shared-memory table; the block writes one row of sums;
+//   * the 2D+2 gradient partials of a layer go to a per-warp staging area in shared memory (one store per value,
+//     nothing waits on it); after every fourth layer the lanes of the warp each add up one staged row (one value of one
+//     layer over the 32 lanes: eight 128-bit loads, rows padded so that the loads do not collide) into the warp's
+//     table of sums.  No chain of dependent shuffles sits in the layer loop; the block writes one row of sums;
 //   * the last block to finish (ticket in the workspace header) adds the rows in a fixed order and writes
 //     the caller's outputs: one launch per call, bitwise reproducible for a fixed grid.
 #pragma once
@@ -86,8 +88,11 @@ __host__ __device__ constexpr int tm_columns(int n) { int c = 32; while (c < n) 
 template <int D> __host__ __device__ constexpr int recf_pairs() { return (2 * D + 2) & ~1; }
 template <int D> __host__ __device__ constexpr int recb_pairs() { return 2 * D + 2; }
 
+constexpr int kStageLayers = 4;            // layers whose partials are staged before the lanes add them up
+constexpr int kStagePitch = 36;            // floats per staged row: 32 lanes + 4 (128-bit reads of 8 rows hit 8 distinct bank groups)
+
 struct Smem {
-    int lcf, lcb, tp, acc, hist, total;      // offsets in floats
+    int lcf, lcb, tp, acc, stg, hist, total;      // offsets in floats
     __host__ __device__ Smem(int K, int D, int ssp /*pairs per thread kept in shared memory*/, int ntp_s, int nthreads) {
         const int V = 2 * D + 2;
         const int rf = 2 * ((2 * D + 2) & ~1), rb = 2 * (2 * D + 2);
@@ -95,7 +100,8 @@ struct Smem {
         lcb = lcf + K * rf;
         tp = lcb + K * rb;
         acc = (tp + ntp_s + 3) & ~3;
-        hist = (acc + (nthreads / 32) * K * V + 3) & ~3;
+        stg = (acc + (nthreads / 32) * K * V + 3) & ~3;
+        hist = stg + (nthreads / 32) * kStageLayers * V * kStagePitch;
         total = hist + 2 * K * ssp * nthreads;
     }
 };
@@ -112,7 +118,7 @@ __device__ __forceinline__ void pair_tile(const float* __restrict__ eps, long lo
                                           const float* __restrict__ lcf, const float* __restrict__ lcb,
                                           const float* __restrict__ tp, int ntp, float epsv,
                                           u64* __restrict__ hist_t, uint32_t taddr, float* __restrict__ acc_w, int lane,
-                                          int my_slot, bool my_own, float& sum_q, float& sum_p) {
+                                          float* __restrict__ stg_w /* staging area of this warp */, float& sum_q, float& sum_p) {
     using M = Mth<float>;
     constexpr int V = 2 * D + 2;
     constexpr int P = S / 2;                        // pairs this round
@@ -226,9 +232,9 @@ __device__ __forceinline__ void pair_tile(const float* __restrict__ eps, long lo
     // inside iteration k, next to arithmetic they do not depend on.  History held in tensor memory is fetched one
     // layer ahead; the loop is unrolled by two so that the prefetch buffers alternate instead of being copied.
     constexpr int NTV = 2 * (PT > 0 ? PT : 1);
-    float ta[NTV], tb[NTV], vp[V];
-#pragma unroll
-    for (int i = 0; i < V; ++i) vp[i] = 0.f;
+    float ta[NTV], tb[NTV];
+    float* const stg_wr = stg_w + lane;                           // lane's column of the staged rows
+    const float* const stg_rd = stg_w + lane * kStagePitch;       // the row this lane adds up (lane < kStageLayers * V)
     if (PT > 0) Tm<NTV>::ld(taddr + (K - 1) * ST, ta);
     auto layer = [&](int k, float (&tc)[NTV], float (&tn)[NTV]) {
         if (PT > 0) {
@@ -281,13 +287,27 @@ __device__ __forceinline__ void pair_tile(const float* __restrict__ eps, long lo
                 prod[p] = one2;
             }
         }
-        // cross-lane reduction of layer k+1's partials
-        if (k < K - 1) {
-            warp_reduce_multi<float, V>(vp, lane);
-            if (my_own) acc_w[(k + 1) * V + my_slot] += vp[0];
-        }
+        // stage this layer's partials (pair halves added); row = (layer within the group of four, value)
+        {
+            float* dst = stg_wr + (k & (kStageLayers - 1)) * (V * kStagePitch);
 #pragma unroll
-        for (int i = 0; i < V; ++i) { float a, b; upk(v[i], a, b); vp[i] = a + b; }
+            for (int i = 0; i < V; ++i) { float a, b; upk(v[i], a, b); dst[i * kStagePitch] = a + b; }
+        }
+        if ((k & (kStageLayers - 1)) == 0) {
+            // layers k .. k+3 are staged: lane r adds up row r = 32 lane values of (layer k + r / V, value r % V).  Rows of
+            // layers >= K (first, partial group) hold stale data and are skipped.
+            __syncwarp();
+            if (lane < kStageLayers * V && k * V + lane < K * V) {
+                float4 q[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) q[j] = *reinterpret_cast<const float4*>(stg_rd + 4 * j);
+                float a0 = q[0].x, a1 = q[0].y, a2 = q[0].z, a3 = q[0].w;
+#pragma unroll
+                for (int j = 1; j < 8; ++j) { a0 += q[j].x; a1 += q[j].y; a2 += q[j].z; a3 += q[j].w; }
+                acc_w[k * V + lane] += (a0 + a1) + (a2 + a3);
+            }
+            __syncwarp();
+        }
     };
     int k = K - 1;
     for (; k >= 1; k -= 2) {
@@ -295,8 +315,6 @@ __device__ __forceinline__ void pair_tile(const float* __restrict__ eps, long lo
         layer(k - 1, tb, ta);
     }
     if (k == 0) layer(0, ta, tb);
-    warp_reduce_multi<float, V>(vp, lane);
-    if (my_own) acc_w[my_slot] += vp[0];
 #pragma unroll
     for (int p = 0; p < P; ++p) {
         float a, b;
@@ -311,7 +329,8 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
                  const float* __restrict__ s, const float* __restrict__ b, const float* __restrict__ c,
                  const float* __restrict__ tparams, int ntp, float epsv, float* __restrict__ partials /*[gridDim.x][K*V+2]*/,
                  SyncHeader* __restrict__ sync /* NULL: rows only, the caller sums them */, float* __restrict__ out_F,
-                 float* __restrict__ g_w, float* __restrict__ g_s, float* __restrict__ g_b, float* __restrict__ g_c) {
+                 float* __restrict__ g_w, float* __restrict__ g_s, float* __restrict__ g_b, float* __restrict__ g_c,
+                 int flags /* tuning: bit 0 = no rotation of the rounds */) {
     using M = Mth<float>;
     constexpr int NT = NW * 32;
     constexpr int V = 2 * D + 2;
@@ -381,9 +400,8 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         taddr = tmem_base_smem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((warp >> 2) * ST * K);
     }
-    const int my_slot = warp_slot<V>(lane);
-    const bool my_own = warp_slot_owner<V>(lane);
     float* acc_w = acc + warp * K * V;
+    float* stg_w = sm + L.stg + warp * (kStageLayers * V * kStagePitch);
     u64* hist_t = hist + tid;
 
     float sum_q = 0.f, sum_p = 0.f;
@@ -393,24 +411,31 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
     const long long nfull = per / SMAX;
     const int srem = (int)(per - nfull * SMAX);
     const long long gw = (long long)blockIdx.x * NW + warp;
-    for (long long r = 0; r < nfull; ++r) {
-        const long long start = r * T * SMAX + gw * 32 * SMAX;
-        if (start >= N) break;
-        const long long n0 = start + (long long)lane * SMAX;
-        if (start + 32 * SMAX <= N)
-            pair_tile<D, SMAX, SMAX, ST, NT, TGT, false>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, my_slot, my_own, sum_q, sum_p);
-        else
-            pair_tile<D, SMAX, SMAX, ST, NT, TGT, true>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, my_slot, my_own, sum_q, sum_p);
-    }
-    if (srem > 0) {
+    // The warps that share a scheduler (warp, warp + 4, ...) visit the rounds in rotated order: their forward sweeps
+    // (transcendental-bound) and reverse sweeps (multiply-add-bound) then overlap instead of all warps of the SM
+    // competing for the same pipe at the same time.  Which warp owns which samples does not change.
+    const int nrounds = (int)nfull + (srem > 0 ? 1 : 0);
+    const int rot = (nrounds > 1 && !(flags & 1)) ? (warp >> 2) % nrounds : 0;
+    for (int rr = 0; rr < nrounds; ++rr) {
+        const long long r = (rr + rot) % nrounds;
+        if (r < nfull) {
+            const long long start = r * T * SMAX + gw * 32 * SMAX;
+            if (start >= N) continue;
+            const long long n0 = start + (long long)lane * SMAX;
+            if (start + 32 * SMAX <= N)
+                pair_tile<D, SMAX, SMAX, ST, NT, TGT, false>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p);
+            else
+                pair_tile<D, SMAX, SMAX, ST, NT, TGT, true>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p);
+            continue;
+        }
         const long long start = nfull * T * SMAX + gw * 32 * srem;
         const long long n0 = start + (long long)lane * srem;
         if (start < N) {
             const bool full = start + 32LL * srem <= N;
 #define NF_PR_REM(S_)                                                                                                        \
     if (SMAX > S_ && srem == S_) {                                                                                           \
-        if (full) pair_tile<D, (S_ < SMAX ? S_ : 2), SMAX, ST, NT, TGT, false>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, my_slot, my_own, sum_q, sum_p); \
-        else pair_tile<D, (S_ < SMAX ? S_ : 2), SMAX, ST, NT, TGT, true>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, my_slot, my_own, sum_q, sum_p);      \
+        if (full) pair_tile<D, (S_ < SMAX ? S_ : 2), SMAX, ST, NT, TGT, false>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p); \
+        else pair_tile<D, (S_ < SMAX ? S_ : 2), SMAX, ST, NT, TGT, true>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p);      \
     }
             NF_PR_REM(2)
             NF_PR_REM(4)
@@ -450,24 +475,25 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
             __threadfence();
             const int nrows = gridDim.x;
             float* stage = acc;                                   // reuse: [groups][row]
-            const int groups = (NT / row) > 0 ? ((NT / row) < 4 ? (NT / row) : 4) : 1;
-            for (int base = 0; base < row; base += NT) {          // row > NT: several passes, one group
-                const int g = (groups > 1) ? tid / row : 0;
-                const int i = (groups > 1) ? tid - g * row : base + tid;
+            // work item = (group of consecutive rows, value); every thread issues the loads of an item together, so the
+            // whole pass costs a few L2 round trips instead of one per row
+            int groups = (NW * K * V) / row;
+            if (groups > 8) groups = 8;
+            if (groups > nrows) groups = nrows;
+            for (int it = tid; it < groups * row; it += NT) {
+                const int g = it / row, i = it - g * row;
+                const int r0 = (nrows * g) / groups, r1 = (nrows * (g + 1)) / groups;
                 float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-                if (i < row && g < groups) {
-                    const int r0 = (nrows * g) / groups, r1 = (nrows * (g + 1)) / groups;
-                    int r = r0;
-                    for (; r + 4 <= r1; r += 4) {
-                        a0 += __ldcg(partials + (size_t)r * row + i);
-                        a1 += __ldcg(partials + (size_t)(r + 1) * row + i);
-                        a2 += __ldcg(partials + (size_t)(r + 2) * row + i);
-                        a3 += __ldcg(partials + (size_t)(r + 3) * row + i);
-                    }
-                    for (; r < r1; ++r) a0 += __ldcg(partials + (size_t)r * row + i);
-                    stage[g * row + i] = (a0 + a1) + (a2 + a3);
+                int r = r0;
+                for (; r + 8 <= r1; r += 8) {
+                    float t[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) t[j] = __ldcg(partials + (size_t)(r + j) * row + i);
+                    a0 += t[0]; a1 += t[1]; a2 += t[2]; a3 += t[3];
+                    a0 += t[4]; a1 += t[5]; a2 += t[6]; a3 += t[7];
                 }
-                if (groups > 1) break;
+                for (; r < r1; ++r) a0 += __ldcg(partials + (size_t)r * row + i);
+                stage[g * row + i] = (a0 + a1) + (a2 + a3);
             }
             __syncthreads();
             for (int i = tid; i < row; i += NT) {

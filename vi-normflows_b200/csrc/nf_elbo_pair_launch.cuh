@@ -8,7 +8,7 @@
 
 namespace nf {
 
-struct PairCfg { int nw, smax, st; };
+struct PairCfg { int nw, smax, st, flags; };
 const PairCfg& pair_override();
 
 #define NF_PAIR_ARGS const float* eps, long long N, int K, const float* w, const float* s, const float* b, const float* c, \
@@ -24,7 +24,7 @@ static int launch_pair(const float* eps, long long N, int K, const float* w, con
     const int ntp_s = target_smem_count(TGT, D, ntp);
     const pr::Smem L(K, D, (SMAX - ST) / 2, ntp_s, NW * 32);
     const size_t smem = (size_t)L.total * sizeof(float);
-    if (smem > 227 * 1024 - 64 || (NW / 4) * ST * K > 512) return NF_ERR_UNSUPPORTED;
+    if (smem > 227 * 1024 - 256 || (NW / 4) * ST * K > 512) return NF_ERR_UNSUPPORTED;
     int dev = 0;
     NF_CUDA_OK(cudaGetDevice(&dev));
     if (dev < 0 || dev >= kMaxDevices) return NF_ERR_UNSUPPORTED;
@@ -43,7 +43,7 @@ static int launch_pair(const float* eps, long long N, int K, const float* w, con
     if (grid > tiles) grid = tiles;
     if (grid < 1) grid = 1;
     NF_CUDA_OK(launch_pdl(kern, dim3((unsigned)grid), dim3(NW * 32), smem, stream, eps, N, K, w, s, b, c, tparams, ntp, epsv, partials,
-                          sync, out_F, g_w, g_s, g_b, g_c));
+                          sync, out_F, g_w, g_s, g_b, g_c, pair_override().flags));
     *nblocks_out = (int)grid;
     return NF_OK;
 }

@@ -7,8 +7,9 @@ namespace nf {
 // packed-pair kernel off (the launch then takes the scalar kernel of nf_elbo_impl.cuh)
 const PairCfg& pair_override() {
     static const PairCfg cfg = []() {
-        PairCfg c = {0, 0, 0};
+        PairCfg c = {0, 0, 0, 0};
         if (const char* e = getenv("NF_PAIR_CFG")) sscanf(e, "%d,%d,%d", &c.nw, &c.smax, &c.st);
+        if (const char* e = getenv("NF_PAIR_FLAGS")) c.flags = atoi(e);
         if (const char* e = getenv("NF_PAIR")) if (e[0] == '0') c.nw = -1;
         return c;
     }();
