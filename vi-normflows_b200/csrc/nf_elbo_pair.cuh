@@ -112,6 +112,10 @@ struct SyncHeader { u64 cookie; unsigned counter; unsigned pad; };
 constexpr u64 kCookieBusy = 0x6e66636f72655f42ull;       // "nfcore_B": a block is clearing the counter
 __host__ __device__ inline u64 cookie_for(const void* p) { return 0x6e66636f72653032ull ^ (u64)(uintptr_t)p; }
 
+// tuning aid (flags bit 1): per-block phase timestamps (globaltimer, ns): entry, set-up done, samples done, row
+// written and ticket taken, finalize done (last block only; 0 elsewhere), and the SM the block ran on
+__device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+
 // One round of one warp: S samples per thread (S/2 pairs) through all K layers and back.
 template <int D, int S, int SMAX, int ST, int NT, int TGT, bool MASKED>
 __device__ __forceinline__ void pair_tile(const float* __restrict__ eps, long long n0, long long N, int K,
@@ -330,7 +334,7 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
                  const float* __restrict__ tparams, int ntp, float epsv, float* __restrict__ partials /*[gridDim.x][K*V+2]*/,
                  SyncHeader* __restrict__ sync /* NULL: rows only, the caller sums them */, float* __restrict__ out_F,
                  float* __restrict__ g_w, float* __restrict__ g_s, float* __restrict__ g_b, float* __restrict__ g_c,
-                 int flags /* tuning: bit 0 = no rotation of the rounds */) {
+                 int flags /* tuning: bit 0 = no rotation of the rounds */, unsigned long long* __restrict__ stamps /* [256][8] or NULL */) {
     using M = Mth<float>;
     constexpr int NT = NW * 32;
     constexpr int V = 2 * D + 2;
@@ -351,6 +355,8 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
     __shared__ int s_last;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const bool stamp = stamps != nullptr && tid == 0 && blockIdx.x < 256;
+    if (stamp) { stamps[blockIdx.x * 8 + 0] = gtime(); stamps[blockIdx.x * 8 + 4] = 0; }
     const int tmem_cols = tm_columns((NW / 4) * ST * K);
     if (ST > 0 && warp == 0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
@@ -402,6 +408,7 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
     }
     float* acc_w = acc + warp * K * V;
     float* stg_w = sm + L.stg + warp * (kStageLayers * V * kStagePitch);
+    if (stamp) stamps[blockIdx.x * 8 + 1] = gtime();
     u64* hist_t = hist + tid;
 
     float sum_q = 0.f, sum_p = 0.f;
@@ -418,6 +425,13 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
     const int rot = (nrounds > 1 && !(flags & 1)) ? (warp >> 2) % nrounds : 0;
     for (int rr = 0; rr < nrounds; ++rr) {
         const long long r = (rr + rot) % nrounds;
+        if (rr + 1 < nrounds) {
+            // pull the next round's samples of this thread into L2 while this round computes
+            const long long rn = (rr + 1 + rot) % nrounds;
+            const long long sn = rn < nfull ? rn * T * SMAX + gw * 32 * SMAX + (long long)lane * SMAX
+                                            : nfull * T * SMAX + gw * 32 * srem + (long long)lane * srem;
+            if (sn < N) asm volatile("prefetch.global.L2 [%0];" ::"l"(eps + sn * D));
+        }
         if (r < nfull) {
             const long long start = r * T * SMAX + gw * 32 * SMAX;
             if (start >= N) continue;
@@ -445,6 +459,8 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
     }
 
     // ---- block row ----
+    if (stamps) __syncthreads();
+    if (stamp) stamps[blockIdx.x * 8 + 2] = gtime();
     sum_q = warp_sum(sum_q);
     sum_p = warp_sum(sum_p);
     if (lane == 0) { red[warp] = sum_q; red[NW + warp] = sum_p; }
@@ -467,33 +483,41 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
     if (ST > 0) asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     if (sync) {
         // the last block to arrive adds all rows in row order and scatters them into the caller's arrays
-        __threadfence();
         __syncthreads();
-        if (tid == 0) s_last = (atomicAdd(&sync->counter, 1u) == gridDim.x - 1) ? 1 : 0;
+        if (tid == 0) {
+            // release: the row this block wrote (ordered before the barrier) is visible to whoever sees the ticket;
+            // acquire: the last block sees every other block's row
+            unsigned ticket;
+            asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], 1;" : "=r"(ticket) : "l"(&sync->counter) : "memory");
+            s_last = (ticket == gridDim.x - 1) ? 1 : 0;
+        }
         __syncthreads();
+        if (stamp) { stamps[blockIdx.x * 8 + 3] = gtime(); unsigned smid; asm("mov.u32 %0, %smid;" : "=r"(smid)); stamps[blockIdx.x * 8 + 5] = smid; }
         if (s_last) {
-            __threadfence();
             const int nrows = gridDim.x;
-            float* stage = acc;                                   // reuse: [groups][row]
-            // work item = (group of consecutive rows, value); every thread issues the loads of an item together, so the
-            // whole pass costs a few L2 round trips instead of one per row
-            int groups = (NW * K * V) / row;
-            if (groups > 8) groups = 8;
-            if (groups > nrows) groups = nrows;
-            for (int it = tid; it < groups * row; it += NT) {
-                const int g = it / row, i = it - g * row;
-                const int r0 = (nrows * g) / groups, r1 = (nrows * (g + 1)) / groups;
-                float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-                int r = r0;
-                for (; r + 8 <= r1; r += 8) {
-                    float t[8];
+            float* stage = acc;                                   // reuse (the staging areas follow): [groups][row]
+            // work item = (group of 8 consecutive rows, value).  A thread issues the loads of all its items before it
+            // adds anything, so the whole pass costs about one L2 round trip.
+            constexpr int GR = 8, ITEMS = 8;
+            const int groups = (nrows + GR - 1) / GR;
+            const int nitems = groups * row;
+            for (int base = 0; base < nitems; base += NT * ITEMS) {
+                float t[ITEMS][GR];
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) t[j] = __ldcg(partials + (size_t)(r + j) * row + i);
-                    a0 += t[0]; a1 += t[1]; a2 += t[2]; a3 += t[3];
-                    a0 += t[4]; a1 += t[5]; a2 += t[6]; a3 += t[7];
+                for (int q = 0; q < ITEMS; ++q) {
+                    const int it = base + q * NT + tid;
+                    const int g = it / row, i = it - g * row;
+#pragma unroll
+                    for (int j = 0; j < GR; ++j) {
+                        const int r = g * GR + j;
+                        t[q][j] = (it < nitems && r < nrows) ? __ldcg(partials + (size_t)r * row + i) : 0.f;
+                    }
                 }
-                for (; r < r1; ++r) a0 += __ldcg(partials + (size_t)r * row + i);
-                stage[g * row + i] = (a0 + a1) + (a2 + a3);
+#pragma unroll
+                for (int q = 0; q < ITEMS; ++q) {
+                    const int it = base + q * NT + tid;
+                    if (it < nitems) stage[it] = ((t[q][0] + t[q][1]) + (t[q][2] + t[q][3])) + ((t[q][4] + t[q][5]) + (t[q][6] + t[q][7]));
+                }
             }
             __syncthreads();
             for (int i = tid; i < row; i += NT) {
@@ -514,6 +538,7 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
             if (tid == 0) {
                 out_F[0] = stage[K * V] - stage[K * V + 1];
                 sync->counter = 0;
+                if (stamps) stamps[(blockIdx.x < 256 ? blockIdx.x : 0) * 8 + 4] = gtime();
             }
         }
     }

@@ -8,7 +8,7 @@
 
 namespace nf {
 
-struct PairCfg { int nw, smax, st, flags; };
+struct PairCfg { int nw, smax, st, flags; unsigned long long* stamps; };
 const PairCfg& pair_override();
 
 #define NF_PAIR_ARGS const float* eps, long long N, int K, const float* w, const float* s, const float* b, const float* c, \
@@ -43,7 +43,7 @@ static int launch_pair(const float* eps, long long N, int K, const float* w, con
     if (grid > tiles) grid = tiles;
     if (grid < 1) grid = 1;
     NF_CUDA_OK(launch_pdl(kern, dim3((unsigned)grid), dim3(NW * 32), smem, stream, eps, N, K, w, s, b, c, tparams, ntp, epsv, partials,
-                          sync, out_F, g_w, g_s, g_b, g_c, pair_override().flags));
+                          sync, out_F, g_w, g_s, g_b, g_c, pair_override().flags, pair_override().stamps));
     *nblocks_out = (int)grid;
     return NF_OK;
 }

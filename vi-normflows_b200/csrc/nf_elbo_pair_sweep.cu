@@ -7,9 +7,13 @@ namespace nf {
 // packed-pair kernel off (the launch then takes the scalar kernel of nf_elbo_impl.cuh)
 const PairCfg& pair_override() {
     static const PairCfg cfg = []() {
-        PairCfg c = {0, 0, 0, 0};
+        PairCfg c = {0, 0, 0, 0, nullptr};
         if (const char* e = getenv("NF_PAIR_CFG")) sscanf(e, "%d,%d,%d", &c.nw, &c.smax, &c.st);
         if (const char* e = getenv("NF_PAIR_FLAGS")) c.flags = atoi(e);
+        if (c.flags & 2) {      // tuning aid: phase timestamps of every launch (of the device current at the first call)
+            if (cudaMalloc(&c.stamps, sizeof(unsigned long long) * 256 * 8) != cudaSuccess) c.stamps = nullptr;
+            else cudaMemset(c.stamps, 0, sizeof(unsigned long long) * 256 * 8);
+        }
         if (const char* e = getenv("NF_PAIR")) if (e[0] == '0') c.nw = -1;
         return c;
     }();
@@ -51,3 +55,10 @@ int pair_elbo(int tgt, const float* eps, long long N, int D, int K, const float*
 }
 
 }  // namespace nf
+
+// tuning aid: phase timestamps of the last packed-pair launch made with NF_PAIR_FLAGS bit 1 (see nf_elbo_pair.cuh)
+extern "C" int nf_debug_pair_stamps(unsigned long long* out /*[256][8]*/) {
+    if (!nf::pair_override().stamps) return NF_ERR_UNSUPPORTED;
+    NF_CUDA_OK(cudaMemcpy(out, nf::pair_override().stamps, sizeof(unsigned long long) * 256 * 8, cudaMemcpyDeviceToHost));
+    return NF_OK;
+}
