@@ -41,6 +41,8 @@ UNIT = 'samples/s'
 FLOPS_PER_SAMPLE = K_LAYERS * (14 * DIM + 25) + 2 * DIM + 64        # 1764
 MUFU_PER_SAMPLE = 4 * K_LAYERS + 10                                 # 138
 BYTES_PER_SAMPLE = 4 * DIM                                          # 8
+NCU_TRAFFIC_BYTES = 8.447488e6
+NCU_TRAFFIC_SOURCE = 'ncu capture profiles/r02_ncu_elbo_pair_kernel.txt (not measured in this run)'
 
 
 def params_np(seed=7):
@@ -145,7 +147,8 @@ def run_reference(args):
         'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus,
         'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': dt * 1e3, 'higher_is_better': True,
         'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
-        'config': config_dict(args.gpus),
+        'config': dict(config_dict(args.gpus), reference_samples_per_step=n_cpu,
+                       note='the CPU arm times a bounded sample of %d samples per step of this workload; the rate is what is compared' % n_cpu),
         'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': 'port',
                          'sample': '%d samples per step of the same K=32/D=2/U1 workload, torch float64 autograd '
                                    'over oracle/planar_torch.py (stand-in for autograd 1.3, not installable); '
@@ -192,37 +195,58 @@ def run_ours(args):
 
     small_ar = None
     if world > 1 and os.environ.get('NF_BENCH_NCCL', '0') != '1':
+        ok = 1
         try:
             from nfcore.peer import SmallAllReduce
             small_ar = SmallAllReduce(dist.group.WORLD, dev)      # one-shot exchange over NVLink peer memory
         except Exception as e:                                    # no P2P mapping: NCCL carries the vector
             if rank == 0:
                 print('bench: peer all-reduce unavailable (%s); using NCCL' % e, file=sys.stderr)
+            small_ar, ok = None, 0
+        flag = torch.tensor([ok], dtype=torch.int32, device=dev)  # all ranks take the same path
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) == 0:
             small_ar = None
+    resx = torch.zeros(nres + 3, dtype=torch.float32, device=dev)   # exchange form: [results | n_hi, n_lo, status]
 
     def local_step(i):
         ops.planar_elbo(eps[i % N_ROTATE], w_d, s_d, b_d, c_d, TARGET, None, 1e-7, True, out)
 
     def step(i):
-        local_step(i)
-        if world > 1:
-            if small_ar is not None:
-                small_ar(res)
-            else:
-                dist.all_reduce(res)
+        if world == 1:
+            local_step(i)
+        elif small_ar is not None:
+            # objective + exchange: the last block of the objective kernel pushes, waits and adds (one launch)
+            ops.planar_elbo_exchange(eps[i % N_ROTATE], w_d, s_d, b_d, c_d, TARGET, None, 1e-7, resx, small_ar)
+        else:
+            local_step(i)
+            dist.all_reduce(res)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    for i in range(max(args.warmup, 3)):
+    n_warm = max(args.warmup, 3)
+    for i in range(n_warm):
         step(i)
     barrier()
     sampler = ClockSampler(local_rank) if rank == 0 else None
     if sampler:
         sampler.start()
-        time.sleep(0.25)
+    # keep every GPU under this load while the clock sampler comes up (an idle GPU drops its clocks within a fraction
+    # of a second, and the timed region below is only milliseconds long); these steps are untimed warm-up too
+    t_busy = time.time() + 0.4
+    extra_warm = 0
+    while True:
+        for i in range(50):
+            step(i)
+        extra_warm += 50
+        stop = torch.tensor([1 if time.time() >= t_busy else 0], dtype=torch.int32, device=dev)
+        if world > 1:
+            dist.all_reduce(stop, op=dist.ReduceOp.MIN)      # all ranks leave the loop in the same round (lock-step exchange)
+        if int(stop.item()) == 1:
+            break
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
@@ -239,6 +263,8 @@ def run_ours(args):
         torch.cuda.synchronize()
     clocks = sampler.stop() if sampler else None
     barrier()
+    if small_ar is not None and float(resx[nres + 2].item()) != 0.0:
+        raise RuntimeError('bench: the peer exchange reported a missing rank')
     tms = torch.tensor([ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
@@ -263,6 +289,21 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(tdt, op=dist.ReduceOp.MAX)
     e2e_value = N_PER_GPU * world * args.steps / float(tdt.item())
+    # the same call with what a drop-in caller holds: a pageable NumPy array (what np.random.multivariate_normal returns,
+    # get_data.py:100), converted to float32 inside the call; the draw itself is outside the timed region
+    host_np = [h.numpy().astype(np.float64) for h in host[:2]]
+    for i in range(2):
+        obj.value_and_grad(params, host_np[i % 2])
+    barrier()
+    t0 = time.perf_counter()
+    n_pg = max(4, min(args.steps, 20))
+    for i in range(n_pg):
+        obj.value_and_grad(params, host_np[i % 2])
+    torch.cuda.synchronize()
+    tpg = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tpg, op=dist.ReduceOp.MAX)
+    e2e_pageable = N_PER_GPU * world * n_pg / float(tpg.item())
     h2d = N_PER_GPU * BYTES_PER_SAMPLE + 4 * (2 * KD + 2 * K_LAYERS)
     d2h = 4 * nres
 
@@ -285,17 +326,19 @@ def run_ours(args):
         roofline = {
             'bound': 'mufu', 'achieved': per_gpu * MUFU_PER_SAMPLE / 1e9, 'peak': mufu_peak / 1e9, 'unit': 'G MUFU-op/s',
             'frac': fracs['mufu'],
-            # dram__bytes_read.sum + dram__bytes_write.sum of one objective-kernel launch at this workload, from the
-            # committed `ncu --set full` capture (profiles/r01e_ncu_elbo_kernel.txt); algorithmic bytes: 8.39e6
-            'traffic': 8.447488e6,
+            # dram__bytes_read.sum + dram__bytes_write.sum of one objective-kernel launch at this workload: a constant
+            # copied from the committed `ncu --set full` capture named in traffic_source, NOT measured by this run
+            # (algorithmic bytes: 8.39e6)
+            'traffic': NCU_TRAFFIC_BYTES, 'traffic_source': NCU_TRAFFIC_SOURCE,
             'per_unit': {'flops': FLOPS_PER_SAMPLE, 'mufu': MUFU_PER_SAMPLE, 'bytes': BYTES_PER_SAMPLE},
             'peak_source': 'formula SMs*16*sm_max_mhz (SURVEY.md §8d; MEASURED_PEAKS.json has no MUFU figure); '
                            'sm_max_mhz and hbm_gbs %s' % ('of measured' if peaks else 'of fallback'),
             'frac_fp32': fracs['fp32'], 'frac_hbm': fracs['hbm'],
             'achieved_hbm_gbs': per_gpu * BYTES_PER_SAMPLE / 1e9, 'peak_hbm_gbs': hbm_peak / 1e9,
             'frac_mufu_at_clock_under_load': (per_gpu * MUFU_PER_SAMPLE / (sms * 16 * f_load)) if f_load else None,
-            'kernel_ms': ms_per_step, 'kernel_note': 'events bracket objective kernel + partial-sum kernel'
-                                                     + ((' + one-shot NVLink all-reduce kernel' if small_ar is not None else ' + NCCL all-reduce') if world > 1 else ''),
+            'kernel_ms': ms_per_step,
+            'kernel_note': 'events bracket one launch per step: the objective kernel, whose last block adds the per-SM rows'
+                           + ((' and does the NVLink peer exchange' if small_ar is not None else '; + NCCL all-reduce') if world > 1 else ''),
         }
         n_cpu = 1 << 18
         cpu_value, cpu_dt = time_cpu(n_cpu, 6, 1) if world == 1 else (None, None)
@@ -318,15 +361,18 @@ def run_ours(args):
             big = {'samples_per_step': nb, 'value': vb, 'unit': UNIT, 'frac_mufu': vb * MUFU_PER_SAMPLE / mufu_peak}
             del eb
         line = {
-            'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps, 'warmup': max(args.warmup, 3),
+            'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps, 'warmup': n_warm + extra_warm,
             'ms_per_step': ms_per_step, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
             'dtype': 'f32', 'data': 'synthetic', 'config': config_dict(world),
             'roofline': roofline,
             'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
-                    'F': float(F_e2e)},
-            'gpu_launches': (3 if small_ar is not None else 2) * args.steps,
-            'exchange': None if world == 1 else ('nf_allreduce_small_f32 (NVLink peer stores, %d floats)' % nres if small_ar is not None
-                                                 else 'ncclAllReduce (%d floats)' % nres),
+                    'F': float(F_e2e), 'input': 'pinned host float32 samples (best case of the host API)'},
+            'e2e_pageable': {'value': e2e_pageable, 'unit': UNIT, 'steps': n_pg,
+                             'input': 'pageable float64 NumPy array, as np.random.multivariate_normal returns it (get_data.py:100); '
+                                      'the RNG draw itself is not timed'},
+            'gpu_launches': (1 if (world == 1 or small_ar is not None) else 2) * args.steps,
+            'exchange': None if world == 1 else ('in the objective kernel\'s last block: NVLink peer stores + flags, %d floats' % (nres + 2)
+                                                 if small_ar is not None else 'ncclAllReduce (%d floats)' % nres),
             'clocks': clocks,
         }
         if big is not None:

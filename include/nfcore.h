@@ -300,13 +300,34 @@ int nf_gemm_tn_tf32x3(const float* A, int64_t lda, const float* B, int64_t ldb, 
  *   peer_buffers[r] : device pointer, valid in THIS process, to rank r's exchange buffer of
  *                     nf_allreduce_small_buffer_bytes(world) bytes (peer-mapped, zero-filled once).
  *   seq             : 1, 2, 3, ... the same on every rank for the same step.
- *   status[0]       : set to 1 by the kernel if a peer did not arrive within the bounded spin.
+ *   status[0]       : set to 1 by the kernel if a peer did not arrive within 20 s.
  * All ranks add the slots in rank order, so every rank ends with bitwise identical sums.
  * ------------------------------------------------------------------------- */
 size_t nf_allreduce_small_buffer_bytes(int world);
 int nf_allreduce_small_max_count(void);
 int nf_allreduce_small_f32(void* const* peer_buffers, int world, int rank, const float* src, float* dst, int n,
                            uint64_t seq, int* status, void* stream);
+/* The same exchange in place, carrying the caller's sample count along (no counterpart in the reference):
+ * vec[0..n) := sums over ranks; vec[n], vec[n+1] := n_hi, n_lo with global count = n_hi * 2^20 + n_lo (both parts and
+ * their sums over 8 ranks are exact in float32); vec[n+2] := 0, or 1 when a peer did not arrive within 20 s. */
+int nf_allreduce_small_counted_f32(void* const* peer_buffers, int world, int rank, float* vec, int n, int64_t n_local,
+                                   uint64_t seq, void* stream);
+
+/* nf_planar_elbo_fwd_bwd_f32 for a sample-sharded run (one process per GPU): this rank's sums over its
+ * N samples are exchanged with the peers through the buffers above before they are written, so `out` holds the sums
+ * over ALL ranks' samples -- what get_data.py:113/115 needs before its mean.  No counterpart in the reference.
+ *   out : [F parts (3) | g_w (K*D) | g_s (K*D) | g_b (K) | g_c (K) | n_hi | n_lo | status], 3+2KD+2K+3 floats:
+ *         the global sample count is n_hi * 2^20 + n_lo; status is 0, or 1 when a peer did not arrive within 20 s
+ *         (then the other entries are this rank's own sums and must not be used).
+ * For float32, D <= 2, K <= 64 and enough samples the exchange happens inside the objective kernel (its last block
+ * pushes, waits and adds: one launch per step); other shapes run the objective and nf_allreduce_small_f32's kernel
+ * back to back.  3+2KD+2K+2 must not exceed nf_allreduce_small_max_count() + 2 (NF_ERR_UNSUPPORTED otherwise).
+ * Every rank must make the call with the same `seq` (1, 2, 3, ...) for the same step. */
+int nf_planar_elbo_fwd_bwd_exchange_f32(const float* eps, int64_t N, int D, int K,
+                                        const float* w, const float* s, const float* b, const float* c,
+                                        int target_id, const float* target_params, int n_target_params, float log_eps,
+                                        float* out, void* workspace, size_t workspace_bytes,
+                                        void* const* peer_buffers, int world, int rank, uint64_t seq, void* stream);
 
 #ifdef __cplusplus
 }

@@ -173,6 +173,22 @@ def script_terms(params, z0, target, eps, K):      # get_data.py:80-95 / 97-113
     return log_q_K, log_p, z_prev
 
 
+def chain_terms(z0, w, s, b, c, target, eps):
+    """The layer chain in the form the C ABI takes it (include/nfcore.h, nf_planar_elbo_fwd_bwd_*): per layer the
+    direction w_k, the step vector s_k (= u_hat of get_data.py:106), the offset b_k and the log-det coefficient c_k
+    (= w_k.u_k, :107-108) are given; returns the per-sample (log q_K, log p) of :111-112."""
+    K = w.shape[0]
+    z = z0
+    sld = 0.
+    for k in range(K):
+        a = z @ w[k] + b[k]
+        sld = sld + torch.log(eps + torch.abs(1 + h_prime(a) * c[k]))              # :107-108 with affine @ u = h'(a) (w.u)
+        z = z + torch.outer(torch.tanh(a), s[k])                                   # :109
+    log_q_K = -0.5 * torch.sum(LOG2PI + z0 ** 2, 1) - sld                          # :111
+    lp = torch.log(eps + target(z))                                                # :112
+    return log_q_K, lp.reshape(-1)
+
+
 def script_objective(params, z0, target, eps, K):  # get_data.py:97-113
     log_q_K, log_p, _ = script_terms(params, z0, target, eps, K)
     # (N,) - (N,1) broadcasts to (N,N) in the reference for D=1 targets; the mean is

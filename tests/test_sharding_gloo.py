@@ -78,3 +78,41 @@ def test_shard_bounds_cover_all_rows():
             assert all(b[i][1] == b[i + 1][0] for i in range(world - 1))
             sizes = [hi - lo for lo, hi in b]
             assert max(sizes) - min(sizes) <= 1
+
+
+def _count_worker(rank, world, port, q):
+    import sys
+    for p in (ROOT, PKG):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    from nfcore import sharding
+    os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port))
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    out = []
+    for N in (9, 10, 9, 1, 0):                 # rank 0 owns 5 rows for N = 9 and for N = 10: its shard size alone says nothing
+        lo, hi = sharding.shard_bounds(N, rank, world)
+        sums = torch.full((3,), float(hi - lo), dtype=torch.float32)
+        n = sharding.reduce_with_count(sums, hi - lo)
+        out.append((N, n, sums.tolist()))
+    q.put((rank, out))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_global_count_travels_with_every_exchange():
+    """The global sample count is part of every exchange: a caller that changes N between calls gets the right
+    normalisation on every rank and no rank skips a collective (a cache keyed on the local shard size would)."""
+    world, port = 2, _free_port()
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_count_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, out in res:
+        for N, n, sums in out:
+            assert n == N
+            assert sums == [float(N)] * 3

@@ -13,7 +13,8 @@ torch.cuda.set_device(int(os.environ['LOCAL_RANK']))
 dist.init_process_group('nccl', device_id=torch.device('cuda', int(os.environ['LOCAL_RANK'])))
 rs = np.random.RandomState(0)
 ok = True
-for (K, D, N, target) in ((32, 2, 200003, 'p1'), (8, 16, 5001, ('gaussdiag', np.zeros(16), np.zeros(16) - 0.2))):
+for (K, D, N, target) in ((32, 2, 200003, 'p1'), (32, 2, 200003 * world, 'p1'), (64, 2, 333333 * world, 'p4'),
+                          (8, 16, 5001, ('gaussdiag', np.zeros(16), np.zeros(16) - 0.2))):
     z0 = rs.randn(N, D)
     params = np.concatenate([(0.1 + 0.02 * rs.randn(2 * K * D)) / np.sqrt(D / 2), 0.1 * np.ones(K)])
     for dtype, tol in (('float64', 1e-11), ('float32', 1e-5)):
@@ -41,6 +42,18 @@ for it in range(50):
         ok = False
         print('rank %d it %d peer all-reduce mismatch %.3e' % (rank, it, err), flush=True)
 ar.check()
+# the in-place form that carries the sample count (what the objective uses when the kernel did not do the exchange)
+for it in range(6):
+    n = 195 + it
+    v = torch.randn(n + 3, device='cuda', generator=g)
+    ref = v[:n].clone(); dist.all_reduce(ref)
+    ar.counted(v, n, 1000 + rank + it)
+    torch.cuda.synchronize()
+    tail = v[n:].cpu().numpy()
+    cnt = ar.global_count(tail)
+    if float((v[:n] - ref).abs().max()) > 1e-5 or cnt != sum(1000 + r + it for r in range(world)):
+        ok = False
+        print('rank %d counted exchange mismatch (count %d)' % (rank, cnt), flush=True)
 if rank == 0:
     print('peer all-reduce (50 rounds) %s' % ('OK' if ok else 'FAIL'), flush=True)
 dist.barrier()

@@ -44,6 +44,28 @@ int nf_planar_elbo_fwd_bwd_f32(const float* eps, int64_t N, int D, int K, const 
                                  out_F, g_w, g_s, g_b, g_c, workspace, workspace_bytes, stream);
 }
 
+// sample-sharded form: the local sums are exchanged over NVLink peer memory before they reach `out`
+int nf_planar_elbo_fwd_bwd_exchange_f32(const float* eps, int64_t N, int D, int K, const float* w, const float* s,
+                                        const float* b, const float* c, int target_id, const float* target_params,
+                                        int n_target_params, float log_eps, float* out, void* workspace, size_t workspace_bytes,
+                                        void* const* peer_buffers, int world, int rank, uint64_t seq, void* stream) {
+    if (!out || !workspace) return NF_ERR_INVALID;
+    const int nvec = 3 + 2 * K * D + 2 * K;
+    if (nvec + 2 > nf::pr::kArStride) return NF_ERR_UNSUPPORTED;
+    int rc = nf::elbo_validate<float>(eps, N, D, K, w, s, b, c, target_id, target_params, n_target_params);
+    if (rc != NF_OK) return rc;
+    if (workspace_bytes < nf_planar_elbo_workspace_bytes(K, D, 4)) return NF_ERR_WORKSPACE;
+    nf::pr::ArDesc ar;
+    rc = nf::make_ar_desc(&ar, peer_buffers, world, rank, seq, N, out + nvec);
+    if (rc != NF_OK) return rc;
+    float *g_w = out + 3, *g_s = g_w + K * D, *g_b = g_s + K * D, *g_c = g_b + K;
+    bool exchanged = false;
+    rc = nf::elbo_fused<float>(true, eps, N, D, K, w, s, b, c, target_id, target_params, n_target_params, log_eps, out, g_w, g_s, g_b,
+                               g_c, reinterpret_cast<float*>(workspace), (cudaStream_t)stream, &ar, &exchanged);
+    if (rc != NF_OK || exchanged) return rc;
+    return nf::launch_allreduce_small(ar, out, out, nvec, nullptr, (cudaStream_t)stream);
+}
+
 // ---- host-buffer sessions (see nfcore.h) ----
 int nf_session_create(nf_session** out, int64_t max_samples, int D, int K, int elem_size) {
     return nf::session_create(reinterpret_cast<nf::Session**>(out), max_samples, D, K, elem_size);

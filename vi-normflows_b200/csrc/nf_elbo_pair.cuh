@@ -106,6 +106,22 @@ struct Smem {
     }
 };
 
+// One-shot exchange over NVLink peer memory, done by the last block after the row sum (sample-sharded runs, one
+// process per GPU): the block pushes the result vector [F parts | g_w | g_s | g_b | g_c | n_hi | n_lo] into its slot of
+// every peer's exchange buffer (plain stores through the NVLink aperture), publishes a sequence flag with system
+// scope, waits (bounded) for the peers' flags and adds the slots in rank order -- the same order on every rank, so all
+// ranks hold bitwise identical sums.  Buffer layout and slot alternation: csrc/nf_allreduce.cu.
+constexpr int kArMaxWorld = 8;
+constexpr int kArStride = 4096;            // floats per slot
+struct ArDesc {
+    float* buf[kArMaxWorld];               // exchange buffer of every rank, mapped in this process
+    int world, rank;                       // world <= 1: no exchange
+    unsigned long long seq;                // 1, 2, 3, ...: the same on every rank for the same step
+    float n_hi, n_lo;                      // this rank's sample count, split so that sums over 8 ranks stay exact
+    float* xout;                           // [3]: sum of n_hi, sum of n_lo, status (0 ok, 1 a peer did not arrive)
+};
+__host__ __device__ inline size_t ar_flag_offset_floats(int world) { return (size_t)2 * world * kArStride; }
+
 // workspace header of the single-launch mode (16 bytes): a cookie that tells an initialised ticket counter from
 // whatever the caller's memory held, and the ticket counter itself (zero between launches)
 struct SyncHeader { u64 cookie; unsigned counter; unsigned pad; };
@@ -334,7 +350,8 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
                  const float* __restrict__ tparams, int ntp, float epsv, float* __restrict__ partials /*[gridDim.x][K*V+2]*/,
                  SyncHeader* __restrict__ sync /* NULL: rows only, the caller sums them */, float* __restrict__ out_F,
                  float* __restrict__ g_w, float* __restrict__ g_s, float* __restrict__ g_b, float* __restrict__ g_c,
-                 int flags /* tuning: bit 0 = no rotation of the rounds */, unsigned long long* __restrict__ stamps /* [256][8] or NULL */) {
+                 int flags /* tuning: bit 0 = no rotation of the rounds */, unsigned long long* __restrict__ stamps /* [256][8] or NULL */,
+                 const ArDesc ar) {
     using M = Mth<float>;
     constexpr int NT = NW * 32;
     constexpr int V = 2 * D + 2;
@@ -520,23 +537,77 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
                 }
             }
             __syncthreads();
+            // result vector in shared memory, laid out as the caller's arrays follow one another:
+            // [F, sum log q, sum log p | g_w (K*D) | g_s (K*D) | g_b (K) | g_c (K) | n_hi, n_lo]
+            float* vec = stage + groups * row;
+            const int KD = K * D, nvec = 3 + 2 * KD + 2 * K;
             for (int i = tid; i < row; i += NT) {
                 float a = stage[i];
                 for (int g = 1; g < groups; ++g) a += stage[g * row + i];
                 if (i >= K * V) {
-                    out_F[1 + (i - K * V)] = a;
-                    stage[i] = a;
-                } else if (g_w) {
+                    vec[1 + (i - K * V)] = a;
+                } else {
                     const int k = i / V, j = i - k * V;
-                    if (j < D) g_w[k * D + j] = a;
-                    else if (j < 2 * D) g_s[k * D + (j - D)] = a;
-                    else if (j == 2 * D) g_b[k] = a;
-                    else g_c[k] = a;
+                    const int pos = j < D ? 3 + k * D + j : (j < 2 * D ? 3 + KD + k * D + (j - D) : (j == 2 * D ? 3 + 2 * KD + k : 3 + 2 * KD + K + k));
+                    vec[pos] = a;
                 }
             }
             __syncthreads();
+            if (tid == 0) { vec[0] = vec[1] - vec[2]; vec[nvec] = ar.n_hi; vec[nvec + 1] = ar.n_lo; }
+            __syncthreads();
+            bool failed = false;
+            if (ar.world > 1) {
+                const int set = (int)(ar.seq & 1), nx = nvec + 2;
+                // push: NT / world threads per peer
+                {
+                    const int per_peer = NT / ar.world, p = tid / per_peer, t = tid - p * per_peer;
+                    if (p < ar.world) {
+                        float* slot = ar.buf[p] + ((size_t)set * ar.world + ar.rank) * kArStride;
+                        for (int i = t; i < nx; i += per_peer) slot[i] = vec[i];
+                    }
+                }
+                __threadfence_system();
+                __syncthreads();
+                if (tid < ar.world) {
+                    unsigned long long* fl = reinterpret_cast<unsigned long long*>(ar.buf[tid] + ar_flag_offset_floats(ar.world));
+                    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(fl + (size_t)set * ar.world + ar.rank), "l"(ar.seq) : "memory");
+                }
+                s_last = 0;                 // reused as "a peer did not arrive"
+                __syncthreads();
+                if (tid < ar.world) {
+                    const unsigned long long* f = reinterpret_cast<const unsigned long long*>(ar.buf[ar.rank] + ar_flag_offset_floats(ar.world)) +
+                                                  (size_t)set * ar.world + tid;
+                    unsigned long long v = 0;
+                    const unsigned long long t0 = gtime();
+                    do {
+                        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(f) : "memory");
+                    } while (v < ar.seq && gtime() - t0 < 20000000000ull);          // 20 s
+                    if (v < ar.seq) s_last = 1;
+                }
+                __syncthreads();
+                failed = s_last != 0;
+                if (!failed) {
+                    const float* mine = ar.buf[ar.rank] + (size_t)set * ar.world * kArStride;
+                    for (int i = tid; i < nx; i += NT) {
+                        float a = 0.f;
+                        for (int r = 0; r < ar.world; ++r) a += __ldcv(mine + (size_t)r * kArStride + i);
+                        vec[i] = a;
+                    }
+                }
+                __syncthreads();
+            }
+            for (int i = tid; i < nvec; i += NT) {
+                const float a = vec[i];
+                if (i < 3) out_F[i] = a;
+                else if (g_w) {
+                    if (i < 3 + KD) g_w[i - 3] = a;
+                    else if (i < 3 + 2 * KD) g_s[i - 3 - KD] = a;
+                    else if (i < 3 + 2 * KD + K) g_b[i - 3 - 2 * KD] = a;
+                    else g_c[i - 3 - 2 * KD - K] = a;
+                }
+            }
             if (tid == 0) {
-                out_F[0] = stage[K * V] - stage[K * V + 1];
+                if (ar.xout) { ar.xout[0] = vec[nvec]; ar.xout[1] = vec[nvec + 1]; ar.xout[2] = failed ? 1.f : 0.f; }
                 sync->counter = 0;
                 if (stamps) stamps[(blockIdx.x < 256 ? blockIdx.x : 0) * 8 + 4] = gtime();
             }

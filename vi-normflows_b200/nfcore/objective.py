@@ -94,20 +94,31 @@ class SharedFlowObjective:
         # one device buffer for the per-layer constants, one for every result: one H2D, one D2H per call
         self._lc_host = torch.empty(self.n_lc, dtype=self.dtype).pin_memory()
         self._lc = torch.empty(self.n_lc, dtype=self.dtype, device=self.device)
-        self._res = torch.empty(3 + self.n_lc, dtype=self.dtype, device=self.device)
-        self._res_host = torch.empty(3 + self.n_lc, dtype=self.dtype).pin_memory()
+        # results [F parts (3) | g_w | g_s | g_b | g_c] followed by three slots the sharded exchange fills
+        # (sample count in two parts, status): everything a step returns crosses PCIe in one copy
+        self.n_res = 3 + self.n_lc
+        self._res = torch.zeros(self.n_res + 3, dtype=self.dtype, device=self.device)
+        self._res_host = torch.empty(self.n_res + 3, dtype=self.dtype).pin_memory()
         self._eps_dev = None
         self._eps_pinned = None
         self.group = process_group
         self.launches = 0
         self._small_ar = None
-        self._n_cache = {}
-        if process_group is not None and self.dtype == torch.float32 and 3 + self.n_lc <= 1024:
-            try:    # one-shot exchange over NVLink peer memory; NCCL when the peers cannot be mapped
-                from .peer import SmallAllReduce
-                self._small_ar = SmallAllReduce(process_group, self.device)
-            except Exception:
-                self._small_ar = None
+        if process_group is not None:
+            import torch.distributed as dist
+            ok = 0
+            if self.dtype == torch.float32:
+                try:    # one-shot exchange over NVLink peer memory; NCCL when the peers cannot be mapped
+                    from .peer import SmallAllReduce
+                    ar = SmallAllReduce(process_group, self.device)
+                    ok = 1 if self.n_res <= ar.max_count else 0
+                except Exception:
+                    ar, ok = None, 0
+            # every rank must take the same path: one rank in the peer kernel and another in NCCL would hang
+            flag = torch.tensor([ok], dtype=torch.int32, device=self.device)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=process_group)
+            if int(flag.item()) == 1:
+                self._small_ar = ar
         self._session = None
         self._session_cap = 0
         self._tparams_host = None if tparams is None else np.ascontiguousarray(tparams.astype(self.np_dtype))
@@ -228,27 +239,38 @@ class SharedFlowObjective:
         b = lc[2 * K * D:2 * K * D + K]
         cc = lc[2 * K * D + K:]
         r = self._res
+        if backward and self._small_ar is not None:
+            # objective + exchange in one call (one launch when the packed-pair kernel covers the shape)
+            ops.planar_elbo_exchange(eps_dev, w, s, b, cc, self.target_name, self.tparams, self.log_eps, r, self._small_ar)
+            self.launches += 1
+            self._exchanged = True
+            return p64
         out = (r[:3], r[3:3 + K * D].view(K, D), r[3 + K * D:3 + 2 * K * D].view(K, D),
-               r[3 + 2 * K * D:3 + 2 * K * D + K], r[3 + 2 * K * D + K:]) if backward else (r[:3], None, None, None, None)
+               r[3 + 2 * K * D:3 + 2 * K * D + K], r[3 + 2 * K * D + K:self.n_res]) if backward else (r[:3], None, None, None, None)
         ops.planar_elbo(eps_dev, w, s, b, cc, self.target_name, self.tparams, self.log_eps, backward, out)
         self.launches += 2
+        self._exchanged = False
         return p64
 
     def _fetch(self, n_local):
-        """all-reduce (when sharded) + D2H of [F parts | grads]; returns float64 array and global N."""
+        """exchange (when sharded) + D2H of [F parts | grads | count, status]; returns float64 array and global N."""
         n_global = n_local
+        counted = False
         if self.group is not None:
             if self._small_ar is not None:
-                # the row count only changes when the caller changes its shard: exchange it once per value
-                if n_local not in self._n_cache:
-                    self._n_cache[n_local] = sharding.reduce_sums(torch.zeros(1, device=self.device), n_local, self.group)
-                n_global = self._n_cache[n_local]
-                self._small_ar(self._res)
+                if not self._exchanged:
+                    self._small_ar.counted(self._res, self.n_res, n_local)
+                counted = True
             else:
-                n_global = sharding.reduce_sums(self._res, n_local, self.group)
+                # one NCCL all-reduce carries the sums and this rank's sample count (nothing cached between calls)
+                n_global = sharding.reduce_with_count(self._res[:self.n_res], n_local, self.group)
         self._res_host.copy_(self._res, non_blocking=True)
         torch.cuda.current_stream(self.device).synchronize()
-        return self._res_host.numpy().astype(np.float64), n_global
+        res = self._res_host.numpy().astype(np.float64)
+        if counted:
+            from .peer import SmallAllReduce
+            n_global = SmallAllReduce.global_count(res[self.n_res:])
+        return res[:self.n_res], n_global
 
     def value_and_grad(self, params, z0):
         if self._is_host(z0):

@@ -93,6 +93,32 @@ def planar_elbo(eps, w, s, b, c, target, target_params=None, log_eps=1e-7, backw
     return out_F, g_w, g_s, g_b, g_c
 
 
+def planar_elbo_exchange(eps, w, s, b, c, target, target_params, log_eps, out_vec, ar):
+    """nf_planar_elbo_fwd_bwd_exchange_f32 on the current stream: this rank's sums are exchanged with the peers of
+    `ar` (nfcore.peer.SmallAllReduce) before they land in out_vec = [F parts | g_w | g_s | g_b | g_c | n_hi | n_lo | status]."""
+    lib = _lib.load()
+    if eps.dtype != torch.float32 or not eps.is_cuda:
+        raise NFError('planar_elbo_exchange: float32 CUDA tensors')
+    N, D = eps.shape
+    K = w.shape[0]
+    for t in (eps, w, s, b, c, out_vec):
+        if t.dtype != torch.float32 or not t.is_contiguous() or t.device != eps.device:
+            raise NFError('all inputs must be contiguous float32 on one device')
+    if out_vec.numel() < 3 + 2 * K * D + 2 * K + 3:
+        raise NFError('out_vec needs 3 + 2KD + 2K + 3 elements')
+    tid = TARGET_IDS[target] if isinstance(target, str) else int(target)
+    ntp = 0 if target_params is None else target_params.numel()
+    dev = eps.device
+    ws = _workspace(K, D, torch.float32, dev, 0)
+    with torch.cuda.device(dev):
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        rc = lib.nf_planar_elbo_fwd_bwd_exchange_f32(_ptr(eps), N, D, K, _ptr(w), _ptr(s), _ptr(b), _ptr(c), tid, _ptr(target_params), ntp,
+                                                     ctypes.c_float(log_eps), _ptr(out_vec), _ptr(ws), ws.numel(), ar._ptrs, ar.world, ar.rank,
+                                                     ctypes.c_uint64(ar.next_seq()), ctypes.c_void_p(stream))
+    _lib.check(rc)
+    return out_vec
+
+
 def _same(dtype, dev, *ts):
     for t in ts:
         if t is not None and (t.dtype != dtype or not t.is_contiguous() or t.device != dev):

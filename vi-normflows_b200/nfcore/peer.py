@@ -48,6 +48,28 @@ class SmallAllReduce:
         _lib.check(rc)
         return dst
 
+    def counted(self, vec, n, n_local):
+        """In place: vec[:n] = sums over ranks, vec[n:n+3] = (n_hi, n_lo, status) -- nf_allreduce_small_counted_f32.
+        The caller reads vec back and passes it to `global_count`."""
+        if vec.dtype != torch.float32 or not vec.is_contiguous() or vec.numel() < n + 3 or n > self.max_count:
+            raise NFError('SmallAllReduce.counted: float32 contiguous vector of n + 3 <= %d elements' % (self.max_count + 3))
+        self.seq += 1
+        st = torch.cuda.current_stream(self.device).cuda_stream
+        _lib.check(_lib.load().nf_allreduce_small_counted_f32(self._ptrs, self.world, self.rank, ctypes.c_void_p(vec.data_ptr()), n,
+                                                              int(n_local), ctypes.c_uint64(self.seq), ctypes.c_void_p(st)))
+        return vec
+
+    @staticmethod
+    def global_count(tail):
+        """(n_hi, n_lo, status) as read back from the device -> global sample count; raises when a peer did not arrive."""
+        if float(tail[2]) != 0.0:
+            raise NFError('peer exchange: a rank did not arrive within the time limit; the sums are not valid')
+        return int(round(float(tail[0]))) * (1 << 20) + int(round(float(tail[1])))
+
+    def next_seq(self):
+        self.seq += 1
+        return self.seq
+
     def check(self):
         """Synchronising: raises if a peer failed to arrive in some earlier call."""
         if int(self.status.item()) != 0:

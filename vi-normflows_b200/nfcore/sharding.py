@@ -26,3 +26,19 @@ def reduce_sums(sums, n_local, group=None):
     dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group)
     dist.all_reduce(cnt, op=dist.ReduceOp.SUM, group=group)
     return int(round(float(cnt.item())))
+
+
+def reduce_with_count(sums, n_local, group=None):
+    """One all-reduce(sum) that carries the per-rank sums AND this rank's row count (appended to the vector, exact in
+    float64): every rank learns the global count of THIS call -- nothing is cached between calls, so callers may change
+    the number of rows from one call to the next.  `sums` is overwritten with the global sums (in its own dtype);
+    returns the global row count."""
+    import torch.distributed as dist
+    if group is None and not (dist.is_available() and dist.is_initialized()):
+        return int(n_local)
+    buf = torch.empty(sums.numel() + 1, dtype=torch.float64, device=sums.device)
+    buf[:-1] = sums.reshape(-1)
+    buf[-1] = float(n_local)
+    dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=group)
+    sums.reshape(-1).copy_(buf[:-1].to(sums.dtype))
+    return int(round(float(buf[-1].item())))
