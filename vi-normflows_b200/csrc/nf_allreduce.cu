@@ -1,17 +1,13 @@
 // One-shot all-reduce of a small float vector over NVLink peer memory (sm_100a, <= 8 GPUs of one box).
 //
 // The free-energy step ends in a 3+2KD+2K-float result vector per GPU (195 floats at the headline
-// config).  A ring/tree collective is pure latency at that size; here every rank PUSHES its vector into a
-// slot of every peer's exchange buffer (plain stores through the NVLink aperture), publishes a sequence
-// flag with system scope, waits for the peers' flags and adds the world slots in rank order -- the same
-// order on every rank, so all ranks hold bitwise identical sums.  Two slot sets alternate by sequence
-// number: a rank can run at most one step ahead of the slowest peer, so a set is never overwritten while a
-// peer may still read it.  The wait is bounded (20 s); on expiry the kernel reports it instead of hanging.
+// config).  A ring/tree collective is pure latency at that size; the exchange here is one NVLink crossing:
+// see ArDesc / ar_exchange in nf_elbo_pair.cuh (values pushed into every peer's buffer in 8-byte words that
+// carry the step's sequence number; receivers poll their own buffer and add in rank order, so all ranks hold
+// bitwise identical sums; two alternating slot sets; bounded wait).
 //
-// The packed-pair free-energy kernel does this exchange in its last block (nf_elbo_pair.cuh, ArDesc); the
-// kernel here is the same exchange as a launch of its own, for the shapes that kernel does not cover.
-//
-// Buffer layout per rank (floats): set s in {0,1}: [world][kArStride] data, then flags as uint64 [2][world].
+// The packed-pair free-energy kernel does this exchange in its last block; the kernel here is the same
+// exchange as a launch of its own, for the shapes that kernel does not cover.
 #include "nf_elbo_pair.cuh"
 
 namespace nf {
@@ -19,60 +15,29 @@ namespace nf {
 using pr::ArDesc;
 using pr::kArMaxWorld;
 using pr::kArStride;
-using pr::ar_flag_offset_floats;
 
 // src[0..n) (+ n_hi, n_lo when ar.xout != NULL) -> dst[0..n) = sums over ranks, ar.xout = {sum n_hi, sum n_lo, status};
 // status_i (legacy interface) is raised to 1 when a peer did not arrive.
 __global__ void __launch_bounds__(512)
 allreduce_small_kernel(const ArDesc ar, const float* src, float* dst /* may be src */, int n, int* __restrict__ status_i) {
     asm volatile("griddepcontrol.wait;" ::: "memory");
-    const int set = (int)(ar.seq & 1);
+    __shared__ float vec[kArStride];
+    __shared__ int s_flag;
     const int tid = threadIdx.x, NT = blockDim.x;
     const int nx = n + (ar.xout ? 2 : 0);
-    // 1. push my vector into slot `rank` of every peer (including myself): NT / world threads per peer
-    {
-        const int per_peer = NT / ar.world, p = tid / per_peer, t = tid - p * per_peer;
-        if (p < ar.world) {
-            float* slot = ar.buf[p] + ((size_t)set * ar.world + ar.rank) * kArStride;
-            for (int i = t; i < nx; i += per_peer) slot[i] = i < n ? src[i] : (i == n ? ar.n_hi : ar.n_lo);
-        }
-    }
-    __threadfence_system();
+    for (int i = tid; i < nx; i += NT) vec[i] = i < n ? src[i] : (i == n ? ar.n_hi : ar.n_lo);
     __syncthreads();
-    // 2. publish: flag[set][rank] on every peer := seq
-    if (tid < ar.world) {
-        unsigned long long* flags = reinterpret_cast<unsigned long long*>(ar.buf[tid] + ar_flag_offset_floats(ar.world));
-        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(flags + (size_t)set * ar.world + ar.rank), "l"(ar.seq) : "memory");
-    }
-    // 3. wait for every peer's flag in MY buffer
-    __shared__ int failed;
-    if (tid == 0) failed = 0;
-    __syncthreads();
-    if (tid < ar.world) {
-        const unsigned long long* f = reinterpret_cast<const unsigned long long*>(ar.buf[ar.rank] + ar_flag_offset_floats(ar.world)) +
-                                      (size_t)set * ar.world + tid;
-        unsigned long long v = 0;
-        const unsigned long long t0 = pr::gtime();
-        do {
-            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(f) : "memory");
-        } while (v < ar.seq && pr::gtime() - t0 < 20000000000ull);
-        if (v < ar.seq) failed = 1;
-    }
-    __syncthreads();
-    if (failed) {
+    const bool ok = pr::ar_exchange(ar, vec, nx, tid, NT, &s_flag);
+    if (!ok) {
         if (tid == 0) {
             if (status_i) status_i[0] = 1;
             if (ar.xout) ar.xout[2] = 1.f;
         }
         return;
     }
-    // 4. add the slots in rank order
-    const float* mine = ar.buf[ar.rank] + (size_t)set * ar.world * kArStride;
     for (int i = tid; i < nx; i += NT) {
-        float a = 0.f;
-        for (int r = 0; r < ar.world; ++r) a += __ldcv(mine + (size_t)r * kArStride + i);
-        if (i < n) dst[i] = a;
-        else ar.xout[i - n] = a;
+        if (i < n) dst[i] = vec[i];
+        else ar.xout[i - n] = vec[i];
     }
     if (tid == 0 && ar.xout) ar.xout[2] = 0.f;
 }
@@ -104,7 +69,7 @@ extern "C" {
 
 size_t nf_allreduce_small_buffer_bytes(int world) {
     if (world < 1 || world > nf::kArMaxWorld) return 0;
-    return nf::ar_flag_offset_floats(world) * sizeof(float) + (size_t)2 * world * sizeof(unsigned long long);
+    return nf::pr::ar_buffer_bytes(world);
 }
 int nf_allreduce_small_max_count(void) { return nf::kArStride - 2; }
 

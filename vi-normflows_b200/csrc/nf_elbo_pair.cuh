@@ -107,12 +107,17 @@ struct Smem {
 };
 
 // One-shot exchange over NVLink peer memory, done by the last block after the row sum (sample-sharded runs, one
-// process per GPU): the block pushes the result vector [F parts | g_w | g_s | g_b | g_c | n_hi | n_lo] into its slot of
-// every peer's exchange buffer (plain stores through the NVLink aperture), publishes a sequence flag with system
-// scope, waits (bounded) for the peers' flags and adds the slots in rank order -- the same order on every rank, so all
-// ranks hold bitwise identical sums.  Buffer layout and slot alternation: csrc/nf_allreduce.cu.
+// process per GPU).  Every rank PUSHES its result vector [F parts | g_w | g_s | g_b | g_c | n_hi | n_lo] into its slot
+// of every peer's exchange buffer with plain stores through the NVLink aperture, each float travelling in one 8-byte
+// word together with the step's sequence number.  An 8-byte store lands whole, so a receiver that sees the sequence
+// number in a word has the value too: no fence and no separate flag round trip, the latency is one NVLink crossing.
+// Receivers poll the words of their own buffer and add the ranks' values in rank order -- the same order on every
+// rank, so all ranks hold bitwise identical sums.  Two slot sets alternate by sequence number: a rank can be at most
+// one step ahead of the slowest peer, so a set is never overwritten while a peer may still read it.  The wait is
+// bounded (20 s).
+// Buffer layout per rank (8-byte words): set s in {0,1}: [world][kArStride] words = {float value, uint32 sequence}.
 constexpr int kArMaxWorld = 8;
-constexpr int kArStride = 4096;            // floats per slot
+constexpr int kArStride = 4096;            // words per slot
 struct ArDesc {
     float* buf[kArMaxWorld];               // exchange buffer of every rank, mapped in this process
     int world, rank;                       // world <= 1: no exchange
@@ -120,7 +125,46 @@ struct ArDesc {
     float n_hi, n_lo;                      // this rank's sample count, split so that sums over 8 ranks stay exact
     float* xout;                           // [3]: sum of n_hi, sum of n_lo, status (0 ok, 1 a peer did not arrive)
 };
-__host__ __device__ inline size_t ar_flag_offset_floats(int world) { return (size_t)2 * world * kArStride; }
+__host__ __device__ inline size_t ar_buffer_bytes(int world) { return (size_t)2 * world * kArStride * sizeof(unsigned long long); }
+__device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+
+// vec[0..nx) (shared memory) := sums over ranks, by all NT threads of the block; `s_flag` is a shared int.
+// Returns false (vec unspecified) when a peer did not arrive in time.
+__device__ __forceinline__ bool ar_exchange(const ArDesc& ar, float* vec, int nx, int tid, int NT, int* s_flag) {
+    const int set = (int)(ar.seq & 1);
+    const unsigned seq32 = (unsigned)ar.seq;
+    {   // push: NT / world threads per peer
+        const int per_peer = NT / ar.world, p = tid / per_peer, t = tid - p * per_peer;
+        if (p < ar.world) {
+            unsigned long long* slot = reinterpret_cast<unsigned long long*>(ar.buf[p]) + ((size_t)set * ar.world + ar.rank) * kArStride;
+            for (int i = t; i < nx; i += per_peer) {
+                const unsigned long long word = ((unsigned long long)seq32 << 32) | (unsigned long long)__float_as_uint(vec[i]);
+                asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(slot + i), "l"(word) : "memory");
+            }
+        }
+    }
+    if (tid == 0) *s_flag = 0;
+    __syncthreads();                      // every thread has read its part of vec before anyone overwrites it
+    const unsigned long long* mine = reinterpret_cast<const unsigned long long*>(ar.buf[ar.rank]) + (size_t)set * ar.world * kArStride;
+    const unsigned long long t0 = gtime();
+    bool late = false;
+    for (int i = tid; i < nx; i += NT) {
+        float a = 0.f;
+        for (int r = 0; r < ar.world; ++r) {
+            unsigned long long word;
+            for (;;) {
+                asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(word) : "l"(mine + (size_t)r * kArStride + i) : "memory");
+                if ((unsigned)(word >> 32) == seq32) break;
+                if (gtime() - t0 > 20000000000ull) { late = true; break; }
+            }
+            a += __uint_as_float((unsigned)word);
+        }
+        vec[i] = a;
+    }
+    if (late) *s_flag = 1;
+    __syncthreads();
+    return *s_flag == 0;
+}
 
 // workspace header of the single-launch mode (16 bytes): a cookie that tells an initialised ticket counter from
 // whatever the caller's memory held, and the ticket counter itself (zero between launches)
@@ -130,8 +174,6 @@ __host__ __device__ inline u64 cookie_for(const void* p) { return 0x6e66636f7265
 
 // tuning aid (flags bit 1): per-block phase timestamps (globaltimer, ns): entry, set-up done, samples done, row
 // written and ticket taken, finalize done (last block only; 0 elsewhere), and the SM the block ran on
-__device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
-
 // One round of one warp: S samples per thread (S/2 pairs) through all K layers and back.
 template <int D, int S, int SMAX, int ST, int NT, int TGT, bool MASKED>
 __device__ __forceinline__ void pair_tile(const float* __restrict__ eps, long long n0, long long N, int K,
@@ -556,46 +598,7 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
             if (tid == 0) { vec[0] = vec[1] - vec[2]; vec[nvec] = ar.n_hi; vec[nvec + 1] = ar.n_lo; }
             __syncthreads();
             bool failed = false;
-            if (ar.world > 1) {
-                const int set = (int)(ar.seq & 1), nx = nvec + 2;
-                // push: NT / world threads per peer
-                {
-                    const int per_peer = NT / ar.world, p = tid / per_peer, t = tid - p * per_peer;
-                    if (p < ar.world) {
-                        float* slot = ar.buf[p] + ((size_t)set * ar.world + ar.rank) * kArStride;
-                        for (int i = t; i < nx; i += per_peer) slot[i] = vec[i];
-                    }
-                }
-                __threadfence_system();
-                __syncthreads();
-                if (tid < ar.world) {
-                    unsigned long long* fl = reinterpret_cast<unsigned long long*>(ar.buf[tid] + ar_flag_offset_floats(ar.world));
-                    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(fl + (size_t)set * ar.world + ar.rank), "l"(ar.seq) : "memory");
-                }
-                s_last = 0;                 // reused as "a peer did not arrive"
-                __syncthreads();
-                if (tid < ar.world) {
-                    const unsigned long long* f = reinterpret_cast<const unsigned long long*>(ar.buf[ar.rank] + ar_flag_offset_floats(ar.world)) +
-                                                  (size_t)set * ar.world + tid;
-                    unsigned long long v = 0;
-                    const unsigned long long t0 = gtime();
-                    do {
-                        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(f) : "memory");
-                    } while (v < ar.seq && gtime() - t0 < 20000000000ull);          // 20 s
-                    if (v < ar.seq) s_last = 1;
-                }
-                __syncthreads();
-                failed = s_last != 0;
-                if (!failed) {
-                    const float* mine = ar.buf[ar.rank] + (size_t)set * ar.world * kArStride;
-                    for (int i = tid; i < nx; i += NT) {
-                        float a = 0.f;
-                        for (int r = 0; r < ar.world; ++r) a += __ldcv(mine + (size_t)r * kArStride + i);
-                        vec[i] = a;
-                    }
-                }
-                __syncthreads();
-            }
+            if (ar.world > 1) failed = !ar_exchange(ar, vec, nvec + 2, tid, NT, &s_last);
             for (int i = tid; i < nvec; i += NT) {
                 const float a = vec[i];
                 if (i < 3) out_F[i] = a;

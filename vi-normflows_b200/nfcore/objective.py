@@ -252,6 +252,13 @@ class SharedFlowObjective:
         self._exchanged = False
         return p64
 
+    def _exchange_only(self, n_local):
+        """The exchange of `_fetch` without the read-back (enqueued on the current stream): for device-side loops."""
+        if self._small_ar is not None:
+            self._small_ar.counted(self._res, self.n_res, n_local)
+        else:
+            sharding.reduce_with_count(self._res[:self.n_res], n_local, self.group)
+
     def _fetch(self, n_local):
         """exchange (when sharded) + D2H of [F parts | grads | count, status]; returns float64 array and global N."""
         n_global = n_local
