@@ -189,6 +189,23 @@ def chain_terms(z0, w, s, b, c, target, eps):
     return log_q_K, lp.reshape(-1)
 
 
+def script_min_det_factor(params, z0, K):
+    """min over samples and layers of |1 + h'(w.z+b) w.u| (get_data.py:107-108): how close the parameters bring the
+    chain to the log|.| singularity, where gradients grow like 1/|.| and float32 loses digits accordingly."""
+    z0 = _t(z0)
+    params = _t(params)
+    N, D = z0.shape
+    W, U, B = unpack_script(params, K, D)
+    z, mn = z0, float('inf')
+    for k in range(K):
+        w, u, b = W[k], U[k], B[k]
+        wu = torch.dot(w, u)
+        a = z @ w + b
+        mn = min(mn, float(torch.abs(1 + h_prime(a) * wu).min()))
+        z = z + torch.outer(torch.tanh(a), (m(wu) - wu) * (w / torch.linalg.norm(w)) + u)
+    return mn
+
+
 def script_objective(params, z0, target, eps, K):  # get_data.py:97-113
     log_q_K, log_p, _ = script_terms(params, z0, target, eps, K)
     # (N,) - (N,1) broadcasts to (N,N) in the reference for D=1 targets; the mean is
@@ -215,6 +232,20 @@ def amortised_flow_terms(z0, mu0, log_sigma_diag0, W, U, B, eps=1e-7):   # optim
         running_sum = running_sum + torch.log(eps + torch.abs(1. + torch.sum(u * ldj.reshape(-1, 1), dim=1)))
         zk = planar_flow(zk, w, u, b)
     return zk, running_sum
+
+
+def amortised_min_det_factor(z0, mu0, log_sigma_diag0, W, U, B, eps=1e-7):
+    """min over samples and layers of |1 + (sum u)(sum w) h'(w.z+b)| (optimization.py:64,83): distance of the batch from
+    the log|.| singularity, where float32 gradients lose their digits."""
+    K = W.shape[0]
+    zk = z0 * torch.sqrt(eps + torch.exp(log_sigma_diag0)) + mu0
+    mn = float('inf')
+    for k in range(K):
+        w, u, b = W[k], U[k], B[k]
+        ldj = torch.sum(w * h_prime(torch.sum(w * zk, dim=1) + b).reshape(-1, 1), dim=1)
+        mn = min(mn, float(torch.abs(1. + torch.sum(u * ldj.reshape(-1, 1), dim=1)).min()))
+        zk = planar_flow(zk, w, u, b)
+    return mn
 
 
 def beta_schedule(t, max_iter):      # optimization.py:71-72

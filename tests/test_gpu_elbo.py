@@ -3,8 +3,11 @@ oracle, for the shared-parameter free energy forward + backward (get_data.py:97-
 
 Tolerances (north_star): float32 1e-4 relative, float64 1e-10 relative.  "Relative" for a
 gradient vector means max|g - g_ref| <= tol * max|g_ref|; for F, |F - F_ref| <= tol * max(1, |F_ref|).
-The "wide" parameter sets sit next to the log|1 + h'c| singularity, where
-float32 can only hold a looser bound -- stated per case below.
+Every case holds 1e-4 in float32 except those whose parameters bring some sample within 0.02 of the
+log|1 + h'c| singularity (gradients grow like 1/|1 + h'c| there and float32 loses the
+digits): for those the oracle's min|1 + h'c| is computed in the test, the bound is 1e-3, and the
+assertion message carries the error measured and that minimum (measured on B200: 7.8e-4 for
+script_p1_K32_wide, 4.4e-4 for script_p2_K16_wide, everything else below 1e-4).
 """
 import ctypes
 import os
@@ -18,7 +21,8 @@ from conftest import GOLDEN, golden_script_cases
 pytestmark = pytest.mark.gpu
 
 F32_TOL, F64_TOL = 1e-4, 1e-10
-F32_TOL_WIDE = 2e-3
+F32_TOL_SINGULAR = 1e-3          # only for cases with min|1 + h'c| < SINGULAR_BELOW, see the module docstring
+SINGULAR_BELOW = 0.02
 
 
 def _target_arg(g):
@@ -45,10 +49,16 @@ def test_free_energy_and_gradient_match_golden(case, dtype):
     K, D = int(g['K']), int(g['D'])
     obj = SharedFlowObjective(_target_arg(g), K, D, log_eps=float(g['eps']), dtype=dtype)
     F, grad = obj.value_and_grad(g['params'], g['z0'])
-    tol = F64_TOL if dtype == 'float64' else (F32_TOL_WIDE if 'wide' in case else F32_TOL)
+    tol, near = F64_TOL, None
+    if dtype == 'float32':
+        from oracle import planar_torch as pt
+        near = pt.script_min_det_factor(g['params'], g['z0'], K)
+        tol = F32_TOL_SINGULAR if near < SINGULAR_BELOW else F32_TOL
     F_ref = float(g['F_ref'])
-    assert abs(F - F_ref) <= tol * max(1.0, abs(F_ref)), (F, F_ref)
-    assert _relerr(grad, g['g_torch']) <= tol, _relerr(grad, g['g_torch'])
+    eF, eg = abs(F - F_ref) / max(1.0, abs(F_ref)), _relerr(grad, g['g_torch'])
+    print('%s %s: F err %.2e, grad err %.2e, min|1+h\'c| %s, bound %.0e' % (case, dtype, eF, eg, near, tol))
+    assert eF <= tol, 'F error %.2e > %.0e (min|1+h\'c| = %s)' % (eF, tol, near)
+    assert eg <= tol, 'gradient error %.2e > %.0e (min|1+h\'c| = %s)' % (eg, tol, near)
     # forward-only launch and the other_metrics split (get_data.py:80-95)
     assert abs(obj.value(g['params'], g['z0']) - F_ref) <= tol * max(1.0, abs(F_ref))
     mq, mp = obj.metrics(g['params'], g['z0'])
@@ -83,7 +93,7 @@ def test_small_dims_gauss_and_mixture(D):
     mu, ls = 0.5 * rs.randn(D), 0.4 * rs.randn(D)
     tgt = lambda z: torch.exp(pt.log_mvn(z, mu, ls))
     F_ref, g_ref = pt.script_value_and_grad(params, z0, tgt, 1e-7, K)
-    for dtype, tol in (('float64', F64_TOL), ('float32', F32_TOL_WIDE)):
+    for dtype, tol in (('float64', F64_TOL), ('float32', F32_TOL)):
         obj = SharedFlowObjective(('gaussdiag', mu, ls), K, D, dtype=dtype)
         F, grad = obj.value_and_grad(params, z0)
         assert abs(F - F_ref) <= tol * max(1.0, abs(F_ref))

@@ -53,7 +53,7 @@ def test_planar_flow_shared_params_and_errors():
 
 
 @pytest.mark.parametrize('name', ['amortised_K4_D8', 'amortised_K16_D40', 'amortised_K3_D1', 'amortised_K8_D2'])
-@pytest.mark.parametrize('dtype,tol', [(torch.float64, 1e-10), (torch.float32, 2e-4)])
+@pytest.mark.parametrize('dtype,tol', [(torch.float64, 1e-10), (torch.float32, 1e-4)])
 def test_amortised_flow_forward_backward(name, dtype, tol):
     from nfcore import ops
     g = np.load(os.path.join(GOLDEN, name + '.npz'))
@@ -86,7 +86,7 @@ def test_wide_free_energy_matches_oracle(D, K, N):
     mu, ls = 0.2 * rs.randn(D), 0.3 * rs.randn(D) - 4.0 / D      # keeps exp(log_mvn) away from total underflow for small D
     tgt = lambda z: torch.exp(pt.log_mvn(z, mu, ls))
     F_ref, g_ref = pt.script_value_and_grad(params, z0, tgt, 1e-7, K)
-    for dtype, tol in (('float64', 1e-10), ('float32', 2e-4)):
+    for dtype, tol in (('float64', 1e-10), ('float32', 1e-4)):
         obj = SharedFlowObjective(('gaussdiag', mu, ls), K, D, dtype=dtype)
         F, grad = obj.value_and_grad(params, z0)
         assert abs(F - F_ref) <= tol * max(1.0, abs(F_ref)), (dtype, F, F_ref)
@@ -123,7 +123,7 @@ def test_amortised_flow_full_size_float32_vs_float64():
         grads = ops.amortised_backward(a[0], a[2], a[3], a[4], zK, tsave, g_zK.to(dt).contiguous(), -1.0 / N)
         out[dt] = [t.double().cpu().numpy() for t in (zK, logdet) + tuple(grads)]
     for x32, x64 in zip(out[torch.float32], out[torch.float64]):
-        assert _rel(x32, x64) <= 2e-4
+        assert _rel(x32, x64) <= 1e-4
 
 
 # ---- matrix-product ("Gram") formulation of the wide-D free energy: csrc/nf_elbo_gram.cu ----
@@ -150,7 +150,7 @@ def test_gram_free_energy_matches_oracle(D, K, N, chunk, monkeypatch):
     rs, z0, params, mu, ls = _gram_case(D, K, N, 11 * D + K)
     tgt = lambda z: torch.exp(pt.log_mvn(z, mu, ls))
     F_ref, g_ref = pt.script_value_and_grad(params, z0, tgt, 1e-7, K)
-    tol = 2e-4
+    tol = 1e-4
     obj = SharedFlowObjective(('gaussdiag', mu, ls), K, D, dtype='float32')
     z0_dev = torch.tensor(z0, device=DEV)       # device samples go through nf_planar_elbo_fwd_bwd_f32
     F, grad = obj.value_and_grad(params, z0_dev)
@@ -176,8 +176,8 @@ def test_gram_mixture_target_matches_oracle(monkeypatch):
     F_ref, g_ref = pt.script_value_and_grad(params, z0, tgt, 1e-7, K)
     obj = SharedFlowObjective(('mixdiag', pi, mmu, var), K, D, dtype='float32')
     F, grad = obj.value_and_grad(params, torch.tensor(z0, device=DEV))
-    assert abs(F - F_ref) <= 2e-4 * max(1.0, abs(F_ref)), (F, F_ref)
-    assert _rel(grad, g_ref) <= 2e-4, _rel(grad, g_ref)
+    assert abs(F - F_ref) <= 1e-4 * max(1.0, abs(F_ref)), (F, F_ref)
+    assert _rel(grad, g_ref) <= 1e-4, _rel(grad, g_ref)
 
 
 @pytest.mark.parametrize('D,N', [(64, 1 << 19), (256, 1 << 17)])
@@ -195,9 +195,9 @@ def test_gram_full_size_agrees_with_direct_kernel(D, N, monkeypatch):
     monkeypatch.setenv('NF_NO_GRAM', '1')
     ref = [t.double().cpu().numpy() for t in ops.planar_elbo(eps, w, s, b, c, 'gaussdiag', tp)]
     assert np.all(np.isfinite(got[0]))
-    assert np.abs(got[0] - ref[0]).max() <= 2e-4 * np.abs(ref[0]).max()
+    assert np.abs(got[0] - ref[0]).max() <= 1e-4 * np.abs(ref[0]).max()
     for a, r in zip(got[1:], ref[1:]):
-        assert _rel(a, r) <= 5e-4
+        assert _rel(a, r) <= 1e-4
 
 
 def test_device_training_loop_wide_matrix_product_vs_direct(monkeypatch):
@@ -215,11 +215,11 @@ def test_device_training_loop_wide_matrix_product_vs_direct(monkeypatch):
     monkeypatch.setenv('NF_NO_GRAM', '1')
     x_d, tr_d = obj.train(params, eps_all, optimizer='adam', step_size=1e-3)
     assert np.abs(x_g - params).max() > 1e-3
-    assert np.abs(x_g - x_d).max() <= 2e-4 * max(1.0, np.abs(x_d).max())
-    assert np.abs(tr_g - tr_d).max() <= 2e-4 * max(1.0, np.abs(tr_d).max())
+    assert np.abs(x_g - x_d).max() <= 1e-4 * max(1.0, np.abs(x_d).max())
+    assert np.abs(tr_g - tr_d).max() <= 1e-4 * max(1.0, np.abs(tr_d).max())
     tgt = lambda z: torch.exp(pt.log_mvn(z, mu, ls))
     F0, _ = pt.script_value_and_grad(params, eps_all[0], tgt, 1e-7, K)
-    assert abs(tr_g[0] - F0) <= 2e-4 * max(1.0, abs(F0))
+    assert abs(tr_g[0] - F0) <= 1e-4 * max(1.0, abs(F0))
 
 
 @pytest.mark.parametrize('D,K,N,chunk', [(64, 7, 3000, None), (128, 16, 5200, 512)])
@@ -237,11 +237,73 @@ def test_gram_host_samples_session_matches_oracle(D, K, N, chunk, monkeypatch):
     F_ref, g_ref = pt.script_value_and_grad(params, z0, tgt, 1e-7, K)
     obj = SharedFlowObjective(('gaussdiag', mu, ls), K, D, dtype='float32')
     F, grad = obj.value_and_grad(params, z0)
-    assert abs(F - F_ref) <= 2e-4 * max(1.0, abs(F_ref)), (F, F_ref)
-    assert _rel(grad, g_ref) <= 2e-4, _rel(grad, g_ref)
-    assert abs(obj.value(params, z0) - F_ref) <= 2e-4 * max(1.0, abs(F_ref))
+    assert abs(F - F_ref) <= 1e-4 * max(1.0, abs(F_ref)), (F, F_ref)
+    assert _rel(grad, g_ref) <= 1e-4, _rel(grad, g_ref)
+    assert abs(obj.value(params, z0) - F_ref) <= 1e-4 * max(1.0, abs(F_ref))
     monkeypatch.delenv('NF_GRAM')
     monkeypatch.setenv('NF_NO_GRAM', '1')
     F_d, grad_d = obj.value_and_grad(params, z0)
-    assert abs(F - F_d) <= 2e-4 * max(1.0, abs(F_ref))
-    assert _rel(grad, grad_d) <= 2e-4
+    assert abs(F - F_d) <= 1e-4 * max(1.0, abs(F_ref))
+    assert _rel(grad, grad_d) <= 1e-4
+
+
+# ---- BASELINE config 5 shapes against the oracle (K = 64, D in {2, 16, 64, 256}), every path that serves them ----
+@pytest.mark.parametrize('D,N,paths', [(2, 1 << 15, ('default',)), (2, 1 << 18, ('default',)), (16, 1 << 15, ('default',)),
+                                       (64, 1 << 15, ('gram', 'direct')), (256, 1 << 14, ('gram', 'direct'))])
+def test_c5_shapes_match_oracle(D, N, paths, monkeypatch):
+    """SURVEY.md section 8d C5 inputs: W, U = (0.1 + 0.01 N(0,1)) / sqrt(D/2), b = 0.1; target U1 for D = 2, a diagonal
+    Gaussian through log_mvn math for D > 2.  D = 2 runs the scalar kernel (2^15 samples) and the packed-pair kernel
+    (2^18); D = 16 the thread-per-sample kernel; D = 64 and 256 the matrix-product path and the direct wide kernel.
+    float32 against the torch float64 oracle, 1e-4."""
+    from nfcore.objective import SharedFlowObjective
+    from oracle import planar_torch as pt
+    K = 64
+    rs = np.random.RandomState(500 + D)
+    sc = 1.0 / np.sqrt(D / 2)
+    params = np.concatenate([sc * (0.1 + 0.01 * rs.randn(2 * K * D)), 0.1 * np.ones(K)])
+    z0 = rs.randn(N, D)
+    if D == 2:
+        target, fn = 'p1', pt.p1
+    else:
+        mu, ls = rs.uniform(-1, 1, D), rs.uniform(-1, 1, D)
+        target, fn = ('gaussdiag', mu, ls), (lambda z: torch.exp(pt.log_mvn(z, mu, ls)))
+    F_ref, g_ref = pt.script_value_and_grad(params, z0, fn, 1e-7, K)
+    z0_dev = torch.tensor(z0, device=DEV)
+    for path in paths:
+        monkeypatch.delenv('NF_GRAM', raising=False)
+        monkeypatch.delenv('NF_NO_GRAM', raising=False)
+        if path == 'gram':
+            monkeypatch.setenv('NF_GRAM', '1')
+        elif path == 'direct':
+            monkeypatch.setenv('NF_NO_GRAM', '1')
+        obj = SharedFlowObjective(target, K, D, dtype='float32')
+        F, grad = obj.value_and_grad(params, z0_dev)
+        eF, eg = abs(F - F_ref) / max(1.0, abs(F_ref)), _rel(grad, g_ref)
+        print('C5 D=%d N=%d %s: F err %.2e, grad err %.2e' % (D, N, path, eF, eg))
+        assert eF <= 1e-4, (path, eF)
+        assert eg <= 1e-4, (path, eg)
+
+
+def test_sample_from_pz_matches_oracle_on_pinned_draws(monkeypatch):
+    """distributions.sample_from_pz (distributions.py:92-102): randn(N, D) * sd + mu from the GLOBAL NumPy stream, then
+    K planar_flow steps with per-sample parameters.  Same seed -> same draws as the reference makes; the flow steps
+    against the oracle's restatement of flows.py:8-34."""
+    from normflows import distributions
+    from oracle import planar_np as pn
+    rs = np.random.RandomState(8)
+    N, D, K = 257, 5, 3
+    mu, lsd = rs.randn(N, D), 0.3 * rs.randn(N, D)
+    W, U, B = rs.randn(K, N, D), rs.randn(K, N, D), rs.randn(K, N)
+    np.random.seed(123)
+    got = distributions.sample_from_pz(mu, lsd, W, U, B, K)
+    assert np.random.randn() == np.random.RandomState(123).randn(N * D + 1)[-1]      # exactly N*D draws were consumed
+    np.random.seed(123)
+    z = np.random.randn(N, D) * np.sqrt(1e-7 + np.exp(lsd)) + mu         # distributions.py:94-98
+    for k in range(K):
+        z = pn.planar_flow(z, W[k], U[k], B[k])                          # :100-101
+    assert got.shape == (N, D) and got.dtype == np.float64
+    assert _rel(got, z) <= 1e-10
+    assert _rel(distributions.make_samples_z(mu, lsd, W, U, B, 0), mu) < 10      # K = 0: no flow step, still samples
+    got32 = distributions.sample_from_pz(mu.astype(np.float32), lsd.astype(np.float32), W.astype(np.float32), U.astype(np.float32),
+                                         B.astype(np.float32), K)
+    assert got32.dtype == np.float32

@@ -77,14 +77,23 @@ def log_bern_mult(X, p):                              # distributions.py:86-89
 
 
 def sample_from_pz(mu, log_sigma_diag, W, U, b, K):   # distributions.py:92-102
-    eps = 1e-7
+    """randn(N, D) * sd + mu from the global NumPy stream (:96-98, the draws the reference makes), then the K planar
+    steps with per-sample parameters (:100-101) -- on the GPU in ONE launch (nf_planar_amortised_fwd_*, whose
+    reparameterisation sqrt(eps + exp(log_sigma)) and step are optimization.py:74-75,84 = this function's)."""
+    from nfcore import ops
+    mu = np.asarray(mu)
     N, D = mu.shape
-    sd = np.sqrt(eps + np.exp(log_sigma_diag))
-    zk = np.random.randn(N, D)                        # global NumPy RNG, as the reference (:97)
-    zk = zk * sd + mu
-    for k in range(K):
-        zk = planar_flow(zk, W[k], U[k], b[k])        # GPU
-    return zk
+    dt = np.float32 if mu.dtype == np.float32 else np.float64
+    z0 = np.random.randn(N, D)                        # global NumPy RNG, as the reference (:97)
+    if K == 0:
+        return (z0 * np.sqrt(1e-7 + np.exp(np.asarray(log_sigma_diag))) + mu).astype(dt)
+    ops.require_cuda()
+    dev = torch.device('cuda', torch.cuda.current_device())
+    def t(a, shape):
+        return torch.as_tensor(np.ascontiguousarray(a, dtype=dt).reshape(shape)).to(dev)
+    zK, _, _ = ops.amortised_forward(t(z0, (N, D)), t(mu, (N, D)), t(log_sigma_diag, (N, D)), t(np.asarray(W)[:K], (K, N, D)),
+                                     t(np.asarray(U)[:K], (K, N, D)), t(np.asarray(b)[:K], (K, N)), 1e-7, save=False)
+    return zK.cpu().numpy()
 
 
 def make_samples_z(mu, log_sigma_diag, W, U, b, K):   # distributions.py:105-118
