@@ -304,6 +304,20 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(tpg, op=dist.ReduceOp.MAX)
     e2e_pageable = N_PER_GPU * world * n_pg / float(tpg.item())
+    # opt-in: the samples drawn inside the kernel (nf_planar_elbo_fwd_bwd_rng_f32; the library's counter-based stream,
+    # not NumPy's): only the K x D constants go up, only F and the gradient come back
+    e2e_rng = None
+    if world == 1:
+        for i in range(3):
+            obj.value_and_grad_rng(params, N_PER_GPU, 1234, i)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for i in range(args.steps):
+            F_rng, _ = obj.value_and_grad_rng(params, N_PER_GPU, 1234, 3 + i)
+        torch.cuda.synchronize()
+        e2e_rng = {'value': N_PER_GPU * args.steps / (time.perf_counter() - t0), 'unit': UNIT, 'F': float(F_rng),
+                   'h2d_bytes_per_step': 4 * (2 * KD + 2 * K_LAYERS), 'd2h_bytes_per_step': 4 * (nres + 3),
+                   'input': 'none: samples drawn in the kernel (Philox-4x32-10 keyed by seed, counter = (sample pair, step))'}
     h2d = N_PER_GPU * BYTES_PER_SAMPLE + 4 * (2 * KD + 2 * K_LAYERS)
     d2h = 4 * nres
 
@@ -375,6 +389,8 @@ def run_ours(args):
                                                  if small_ar is not None else 'ncclAllReduce (%d floats)' % nres),
             'clocks': clocks,
         }
+        if e2e_rng is not None:
+            line['e2e_rng'] = e2e_rng
         if big is not None:
             line['steady_state_2p24'] = big
         if cpu_value is not None:

@@ -108,6 +108,22 @@ int nf_planar_elbo_fwd_bwd_f64(const double* eps, int64_t N, int D, int K,
                                void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------
+ * The same free energy with the samples drawn inside the kernel.  Replaces the draw the reference makes in every
+ * objective call, z0 = np.random.multivariate_normal(0, I, N) (get_data.py:100-101), together with the pass over z0:
+ * nothing crosses PCIe and nothing is read from HBM but the layer constants.  Opt-in: the stream is this library's own
+ * (Philox-4x32-10 keyed by `seed`, counter = (sample pair, `step`), Box-Muller; csrc/nf_philox.cuh), not NumPy's, so
+ * runs that must reproduce the reference's draws pass their samples to nf_planar_elbo_fwd_bwd_f32 instead.
+ * Sample n of step t depends on (seed, t, n) only; nf_philox_normal_f32 writes the same stream to memory
+ * ([N][D], D = 1 or 2).  float32, D <= 2, K <= 64; all five output arrays are required.
+ * ------------------------------------------------------------------------- */
+int nf_philox_normal_f32(uint64_t seed, uint64_t step, int64_t N, int D, float* out, void* stream);
+int nf_planar_elbo_fwd_bwd_rng_f32(uint64_t seed, uint64_t step, int64_t N, int D, int K,
+                                   const float* w, const float* s, const float* b, const float* c,
+                                   int target_id, const float* target_params, int n_target_params, float log_eps,
+                                   float* out_F, float* g_w, float* g_s, float* g_b, float* g_c,
+                                   void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------
  * Host-buffer form of the shared-parameter free energy: the call the reference's
  * `objective(params, t)` / `gradient(params, t)` make, with everything in host memory
  * (get_data.py:97-115: NumPy parameters, freshly drawn NumPy z0).  A session owns the device

@@ -119,3 +119,16 @@ def test_c_host_algebra_matches_numpy_algebra(semantics, K, D):
                               g[2 * K * D + K:], semantics)
     np.testing.assert_allclose(out, 0.25 * sem.pack(dW, dU, dB), rtol=1e-12, atol=1e-13)
     assert lib.nf_script_constants_host(None, K, D, sid, ctypes.c_void_p(lc.ctypes.data)) != 0
+
+
+def test_philox_restatement_known_answers():
+    """oracle/philox_np.py against the published Philox-4x32-10 known-answer vectors (Random123 kat_vectors)."""
+    from oracle import philox_np as ph
+    kat = [((0, 0, 0, 0), (0, 0), (0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8)),
+           ((0xffffffff,) * 4, (0xffffffff, 0xffffffff), (0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd)),
+           ((0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344), (0xa4093822, 0x299f31d0), (0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1))]
+    for ctr, key, want in kat:
+        got = tuple(int(x[0]) for x in ph.philox4x32_10(*[[c] for c in ctr], *key))
+        assert got == want
+    z = ph.normal(5, 0, 7, 2)
+    assert z.shape == (7, 2) and np.array_equal(ph.normal(5, 0, 3, 2), z[:3])

@@ -66,6 +66,23 @@ int nf_planar_elbo_fwd_bwd_exchange_f32(const float* eps, int64_t N, int D, int 
     return nf::launch_allreduce_small(ar, out, out, nvec, nullptr, (cudaStream_t)stream);
 }
 
+// the samples are drawn inside the kernel (nf_philox.cuh): nothing is read from memory but the layer constants
+int nf_planar_elbo_fwd_bwd_rng_f32(uint64_t seed, uint64_t step, int64_t N, int D, int K, const float* w, const float* s,
+                                   const float* b, const float* c, int target_id, const float* target_params, int n_target_params,
+                                   float log_eps, float* out_F, float* g_w, float* g_s, float* g_b, float* g_c, void* workspace,
+                                   size_t workspace_bytes, void* stream) {
+    if (!out_F || !workspace || !g_w || !g_s || !g_b || !g_c) return NF_ERR_INVALID;
+    if (D != 1 && D != 2) return NF_ERR_UNSUPPORTED;
+    // validation of everything but the (absent) sample pointer
+    const int rc = nf::elbo_validate<float>(reinterpret_cast<const float*>(workspace), N, D, K, w, s, b, c, target_id, target_params,
+                                            n_target_params);
+    if (rc != NF_OK) return rc;
+    if (workspace_bytes < nf_planar_elbo_workspace_bytes(K, D, 4)) return NF_ERR_WORKSPACE;
+    const nf::RngDesc rng = {seed, step};
+    return nf::elbo_fused<float>(true, nullptr, N, D, K, w, s, b, c, target_id, target_params, n_target_params, log_eps, out_F, g_w,
+                                 g_s, g_b, g_c, reinterpret_cast<float*>(workspace), (cudaStream_t)stream, nullptr, nullptr, &rng);
+}
+
 // ---- host-buffer sessions (see nfcore.h) ----
 int nf_session_create(nf_session** out, int64_t max_samples, int D, int K, int elem_size) {
     return nf::session_create(reinterpret_cast<nf::Session**>(out), max_samples, D, K, elem_size);

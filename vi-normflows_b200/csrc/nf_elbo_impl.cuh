@@ -525,7 +525,9 @@ bool pair_applicable(size_t elem, bool bwd, long long N, int D, int K);
 // rows only (sync == NULL: `*nb` rows of partial sums for elbo_finish) or the whole call in one launch
 int pair_elbo(int tgt, const float* eps, long long N, int D, int K, const float* w, const float* s, const float* b,
               const float* c, const float* tp, int ntp, float epsv, float* partials, pr::SyncHeader* sync,
-              float* out_F, float* g_w, float* g_s, float* g_b, float* g_c, int* nb, cudaStream_t st, const pr::ArDesc& ar);
+              float* out_F, float* g_w, float* g_s, float* g_b, float* g_c, int* nb, cudaStream_t st, const pr::ArDesc& ar,
+              const RngDesc& rng);
+static inline RngDesc no_rng() { RngDesc r = {0, 0}; return r; }
 static inline pr::ArDesc no_exchange() { pr::ArDesc a = {}; return a; }
 // nf_allreduce.cu
 int launch_allreduce_small(const pr::ArDesc& ar, const float* src, float* dst, int n, int* status_i, cudaStream_t stream);
@@ -704,7 +706,7 @@ static int elbo_main(bool bwd, const T* eps, int64_t N, int D, int K, const T* w
     if constexpr (sizeof(T) == 4) {
         if (pair_applicable(sizeof(T), bwd, N, D, K))
             return pair_elbo(target_id, eps, N, D, K, w, s, b, c, tparams, ntp, epsv, partials, nullptr, nullptr, nullptr, nullptr,
-                             nullptr, nullptr, nrows, stream, no_exchange());
+                             nullptr, nullptr, nrows, stream, no_exchange(), no_rng());
     }
     switch (D) {
         case 1: return dispatch_target<T, 1>(target_id, bwd, eps, N, K, w, s, b, c, tparams, ntp, epsv, partials, max_blocks, nrows, stream);
@@ -737,16 +739,18 @@ static int elbo_finish(bool bwd, const T* partials, int nrows, int D, int K, T* 
 template <typename T>
 static int elbo_fused(bool bwd, const T* eps, int64_t N, int D, int K, const T* w, const T* s, const T* b, const T* c,
                       int target_id, const T* tparams, int ntp, T epsv, T* out_F, T* g_w, T* g_s, T* g_b, T* g_c, T* partials,
-                      cudaStream_t stream, const pr::ArDesc* ar = nullptr, bool* exchanged = nullptr) {
+                      cudaStream_t stream, const pr::ArDesc* ar = nullptr, bool* exchanged = nullptr, const RngDesc* rng = nullptr) {
     int nb = 0;
     if (exchanged) *exchanged = false;
     if constexpr (sizeof(T) == 4) {
-        if (pair_applicable(sizeof(T), bwd, N, D, K)) {
+        // in-kernel draws (eps == NULL, rng given) exist in the packed-pair kernel only: it then serves every N
+        if (rng && !(bwd && D <= 2 && K <= 64)) return NF_ERR_UNSUPPORTED;
+        if (rng || pair_applicable(sizeof(T), bwd, N, D, K)) {
             unsigned char* base = reinterpret_cast<unsigned char*>(partials);
             pr::SyncHeader* sync = reinterpret_cast<pr::SyncHeader*>(base + nf_planar_elbo_workspace_bytes(K, D, 4) - kSyncHeaderBytes);
             if (exchanged) *exchanged = ar != nullptr;        // the last block also does the exchange
             return pair_elbo(target_id, eps, N, D, K, w, s, b, c, tparams, ntp, epsv, partials, sync, out_F, g_w, g_s, g_b, g_c, &nb, stream,
-                             ar ? *ar : no_exchange());
+                             ar ? *ar : no_exchange(), rng ? *rng : no_rng());
         }
     }
     int rc = elbo_main<T>(bwd, eps, N, D, K, w, s, b, c, target_id, tparams, ntp, epsv, partials, &nb, stream);

@@ -24,6 +24,7 @@
 #include "nf_common.cuh"
 #include "nf_launch.cuh"
 #include "nf_targets.cuh"
+#include "nf_philox.cuh"
 
 namespace nf {
 namespace pr {
@@ -180,7 +181,8 @@ __device__ __forceinline__ void pair_tile(const float* __restrict__ eps, long lo
                                           const float* __restrict__ lcf, const float* __restrict__ lcb,
                                           const float* __restrict__ tp, int ntp, float epsv,
                                           u64* __restrict__ hist_t, uint32_t taddr, float* __restrict__ acc_w, int lane,
-                                          float* __restrict__ stg_w /* staging area of this warp */, float& sum_q, float& sum_p) {
+                                          float* __restrict__ stg_w /* staging area of this warp */, float& sum_q, float& sum_p,
+                                          const RngDesc& rng /* eps == NULL: the samples are drawn here (nf_philox.cuh) */) {
     using M = Mth<float>;
     constexpr int V = 2 * D + 2;
     constexpr int P = S / 2;                        // pairs this round
@@ -197,7 +199,13 @@ __device__ __forceinline__ void pair_tile(const float* __restrict__ eps, long lo
     bool ok[S];
     {
         float zs[S][D];
-        if (!MASKED) {
+        if (eps == nullptr) {
+            // n0 is even: pair p of this thread is Philox call number n0/2 + p
+#pragma unroll
+            for (int p = 0; p < P; ++p) rng_pair<D>(rng, (unsigned long long)(n0 >> 1) + p, zs[2 * p], zs[2 * p + 1]);
+#pragma unroll
+            for (int j = 0; j < S; ++j) ok[j] = !MASKED || n0 + j < N;
+        } else if (!MASKED) {
             constexpr int E = S * D;
             float buf[E];
             const float* src = eps + n0 * D;
@@ -393,7 +401,7 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
                  SyncHeader* __restrict__ sync /* NULL: rows only, the caller sums them */, float* __restrict__ out_F,
                  float* __restrict__ g_w, float* __restrict__ g_s, float* __restrict__ g_b, float* __restrict__ g_c,
                  int flags /* tuning: bit 0 = no rotation of the rounds */, unsigned long long* __restrict__ stamps /* [256][8] or NULL */,
-                 const ArDesc ar) {
+                 const ArDesc ar, const RngDesc rng) {
     using M = Mth<float>;
     constexpr int NT = NW * 32;
     constexpr int V = 2 * D + 2;
@@ -489,16 +497,16 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
             const long long rn = (rr + 1 + rot) % nrounds;
             const long long sn = rn < nfull ? rn * T * SMAX + gw * 32 * SMAX + (long long)lane * SMAX
                                             : nfull * T * SMAX + gw * 32 * srem + (long long)lane * srem;
-            if (sn < N) asm volatile("prefetch.global.L2 [%0];" ::"l"(eps + sn * D));
+            if (eps && sn < N) asm volatile("prefetch.global.L2 [%0];" ::"l"(eps + sn * D));
         }
         if (r < nfull) {
             const long long start = r * T * SMAX + gw * 32 * SMAX;
             if (start >= N) continue;
             const long long n0 = start + (long long)lane * SMAX;
             if (start + 32 * SMAX <= N)
-                pair_tile<D, SMAX, SMAX, ST, NT, TGT, false>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p);
+                pair_tile<D, SMAX, SMAX, ST, NT, TGT, false>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p, rng);
             else
-                pair_tile<D, SMAX, SMAX, ST, NT, TGT, true>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p);
+                pair_tile<D, SMAX, SMAX, ST, NT, TGT, true>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p, rng);
             continue;
         }
         const long long start = nfull * T * SMAX + gw * 32 * srem;
@@ -507,8 +515,8 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
             const bool full = start + 32LL * srem <= N;
 #define NF_PR_REM(S_)                                                                                                        \
     if (SMAX > S_ && srem == S_) {                                                                                           \
-        if (full) pair_tile<D, (S_ < SMAX ? S_ : 2), SMAX, ST, NT, TGT, false>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p); \
-        else pair_tile<D, (S_ < SMAX ? S_ : 2), SMAX, ST, NT, TGT, true>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p);      \
+        if (full) pair_tile<D, (S_ < SMAX ? S_ : 2), SMAX, ST, NT, TGT, false>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p, rng); \
+        else pair_tile<D, (S_ < SMAX ? S_ : 2), SMAX, ST, NT, TGT, true>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p, rng);      \
     }
             NF_PR_REM(2)
             NF_PR_REM(4)

@@ -13,13 +13,13 @@ const PairCfg& pair_override();
 
 #define NF_PAIR_ARGS const float* eps, long long N, int K, const float* w, const float* s, const float* b, const float* c, \
                      const float* tp, int ntp, float epsv, float* partials, pr::SyncHeader* sync, float* out_F, float* g_w, \
-                     float* g_s, float* g_b, float* g_c, int* nb, cudaStream_t st, const pr::ArDesc& ar
-#define NF_PAIR_PASS eps, N, K, w, s, b, c, tp, ntp, epsv, partials, sync, out_F, g_w, g_s, g_b, g_c, nb, st, ar
+                     float* g_s, float* g_b, float* g_c, int* nb, cudaStream_t st, const pr::ArDesc& ar, const RngDesc& rng
+#define NF_PAIR_PASS eps, N, K, w, s, b, c, tp, ntp, epsv, partials, sync, out_F, g_w, g_s, g_b, g_c, nb, st, ar, rng
 
 template <int D, int NW, int SMAX, int ST, int TGT>
 static int launch_pair(const float* eps, long long N, int K, const float* w, const float* s, const float* b, const float* c,
                        const float* tparams, int ntp, float epsv, float* partials, pr::SyncHeader* sync, float* out_F,
-                       float* g_w, float* g_s, float* g_b, float* g_c, int* nblocks_out, cudaStream_t stream, const pr::ArDesc& ar) {
+                       float* g_w, float* g_s, float* g_b, float* g_c, int* nblocks_out, cudaStream_t stream, const pr::ArDesc& ar, const RngDesc& rng) {
     auto kern = pr::elbo_pair_kernel<D, NW, SMAX, ST, TGT>;
     const int ntp_s = target_smem_count(TGT, D, ntp);
     const pr::Smem L(K, D, (SMAX - ST) / 2, ntp_s, NW * 32);
@@ -43,7 +43,7 @@ static int launch_pair(const float* eps, long long N, int K, const float* w, con
     if (grid > tiles) grid = tiles;
     if (grid < 1) grid = 1;
     NF_CUDA_OK(launch_pdl(kern, dim3((unsigned)grid), dim3(NW * 32), smem, stream, eps, N, K, w, s, b, c, tparams, ntp, epsv, partials,
-                          sync, out_F, g_w, g_s, g_b, g_c, pair_override().flags, pair_override().stamps, ar));
+                          sync, out_F, g_w, g_s, g_b, g_c, pair_override().flags, pair_override().stamps, ar, rng));
     *nblocks_out = (int)grid;
     return NF_OK;
 }

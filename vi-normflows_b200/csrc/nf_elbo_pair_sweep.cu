@@ -42,7 +42,7 @@ int pair_group_sweep(NF_PAIR_ARGS) {
 
 int pair_elbo(int tgt, const float* eps, long long N, int D, int K, const float* w, const float* s, const float* b,
               const float* c, const float* tp, int ntp, float epsv, float* partials, pr::SyncHeader* sync,
-              float* out_F, float* g_w, float* g_s, float* g_b, float* g_c, int* nb, cudaStream_t st, const pr::ArDesc& ar) {
+              float* out_F, float* g_w, float* g_s, float* g_b, float* g_c, int* nb, cudaStream_t st, const pr::ArDesc& ar, const RngDesc& rng) {
     if (tgt == NF_TARGET_U1 && D == 2 && pair_override().nw > 0) {
         const int rc = pair_group_sweep(NF_PAIR_PASS);
         if (rc != NF_ERR_UNSUPPORTED) return rc;

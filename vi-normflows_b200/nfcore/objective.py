@@ -288,6 +288,28 @@ class SharedFlowObjective:
             res, n = self._fetch(eps_dev.shape[0])
         return res[0] / n, self._chain(p64, res, n)
 
+    def value_and_grad_rng(self, params, num_samples, seed, step):
+        """value_and_grad with the samples drawn inside the kernel (nf_planar_elbo_fwd_bwd_rng_f32): the library's own
+        counter-based stream for (seed, step) instead of the NumPy draw of get_data.py:100-101 -- opt-in, for runs that
+        do not have to reproduce the reference's draws.  Nothing but the K x D constants goes up, nothing but F and the
+        gradient comes back.  float32, D <= 2, single process."""
+        if self.group is not None or self.dtype != torch.float32:
+            raise NFError('value_and_grad_rng: float32, single process')
+        K, D = self.K, self.D
+        lc64, p64 = self._constants(params)
+        self._lc_host.numpy()[:] = lc64
+        self._lc.copy_(self._lc_host, non_blocking=True)
+        lc, r = self._lc, self._res
+        out = (r[:3], r[3:3 + K * D].view(K, D), r[3 + K * D:3 + 2 * K * D].view(K, D), r[3 + 2 * K * D:3 + 2 * K * D + K],
+               r[3 + 2 * K * D + K:self.n_res])
+        ops.planar_elbo_rng(seed, step, int(num_samples), lc[:K * D].view(K, D), lc[K * D:2 * K * D].view(K, D), lc[2 * K * D:2 * K * D + K],
+                            lc[2 * K * D + K:], self.target_name, self.tparams, self.log_eps, out)
+        self.launches += 1
+        self._res_host.copy_(self._res, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        res = self._res_host.numpy().astype(np.float64)[:self.n_res]
+        return res[0] / num_samples, self._chain(p64, res, num_samples)
+
     def value(self, params, z0):
         if self._is_host(z0):
             res, n, _ = self._host_eval(params, z0, False)

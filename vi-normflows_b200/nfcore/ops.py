@@ -119,6 +119,44 @@ def planar_elbo_exchange(eps, w, s, b, c, target, target_params, log_eps, out_ve
     return out_vec
 
 
+def philox_normal(seed, step, N, D, device=None, out=None):
+    """nf_philox_normal_f32: the [N, D] float32 samples the free-energy kernel draws in place for (seed, step)."""
+    lib = _lib.load()
+    dev = torch.device('cuda', torch.cuda.current_device()) if device is None else torch.device(device)
+    if out is None:
+        out = torch.empty(N, D, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        st = torch.cuda.current_stream(dev).cuda_stream
+        _lib.check(lib.nf_philox_normal_f32(ctypes.c_uint64(seed), ctypes.c_uint64(step), N, D, _ptr(out), ctypes.c_void_p(st)))
+    return out
+
+
+def planar_elbo_rng(seed, step, N, w, s, b, c, target, target_params=None, log_eps=1e-7, out=None):
+    """nf_planar_elbo_fwd_bwd_rng_f32 on the current stream: free energy and gradient sums over N samples drawn inside
+    the kernel (float32, D <= 2).  Returns (out_F[3], g_w, g_s, g_b, g_c); nothing is synchronised."""
+    lib = _lib.load()
+    K, D = w.shape
+    dev = w.device
+    for t in (w, s, b, c):
+        if t.dtype != torch.float32 or not t.is_contiguous() or t.device != dev or not t.is_cuda:
+            raise NFError('planar_elbo_rng: contiguous float32 CUDA tensors on one device')
+    tid = TARGET_IDS[target] if isinstance(target, str) else int(target)
+    ntp = 0 if target_params is None else target_params.numel()
+    if out is None:
+        out = (torch.empty(3, dtype=torch.float32, device=dev), torch.empty(K, D, dtype=torch.float32, device=dev),
+               torch.empty(K, D, dtype=torch.float32, device=dev), torch.empty(K, dtype=torch.float32, device=dev),
+               torch.empty(K, dtype=torch.float32, device=dev))
+    out_F, g_w, g_s, g_b, g_c = out
+    ws = _workspace(K, D, torch.float32, dev, 0)
+    with torch.cuda.device(dev):
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        rc = lib.nf_planar_elbo_fwd_bwd_rng_f32(ctypes.c_uint64(seed), ctypes.c_uint64(step), N, D, K, _ptr(w), _ptr(s), _ptr(b), _ptr(c), tid,
+                                                _ptr(target_params), ntp, ctypes.c_float(log_eps), _ptr(out_F), _ptr(g_w), _ptr(g_s),
+                                                _ptr(g_b), _ptr(g_c), _ptr(ws), ws.numel(), ctypes.c_void_p(stream))
+    _lib.check(rc)
+    return out
+
+
 def _same(dtype, dev, *ts):
     for t in ts:
         if t is not None and (t.dtype != dtype or not t.is_contiguous() or t.device != dev):
