@@ -45,6 +45,10 @@ typedef enum {
  *                    pi_{G-1} is passed explicitly (= 1 - sum of the others).
  *   GAUSSDIAG      : exp(distributions.py:35-54 log_mvn); params = [mu (D) | log_sigma_diag (D)];
  *                    for D == 1 the inverse variance is exp(1 - log_sigma) as at :46-47.
+ *   MIXFULL        : distributions.py:60-69 prob_gm with FULL covariance matrices, which is what mvn takes when
+ *                    len(sigma_diag) > 1 (:20-25: np.linalg.inv / np.linalg.det of a D x D matrix);
+ *                    params = [pi (G) | mu (G*D) | Sigma (G*D*D, row-major)], G = n/(1+D+D*D); D <= 4.
+ *                    The kernels invert the matrices once per block (Gauss-Jordan in float64).
  */
 typedef enum {
     NF_TARGET_U1 = 0,
@@ -53,7 +57,8 @@ typedef enum {
     NF_TARGET_U4 = 3,
     NF_TARGET_TRIAL1 = 4,
     NF_TARGET_MIXDIAG = 5,
-    NF_TARGET_GAUSSDIAG = 6
+    NF_TARGET_GAUSSDIAG = 6,
+    NF_TARGET_MIXFULL = 7
 } nf_target;
 
 const char* nf_status_string(int status);

@@ -327,3 +327,31 @@ def test_training_loop_resume_equals_one_call():
             assert np.array_equal(np.concatenate(traces), tr_one)
             x_again, _ = obj.train(init, eps_all, optimizer=optimizer, step_size=1e-3)
             assert np.array_equal(x_again, x_one)
+
+
+@pytest.mark.parametrize('D,N', [(2, 3001), (3, 1500), (4, 900), (2, 160001)])
+def test_mixture_with_full_covariance_matrices(D, N):
+    """distributions.py:20-25: for len(sigma_diag) > 1 `mvn` inverts a full D x D matrix, so prob_gm takes (G, D, D)
+    covariances.  Non-diagonal ones run as their own fused target (the kernel inverts them); against the oracle's
+    prob_gm on the same matrices, float64 1e-10 and float32 1e-4; D = 2 also on the packed-pair kernel (N = 160 001)."""
+    from nfcore.objective import SharedFlowObjective
+    from oracle import planar_torch as pt
+    rs = np.random.RandomState(70 + D)
+    K, G = 6, 3
+    z0 = rs.randn(N, D)
+    params = np.concatenate([0.3 * rs.randn(2 * K * D), 0.2 * rs.randn(K)])
+    pi = np.array([0.25, 0.4]); mmu = rs.randn(G, D)
+    A = rs.randn(G, D, D)
+    cov = np.einsum('gij,gkj->gik', A, A) + 0.5 * np.eye(D)              # symmetric positive definite, far from diagonal
+    tgt = lambda z: pt.prob_gm(z, torch.tensor(mmu), torch.tensor(cov), torch.tensor(pi))
+    F_ref, g_ref = pt.script_value_and_grad(params, z0, tgt, 1e-7, K)
+    for dtype, tol in (('float64', F64_TOL), ('float32', F32_TOL)):
+        obj = SharedFlowObjective(('mixdiag', pi, mmu, cov), K, D, dtype=dtype)
+        assert obj.target_name == 'mixfull'
+        F, grad = obj.value_and_grad(params, torch.as_tensor(z0, dtype=obj.dtype).cuda())
+        eF, eg = abs(F - F_ref) / max(1.0, abs(F_ref)), _relerr(grad, g_ref)
+        print('mixfull D=%d N=%d %s: F err %.2e, grad err %.2e' % (D, N, dtype, eF, eg))
+        assert eF <= tol and eg <= tol, (dtype, eF, eg)
+        assert abs(obj.value(params, z0) - F_ref) <= tol * max(1.0, abs(F_ref))      # forward-only launch, host samples
+    with pytest.raises(Exception):
+        SharedFlowObjective(('mixdiag', pi, rs.randn(G, 5), np.tile(np.eye(5) + 0.1, (G, 1, 1))), K, 5)

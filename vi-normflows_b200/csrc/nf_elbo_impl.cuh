@@ -596,6 +596,9 @@ static int dispatch_target(int tgt, bool bwd, const T* eps, long long N, int K, 
         NF_CASE(NF_TARGET_GAUSSDIAG);
         default: break;
     }
+    if constexpr (D <= 4) {
+        if (tgt == NF_TARGET_MIXFULL) return dispatch_bwd<T, D, NF_TARGET_MIXFULL>(bwd, eps, N, K, w, s, b, c, tp, ntp, epsv, partials, max_blocks, nb, st);
+    }
     if (D == 2) {
         switch (tgt) {
             case NF_TARGET_U1: return dispatch_bwd<T, 2, NF_TARGET_U1>(bwd, eps, N, K, w, s, b, c, tp, ntp, epsv, partials, max_blocks, nb, st);
@@ -688,7 +691,10 @@ static int elbo_validate(const T* eps, int64_t N, int D, int K, const T* w, cons
         if (!tparams || ntp < 1 + 2 * D || ntp % (1 + 2 * D) != 0) return NF_ERR_INVALID;
     } else if (target_id == NF_TARGET_GAUSSDIAG) {
         if (!tparams || ntp != 2 * D) return NF_ERR_INVALID;
-    } else if (target_id < 0 || target_id > NF_TARGET_GAUSSDIAG) {
+    } else if (target_id == NF_TARGET_MIXFULL) {
+        if (!tparams || ntp < 1 + D + D * D || ntp % (1 + D + D * D) != 0) return NF_ERR_INVALID;
+        if (D > 4) return NF_ERR_UNSUPPORTED;
+    } else if (target_id < 0 || target_id > NF_TARGET_MIXFULL) {
         return NF_ERR_INVALID;
     } else if (D != 2) {
         return NF_ERR_INVALID;      // the 2-D potentials index z[:,0], z[:,1] (get_data.py:29)

@@ -12,6 +12,10 @@ int pair_group_gauss(int tgt, int D, NF_PAIR_ARGS) {
         if (D == 1) return dispatch_pair<1, NF_TARGET_GAUSSDIAG>(NF_PAIR_PASS);
         if (D == 2) return dispatch_pair<2, NF_TARGET_GAUSSDIAG>(NF_PAIR_PASS);
     }
+    if (tgt == NF_TARGET_MIXFULL) {
+        if (D == 1) return dispatch_pair<1, NF_TARGET_MIXFULL>(NF_PAIR_PASS);
+        if (D == 2) return dispatch_pair<2, NF_TARGET_MIXFULL>(NF_PAIR_PASS);
+    }
     return NF_ERR_UNSUPPORTED;
 }
 

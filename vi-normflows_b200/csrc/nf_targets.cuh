@@ -10,6 +10,7 @@ namespace nf {
 __host__ __device__ inline int target_smem_count(int tgt, int D, int ntp) {
     if (tgt == NF_TARGET_MIXDIAG) return ntp;          // coef(G) | mu(G*D) | inv_var(G*D)
     if (tgt == NF_TARGET_GAUSSDIAG) return 1 + 2 * D;  // const | mu(D) | inv_var(D)
+    if (tgt == NF_TARGET_MIXFULL) return ntp;          // coef(G) | mu(G*D) | precision(G*D*D)
     return 0;
 }
 
@@ -29,6 +30,38 @@ __device__ inline void target_prepare(int tgt, int D, const T* __restrict__ raw,
             for (int d = 0; d < D; ++d) logdet += ::log((double)raw[G + G * D + g * D + d]);
             // pi_g (2 pi)^{-D/2} det^{-1/2}   -- distributions.py:29
             tp[g] = (T)((double)raw[g] * ::exp(-0.5 * D * LOG2PI - 0.5 * logdet));
+        }
+    } else if (tgt == NF_TARGET_MIXFULL) {
+        // distributions.py:23-25: siginv = inv(Sigma), det(Sigma); one thread per component, D <= 4, float64
+        const int G = ntp / (1 + D + D * D);
+        for (int i = threadIdx.x; i < G * D; i += blockDim.x) tp[G + i] = raw[G + i];
+        for (int g = threadIdx.x; g < G; g += blockDim.x) {
+            double a[4][8];
+            const T* S = raw + G + G * D + g * D * D;
+            for (int i = 0; i < D && i < 4; ++i)
+                for (int j = 0; j < D && j < 4; ++j) { a[i][j] = (double)S[i * D + j]; a[i][4 + j] = i == j ? 1.0 : 0.0; }
+            double det = 1.0;
+            for (int c0 = 0; c0 < D && c0 < 4; ++c0) {
+                int piv = c0;
+                for (int r = c0 + 1; r < D && r < 4; ++r) if (::fabs(a[r][c0]) > ::fabs(a[piv][c0])) piv = r;
+                if (piv != c0) {
+                    for (int j = 0; j < 8; ++j) { const double t = a[c0][j]; a[c0][j] = a[piv][j]; a[piv][j] = t; }
+                    det = -det;
+                }
+                const double pv = a[c0][c0];
+                det *= pv;
+                const double ip = 1.0 / pv;
+                for (int j = 0; j < 8; ++j) a[c0][j] *= ip;
+                for (int r = 0; r < D && r < 4; ++r) {
+                    if (r == c0) continue;
+                    const double f = a[r][c0];
+                    for (int j = 0; j < 8; ++j) a[r][j] -= f * a[c0][j];
+                }
+            }
+            for (int i = 0; i < D && i < 4; ++i)
+                for (int j = 0; j < D && j < 4; ++j) tp[G + G * D + g * D * D + i * D + j] = (T)a[i][4 + j];
+            // pi_g (2 pi)^{-D/2} det^{-1/2}   -- distributions.py:29
+            tp[g] = (T)((double)raw[g] * ::exp(-0.5 * D * LOG2PI) / ::sqrt(det));
         }
     } else if (tgt == NF_TARGET_GAUSSDIAG) {
         for (int d = threadIdx.x; d < D; d += blockDim.x) {
@@ -177,6 +210,53 @@ template <typename T, int D, bool BWD> struct Target<T, D, NF_TARGET_MIXDIAG, BW
             if (BWD) {
 #pragma unroll
                 for (int d = 0; d < D; ++d) dd[d] = M::fma(e, sc[d], dd[d]);   // -d dens/d z_d
+            }
+        }
+        const T den = eps + dens;
+        lp = M::flog(den);
+        if (BWD) {
+            const T inv = M::div((T)1, den);
+#pragma unroll
+            for (int d = 0; d < D; ++d) gz[d] = dd[d] * inv;
+        }
+    }
+};
+
+// mixture of Gaussians with full covariance matrices -- distributions.py:60-69 (prob_gm) over :10-32 (mvn, matrix branch)
+template <typename T, int D, bool BWD> struct Target<T, D, NF_TARGET_MIXFULL, BWD> {
+    static __device__ __forceinline__ void eval(const T* z, const T* tp, int ntp, T eps, T& lp, T* gz) {
+        using M = Mth<T>;
+        const int G = ntp / (1 + D + D * D);
+        T dens = (T)0;
+        T dd[D];
+#pragma unroll
+        for (int d = 0; d < D; ++d) dd[d] = (T)0;
+        for (int g = 0; g < G; ++g) {
+            T df[D], sc[D];
+#pragma unroll
+            for (int d = 0; d < D; ++d) df[d] = z[d] - tp[G + g * D + d];
+            T q = (T)0;
+            const T* P = tp + G + G * D + g * D * D;
+#pragma unroll
+            for (int i = 0; i < D; ++i) {
+                T a = (T)0;
+#pragma unroll
+                for (int j = 0; j < D; ++j) a = M::fma(df[j], P[j * D + i], a);      // (zdiff @ siginv)_i, :30
+                sc[i] = a;
+                q = M::fma(a, df[i], q);
+            }
+            const T e = tp[g] * M::fexp((T)-0.5 * q);
+            dens += e;
+            if (BWD) {
+                // d q / d z_i = sum_j (P_ij + P_ji) df_j; the reference's inverse of a symmetric matrix is symmetric up to
+                // rounding, the gradient follows the formula as written
+#pragma unroll
+                for (int i = 0; i < D; ++i) {
+                    T b = (T)0;
+#pragma unroll
+                    for (int j = 0; j < D; ++j) b = M::fma(P[i * D + j], df[j], b);
+                    dd[i] = M::fma(e, (T)0.5 * (sc[i] + b), dd[i]);                    // -d dens/d z_i
+                }
             }
         }
         const T den = eps + dens;

@@ -22,7 +22,8 @@ def resolve_target(target, D):
     Accepted: the names 'p1'..'p4', 'trial1', 'gmm' (get_data.py:61-66 constants),
     'gmm_exp' (experimentation.py:18-23 constants); a callable whose __name__ is one of
     those (the reference's own functions are recognised by name); or a tuple
-    ('mixdiag', pi[G], mu[G,D], var[G,D]) / ('gaussdiag', mu[D], log_sigma_diag[D]).
+    ('mixdiag', pi[G], mu[G,D], var[G,D] or covariance matrices [G,D,D] -- full matrices for D <= 4, as
+    distributions.py:20-25 takes them) / ('gaussdiag', mu[D], log_sigma_diag[D]).
     Arbitrary Python callables cannot be fused into the kernel and are rejected.
     """
     if callable(target) and not isinstance(target, (str, tuple)):
@@ -49,10 +50,18 @@ def resolve_target(target, D):
     if kind == 'mixdiag':
         pi, mu, var = (np.asarray(a, dtype=np.float64) for a in target[1:])
         mu = mu.reshape(-1, D)
-        if var.ndim == 3:      # distributions.py:23-25 takes (G, D, D) covariance matrices; only diagonal ones are fused
+        if var.ndim == 3:      # distributions.py:23-25 takes (G, D, D) covariance matrices
             off = var - np.array([np.diag(np.diag(v)) for v in var])
             if np.abs(off).max() > 0:
-                raise NFError('mixdiag: covariance matrices must be diagonal to be fused into the kernel')
+                # full covariances: their own target (the kernel inverts the matrices, D <= 4)
+                if D > 4:
+                    raise NFError('mixture with full covariance matrices: dim_z <= 4 (diagonal covariances have no limit)')
+                G = mu.shape[0]
+                if pi.shape[0] == G - 1:
+                    pi = np.concatenate([pi, [1 - pi.sum()]])
+                if pi.shape[0] != G or var.shape != (G, D, D):
+                    raise NFError('mixture: inconsistent component count')
+                return 'mixfull', np.concatenate([pi, mu.ravel(), var.ravel()])
             var = np.array([np.diag(v) for v in var])
         var = var.reshape(-1, D)
         G = mu.shape[0]

@@ -10,7 +10,7 @@ from . import _lib
 from ._lib import NFError
 
 TARGET_IDS = {'p1': 0, 'U1': 0, 'p2': 1, 'U2': 1, 'p3': 2, 'U3': 2, 'p4': 3, 'U4': 3, 'trial1': 4,
-              'mixdiag': 5, 'gaussdiag': 6}
+              'mixdiag': 5, 'gaussdiag': 6, 'mixfull': 7}
 
 _DT = {torch.float32: ('f32', 4, ctypes.c_float), torch.float64: ('f64', 8, ctypes.c_double)}
 
