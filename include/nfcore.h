@@ -221,6 +221,26 @@ int nf_planar_elbo_fwd_bwd_noalloc_f32(const float* eps, int64_t N, int D, int K
                                        void* stream);
 
 /* ---------------------------------------------------------------------------
+ * Evaluation surface of the shared-parameter path (forward only), what visualise_flow (Final (master).ipynb cell 16)
+ * computes with NumPy: the target density at given points (its contour grid), and samples pushed through the
+ * learned flow.
+ *   nf_target_density_* : out[n] = target(z[n]), the density itself (get_data.py:20-66 p1..p4, trial1, gmm;
+ *                         distributions.py:10-32 mvn, :60-69 prob_gm); target ids and parameters as above.
+ *                         D <= 4 for every target; D <= 512 for MIXDIAG / GAUSSDIAG.
+ *   nf_planar_chain_forward_* : z_K[n] (get_data.py:104-109 applied to the given z0[n]) and, when log_qK != NULL,
+ *                         log q_K[n] = -1/2 sum_d (log 2 pi + z0_d^2) - sum_k log(eps + |1 + h'(a_k) c_k|) (:111).
+ *                         Layer constants (w, s, b, c) as for nf_planar_elbo_fwd_bwd_*; D <= 512.
+ * ------------------------------------------------------------------------- */
+int nf_target_density_f32(const float* z, int64_t N, int D, int target_id, const float* target_params, int n_target_params,
+                          float* out, void* stream);
+int nf_target_density_f64(const double* z, int64_t N, int D, int target_id, const double* target_params, int n_target_params,
+                          double* out, void* stream);
+int nf_planar_chain_forward_f32(const float* z0, int64_t N, int D, int K, const float* w, const float* s, const float* b,
+                                const float* c, float log_eps, float* zK, float* log_qK, void* stream);
+int nf_planar_chain_forward_f64(const double* z0, int64_t N, int D, int K, const double* w, const double* s, const double* b,
+                                const double* c, double log_eps, double* zK, double* log_qK, void* stream);
+
+/* ---------------------------------------------------------------------------
  * flows.planar_flow (normflows/normflows/flows.py:8-34, _get_uhat :37-39, m :42-43).
  * z, out: [N][D].  per_sample != 0: w,u are [N][D] and b is [N] (the HEAD signature,
  * flows.py:26-27); per_sample == 0: w,u are [D], b is [1] (the call the stale drivers

@@ -65,6 +65,10 @@ PROTOTYPES = {
     'nf_allreduce_small_buffer_bytes': (c_size_t, [c_int]),
     'nf_allreduce_small_max_count': (c_int, []),
     'nf_allreduce_small_f32': (c_int, [ctypes.POINTER(c_void_p), c_int, c_int, c_void_p, c_void_p, c_int, ctypes.c_uint64, c_void_p, c_void_p]),
+    'nf_target_density_f32': (c_int, [c_void_p, c_int64, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p]),
+    'nf_target_density_f64': (c_int, [c_void_p, c_int64, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p]),
+    'nf_planar_chain_forward_f32': (c_int, [c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_void_p]),
+    'nf_planar_chain_forward_f64': (c_int, [c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_double, c_void_p, c_void_p, c_void_p]),
     'nf_philox_normal_f32': (c_int, [ctypes.c_uint64, ctypes.c_uint64, c_int64, c_int, c_void_p, c_void_p]),
     'nf_planar_elbo_fwd_bwd_rng_f32': (c_int, [ctypes.c_uint64, ctypes.c_uint64, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
                                                c_void_p, c_int, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),

@@ -119,6 +119,43 @@ def planar_elbo_exchange(eps, w, s, b, c, target, target_params, log_eps, out_ve
     return out_vec
 
 
+def target_density(z, target, target_params=None):
+    """nf_target_density_*: out[n] = target(z[n]) for CUDA z [N, D] (float32 or float64)."""
+    lib = _lib.load()
+    if not z.is_cuda or z.dtype not in _DT:
+        raise NFError('target_density needs a float32/float64 CUDA tensor (no CPU fallback)')
+    z = z.contiguous()
+    N, D = z.shape
+    tid = TARGET_IDS[target] if isinstance(target, str) else int(target)
+    ntp = 0 if target_params is None else target_params.numel()
+    if target_params is not None:
+        _same(z.dtype, z.device, target_params)
+    out = torch.empty(N, dtype=z.dtype, device=z.device)
+    fn = getattr(lib, 'nf_target_density_' + _DT[z.dtype][0])
+    with torch.cuda.device(z.device):
+        st = torch.cuda.current_stream(z.device).cuda_stream
+        _lib.check(fn(_ptr(z), N, D, tid, _ptr(target_params), ntp, _ptr(out), ctypes.c_void_p(st)))
+    return out
+
+
+def chain_forward(z0, w, s, b, c, log_eps=1e-7, want_logq=True):
+    """nf_planar_chain_forward_*: (z_K [N, D], log q_K [N] or None) for CUDA samples z0 and layer constants."""
+    lib = _lib.load()
+    if not z0.is_cuda or z0.dtype not in _DT:
+        raise NFError('chain_forward needs float32/float64 CUDA tensors (no CPU fallback)')
+    z0 = z0.contiguous()
+    _same(z0.dtype, z0.device, w, s, b, c)
+    N, D = z0.shape
+    K = w.shape[0]
+    zK = torch.empty_like(z0)
+    lq = torch.empty(N, dtype=z0.dtype, device=z0.device) if want_logq else None
+    fn = getattr(lib, 'nf_planar_chain_forward_' + _DT[z0.dtype][0])
+    with torch.cuda.device(z0.device):
+        st = torch.cuda.current_stream(z0.device).cuda_stream
+        _lib.check(fn(_ptr(z0), N, D, K, _ptr(w), _ptr(s), _ptr(b), _ptr(c), _DT[z0.dtype][2](log_eps), _ptr(zK), _ptr(lq), ctypes.c_void_p(st)))
+    return zK, lq
+
+
 def philox_normal(seed, step, N, D, device=None, out=None):
     """nf_philox_normal_f32: the [N, D] float32 samples the free-energy kernel draws in place for (seed, step)."""
     lib = _lib.load()

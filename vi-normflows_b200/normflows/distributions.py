@@ -1,9 +1,10 @@
 """normflows/normflows/distributions.py: densities and sampling.
 
-The density helpers are the reference's host-side NumPy utilities (they act on small
-arrays the drivers hold on the host; inside the objectives the same math runs fused in
-the CUDA kernels -- nf_targets.cuh, nf_flow_rows.cu).  ``sample_from_pz`` pushes the
-samples through the K planar layers on the GPU.
+Given CUDA tensors, ``mvn`` / ``prob_gm`` / ``log_mvn`` evaluate on the GPU (nf_target_density_*: the same fused
+target code the objectives run, csrc/nf_targets.cuh) and return CUDA tensors.  Given NumPy arrays they are the
+reference's host-side formulas: small conveniences the drivers apply to a few hundred points they hold on the host
+(test_gmm.py:6-11, the plotting paths) -- by design not a compute path; the objectives never go through them.
+``sample_from_pz`` pushes its samples through the K planar layers on the GPU.
 """
 import numpy as np
 import torch
@@ -16,8 +17,22 @@ def _is_t(*xs):
     return any(isinstance(x, torch.Tensor) for x in xs)
 
 
+def _gpu_density(Z, kind, *parts):
+    """CUDA tensor Z (N, D) -> (N,) density through nf_target_density_* (kind: 'mixdiag' | 'mixfull' | 'gaussdiag')."""
+    from nfcore import ops
+    tp = torch.cat([torch.as_tensor(np.asarray(p.detach().cpu() if isinstance(p, torch.Tensor) else p, dtype=np.float64).ravel())
+                    for p in parts]).to(Z.device, Z.dtype)
+    return ops.target_density(Z, kind, tp)
+
+
 def mvn(Z, mu, sigma_diag):                           # distributions.py:10-32
     N, D = Z.shape
+    if isinstance(Z, torch.Tensor) and Z.is_cuda:
+        sg = np.asarray(sigma_diag.detach().cpu() if isinstance(sigma_diag, torch.Tensor) else sigma_diag, dtype=np.float64)
+        if len(sg) == 1:                              # a scalar variance (:20-22): D must be 1
+            return _gpu_density(Z, 'mixdiag', [1.0], mu, sg.reshape(-1)[:1]).reshape(N, 1)
+        if D <= 4:                                    # a full matrix (:23-25)
+            return _gpu_density(Z, 'mixfull', [1.0], mu, sg.reshape(D, D)).reshape(N, 1)
     mu = mu.reshape(-1, D)
     if len(sigma_diag) == 1:
         siginv = 1 / sigma_diag
@@ -33,6 +48,8 @@ def mvn(Z, mu, sigma_diag):                           # distributions.py:10-32
 
 def log_mvn(Z, mu, log_sigma_diag):                   # distributions.py:35-54
     N, D = Z.shape
+    if isinstance(Z, torch.Tensor) and Z.is_cuda and not (isinstance(mu, torch.Tensor) and mu.requires_grad):
+        return torch.log(_gpu_density(Z, 'gaussdiag', mu, log_sigma_diag))
     mu = mu.reshape(-1, D)
     logdet_sigma = np.sum(log_sigma_diag)
     if len(log_sigma_diag) == 1:
@@ -52,6 +69,15 @@ def log_std_norm(x):                                  # distributions.py:57
 
 def prob_gm(Z, mu, sigma_diag, pi):                   # distributions.py:60-69
     G = pi.shape[0] + 1
+    if isinstance(Z, torch.Tensor) and Z.is_cuda:
+        N, D = Z.shape
+        tonp = lambda a: np.asarray(a.detach().cpu() if isinstance(a, torch.Tensor) else a, dtype=np.float64)
+        pi_all = np.concatenate([tonp(pi).ravel(), [1 - tonp(pi).sum()]])
+        sg = tonp(sigma_diag)
+        if D == 1:
+            return _gpu_density(Z, 'mixdiag', pi_all, tonp(mu), sg.reshape(G)).reshape(N, 1)
+        if D <= 4:
+            return _gpu_density(Z, 'mixfull', pi_all, tonp(mu), sg.reshape(G, D, D)).reshape(N, 1)
     prob = 0
     for g in range(G):
         pi_g = 1 - np.sum(pi) if g == G - 1 else pi[g]

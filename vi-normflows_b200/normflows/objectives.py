@@ -96,3 +96,46 @@ def optimise(func, num_samples, num_iter, lr, K, dim_z=2, optimizer='rmsprop', e
     if pending:
         x, _ = obj.train(x, np.stack(pending), optimizer=optimizer, step_size=lr, state=state)
     return x
+
+
+def target_density(target, Z, dim_z=None, dtype='float64'):
+    """The target density at the points Z (N, dim_z) on the GPU: what visualise_flow (Final (master).ipynb cell 16)
+    evaluates on its contour grid with `func(z)`.  `target` as for gradient_create.  NumPy in, NumPy out (N,)."""
+    import torch
+    from nfcore import ops
+    from nfcore.objective import resolve_target
+    Z = np.asarray(Z)
+    D = Z.shape[1] if dim_z is None else dim_z
+    name, tparams = resolve_target(target, D)
+    ops.require_cuda()
+    dev = torch.device('cuda', torch.cuda.current_device())
+    dt = torch.float32 if np.dtype(dtype) == np.float32 else torch.float64
+    tp = None if tparams is None else torch.as_tensor(tparams).to(dev, dt)
+    return ops.target_density(torch.as_tensor(np.ascontiguousarray(Z)).to(dev, dt), name, tp).cpu().numpy()
+
+
+def density_grid(target, xs, ys, dtype='float64'):
+    """Density of a 2-D target on the grid xs x ys -> array (len(ys), len(xs)), as np.meshgrid(xs, ys) orders it."""
+    X, Y = np.meshgrid(np.asarray(xs, dtype=np.float64), np.asarray(ys, dtype=np.float64))
+    return target_density(target, np.stack([X.ravel(), Y.ravel()], axis=1), 2, dtype).reshape(Y.shape)
+
+
+def flow_samples(params, z0, K, dim_z, dtype='float64', semantics='script', log_eps=1e-7):
+    """Samples z0 (N, dim_z) pushed through the K shared-parameter layers described by `params` ([W | U | B],
+    get_data.py:74-78): returns (z_K, log q_K) -- the scatter visualise_flow draws over the contours, and the
+    variational log-density of those points (get_data.py:104-111).  NumPy in, NumPy out."""
+    import ctypes
+    import torch
+    from nfcore import _lib, ops, semantics as sem
+    ops.require_cuda()
+    lib = _lib.load()
+    p = np.ascontiguousarray(params, dtype=np.float64).ravel()
+    lc = np.empty(2 * K * dim_z + 2 * K, dtype=np.float64)
+    _lib.check(lib.nf_script_constants_host(ctypes.c_void_p(p.ctypes.data), K, dim_z, sem.SEMANTICS.index(semantics), ctypes.c_void_p(lc.ctypes.data)))
+    dev = torch.device('cuda', torch.cuda.current_device())
+    dt = torch.float32 if np.dtype(dtype) == np.float32 else torch.float64
+    t = torch.as_tensor(lc).to(dev, dt)
+    KD = K * dim_z
+    zK, lq = ops.chain_forward(torch.as_tensor(np.ascontiguousarray(z0)).to(dev, dt), t[:KD].view(K, dim_z).contiguous(),
+                               t[KD:2 * KD].view(K, dim_z).contiguous(), t[2 * KD:2 * KD + K].contiguous(), t[2 * KD + K:].contiguous(), log_eps)
+    return zK.cpu().numpy(), lq.cpu().numpy()
