@@ -6,10 +6,12 @@
 Workload (the configuration BASELINE's metric is quoted on): K=32 planar
 layers, D=2, target U1 (`p1`), 2^20 Monte-Carlo samples per GPU per step, float32, script
 semantics (get_data.py:97-115).  One "step" = one fused forward+backward over one batch of
-2^20 fresh samples: the objective kernel + the fixed-order partial-sum kernel (+ one NCCL
-all-reduce of the 3+2KD+2K result vector when N>1).  Samples are resident in HBM for
-`value`; `e2e` goes through the NumPy-facing objective with pinned host samples (H2D of the
-samples, D2H of F and the gradient inside the timed region).
+2^20 fresh samples: ONE launch of the objective kernel, whose last block adds the per-SM rows
+in a fixed order and, when N>1, exchanges the 3+2KD+2K result sums with the peers over NVLink.
+Samples are resident in HBM for `value`; `e2e` goes through the NumPy-facing objective with
+pinned host samples (H2D of the samples, D2H of F and the gradient inside the timed region);
+`e2e_pageable` is the same call on a pageable float64 NumPy array, `e2e_rng` the opt-in call that
+draws the samples inside the kernel.
 
 Prints ONE JSON line (rank 0).  `--impl reference` times the CPU stand-in for the reference's
 autograd path (torch float64 op-for-op restatement from oracle/, all host threads) on the

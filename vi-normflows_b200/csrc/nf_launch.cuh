@@ -1,5 +1,6 @@
 // Host-side launch helpers shared by the translation units of libnfcore.
 #pragma once
+#include <cstdlib>
 #include <mutex>
 #include "nf_common.cuh"
 
@@ -18,7 +19,8 @@ static inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 blo
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
+    static const bool plain = getenv("NF_NO_PDL") != nullptr;      // tuning knob: ordinary stream-ordered launches
+    cfg.attrs = attr; cfg.numAttrs = plain ? 0 : 1;
     return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
 }
 
