@@ -284,6 +284,23 @@ int nf_planar_amortised_bwd_f64(const double* z0, const double* log_sigma0, cons
                                 int64_t N, int D, int K, double log_eps, double* g_mu0, double* g_log_sigma0,
                                 double* g_W, double* g_U, double* g_Bb, void* stream);
 
+/* The same reverse pass with dF/dlogdet given per sample in device memory (g_logdet_vec[N]): what a tape hands back
+ * without a host round trip for the scalar (optimization.py:85,92 make it -1/N for every n, but it lives on the device). */
+int nf_planar_amortised_bwd_v_f32(const float* z0, const float* log_sigma0, const float* W, const float* U,
+                                  const float* zK, const float* t_save, const float* g_zK, const float* g_logdet_vec,
+                                  int64_t N, int D, int K, float log_eps, float* g_mu0, float* g_log_sigma0,
+                                  float* g_W, float* g_U, float* g_Bb, void* stream);
+int nf_planar_amortised_bwd_v_f64(const double* z0, const double* log_sigma0, const double* W, const double* U,
+                                  const double* zK, const double* t_save, const double* g_zK, const double* g_logdet_vec,
+                                  int64_t N, int D, int K, double log_eps, double* g_mu0, double* g_log_sigma0,
+                                  double* g_W, double* g_U, double* g_Bb, void* stream);
+
+/* autograd.misc.optimizers.adam (autograd 1.3; call site optimization.py:118), one step on the device:
+ *   m = (1-b1) g + b1 m;  v = (1-b2) g^2 + b2 v;  x -= step * (m / (1 - b1^(t+1))) / (sqrt(v / (1 - b2^(t+1))) + eps)
+ * params, m, v: float64[n] in device memory (m, v zero before step t = 0); grad: float32 or float64 (grad_elem_size). */
+int nf_adam_step(double* params, const void* grad, int grad_elem_size, double* m, double* v, int64_t n, double step_size,
+                 double b1, double b2, double eps, int64_t t, void* stream);
+
 /* ---------------------------------------------------------------------------
  * Encoder / decoder MLP: nn_models.Feedforward.forward (normflows/normflows/nn_models.py:41-84)
  * as used by src/learning_mnist.py:60-73, and its reverse pass (the autograd tape replay of
@@ -321,6 +338,12 @@ int nf_bernoulli_ll_f32(const float* x, const float* p, int64_t count, float log
                         float* out_sum, float* g_p, float* workspace, void* stream);
 int nf_bernoulli_ll_f64(const double* x, const double* p, int64_t count, double log_eps, double g_scale,
                         double* out_sum, double* g_p, double* workspace, void* stream);
+
+/* nf_bernoulli_ll_* with the upstream scalar dF/d out_sum read from device memory (g_scale_dev[0]): no host round trip. */
+int nf_bernoulli_ll_dev_f32(const float* x, const float* p, int64_t count, float log_eps, const float* g_scale_dev,
+                            float* out_sum, float* g_p, float* workspace, void* stream);
+int nf_bernoulli_ll_dev_f64(const double* x, const double* p, int64_t count, double log_eps, const double* g_scale_dev,
+                            double* out_sum, double* g_p, double* workspace, void* stream);
 
 /* Tensor-core GEMM used by the MLP entry points above, exposed for testing and reuse:
  *   C[m][n] = act( sum_k A[m][k] B[n][k] + bias[n] ),  A: [M][K] (lda), B: [N][K] (ldb), float32.

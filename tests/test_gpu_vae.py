@@ -256,3 +256,50 @@ def test_optimize_runs_and_decreases_free_energy(tmp_path, monkeypatch):
     after = np.mean([obj(np.concatenate([phi, theta]), 59) for _ in range(4)])
     assert np.isfinite(after) and after < before
     assert (tmp_path / 'free_energy.txt').read_text().startswith(f'\n{K} flows: ')
+
+
+def test_device_adam_loop_equals_host_adam_loop(tmp_path, monkeypatch):
+    """optimize() keeps parameters, Adam moments and the update on the device (nf_adam_step).  In float64 its result
+    after 25 iterations equals autograd.misc.optimizers.adam(gradient, init, ...) driven from the host on the same
+    mini-batches and the same z0 draws (optimization.py:118), to 1e-10."""
+    from autograd.misc.optimizers import adam
+    from normflows import optimization
+    K, D, T, Bsz = 2, 8, 25, 64
+    encoder, decoder, encode, decode, unpack_params, logp = _mnist_closures(K, D)
+    X = (np.random.RandomState(2).rand(256, 784) < 0.13).astype(int)
+    init = np.random.RandomState(3).randn(encoder.D + decoder.D) * 0.05
+    monkeypatch.setattr(optimization, 'results', tmp_path)
+    monkeypatch.setenv('NORMFLOWS_PRECISION', 'fp64')
+    np.random.seed(0)
+    optimization.rs = np.random.RandomState(0)
+    F = optimization.make_free_energy(logp, X, D, K, encode, decode, T, Bsz)
+    _, gradient = optimization.gradient_create(F, D, 256, unpack_params)
+    x_host = adam(gradient, init, step_size=1e-3, num_iters=T)
+    np.random.seed(0)
+    optimization.rs = np.random.RandomState(0)
+    phi, theta = optimization.optimize(logp, X, D, K, 256, init, unpack_params, encode, decode, T, Bsz, 1e-3, verbose=False)
+    x_dev = np.concatenate([phi, theta])
+    assert np.abs(x_host - init).max() > 1e-3
+    assert np.abs(x_dev - x_host).max() <= 1e-10 * max(1.0, np.abs(x_host).max()), np.abs(x_dev - x_host).max()
+
+
+def test_free_energy_with_device_side_draws():
+    """make_free_energy(device_rng=seed): z0 drawn on the device (opt-in, not the reference's stream).  Same seed, same
+    value; the value is a plausible free energy of the same model (close to the host-draw value at the same parameters)."""
+    from normflows import optimization
+    K, D, Bsz = 4, 8, 512
+    encoder, decoder, encode, decode, unpack_params, logp = _mnist_closures(K, D)
+    X = (np.random.RandomState(2).rand(Bsz, 784) < 0.13).astype(np.float64)
+    params = np.random.RandomState(3).randn(encoder.D + decoder.D) * 0.05
+    vals = []
+    for rep in range(2):
+        F = optimization.make_free_energy(logp, X, D, K, encode, decode, 100, Bsz, dtype=torch.float64, batch_iter=lambda tt: X, device_rng=7)
+        objective, gradient = optimization.gradient_create(F, D, Bsz, unpack_params, dtype=torch.float64)
+        vals.append(objective(params, 50))
+        g = gradient(params, 50)
+        assert np.isfinite(g).all() and np.abs(g).max() > 0
+    assert vals[0] == vals[1]
+    optimization.rs = np.random.RandomState(0)
+    F = optimization.make_free_energy(logp, X, D, K, encode, decode, 100, Bsz, dtype=torch.float64, batch_iter=lambda tt: X)
+    host = optimization.gradient_create(F, D, Bsz, unpack_params, dtype=torch.float64)[0](params, 50)
+    assert abs(vals[0] - host) <= 0.05 * abs(host)

@@ -35,6 +35,6 @@ def run(tag, K=32, N=1 << 20, steps=100, target='p1'):
 
 if __name__ == '__main__':
     K = os.environ.get('SWEEP_K', '32')
-    for cfg in os.environ.get('SWEEP', '16,6,4;12,8,4;12,6,4;24,4,2;20,4,2;16,4,4;16,8,4;8,6,4;12,4,2;off').split(';'):
+    for cfg in os.environ.get('SWEEP', 'default;16,6,4,0;14,8,4,2;16,8,4,2;12,8,4,2;off').split(';'):
         for lg, steps in ((20, 100), (24, 10)):
             subprocess.run([sys.executable, os.path.join(ROOT, 'tools', 'one.py'), cfg, K, str(lg), str(steps)])

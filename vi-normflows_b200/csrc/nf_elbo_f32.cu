@@ -22,6 +22,8 @@ size_t nf_planar_elbo_workspace_bytes_n(int64_t N, int K, int D, int elem_size) 
         const size_t g = nf::gram_workspace_bytes(N, D, K);
         if (g > need) need = g;
     }
+    // packed-pair kernel: room behind the rows for the L2-resident part of the tanh history (8 samples per thread)
+    if (need && nf::pair_applicable((size_t)elem_size, true, N, D, K)) need = ((need + 255) & ~(size_t)255) + nf::pair_stash_bytes_max(K);
     return need;
 }
 
@@ -61,7 +63,7 @@ int nf_planar_elbo_fwd_bwd_exchange_f32(const float* eps, int64_t N, int D, int 
     float *g_w = out + 3, *g_s = g_w + K * D, *g_b = g_s + K * D, *g_c = g_b + K;
     bool exchanged = false;
     rc = nf::elbo_fused<float>(true, eps, N, D, K, w, s, b, c, target_id, target_params, n_target_params, log_eps, out, g_w, g_s, g_b,
-                               g_c, reinterpret_cast<float*>(workspace), (cudaStream_t)stream, &ar, &exchanged);
+                               g_c, reinterpret_cast<float*>(workspace), (cudaStream_t)stream, &ar, &exchanged, nullptr, workspace_bytes);
     if (rc != NF_OK || exchanged) return rc;
     return nf::launch_allreduce_small(ar, out, out, nvec, nullptr, (cudaStream_t)stream);
 }
@@ -80,7 +82,7 @@ int nf_planar_elbo_fwd_bwd_rng_f32(uint64_t seed, uint64_t step, int64_t N, int 
     if (workspace_bytes < nf_planar_elbo_workspace_bytes(K, D, 4)) return NF_ERR_WORKSPACE;
     const nf::RngDesc rng = {seed, step};
     return nf::elbo_fused<float>(true, nullptr, N, D, K, w, s, b, c, target_id, target_params, n_target_params, log_eps, out_F, g_w,
-                                 g_s, g_b, g_c, reinterpret_cast<float*>(workspace), (cudaStream_t)stream, nullptr, nullptr, &rng);
+                                 g_s, g_b, g_c, reinterpret_cast<float*>(workspace), (cudaStream_t)stream, nullptr, nullptr, &rng, workspace_bytes);
 }
 
 // ---- host-buffer sessions (see nfcore.h) ----

@@ -526,7 +526,8 @@ bool pair_applicable(size_t elem, bool bwd, long long N, int D, int K);
 int pair_elbo(int tgt, const float* eps, long long N, int D, int K, const float* w, const float* s, const float* b,
               const float* c, const float* tp, int ntp, float epsv, float* partials, pr::SyncHeader* sync,
               float* out_F, float* g_w, float* g_s, float* g_b, float* g_c, int* nb, cudaStream_t st, const pr::ArDesc& ar,
-              const RngDesc& rng);
+              const RngDesc& rng, void* stash, size_t stash_bytes);
+size_t pair_stash_bytes_max(int K);        // room for the L2-resident part of the tanh history (nf_elbo_pair_launch.cuh)
 static inline RngDesc no_rng() { RngDesc r = {0, 0}; return r; }
 static inline pr::ArDesc no_exchange() { pr::ArDesc a = {}; return a; }
 // nf_allreduce.cu
@@ -712,7 +713,7 @@ static int elbo_main(bool bwd, const T* eps, int64_t N, int D, int K, const T* w
     if constexpr (sizeof(T) == 4) {
         if (pair_applicable(sizeof(T), bwd, N, D, K))
             return pair_elbo(target_id, eps, N, D, K, w, s, b, c, tparams, ntp, epsv, partials, nullptr, nullptr, nullptr, nullptr,
-                             nullptr, nullptr, nrows, stream, no_exchange(), no_rng());
+                             nullptr, nullptr, nrows, stream, no_exchange(), no_rng(), nullptr, 0);
     }
     switch (D) {
         case 1: return dispatch_target<T, 1>(target_id, bwd, eps, N, K, w, s, b, c, tparams, ntp, epsv, partials, max_blocks, nrows, stream);
@@ -745,7 +746,9 @@ static int elbo_finish(bool bwd, const T* partials, int nrows, int D, int K, T* 
 template <typename T>
 static int elbo_fused(bool bwd, const T* eps, int64_t N, int D, int K, const T* w, const T* s, const T* b, const T* c,
                       int target_id, const T* tparams, int ntp, T epsv, T* out_F, T* g_w, T* g_s, T* g_b, T* g_c, T* partials,
-                      cudaStream_t stream, const pr::ArDesc* ar = nullptr, bool* exchanged = nullptr, const RngDesc* rng = nullptr) {
+                      cudaStream_t stream, const pr::ArDesc* ar = nullptr, bool* exchanged = nullptr, const RngDesc* rng = nullptr,
+                      size_t ws_bytes = 0 /* size of the workspace `partials` points to, when known: what lies beyond
+                                             nf_planar_elbo_workspace_bytes() may hold part of the tanh history */) {
     int nb = 0;
     if (exchanged) *exchanged = false;
     if constexpr (sizeof(T) == 4) {
@@ -755,8 +758,10 @@ static int elbo_fused(bool bwd, const T* eps, int64_t N, int D, int K, const T* 
             unsigned char* base = reinterpret_cast<unsigned char*>(partials);
             pr::SyncHeader* sync = reinterpret_cast<pr::SyncHeader*>(base + nf_planar_elbo_workspace_bytes(K, D, 4) - kSyncHeaderBytes);
             if (exchanged) *exchanged = ar != nullptr;        // the last block also does the exchange
+            const size_t min_bytes = (nf_planar_elbo_workspace_bytes(K, D, 4) + 255) & ~(size_t)255;
+            void* stash = ws_bytes > min_bytes ? base + min_bytes : nullptr;
             return pair_elbo(target_id, eps, N, D, K, w, s, b, c, tparams, ntp, epsv, partials, sync, out_F, g_w, g_s, g_b, g_c, &nb, stream,
-                             ar ? *ar : no_exchange(), rng ? *rng : no_rng());
+                             ar ? *ar : no_exchange(), rng ? *rng : no_rng(), stash, stash ? ws_bytes - min_bytes : 0);
         }
     }
     int rc = elbo_main<T>(bwd, eps, N, D, K, w, s, b, c, target_id, tparams, ntp, epsv, partials, &nb, stream);
@@ -777,7 +782,8 @@ static int elbo_entry(const T* eps, int64_t N, int D, int K, const T* w, const T
     if (rc != NF_OK) return rc;
     if (workspace_bytes < nf_planar_elbo_workspace_bytes(K, D, (int)sizeof(T))) return NF_ERR_WORKSPACE;
     T* partials = reinterpret_cast<T*>(workspace);
-    return elbo_fused<T>(all_g, eps, N, D, K, w, s, b, c, target_id, tparams, ntp, epsv, out_F, g_w, g_s, g_b, g_c, partials, stream);
+    return elbo_fused<T>(all_g, eps, N, D, K, w, s, b, c, target_id, tparams, ntp, epsv, out_F, g_w, g_s, g_b, g_c, partials, stream,
+                         nullptr, nullptr, nullptr, workspace_bytes);
 }
 
 // ---- host-buffer session: H2D of the samples overlapped with the objective kernel -------------
@@ -1098,7 +1104,7 @@ static int script_train(const T* eps_all, int64_t n_iters, int64_t N, int D, int
             continue;
         }
         rc = elbo_fused<T>(true, eps_it, N, D, K, w, s, b, c, target_id, tparams, ntp, epsv, res, res + 3, res + 3 + K * D,
-                           res + 3 + 2 * K * D, res + 3 + 2 * K * D + K, rows, st);
+                           res + 3 + 2 * K * D, res + 3 + 2 * K * D + K, rows, st, nullptr, nullptr, nullptr, workspace_bytes - head);
         if (rc != NF_OK) return rc;
     }
     return NF_OK;

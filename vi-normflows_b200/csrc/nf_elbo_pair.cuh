@@ -13,7 +13,9 @@
 //     The samples are dealt in rounds of SMAX per thread plus one shorter round, so that every warp of
 //     the grid does the same amount of work for any N (no tail wave);
 //   * tanh history: the first ST samples of a thread in tensor memory (tcgen05.st/ld, fetched one layer
-//     ahead), the rest in shared memory as 64-bit pairs;
+//     ahead), the next ones in shared memory as 64-bit pairs, and -- when the caller's workspace has room for
+//     it (nf_planar_elbo_workspace_bytes_n) -- the last SG in an L2-resident slice of global memory, fetched
+//     one layer ahead as well: 8 samples per thread at K = 32, so 2^20 samples take two rounds instead of three;
 //   * the 2D+2 gradient partials of a layer go to a per-warp staging area in shared memory (one store per value,
 //     nothing waits on it); after every fourth layer the lanes of the warp each add up one staged row (one value of one
 //     layer over the 32 lanes: eight 128-bit loads, rows padded so that the loads do not collide) into the warp's
@@ -176,21 +178,25 @@ __host__ __device__ inline u64 cookie_for(const void* p) { return 0x6e66636f7265
 // tuning aid (flags bit 1): per-block phase timestamps (globaltimer, ns): entry, set-up done, samples done, row
 // written and ticket taken, finalize done (last block only; 0 elsewhere), and the SM the block ran on
 // One round of one warp: S samples per thread (S/2 pairs) through all K layers and back.
-template <int D, int S, int SMAX, int ST, int NT, int TGT, bool MASKED>
+template <int D, int S, int SMAX, int ST, int SG, int NT, int TGT, bool MASKED>
 __device__ __forceinline__ void pair_tile(const float* __restrict__ eps, long long n0, long long N, int K,
                                           const float* __restrict__ lcf, const float* __restrict__ lcb,
                                           const float* __restrict__ tp, int ntp, float epsv,
                                           u64* __restrict__ hist_t, uint32_t taddr, float* __restrict__ acc_w, int lane,
                                           float* __restrict__ stg_w /* staging area of this warp */, float& sum_q, float& sum_p,
-                                          const RngDesc& rng /* eps == NULL: the samples are drawn here (nf_philox.cuh) */) {
+                                          const RngDesc& rng /* eps == NULL: the samples are drawn here (nf_philox.cuh) */,
+                                          u64* __restrict__ gst_t /* this thread's column of the global-memory history [K][SG/2][NT] */) {
     using M = Mth<float>;
     constexpr int V = 2 * D + 2;
     constexpr int P = S / 2;                        // pairs this round
     constexpr int STP = ST / 2;                     // pairs per thread that tensor memory can hold
     constexpr int PT = P < STP ? P : STP;           // pairs of this round whose history goes to tensor memory
-    constexpr int SSP = (SMAX - ST) / 2;            // shared-memory pair slots per thread and layer
+    constexpr int SSP = (SMAX - ST - SG) / 2;       // shared-memory pair slots per thread and layer
+    constexpr int SGP = SG / 2;                     // global-memory (L2-resident) pair slots per thread and layer
+    constexpr int PS = (P - PT) < SSP ? (P - PT) : SSP;      // pairs of this round in shared memory
+    constexpr int PG = P - PT - PS;                          // ... and in global memory
     constexpr int RF = 2 * recf_pairs<D>(), RB = 2 * recb_pairs<D>();
-    static_assert(S % 2 == 0 && S <= SMAX && P - PT <= SSP, "round size");
+    static_assert(S % 2 == 0 && S <= SMAX && PG <= SGP, "round size");
     const float LOG2PI = 1.8378770664093453f;
     const u64 one2 = pk(1.0f, 1.0f), mone2 = pk(-1.0f, -1.0f), mtwo2 = pk(-2.0f, -2.0f);
     const u64 nln2 = pk(-0.6931471805599453f, -0.6931471805599453f);
@@ -274,7 +280,8 @@ __device__ __forceinline__ void pair_tile(const float* __restrict__ eps, long lo
 #pragma unroll
             for (int d = 0; d < D; ++d) z[p][d] = fma2(rf[D + 1 + d], t, z[p][d]);
             if (p < PT) upk(t, tt[2 * p], tt[2 * p + 1]);
-            else hist_t[(k * SSP + (p - PT)) * NT] = t;
+            else if (p < PT + PS) hist_t[(k * SSP + (p - PT)) * NT] = t;
+            else gst_t[(size_t)(k * SGP + (p - PT - PS)) * NT] = t;
         }
         if (PT > 0) Tm<2 * (PT > 0 ? PT : 1)>::st(taddr + k * ST, tt);
     }
@@ -301,15 +308,22 @@ __device__ __forceinline__ void pair_tile(const float* __restrict__ eps, long lo
     // Layer k+1's partials are merged (pair halves added) at the end of its iteration and reduced across the warp
     // inside iteration k, next to arithmetic they do not depend on.  History held in tensor memory is fetched one
     // layer ahead; the loop is unrolled by two so that the prefetch buffers alternate instead of being copied.
-    constexpr int NTV = 2 * (PT > 0 ? PT : 1);
+    constexpr int NTV = 2 * (PT > 0 ? PT : 1), NGV = PG > 0 ? PG : 1;
     float ta[NTV], tb[NTV];
+    u64 ga_[NGV], gb_[NGV];                                       // global-memory history, fetched one layer ahead like ta / tb
     float* const stg_wr = stg_w + lane;                           // lane's column of the staged rows
     const float* const stg_rd = stg_w + lane * kStagePitch;       // the row this lane adds up (lane < kStageLayers * V)
     if (PT > 0) Tm<NTV>::ld(taddr + (K - 1) * ST, ta);
-    auto layer = [&](int k, float (&tc)[NTV], float (&tn)[NTV]) {
+#pragma unroll
+    for (int i = 0; i < PG; ++i) ga_[i] = __ldcg(gst_t + (size_t)((K - 1) * SGP + i) * NT);
+    auto layer = [&](int k, float (&tc)[NTV], float (&tn)[NTV], u64 (&gc)[NGV], u64 (&gn)[NGV]) {
         if (PT > 0) {
             tm_wait_ld();
             if (k > 0) Tm<NTV>::ld(taddr + (k - 1) * ST, tn);
+        }
+        if (PG > 0 && k > 0) {
+#pragma unroll
+            for (int i = 0; i < PG; ++i) gn[i] = __ldcg(gst_t + (size_t)((k - 1) * SGP + i) * NT);
         }
         u64 rb[RB / 2];
         {
@@ -321,7 +335,8 @@ __device__ __forceinline__ void pair_tile(const float* __restrict__ eps, long lo
         u64 v[V];                                   // the first pair starts the per-layer sums (no zero fill)
 #pragma unroll
         for (int p = 0; p < P; ++p) {
-            const u64 t = (p < PT) ? pk(tc[p < PT ? 2 * p : 0], tc[p < PT ? 2 * p + 1 : 0]) : hist_t[(k * SSP + (p - PT)) * NT];
+            const u64 t = (p < PT) ? pk(tc[p < PT ? 2 * p : 0], tc[p < PT ? 2 * p + 1 : 0])
+                          : ((p < PT + PS) ? hist_t[(k * SSP + (p - PT)) * NT] : gc[(p >= PT + PS) ? p - PT - PS : 0]);
 #pragma unroll
             for (int d = 0; d < D; ++d) z[p][d] = fma2(rb[d], t, z[p][d]);        // z_{k-1} = z_k - s_k t_k
             const u64 nhp = fma2(t, t, mone2);                                     // -(1 - t^2)
@@ -381,10 +396,10 @@ __device__ __forceinline__ void pair_tile(const float* __restrict__ eps, long lo
     };
     int k = K - 1;
     for (; k >= 1; k -= 2) {
-        layer(k, ta, tb);
-        layer(k - 1, tb, ta);
+        layer(k, ta, tb, ga_, gb_);
+        layer(k - 1, tb, ta, gb_, ga_);
     }
-    if (k == 0) layer(0, ta, tb);
+    if (k == 0) layer(0, ta, tb, ga_, gb_);
 #pragma unroll
     for (int p = 0; p < P; ++p) {
         float a, b;
@@ -393,7 +408,7 @@ __device__ __forceinline__ void pair_tile(const float* __restrict__ eps, long lo
     }
 }
 
-template <int D, int NW, int SMAX, int ST, int TGT>
+template <int D, int NW, int SMAX, int ST, int SG, int TGT>
 __global__ void __launch_bounds__(NW * 32, 1)
 elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float* __restrict__ w,
                  const float* __restrict__ s, const float* __restrict__ b, const float* __restrict__ c,
@@ -401,13 +416,13 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
                  SyncHeader* __restrict__ sync /* NULL: rows only, the caller sums them */, float* __restrict__ out_F,
                  float* __restrict__ g_w, float* __restrict__ g_s, float* __restrict__ g_b, float* __restrict__ g_c,
                  int flags /* tuning: bit 0 = no rotation of the rounds */, unsigned long long* __restrict__ stamps /* [256][8] or NULL */,
-                 const ArDesc ar, const RngDesc rng) {
+                 const ArDesc ar, const RngDesc rng, u64* __restrict__ gstash /* [gridDim.x][K][SG/2][NT] pairs, or NULL when SG == 0 */) {
     using M = Mth<float>;
     constexpr int NT = NW * 32;
     constexpr int V = 2 * D + 2;
     constexpr int RF = 2 * recf_pairs<D>(), RB = 2 * recb_pairs<D>();
-    constexpr int SSP = (SMAX - ST) / 2;
-    static_assert(NW % 4 == 0 && SMAX % 2 == 0 && ST % 2 == 0 && ST <= SMAX && (ST == 0 || ST == 2 || ST == 4 || ST == 8), "configuration");
+    constexpr int SSP = (SMAX - ST - SG) / 2;
+    static_assert(SMAX % 2 == 0 && ST % 2 == 0 && SG % 2 == 0 && ST + SG <= SMAX && (ST == 0 || ST == 2 || ST == 4 || ST == 8), "configuration");
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float* sm = reinterpret_cast<float*>(smem_raw);
     const int ntp_s = target_smem_count(TGT, D, ntp);
@@ -424,7 +439,7 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const bool stamp = stamps != nullptr && tid == 0 && blockIdx.x < 256;
     if (stamp) { stamps[blockIdx.x * 8 + 0] = gtime(); stamps[blockIdx.x * 8 + 4] = 0; }
-    const int tmem_cols = tm_columns((NW / 4) * ST * K);
+    const int tmem_cols = tm_columns(((NW + 3) / 4) * ST * K);
     if (ST > 0 && warp == 0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
                          (uint32_t)__cvta_generic_to_shared(&tmem_base_smem)), "r"(tmem_cols) : "memory");
@@ -477,6 +492,7 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
     float* stg_w = sm + L.stg + warp * (kStageLayers * V * kStagePitch);
     if (stamp) stamps[blockIdx.x * 8 + 1] = gtime();
     u64* hist_t = hist + tid;
+    u64* gst_t = SG > 0 ? gstash + (size_t)blockIdx.x * K * (SG / 2) * NT + tid : nullptr;
 
     float sum_q = 0.f, sum_p = 0.f;
     // rounds: every thread of the grid takes SMAX samples per full round and `srem` in the last one
@@ -504,9 +520,9 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
             if (start >= N) continue;
             const long long n0 = start + (long long)lane * SMAX;
             if (start + 32 * SMAX <= N)
-                pair_tile<D, SMAX, SMAX, ST, NT, TGT, false>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p, rng);
+                pair_tile<D, SMAX, SMAX, ST, SG, NT, TGT, false>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p, rng, gst_t);
             else
-                pair_tile<D, SMAX, SMAX, ST, NT, TGT, true>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p, rng);
+                pair_tile<D, SMAX, SMAX, ST, SG, NT, TGT, true>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p, rng, gst_t);
             continue;
         }
         const long long start = nfull * T * SMAX + gw * 32 * srem;
@@ -515,8 +531,8 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
             const bool full = start + 32LL * srem <= N;
 #define NF_PR_REM(S_)                                                                                                        \
     if (SMAX > S_ && srem == S_) {                                                                                           \
-        if (full) pair_tile<D, (S_ < SMAX ? S_ : 2), SMAX, ST, NT, TGT, false>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p, rng); \
-        else pair_tile<D, (S_ < SMAX ? S_ : 2), SMAX, ST, NT, TGT, true>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p, rng);      \
+        if (full) pair_tile<D, (S_ < SMAX ? S_ : 2), SMAX, ST, SG, NT, TGT, false>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p, rng, gst_t); \
+        else pair_tile<D, (S_ < SMAX ? S_ : 2), SMAX, ST, SG, NT, TGT, true>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p, rng, gst_t);      \
     }
             NF_PR_REM(2)
             NF_PR_REM(4)

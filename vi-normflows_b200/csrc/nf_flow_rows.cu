@@ -151,7 +151,8 @@ template <typename T, int DPL>
 __global__ void __launch_bounds__(kRowThreads)
 amortised_bwd_kernel(const T* __restrict__ z0, const T* __restrict__ ls0,
                      const T* __restrict__ W, const T* __restrict__ U,
-                     const T* __restrict__ zK, const T* __restrict__ tsave, const T* __restrict__ g_zK, T g_ld,
+                     const T* __restrict__ zK, const T* __restrict__ tsave, const T* __restrict__ g_zK, T g_ld_all,
+                     const T* __restrict__ g_ld_vec /* dF/dlogdet[n] per sample, or NULL: g_ld_all for every n */,
                      long long N, int D, int K, T epsv,
                      T* __restrict__ g_mu0, T* __restrict__ g_ls0, T* __restrict__ g_W, T* __restrict__ g_U,
                      T* __restrict__ g_Bb) {
@@ -163,6 +164,7 @@ amortised_bwd_kernel(const T* __restrict__ z0, const T* __restrict__ ls0,
         T zr[DPL], gz[DPL], wr[DPL], ur[DPL];
         load_row<T, DPL>(zK + n * D, D, lane, zr);
         load_row<T, DPL>(g_zK + n * D, D, lane, gz);
+        const T g_ld = g_ld_vec ? g_ld_vec[n] : g_ld_all;
         for (int k = K - 1; k >= 0; --k) {
             const size_t off = ((size_t)k * N + n) * D;
             load_row<T, DPL>(W + off, D, lane, wr);
@@ -268,15 +270,15 @@ static int amortised_fwd_entry(const T* z0, const T* mu0, const T* ls0, const T*
 
 template <typename T>
 static int amortised_bwd_entry(const T* z0, const T* ls0, const T* W, const T* U, const T* zK, const T* tsave,
-                               const T* g_zK, T g_ld, int64_t N, int D, int K, T epsv, T* g_mu0, T* g_ls0, T* g_W,
-                               T* g_U, T* g_Bb, void* stream_) {
+                               const T* g_zK, T g_ld, const T* g_ld_vec, int64_t N, int D, int K, T epsv, T* g_mu0, T* g_ls0,
+                               T* g_W, T* g_U, T* g_Bb, void* stream_) {
     if (N < 0 || D < 1 || K < 0) return NF_ERR_INVALID;
     if (N > 0 && (!z0 || !ls0 || !zK || !g_zK || !g_mu0 || !g_ls0)) return NF_ERR_INVALID;
     if (N > 0 && K > 0 && (!W || !U || !tsave || !g_W || !g_U || !g_Bb)) return NF_ERR_INVALID;
     if (N == 0) return NF_OK;
     cudaStream_t st = (cudaStream_t)stream_;
     NF_DPL_DISPATCH(D, (amortised_bwd_kernel<T, DPL><<<rows_grid(N), kRowThreads, 0, st>>>(
-                           z0, ls0, W, U, zK, tsave, g_zK, g_ld, N, D, K, epsv, g_mu0, g_ls0, g_W, g_U, g_Bb)));
+                           z0, ls0, W, U, zK, tsave, g_zK, g_ld, g_ld_vec, N, D, K, epsv, g_mu0, g_ls0, g_W, g_U, g_Bb)));
     NF_CUDA_OK(cudaGetLastError());
     return NF_OK;
 }
@@ -309,14 +311,30 @@ int nf_planar_amortised_bwd_f32(const float* z0, const float* log_sigma0, const 
                                 const float* zK, const float* t_save, const float* g_zK, float g_logdet,
                                 int64_t N, int D, int K, float log_eps, float* g_mu0, float* g_log_sigma0,
                                 float* g_W, float* g_U, float* g_Bb, void* stream) {
-    return nf::amortised_bwd_entry<float>(z0, log_sigma0, W, U, zK, t_save, g_zK, g_logdet, N, D, K, log_eps, g_mu0,
+    return nf::amortised_bwd_entry<float>(z0, log_sigma0, W, U, zK, t_save, g_zK, g_logdet, nullptr, N, D, K, log_eps, g_mu0,
+                                          g_log_sigma0, g_W, g_U, g_Bb, stream);
+}
+int nf_planar_amortised_bwd_v_f32(const float* z0, const float* log_sigma0, const float* W, const float* U,
+                                  const float* zK, const float* t_save, const float* g_zK, const float* g_logdet_vec,
+                                  int64_t N, int D, int K, float log_eps, float* g_mu0, float* g_log_sigma0,
+                                  float* g_W, float* g_U, float* g_Bb, void* stream) {
+    if (N > 0 && !g_logdet_vec) return NF_ERR_INVALID;
+    return nf::amortised_bwd_entry<float>(z0, log_sigma0, W, U, zK, t_save, g_zK, 0.f, g_logdet_vec, N, D, K, log_eps, g_mu0,
                                           g_log_sigma0, g_W, g_U, g_Bb, stream);
 }
 int nf_planar_amortised_bwd_f64(const double* z0, const double* log_sigma0, const double* W, const double* U,
                                 const double* zK, const double* t_save, const double* g_zK, double g_logdet,
                                 int64_t N, int D, int K, double log_eps, double* g_mu0, double* g_log_sigma0,
                                 double* g_W, double* g_U, double* g_Bb, void* stream) {
-    return nf::amortised_bwd_entry<double>(z0, log_sigma0, W, U, zK, t_save, g_zK, g_logdet, N, D, K, log_eps, g_mu0,
+    return nf::amortised_bwd_entry<double>(z0, log_sigma0, W, U, zK, t_save, g_zK, g_logdet, nullptr, N, D, K, log_eps, g_mu0,
+                                           g_log_sigma0, g_W, g_U, g_Bb, stream);
+}
+int nf_planar_amortised_bwd_v_f64(const double* z0, const double* log_sigma0, const double* W, const double* U,
+                                  const double* zK, const double* t_save, const double* g_zK, const double* g_logdet_vec,
+                                  int64_t N, int D, int K, double log_eps, double* g_mu0, double* g_log_sigma0,
+                                  double* g_W, double* g_U, double* g_Bb, void* stream) {
+    if (N > 0 && !g_logdet_vec) return NF_ERR_INVALID;
+    return nf::amortised_bwd_entry<double>(z0, log_sigma0, W, U, zK, t_save, g_zK, 0.0, g_logdet_vec, N, D, K, log_eps, g_mu0,
                                            g_log_sigma0, g_W, g_U, g_Bb, stream);
 }
 

@@ -420,9 +420,11 @@ static int mlp_backward_tc(const float* wts, const float* x, MlpDims d, int hidd
 // ---- Bernoulli log-likelihood: sum x log(eps+p) + (1-x) log(eps+1-p), and d/dp ------------------
 template <typename T>
 __global__ void __launch_bounds__(256)
-bernoulli_kernel(const T* __restrict__ x, const T* __restrict__ p, long long count, T epsv, T g_scale,
+bernoulli_kernel(const T* __restrict__ x, const T* __restrict__ p, long long count, T epsv, T g_scale_host,
+                 const T* __restrict__ g_scale_dev /* upstream scalar in device memory, or NULL */,
                  T* __restrict__ partial, T* __restrict__ g_p) {
     using M = Mth<T>;
+    const T g_scale = g_scale_dev ? g_scale_dev[0] * g_scale_host : g_scale_host;
     T s = (T)0;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x) {
         const T xv = x[i], pv = p[i];
@@ -451,10 +453,11 @@ __global__ void bernoulli_final_kernel(const T* __restrict__ partial, int n, T* 
 constexpr int kBernBlocks = 592;
 
 template <typename T>
-static int bernoulli_entry(const T* x, const T* p, long long count, T epsv, T g_scale, T* out, T* g_p, T* ws, cudaStream_t st) {
+static int bernoulli_entry(const T* x, const T* p, long long count, T epsv, T g_scale, T* out, T* g_p, T* ws, cudaStream_t st,
+                           const T* g_scale_dev = nullptr) {
     if (count < 0 || !out || !ws || (count > 0 && (!x || !p))) return NF_ERR_INVALID;
     const int blocks = (int)max(1LL, min((long long)kBernBlocks, (count + 255) / 256));
-    bernoulli_kernel<T><<<blocks, 256, 0, st>>>(x, p, count, epsv, g_scale, ws, g_p);
+    bernoulli_kernel<T><<<blocks, 256, 0, st>>>(x, p, count, epsv, g_scale, g_scale_dev, ws, g_p);
     NF_CUDA_OK(cudaGetLastError());
     bernoulli_final_kernel<T><<<1, 32, 0, st>>>(ws, blocks, out);
     NF_CUDA_OK(cudaGetLastError());
@@ -501,6 +504,16 @@ size_t nf_bernoulli_workspace_bytes(int elem_size) { return (size_t)nf::kBernBlo
 int nf_bernoulli_ll_f32(const float* x, const float* p, int64_t count, float log_eps, float g_scale, float* out_sum,
                         float* g_p, float* workspace, void* stream) {
     return nf::bernoulli_entry<float>(x, p, count, log_eps, g_scale, out_sum, g_p, workspace, (cudaStream_t)stream);
+}
+int nf_bernoulli_ll_dev_f32(const float* x, const float* p, int64_t count, float log_eps, const float* g_scale_dev, float* out_sum,
+                            float* g_p, float* workspace, void* stream) {
+    if (!g_scale_dev) return NF_ERR_INVALID;
+    return nf::bernoulli_entry<float>(x, p, count, log_eps, 1.f, out_sum, g_p, workspace, (cudaStream_t)stream, g_scale_dev);
+}
+int nf_bernoulli_ll_dev_f64(const double* x, const double* p, int64_t count, double log_eps, const double* g_scale_dev, double* out_sum,
+                            double* g_p, double* workspace, void* stream) {
+    if (!g_scale_dev) return NF_ERR_INVALID;
+    return nf::bernoulli_entry<double>(x, p, count, log_eps, 1.0, out_sum, g_p, workspace, (cudaStream_t)stream, g_scale_dev);
 }
 int nf_bernoulli_ll_f64(const double* x, const double* p, int64_t count, double log_eps, double g_scale, double* out_sum,
                         double* g_p, double* workspace, void* stream) {

@@ -54,6 +54,11 @@ PROTOTYPES = {
     'nf_planar_amortised_fwd_f64': (c_int, [c_void_p] * 6 + [c_int64, c_int, c_int, c_double] + [c_void_p] * 4),
     'nf_planar_amortised_bwd_f32': (c_int, [c_void_p] * 7 + [c_float, c_int64, c_int, c_int, c_float] + [c_void_p] * 6),
     'nf_planar_amortised_bwd_f64': (c_int, [c_void_p] * 7 + [c_double, c_int64, c_int, c_int, c_double] + [c_void_p] * 6),
+    'nf_planar_amortised_bwd_v_f32': (c_int, [c_void_p] * 8 + [c_int64, c_int, c_int, c_float] + [c_void_p] * 6),
+    'nf_planar_amortised_bwd_v_f64': (c_int, [c_void_p] * 8 + [c_int64, c_int, c_int, c_double] + [c_void_p] * 6),
+    'nf_adam_step': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int64, c_double, c_double, c_double, c_double, c_int64, c_void_p]),
+    'nf_bernoulli_ll_dev_f32': (c_int, [c_void_p, c_void_p, c_int64, c_float] + [c_void_p] * 5),
+    'nf_bernoulli_ll_dev_f64': (c_int, [c_void_p, c_void_p, c_int64, c_double] + [c_void_p] * 5),
     'nf_mlp_param_count': (c_int64, [c_int] * 4),
     'nf_mlp_forward_workspace_bytes': (c_size_t, [c_int64] + [c_int] * 6),
     'nf_mlp_backward_workspace_bytes': (c_size_t, [c_int64] + [c_int] * 5),

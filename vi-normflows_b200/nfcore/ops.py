@@ -109,7 +109,7 @@ def planar_elbo_exchange(eps, w, s, b, c, target, target_params, log_eps, out_ve
     tid = TARGET_IDS[target] if isinstance(target, str) else int(target)
     ntp = 0 if target_params is None else target_params.numel()
     dev = eps.device
-    ws = _workspace(K, D, torch.float32, dev, 0)
+    ws = _workspace(K, D, torch.float32, dev, N)
     with torch.cuda.device(dev):
         stream = torch.cuda.current_stream(dev).cuda_stream
         rc = lib.nf_planar_elbo_fwd_bwd_exchange_f32(_ptr(eps), N, D, K, _ptr(w), _ptr(s), _ptr(b), _ptr(c), tid, _ptr(target_params), ntp,
@@ -184,7 +184,7 @@ def planar_elbo_rng(seed, step, N, w, s, b, c, target, target_params=None, log_e
                torch.empty(K, D, dtype=torch.float32, device=dev), torch.empty(K, dtype=torch.float32, device=dev),
                torch.empty(K, dtype=torch.float32, device=dev))
     out_F, g_w, g_s, g_b, g_c = out
-    ws = _workspace(K, D, torch.float32, dev, 0)
+    ws = _workspace(K, D, torch.float32, dev, N)
     with torch.cuda.device(dev):
         stream = torch.cuda.current_stream(dev).cuda_stream
         rc = lib.nf_planar_elbo_fwd_bwd_rng_f32(ctypes.c_uint64(seed), ctypes.c_uint64(step), N, D, K, _ptr(w), _ptr(s), _ptr(b), _ptr(c), tid,
@@ -251,14 +251,32 @@ def amortised_backward(z0, ls0, W, U, zK, tsave, g_zK, g_logdet, log_eps=1e-7):
     g_W, g_U = torch.empty_like(W), torch.empty_like(U)
     g_B = torch.empty(K, N, dtype=dtype, device=dev)
     creal = _DT[dtype][2]
-    fn = getattr(lib, 'nf_planar_amortised_bwd_' + _DT[dtype][0])
+    vec = isinstance(g_logdet, torch.Tensor)         # per-sample dF/dlogdet in device memory: no host round trip
+    if vec:
+        g_logdet = g_logdet.detach().to(dtype).reshape(N).contiguous()
+    fn = getattr(lib, 'nf_planar_amortised_bwd_' + ('v_' if vec else '') + _DT[dtype][0])
     with torch.cuda.device(dev):
         st = torch.cuda.current_stream(dev).cuda_stream
-        rc = fn(_ptr(z0), _ptr(ls0), _ptr(W), _ptr(U), _ptr(zK), _ptr(tsave), _ptr(g_zK), creal(g_logdet),
+        rc = fn(_ptr(z0), _ptr(ls0), _ptr(W), _ptr(U), _ptr(zK), _ptr(tsave), _ptr(g_zK), _ptr(g_logdet) if vec else creal(g_logdet),
                 N, D, K, creal(log_eps), _ptr(g_mu0), _ptr(g_ls0), _ptr(g_W), _ptr(g_U), _ptr(g_B),
                 ctypes.c_void_p(st))
     _lib.check(rc)
     return g_mu0, g_ls0, g_W, g_U, g_B
+
+
+def adam_step(params64, grad, m, v, t, step_size=1e-3, b1=0.9, b2=0.999, eps=1e-8):
+    """nf_adam_step: one Adam update of the float64 master parameters on the device (autograd.misc.optimizers.adam)."""
+    lib = _lib.load()
+    for x in (params64, m, v):
+        if x.dtype != torch.float64 or not x.is_cuda or not x.is_contiguous():
+            raise NFError('adam_step: params, m, v must be contiguous float64 CUDA tensors')
+    grad = grad.contiguous()
+    if grad.dtype not in _DT or grad.numel() != params64.numel():
+        raise NFError('adam_step: gradient of the wrong type or size')
+    with torch.cuda.device(params64.device):
+        st = torch.cuda.current_stream(params64.device).cuda_stream
+        _lib.check(lib.nf_adam_step(_ptr(params64), _ptr(grad), _DT[grad.dtype][1], _ptr(m), _ptr(v), params64.numel(), float(step_size),
+                                    float(b1), float(b2), float(eps), int(t), ctypes.c_void_p(st)))
 
 
 ACT_IDS = {None: 0, 'none': 0, 'identity': 0, 'relu': 1, 'sigmoid': 2, 'rbf': 3}
@@ -306,8 +324,22 @@ def mlp_backward(weights, x, dims, hidden_act, out_act, fwd_ws, out, g_out, need
 
 
 def bernoulli_ll(x, p, log_eps=1e-7, g_scale=None):
-    """nf_bernoulli_ll_*: (sum [1], g_p or None) with g_p = g_scale * d sum / d p."""
+    """nf_bernoulli_ll_*: (sum [1], g_p or None) with g_p = g_scale * d sum / d p.  g_scale may be a Python float or a
+    one-element CUDA tensor (then it is read on the device: nothing synchronises)."""
     lib = _lib.load()
+    if isinstance(g_scale, torch.Tensor):
+        dtype, dev = p.dtype, p.device
+        _same(dtype, dev, x, p)
+        es = _DT[dtype][1]
+        gs = g_scale.detach().to(dtype).reshape(1).contiguous()
+        ws = torch.empty(lib.nf_bernoulli_workspace_bytes(es) // es, dtype=dtype, device=dev)
+        out = torch.empty(1, dtype=dtype, device=dev)
+        g_p = torch.empty_like(p)
+        fn = getattr(lib, 'nf_bernoulli_ll_dev_' + _DT[dtype][0])
+        with torch.cuda.device(dev):
+            st = torch.cuda.current_stream(dev).cuda_stream
+            _lib.check(fn(_ptr(x), _ptr(p), p.numel(), _DT[dtype][2](log_eps), _ptr(gs), _ptr(out), _ptr(g_p), _ptr(ws), ctypes.c_void_p(st)))
+        return out, g_p
     if not p.is_cuda:
         raise NFError('bernoulli_ll needs CUDA tensors (no CPU fallback)')
     dtype, dev = p.dtype, p.device

@@ -49,15 +49,9 @@ class AmortisedFlow(torch.autograd.Function):
         N = z0.shape[0]
         if g_zK is None:
             g_zK = torch.zeros_like(zK)
-        # the kernel takes one scalar for dF/dlogdet[n]; optimization.py:85 averages, so it is uniform
-        if g_logdet is None:
-            g_ld = 0.0
-        else:
-            g_ld = float(g_logdet[0])
-            if N > 1 and not bool(torch.all(g_logdet == g_logdet[0])):
-                raise ops.NFError('AmortisedFlow.backward: dF/dlogdet must be the same for every sample')
-        g_mu0, g_ls0, g_W, g_U, g_B = ops.amortised_backward(z0, ls0, W, U, zK, tsave, g_zK.contiguous(), g_ld,
-                                                              ctx.log_eps)
+        # dF/dlogdet[n] stays on the device (per-sample vector; optimization.py:85 averages, so it is -1/N everywhere)
+        g_ld = 0.0 if g_logdet is None else g_logdet
+        g_mu0, g_ls0, g_W, g_U, g_B = ops.amortised_backward(z0, ls0, W, U, zK, tsave, g_zK.contiguous(), g_ld, ctx.log_eps)
         return None, g_mu0, g_ls0, g_W, g_U, g_B, None
 
 
@@ -76,5 +70,5 @@ class BernoulliLL(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g):
         x, p = ctx.saved_tensors
-        _, g_p = ops.bernoulli_ll(x, p, ctx.log_eps, float(g))
+        _, g_p = ops.bernoulli_ll(x, p, ctx.log_eps, g)          # the upstream scalar is read on the device
         return None, g_p, None

@@ -60,10 +60,17 @@ def gradient_create(F, D, N, unpack_params, dtype=None):
     return variational_objective, gradient
 
 
-def make_free_energy(logp, X, D, K, encode, decode, max_iter, batch_size, dtype=None, batch_iter=None):
-    """The F(phi, theta, t) of optimization.py:66-92 as a function of CUDA tensors."""
+def make_free_energy(logp, X, D, K, encode, decode, max_iter, batch_size, dtype=None, batch_iter=None, device_rng=None):
+    """The F(phi, theta, t) of optimization.py:66-92 as a function of CUDA tensors.
+
+    device_rng: None (default) draws z0 from the module's RandomState like the reference (:69) -- 164 k host draws per
+    step at the BASELINE batch; an integer seed (or NORMFLOWS_DEVICE_RNG=<seed> in the environment) draws z0 on the
+    device instead (opt-in: another stream than the reference's, nothing crosses PCIe)."""
     dt = default_dtype() if dtype is None else dtype
     dev = torch.device('cuda', torch.cuda.current_device())
+    if device_rng is None and os.environ.get('NORMFLOWS_DEVICE_RNG'):
+        device_rng = int(os.environ['NORMFLOWS_DEVICE_RNG'])
+    gen = None if device_rng is None else torch.Generator(device=dev).manual_seed(int(device_rng))
     X_dev = None
     if batch_iter is None:
         # optimization.py:55: same schedule, same consumption of the global NumPy RNG as make_batch_iter,
@@ -77,13 +84,17 @@ def make_free_energy(logp, X, D, K, encode, decode, max_iter, batch_size, dtype=
             Xbatch = X_dev.index_select(0, torch.as_tensor(batch_indices(t), device=dev))  # :68
         else:
             Xbatch = torch.as_tensor(np.ascontiguousarray(batch_iter(t))).to(dev, dt)
-        z0_np = rs.randn(Xbatch.shape[0], D)                                              # :69 (module RandomState)
-        z0 = torch.as_tensor(z0_np).to(dev, dt)
+        if gen is None:
+            z0_np = rs.randn(Xbatch.shape[0], D)                                          # :69 (module RandomState)
+            z0 = torch.as_tensor(z0_np).to(dev, dt)
+            # first = mean over d of logq0 summed over SAMPLES (:56-59, :77); constant in the parameters
+            first = float(np.mean(-D / 2 * np.log(2 * np.pi) - 0.5 * np.sum(z0_np ** 2, axis=0)))
+        else:
+            z0 = torch.randn(Xbatch.shape[0], D, dtype=dt, device=dev, generator=gen)
+            first = torch.mean(-D / 2 * np.log(2 * np.pi) - 0.5 * torch.sum(z0.double() ** 2, dim=0)).to(dt)
         mu0, log_sigma_diag0, W, U, B = encode(phi, Xbatch)                               # :70
         cooling_max = min(max_iter / 4, 10000)                                            # :71
         beta_t = min(1.0, 0.001 + t / cooling_max)                                        # :72
-        # first = mean over d of logq0 summed over SAMPLES (:56-59, :77); constant in the parameters
-        first = float(np.mean(-D / 2 * np.log(2 * np.pi) - 0.5 * np.sum(z0_np ** 2, axis=0)))
         zk, logdet = tape.AmortisedFlow.apply(z0, mu0, log_sigma_diag0, W, U, B, eps)     # :74-84
         third = torch.mean(logdet)                                                        # :85
         logits = decode(theta, zk)                                                        # :87
@@ -138,6 +149,23 @@ def optimize(*args, verbose=True, **kwargs):
                 except OSError:
                     pass
 
-    variational_params = adam(gradient, init_params, step_size=step_size, callback=callback, num_iters=max_iter)
+    # adam(gradient, init_params, step_size=step_size, callback=callback, num_iters=max_iter) (optimization.py:118) with
+    # the parameters, both moment vectors and the update on the device (nf_adam_step, float64 like the reference): per
+    # iteration nothing crosses PCIe but the mini-batch indices; the callback sees host copies only when it prints.
+    dev = torch.device('cuda', torch.cuda.current_device())
+    dt = default_dtype()
+    x = torch.as_tensor(np.asarray(init_params, dtype=np.float64)).to(dev)
+    m, v = torch.zeros_like(x), torch.zeros_like(x)
+    for t in range(max_iter):
+        p = x.to(dt, copy=True).requires_grad_(True)
+        phi, theta = unpack_params(p)
+        fe = F(phi, theta, t)
+        g, = torch.autograd.grad(fe, p)
+        if verbose and (t % 100 == 0 or t == max_iter - 1):
+            callback(x.cpu().numpy(), t, None)
+        else:
+            pbar.update()
+        ops.adam_step(x, g, m, v, t, step_size)
+    variational_params = x.cpu().numpy()
     pbar.close()
     return unpack_params(variational_params)
