@@ -85,11 +85,15 @@ __device__ __forceinline__ void tm_wait_st() { asm volatile("tcgen05.wait::st.sy
 __device__ __forceinline__ void tm_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __host__ __device__ constexpr int tm_columns(int n) { int c = 32; while (c < n) c <<= 1; return c; }
 
-// per-layer constant records in shared memory, every value duplicated into both halves of a pair
-//   forward : w[D]*kappa | b*kappa | s[D]            (2D+1 pairs, padded to an even count)
-//   backward: -s[D] | -c | -2c | w[D]                (2D+2 pairs)
-template <int D> __host__ __device__ constexpr int recf_pairs() { return (2 * D + 2) & ~1; }
+// per-layer constant records in shared memory
+//   forward : w[D]*kappa | b*kappa | s[D]            (2D+1 floats, padded to a multiple of four)
+//   backward: -s[D] | -c | -2c | w[D]                (2D+2 floats, padded to a multiple of four)
+template <int D> __host__ __device__ constexpr int recf_pairs() { return 2 * D + 1; }
 template <int D> __host__ __device__ constexpr int recb_pairs() { return 2 * D + 2; }
+// the records hold each constant once (padded to a multiple of four floats); the packed instructions take them as
+// scalar operands broadcast to both halves
+template <int D> __host__ __device__ constexpr int recf_floats() { return (2 * D + 1 + 3) & ~3; }
+template <int D> __host__ __device__ constexpr int recb_floats() { return (2 * D + 2 + 3) & ~3; }
 
 constexpr int kStageLayers = 4;            // layers whose partials are staged before the lanes add them up
 constexpr int kStagePitch = 36;            // floats per staged row: 32 lanes + 4 (128-bit reads of 8 rows hit 8 distinct bank groups)
@@ -98,7 +102,7 @@ struct Smem {
     int lcf, lcb, tp, acc, stg, hist, total;      // offsets in floats
     __host__ __device__ Smem(int K, int D, int ssp /*pairs per thread kept in shared memory*/, int ntp_s, int nthreads) {
         const int V = 2 * D + 2;
-        const int rf = 2 * ((2 * D + 2) & ~1), rb = 2 * (2 * D + 2);
+        const int rf = (2 * D + 1 + 3) & ~3, rb = (2 * D + 2 + 3) & ~3;
         lcf = 0;
         lcb = lcf + K * rf;
         tp = lcb + K * rb;
@@ -195,7 +199,7 @@ __device__ __forceinline__ void pair_tile(const float* __restrict__ eps, long lo
     constexpr int SGP = SG / 2;                     // global-memory (L2-resident) pair slots per thread and layer
     constexpr int PS = (P - PT) < SSP ? (P - PT) : SSP;      // pairs of this round in shared memory
     constexpr int PG = P - PT - PS;                          // ... and in global memory
-    constexpr int RF = 2 * recf_pairs<D>(), RB = 2 * recb_pairs<D>();
+    constexpr int RF = recf_floats<D>(), RB = recb_floats<D>();
     static_assert(S % 2 == 0 && S <= SMAX && PG <= SGP, "round size");
     const float LOG2PI = 1.8378770664093453f;
     const u64 one2 = pk(1.0f, 1.0f), mone2 = pk(-1.0f, -1.0f), mtwo2 = pk(-2.0f, -2.0f);
@@ -259,11 +263,14 @@ __device__ __forceinline__ void pair_tile(const float* __restrict__ eps, long lo
     }
     // ---- forward over the K layers (get_data.py:104-109); the log-det is left to the reverse sweep ----
     for (int k = 0; k < K; ++k) {
-        u64 rf[RF / 2];
+        u64 rf[recf_pairs<D>()];
         {
-            const ulonglong2* src = reinterpret_cast<const ulonglong2*>(lcf + k * RF);
+            float f[RF];
+            const float4* src = reinterpret_cast<const float4*>(lcf + k * RF);
 #pragma unroll
-            for (int i = 0; i < RF / 4; ++i) { const ulonglong2 v = src[i]; rf[2 * i] = v.x; rf[2 * i + 1] = v.y; }
+            for (int i = 0; i < RF / 4; ++i) { const float4 v = src[i]; f[4 * i] = v.x; f[4 * i + 1] = v.y; f[4 * i + 2] = v.z; f[4 * i + 3] = v.w; }
+#pragma unroll
+            for (int i = 0; i < recf_pairs<D>(); ++i) rf[i] = pk(f[i], f[i]);
         }
         float tt[2 * (PT > 0 ? PT : 1)];
 #pragma unroll
@@ -325,11 +332,14 @@ __device__ __forceinline__ void pair_tile(const float* __restrict__ eps, long lo
 #pragma unroll
             for (int i = 0; i < PG; ++i) gn[i] = __ldcg(gst_t + (size_t)((k - 1) * SGP + i) * NT);
         }
-        u64 rb[RB / 2];
+        u64 rb[recb_pairs<D>()];
         {
-            const ulonglong2* src = reinterpret_cast<const ulonglong2*>(lcb + k * RB);
+            float f[RB];
+            const float4* src = reinterpret_cast<const float4*>(lcb + k * RB);
 #pragma unroll
-            for (int i = 0; i < RB / 4; ++i) { const ulonglong2 v = src[i]; rb[2 * i] = v.x; rb[2 * i + 1] = v.y; }
+            for (int i = 0; i < RB / 4; ++i) { const float4 v = src[i]; f[4 * i] = v.x; f[4 * i + 1] = v.y; f[4 * i + 2] = v.z; f[4 * i + 3] = v.w; }
+#pragma unroll
+            for (int i = 0; i < recb_pairs<D>(); ++i) rb[i] = pk(f[i], f[i]);
         }
         const u64 nc = rb[D], c2 = rb[D + 1];
         u64 v[V];                                   // the first pair starts the per-layer sums (no zero fill)
@@ -420,7 +430,7 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
     using M = Mth<float>;
     constexpr int NT = NW * 32;
     constexpr int V = 2 * D + 2;
-    constexpr int RF = 2 * recf_pairs<D>(), RB = 2 * recb_pairs<D>();
+    constexpr int RF = recf_floats<D>(), RB = recb_floats<D>();
     constexpr int SSP = (SMAX - ST - SG) / 2;
     static_assert(SMAX % 2 == 0 && ST % 2 == 0 && SG % 2 == 0 && ST + SG <= SMAX && (ST == 0 || ST == 2 || ST == 4 || ST == 8), "configuration");
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -469,15 +479,14 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
 #pragma unroll
         for (int d = 0; d < D; ++d) {
             const float wv = w[k * D + d], sv = s[k * D + d];
-            lcf[k * RF + 2 * d] = lcf[k * RF + 2 * d + 1] = wv * kap;
-            lcf[k * RF + 2 * (D + 1 + d)] = lcf[k * RF + 2 * (D + 1 + d) + 1] = sv;
-            lcb[k * RB + 2 * d] = lcb[k * RB + 2 * d + 1] = -sv;
-            lcb[k * RB + 2 * (D + 2 + d)] = lcb[k * RB + 2 * (D + 2 + d) + 1] = wv;
+            lcf[k * RF + d] = wv * kap;
+            lcf[k * RF + D + 1 + d] = sv;
+            lcb[k * RB + d] = -sv;
+            lcb[k * RB + D + 2 + d] = wv;
         }
-        lcf[k * RF + 2 * D] = lcf[k * RF + 2 * D + 1] = b[k] * kap;
-        if (RF > 2 * (2 * D + 1)) lcf[k * RF + 2 * (2 * D + 1)] = lcf[k * RF + 2 * (2 * D + 1) + 1] = 0.f;
-        lcb[k * RB + 2 * D] = lcb[k * RB + 2 * D + 1] = -c[k];
-        lcb[k * RB + 2 * (D + 1)] = lcb[k * RB + 2 * (D + 1) + 1] = -2.f * c[k];
+        lcf[k * RF + D] = b[k] * kap;
+        lcb[k * RB + D] = -c[k];
+        lcb[k * RB + D + 1] = -2.f * c[k];
     }
     target_prepare<float>(TGT, D, tparams, ntp, tp);
     for (int i = tid; i < NW * K * V; i += NT) acc[i] = 0.f;
