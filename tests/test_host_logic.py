@@ -87,8 +87,13 @@ def test_resolve_target():
     np.testing.assert_allclose(tp[:2], [0.3, 0.7])
     name, tp2 = resolve_target(('mixdiag', [0.3], [[0, 1], [2, 3]], [np.diag([1., 1.]), np.diag([2., 2.])]), 2)
     np.testing.assert_allclose(tp2, tp)
+    # non-diagonal covariance matrices (distributions.py:23-25) are a target of their own, up to four dimensions
+    name, tp3 = resolve_target(('mixdiag', [0.3], [[0, 1], [2, 3]], [np.array([[1., .2], [.2, 1.]]), np.diag([2., 2.])]), 2)
+    assert name == 'mixfull' and tp3.size == 2 * (1 + 2 + 4)
+    np.testing.assert_allclose(tp3[:2], [0.3, 0.7])
+    np.testing.assert_allclose(tp3[6:10], [1., .2, .2, 1.])
     with pytest.raises(nfcore.NFError):
-        resolve_target(('mixdiag', [0.3], [[0, 1], [2, 3]], [np.array([[1., .2], [.2, 1.]]), np.diag([2., 2.])]), 2)
+        resolve_target(('mixdiag', [0.3], np.zeros((2, 5)), np.tile(np.eye(5) + 0.1, (2, 1, 1))), 5)
     with pytest.raises(nfcore.NFError):
         resolve_target(lambda z: z, 2)
     with pytest.raises(nfcore.NFError):
