@@ -352,6 +352,10 @@ def run_ours(args):
             'frac_fp32': fracs['fp32'], 'frac_hbm': fracs['hbm'],
             'achieved_hbm_gbs': per_gpu * BYTES_PER_SAMPLE / 1e9, 'peak_hbm_gbs': hbm_peak / 1e9,
             'frac_mufu_at_clock_under_load': (per_gpu * MUFU_PER_SAMPLE / (sms * 16 * f_load)) if f_load else None,
+            # what the kernel issues, from the committed ncu capture (not measured by this run): the instruction-issue bound
+            # sits below the MUFU bound and is the one the kernel runs into
+            'issue_model': {'lane_instructions_per_sample': 1069, 'issue_bound_samples_per_s': sms * 128 * f_max / 1069.0,
+                            'smsp_issue_active_pct': 57.0, 'source': 'profiles/r02_ncu_elbo_pair_kernel.txt'},
             'kernel_ms': ms_per_step,
             'kernel_note': 'events bracket one launch per step: the objective kernel, whose last block adds the per-SM rows'
                            + ((' and does the NVLink peer exchange' if small_ar is not None else '; + NCCL all-reduce') if world > 1 else ''),
@@ -376,6 +380,32 @@ def run_ours(args):
             vb = nb * 10 / (b0.elapsed_time(b1) * 1e-3)
             big = {'samples_per_step': nb, 'value': vb, 'unit': UNIT, 'frac_mufu': vb * MUFU_PER_SAMPLE / mufu_peak}
             del eb
+        # informational: one more BASELINE configuration, device-timed (C5 at D = 64: K = 64, 2^19 samples, diagonal
+        # Gaussian target; the matrix-product path).  Not part of `value`.
+        other = None
+        if world == 1:
+            try:
+                Kc, Dc, Nc = 64, 64, 1 << 19
+                rsx = np.random.RandomState(5)
+                Wc = (0.1 + 0.01 * rsx.randn(Kc, Dc)) / np.sqrt(Dc / 2); Uc = (0.1 + 0.01 * rsx.randn(Kc, Dc)) / np.sqrt(Dc / 2)
+                Sc, cc = sem.forward(Wc, Uc)
+                ac = [torch.as_tensor(x, dtype=torch.float32).to(dev).contiguous() for x in (Wc, Sc, 0.1 * np.ones(Kc), cc)]
+                tpc = torch.as_tensor(np.concatenate([rsx.uniform(-1, 1, Dc), rsx.uniform(-1, 1, Dc)]), dtype=torch.float32).to(dev)
+                ec = [torch.randn(Nc, Dc, dtype=torch.float32, device=dev, generator=gen) for _ in range(2)]
+                oc = ops.planar_elbo(ec[0], *ac, 'gaussdiag', tpc)
+                torch.cuda.synchronize()
+                c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                c0.record()
+                for i in range(10):
+                    ops.planar_elbo(ec[i % 2], *ac, 'gaussdiag', tpc, out=oc)
+                c1.record()
+                torch.cuda.synchronize()
+                msc = c0.elapsed_time(c1) / 10
+                other = {'c5_d64': {'K': Kc, 'D': Dc, 'samples_per_step': Nc, 'ms_per_step': msc, 'value': Nc / msc * 1e3, 'unit': UNIT,
+                                    'path': 'matrix-product formulation (csrc/nf_elbo_gram.cu)'}}
+                del ec
+            except Exception as e:          # informational only
+                other = {'c5_d64': {'error': str(e)}}
         line = {
             'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps, 'warmup': n_warm + extra_warm,
             'ms_per_step': ms_per_step, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
@@ -395,6 +425,8 @@ def run_ours(args):
             line['e2e_rng'] = e2e_rng
         if big is not None:
             line['steady_state_2p24'] = big
+        if other is not None:
+            line['other_configs'] = other
         if cpu_value is not None:
             line['cpu_baseline'] = {
                 'value': cpu_value, 'unit': UNIT, 'cores': torch.get_num_threads(), 'kind': 'port',
