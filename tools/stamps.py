@@ -31,6 +31,8 @@ for rep in range(3):
     t0 = st[:, 0].min()
     rel = (st[:, :5] - t0) / 1e3
     last = int(np.argmax(st[:, 4]))
+    print('   last block %d: ticket %.2f | rows loaded and staged %.2f | vector built %.2f | outputs written %.2f us'
+          % (last, rel[last, 3], (st[last, 6] - t0) / 1e3, (st[last, 7] - t0) / 1e3, rel[last, 4]))
     print('N=2^%d  entry %.1f..%.1f us | set-up done %.1f..%.1f | samples done %.1f..%.1f (median %.1f) | ticket %.1f..%.1f | finalize done %.1f (block %d; its ticket at %.1f)'
           % (lg, rel[:, 0].min(), rel[:, 0].max(), rel[:, 1].min(), rel[:, 1].max(), rel[:, 2].min(), rel[:, 2].max(), np.median(rel[:, 2]),
              rel[:, 3].min(), rel[:, 3].max(), rel[last, 4], last, rel[last, 3]))

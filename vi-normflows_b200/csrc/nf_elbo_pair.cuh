@@ -588,30 +588,38 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
         if (s_last) {
             const int nrows = gridDim.x;
             float* stage = acc;                                   // reuse (the staging areas follow): [groups][row]
-            // work item = (group of 8 consecutive rows, value).  A thread issues the loads of all its items before it
-            // adds anything, so the whole pass costs about one L2 round trip.
-            constexpr int GR = 8, ITEMS = 8;
+            // A warp takes a group of 8 consecutive rows at a time, its lanes stride over the row's values two at a time
+            // (a row is K*V+2 floats: an even count, 8-byte aligned).  A lane issues the loads of a whole row group before it
+            // adds anything, so the pass costs a few L2 round trips; no integer division on the way.
+            constexpr int GR = NW >= 16 ? 10 : 8, U = NW >= 16 ? 4 : 2;      // 16 warps x 10 rows cover 148 SMs in one batch per warp
             const int groups = (nrows + GR - 1) / GR;
-            const int nitems = groups * row;
-            for (int base = 0; base < nitems; base += NT * ITEMS) {
-                float t[ITEMS][GR];
+            const int row2 = row >> 1;
+            for (int g = warp; g < groups; g += NW) {
+                const float2* base = reinterpret_cast<const float2*>(partials + (size_t)g * GR * row);
+                const int nr = (nrows - g * GR) < GR ? (nrows - g * GR) : GR;
+                for (int i0 = 0; i0 < row2; i0 += 32 * U) {
+                    float2 t[U][GR];
 #pragma unroll
-                for (int q = 0; q < ITEMS; ++q) {
-                    const int it = base + q * NT + tid;
-                    const int g = it / row, i = it - g * row;
+                    for (int u = 0; u < U; ++u) {
+                        const int i = i0 + u * 32 + lane;
 #pragma unroll
-                    for (int j = 0; j < GR; ++j) {
-                        const int r = g * GR + j;
-                        t[q][j] = (it < nitems && r < nrows) ? __ldcg(partials + (size_t)r * row + i) : 0.f;
+                        for (int j = 0; j < GR; ++j)
+                            t[u][j] = (i < row2 && j < nr) ? __ldcg(base + (size_t)j * row2 + i) : make_float2(0.f, 0.f);
                     }
-                }
 #pragma unroll
-                for (int q = 0; q < ITEMS; ++q) {
-                    const int it = base + q * NT + tid;
-                    if (it < nitems) stage[it] = ((t[q][0] + t[q][1]) + (t[q][2] + t[q][3])) + ((t[q][4] + t[q][5]) + (t[q][6] + t[q][7]));
+                    for (int u = 0; u < U; ++u) {
+                        const int i = i0 + u * 32 + lane;
+                        if (i < row2) {
+                            float2 r = t[u][0];
+#pragma unroll
+                            for (int j = 1; j < GR; ++j) { r.x += t[u][j].x; r.y += t[u][j].y; }
+                            reinterpret_cast<float2*>(stage + g * row)[i] = r;
+                        }
+                    }
                 }
             }
             __syncthreads();
+            if (stamps && tid == 0) stamps[(blockIdx.x < 256 ? blockIdx.x : 0) * 8 + 6] = gtime();
             // result vector in shared memory, laid out as the caller's arrays follow one another:
             // [F, sum log q, sum log p | g_w (K*D) | g_s (K*D) | g_b (K) | g_c (K) | n_hi, n_lo]
             float* vec = stage + groups * row;
@@ -630,6 +638,7 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
             __syncthreads();
             if (tid == 0) { vec[0] = vec[1] - vec[2]; vec[nvec] = ar.n_hi; vec[nvec + 1] = ar.n_lo; }
             __syncthreads();
+            if (stamps && tid == 0) stamps[(blockIdx.x < 256 ? blockIdx.x : 0) * 8 + 7] = gtime();
             bool failed = false;
             if (ar.world > 1) failed = !ar_exchange(ar, vec, nvec + 2, tid, NT, &s_last);
             for (int i = tid; i < nvec; i += NT) {
