@@ -27,10 +27,15 @@ for rep in range(3):
     torch.cuda.synchronize()
     st = np.zeros((256, 8), dtype=np.uint64)
     lib.nf_debug_pair_stamps(st.ctypes.data)
+    full = st.astype(np.int64)
     st = st[:148].astype(np.int64)
     t0 = st[:, 0].min()
     rel = (st[:, :5] - t0) / 1e3
     last = int(np.argmax(st[:, 4]))
+    for b in range(2):
+        wt = (full[200 + 4 * b:200 + 4 * b + 4].reshape(-1)[:32] - st[:, 0].min()) / 1e3
+        wt = wt[wt > 0]
+        print('   block %d: warps finish at ' % b + ' '.join('%.1f' % x for x in wt))
     print('   last block %d: ticket %.2f | rows loaded and staged %.2f | vector built %.2f | outputs written %.2f us'
           % (last, rel[last, 3], (st[last, 6] - t0) / 1e3, (st[last, 7] - t0) / 1e3, rel[last, 4]))
     print('N=2^%d  entry %.1f..%.1f us | set-up done %.1f..%.1f | samples done %.1f..%.1f (median %.1f) | ticket %.1f..%.1f | finalize done %.1f (block %d; its ticket at %.1f)'

@@ -551,6 +551,7 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
     }
 
     // ---- block row ----
+    if (stamps && lane == 0 && blockIdx.x < 4) stamps[(200 + 4 * blockIdx.x) * 8 + warp] = gtime();      // per-warp finish times (rows 200..215)
     if (stamps) __syncthreads();
     if (stamp) stamps[blockIdx.x * 8 + 2] = gtime();
     sum_q = warp_sum(sum_q);
