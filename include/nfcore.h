@@ -188,6 +188,20 @@ int nf_script_train_f64(const double* eps_all, int64_t n_iters, int64_t N, int D
                         double step_size, double h1, double h2, double h3, int64_t first_iter, int resume, int64_t eps_stride,
                         double* opt_state, double* trace_F, void* workspace, size_t workspace_bytes, void* stream);
 
+/* nf_script_train_f32 for a sample-sharded run (one process per GPU): every iteration's sums over this rank's N samples are
+ * exchanged with the peers (inside the objective kernel's last block where the shape allows it, see
+ * nf_planar_elbo_fwd_bwd_exchange_f32) before the update kernel reads them, normalised by `n_global` (the samples of all
+ * ranks).  Every rank applies the same update to its own copy of the parameters -- the sums are bitwise identical on all
+ * ranks -- so the copies stay equal without a broadcast.  No counterpart in the reference (single process).
+ *   seq0   : sequence number of the first iteration's exchange; the call uses seq0 .. seq0 + n_iters - 1
+ *   status : one float in device memory; cleared at the start, raised to 1 if a peer ever failed to arrive within 20 s
+ * float32, result vectors of at most nf_allreduce_small_max_count() floats, not the matrix-product path. */
+int nf_script_train_sharded_f32(const float* eps_all, int64_t n_iters, int64_t N, int64_t n_global, int D, int K, float* params,
+                                int target_id, const float* target_params, int n_target_params, float log_eps, int optimizer,
+                                float step_size, float h1, float h2, float h3, int64_t first_iter, int resume, int64_t eps_stride,
+                                float* opt_state, float* trace_F, void* workspace, size_t workspace_bytes,
+                                void* const* peer_buffers, int world, int rank, uint64_t seq0, float* status, void* stream);
+
 /* Host-side parameter algebra of the shared-parameter path (float64, K*D numbers, no GPU involved).
  * get_data.py:106-108 derives the step vector u_hat and the log-det coefficient w.u from the raw (w, u) inside
  * the objective; the entry points above take them as inputs (s, c) and return gradients with respect to them.

@@ -28,6 +28,25 @@ for (K, D, N, target) in ((32, 2, 200003, 'p1'), (32, 2, 200003 * world, 'p1'), 
         ok &= good
         if rank == 0:
             print('K=%d D=%d N=%d %s world=%d: |dF|=%.2e |dg|=%.2e %s' % (K, D, N, dtype, world, eF, eg, 'OK' if good else 'FAIL'), flush=True)
+# the device optimisation loop, sample-sharded: every rank trains on its shard, all end with the parameters one GPU finds
+K, D, N, T = 8, 2, 4096 * world + 12, 40
+eps_all = rs.randn(T, N, D).astype(np.float32)
+init = np.concatenate([0.1 * np.ones(2 * K * D), 0.1 * np.ones(K)])
+solo = SharedFlowObjective('p1', K, D, dtype='float32')
+for optimizer in ('adam', 'rmsprop'):
+    x1, tr1 = solo.train(init, eps_all, optimizer=optimizer, step_size=1e-3)
+    lo, hi = sharding.shard_bounds(N, rank, world)
+    sh = SharedFlowObjective('p1', K, D, dtype='float32', process_group=dist.group.WORLD)
+    x2, tr2 = sh.train(init, np.ascontiguousarray(eps_all[:, lo:hi]), optimizer=optimizer, step_size=1e-3)
+    ex, et = np.abs(x1 - x2).max(), np.abs(tr1 - tr2).max()
+    allx = [None] * world
+    dist.all_gather_object(allx, x2.tobytes())
+    same = all(a == allx[0] for a in allx)
+    good = ex <= 2e-5 and et <= 2e-5 and same and np.abs(x1 - init).max() > 1e-3
+    ok &= good
+    if rank == 0:
+        print('sharded device loop %s, %d steps, world=%d: |dx|=%.2e |dF trace|=%.2e identical on all ranks=%s %s'
+              % (optimizer, T, world, ex, et, same, 'OK' if good else 'FAIL'), flush=True)
 # the NVLink one-shot exchange against NCCL, repeated so that both slot sets and the sequence logic are exercised
 from nfcore.peer import SmallAllReduce
 ar = SmallAllReduce(dist.group.WORLD)

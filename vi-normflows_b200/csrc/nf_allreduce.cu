@@ -32,6 +32,7 @@ allreduce_small_kernel(const ArDesc ar, const float* src, float* dst /* may be s
         if (tid == 0) {
             if (status_i) status_i[0] = 1;
             if (ar.xout) ar.xout[2] = 1.f;
+            if (ar.sticky_status) ar.sticky_status[0] = 1.f;
         }
         return;
     }
@@ -60,6 +61,7 @@ int make_ar_desc(ArDesc* ar, void* const* peer_buffers, int world, int rank, uin
     ar->world = world; ar->rank = rank; ar->seq = (unsigned long long)seq;
     ar->n_hi = (float)(n_local >> 20); ar->n_lo = (float)(n_local & ((1 << 20) - 1));      // both exact; so are their sums over 8 ranks
     ar->xout = xout;
+    ar->sticky_status = nullptr;
     return NF_OK;
 }
 

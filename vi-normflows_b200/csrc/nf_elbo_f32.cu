@@ -108,16 +108,24 @@ int nf_script_train_f32(const float* eps_all, int64_t n_iters, int64_t N, int D,
 
 size_t nf_script_train_workspace_bytes(int K, int D, int elem_size) {
     if (K < 1 || D < 1 || elem_size < 1) return 0;
-    const size_t nlc = (size_t)2 * K * D + 2 * K, nres = 3 + nlc;
-    const size_t head = ((nlc + nres) * (size_t)elem_size + 255) & ~(size_t)255;
-    return head + nf_planar_elbo_workspace_bytes(K, D, elem_size);
+    return nf::script_head_bytes(K, D, (size_t)elem_size) + nf_planar_elbo_workspace_bytes(K, D, elem_size);
 }
 
 size_t nf_script_train_workspace_bytes_n(int64_t N, int K, int D, int elem_size) {
     if (K < 1 || D < 1 || elem_size < 1) return 0;
-    const size_t nlc = (size_t)2 * K * D + 2 * K, nres = 3 + nlc;
-    const size_t head = ((nlc + nres) * (size_t)elem_size + 255) & ~(size_t)255;
-    return head + nf_planar_elbo_workspace_bytes_n(N, K, D, elem_size);
+    return nf::script_head_bytes(K, D, (size_t)elem_size) + nf_planar_elbo_workspace_bytes_n(N, K, D, elem_size);
+}
+
+int nf_script_train_sharded_f32(const float* eps_all, int64_t n_iters, int64_t N, int64_t n_global, int D, int K, float* params,
+                                int target_id, const float* target_params, int n_target_params, float log_eps, int optimizer,
+                                float step_size, float h1, float h2, float h3, int64_t first_iter, int resume, int64_t eps_stride,
+                                float* opt_state, float* trace_F, void* workspace, size_t workspace_bytes,
+                                void* const* peer_buffers, int world, int rank, uint64_t seq0, float* status, void* stream) {
+    if (!peer_buffers || !status || seq0 == 0) return NF_ERR_INVALID;
+    const nf::ShardDesc sh = {peer_buffers, world, rank, seq0, n_global, status};
+    return nf::script_train<float>(eps_all, n_iters, N, D, K, params, target_id, target_params, n_target_params, log_eps, optimizer,
+                                   step_size, h1, h2, h3, first_iter, resume, eps_stride, opt_state, trace_F, workspace,
+                                   workspace_bytes, stream, &sh);
 }
 
 }  // extern "C"

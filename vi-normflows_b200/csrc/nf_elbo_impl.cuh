@@ -1049,6 +1049,15 @@ script_step_kernel(T* __restrict__ params /*[2KD+K]*/, T* __restrict__ lc /*w|s|
     }
 }
 
+// device loop workspace: [lc (2KD+2K) | res (3+2KD+2K) | count and status of the sharded exchange (3) | pad to 256 B | rows]
+static inline size_t script_head_bytes(int K, int D, size_t elem) {
+    const size_t nlc = (size_t)2 * K * D + 2 * K;
+    return ((nlc + (3 + nlc) + 3) * elem + 255) & ~(size_t)255;
+}
+
+// the ranks of a sample-sharded device loop (nf_script_train_sharded_f32)
+struct ShardDesc { void* const* peer_buffers; int world, rank; uint64_t seq0; int64_t n_global; float* status; };
+
 // optimiser state at the start of a run: zeros, except rmsprop's running average (ones, autograd 1.3)
 template <typename T>
 __global__ void script_state_init_kernel(T* __restrict__ state, int P, int optimizer) {
@@ -1065,7 +1074,7 @@ template <typename T>
 static int script_train(const T* eps_all, int64_t n_iters, int64_t N, int D, int K, T* params, int target_id,
                         const T* tparams, int ntp, T epsv, int optimizer, T step, T h1, T h2, T h3, int64_t first_iter,
                         int resume, int64_t eps_stride, T* state, T* trace_F, void* workspace, size_t workspace_bytes,
-                        void* stream_) {
+                        void* stream_, const ShardDesc* sh = nullptr) {
     cudaStream_t st = (cudaStream_t)stream_;
     if (n_iters < 0 || N < 1 || !params || !state || !workspace || optimizer < 0 || optimizer > 2 || first_iter < 0) return NF_ERR_INVALID;
     if (eps_stride == 0) eps_stride = N * D;
@@ -1073,8 +1082,7 @@ static int script_train(const T* eps_all, int64_t n_iters, int64_t N, int D, int
     // every iteration's slice is read with 16-byte vector loads (load_samples)
     if (n_iters > 1 && ((size_t)eps_stride * sizeof(T)) % 16 != 0) return NF_ERR_INVALID;
     const size_t P = (size_t)2 * K * D + K, nlc = (size_t)2 * K * D + 2 * K, nres = 3 + nlc;
-    // workspace: [lc | res | pad to 256 B | rows]
-    const size_t head = ((nlc + nres) * sizeof(T) + 255) & ~(size_t)255;
+    const size_t head = script_head_bytes(K, D, sizeof(T));
     const size_t need = head + nf_planar_elbo_workspace_bytes(K, D, (int)sizeof(T));
     if (workspace_bytes < need) return NF_ERR_WORKSPACE;
     T* lc = reinterpret_cast<T*>(workspace);
@@ -1089,10 +1097,15 @@ static int script_train(const T* eps_all, int64_t n_iters, int64_t N, int D, int
         use_gram = gram_applicable(N, D, K, target_id, ntp) && workspace_bytes >= head + gram_workspace_bytes(N, D, K);
     if (!resume)
         NF_CUDA_OK(launch_pdl(script_state_init_kernel<T>, dim3(8), dim3(256), 0, st, state, (int)P, optimizer));
+    if (sh) {
+        if (sizeof(T) != 4 || use_gram || (int)nres + 2 > pr::kArStride || !sh->status || sh->n_global < N) return NF_ERR_UNSUPPORTED;
+        NF_CUDA_OK(cudaMemsetAsync(sh->status, 0, sizeof(float), st));
+    }
+    const long long n_norm = sh ? (long long)sh->n_global : (long long)N;      // the mean of get_data.py:113 is over ALL ranks' samples
     for (int64_t it = 0; it <= n_iters; ++it) {
         // apply update of iteration it-1 (if any), then prepare constants for iteration it
         NF_CUDA_OK(launch_pdl(script_step_kernel<T>, dim3(1), dim3(256), 0, st, params, lc, (const T*)res, state, K, D,
-                              (long long)N, it > 0 ? 1 : 0, (long long)(first_iter + it), (long long)(it - 1), optimizer, step,
+                              n_norm, it > 0 ? 1 : 0, (long long)(first_iter + it), (long long)(it - 1), optimizer, step,
                               h1, h2, h3, trace_F, 0));
         if (it == n_iters) break;
         const T* eps_it = eps_all + (size_t)it * (size_t)eps_stride;
@@ -1102,6 +1115,22 @@ static int script_train(const T* eps_all, int64_t n_iters, int64_t N, int D, int
                                    res + 3 + K * D, res + 3 + 2 * K * D, res + 3 + 2 * K * D + K, rows, st);
             if (rc != NF_OK) return rc;
             continue;
+        }
+        if constexpr (sizeof(T) == 4) {
+            if (sh) {
+                // this rank's sums are exchanged with the peers before the update kernel reads them (every rank then applies
+                // the same update to its copy of the parameters); a missing peer raises the sticky status word
+                pr::ArDesc ar;
+                rc = make_ar_desc(&ar, sh->peer_buffers, sh->world, sh->rank, sh->seq0 + (uint64_t)it, N, res + nres);
+                if (rc != NF_OK) return rc;
+                ar.sticky_status = sh->status;
+                bool exchanged = false;
+                rc = elbo_fused<T>(true, eps_it, N, D, K, w, s, b, c, target_id, tparams, ntp, epsv, res, res + 3, res + 3 + K * D,
+                                   res + 3 + 2 * K * D, res + 3 + 2 * K * D + K, rows, st, &ar, &exchanged, nullptr, workspace_bytes - head);
+                if (rc == NF_OK && !exchanged) rc = launch_allreduce_small(ar, res, res, (int)nres, nullptr, st);
+                if (rc != NF_OK) return rc;
+                continue;
+            }
         }
         rc = elbo_fused<T>(true, eps_it, N, D, K, w, s, b, c, target_id, tparams, ntp, epsv, res, res + 3, res + 3 + K * D,
                            res + 3 + 2 * K * D, res + 3 + 2 * K * D + K, rows, st, nullptr, nullptr, nullptr, workspace_bytes - head);

@@ -131,6 +131,7 @@ struct ArDesc {
     unsigned long long seq;                // 1, 2, 3, ...: the same on every rank for the same step
     float n_hi, n_lo;                      // this rank's sample count, split so that sums over 8 ranks stay exact
     float* xout;                           // [3]: sum of n_hi, sum of n_lo, status (0 ok, 1 a peer did not arrive)
+    float* sticky_status;                  // optional: raised to 1 when a peer did not arrive, never cleared (device loops)
 };
 __host__ __device__ inline size_t ar_buffer_bytes(int world) { return (size_t)2 * world * kArStride * sizeof(unsigned long long); }
 __device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
@@ -654,6 +655,7 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
             }
             if (tid == 0) {
                 if (ar.xout) { ar.xout[0] = vec[nvec]; ar.xout[1] = vec[nvec + 1]; ar.xout[2] = failed ? 1.f : 0.f; }
+                if (failed && ar.sticky_status) ar.sticky_status[0] = 1.f;
                 sync->counter = 0;
                 if (stamps) stamps[(blockIdx.x < 256 ? blockIdx.x : 0) * 8 + 4] = gtime();
             }

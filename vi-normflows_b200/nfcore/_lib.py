@@ -44,6 +44,9 @@ PROTOTYPES = {
     'nf_script_train_workspace_bytes_n': (c_size_t, [c_int64, c_int, c_int, c_int]),
     'nf_script_train_f32': (c_int, [c_void_p, c_int64, c_int64, c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_float, c_int] + [c_float] * 4 + [c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     'nf_script_train_f64': (c_int, [c_void_p, c_int64, c_int64, c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_double, c_int] + [c_double] * 4 + [c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    'nf_script_train_sharded_f32': (c_int, [c_void_p, c_int64, c_int64, c_int64, c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_float, c_int] + [c_float] * 4
+                                    + [c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_size_t, ctypes.POINTER(c_void_p), c_int, c_int, ctypes.c_uint64,
+                                       c_void_p, c_void_p]),
     'nf_session_create': (c_int, [ctypes.POINTER(c_void_p), c_int64, c_int, c_int, c_int]),
     'nf_session_destroy': (None, [c_void_p]),
     'nf_session_elbo_host_f32': (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int, c_void_p, c_int, c_float, c_int, c_void_p]),

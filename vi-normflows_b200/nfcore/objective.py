@@ -352,9 +352,13 @@ class SharedFlowObjective:
         After the call ``self.train_state`` describes the optimiser (its running averages and the number of
         iterations done); passing it back as ``state`` continues the same run -- a run cut into several calls
         follows the trajectory of one call (the reference keeps one optimiser for all iterations, get_data.py:140).
-        Script semantics only; not available with a process group."""
-        if self.group is not None or self.semantics != 'script':
-            raise NFError('train(): single-process, script semantics only')
+        Script semantics only.  With a process group (float32, NVLink peer exchange available) every rank passes ITS
+        shard of the samples, (n_iters, N_local, D): each iteration's sums are exchanged on the device and every rank
+        applies the same update (nf_script_train_sharded_f32); all ranks return the same parameters."""
+        if self.semantics != 'script':
+            raise NFError('train(): script semantics only')
+        if self.group is not None and self._small_ar is None:
+            raise NFError('train() with a process group needs the NVLink peer exchange (float32, <= 8 ranks of one box)')
         lib = _lib.load()
         eps_all = np.ascontiguousarray(eps_all, dtype=self.np_dtype)
         if eps_all.ndim != 3 or eps_all.shape[2] != self.D:
@@ -390,10 +394,30 @@ class SharedFlowObjective:
         vp = lambda t: ctypes.c_void_p(t.data_ptr()) if t is not None else None
         with torch.cuda.device(dev):
             st = torch.cuda.current_stream(dev).cuda_stream
-            rc = fn(vp(eps_dev), n_iters, N, D, K, vp(p_dev), ops.TARGET_IDS[self.target_name], vp(self.tparams),
-                    0 if self.tparams is None else self.tparams.numel(), creal(self.log_eps), code, creal(step_size),
-                    creal(h1), creal(h2), creal(h3), first_iter, resume, stride, vp(opt), vp(trace), vp(ws), nws,
-                    ctypes.c_void_p(st))
+            if self.group is None:
+                rc = fn(vp(eps_dev), n_iters, N, D, K, vp(p_dev), ops.TARGET_IDS[self.target_name], vp(self.tparams),
+                        0 if self.tparams is None else self.tparams.numel(), creal(self.log_eps), code, creal(step_size),
+                        creal(h1), creal(h2), creal(h3), first_iter, resume, stride, vp(opt), vp(trace), vp(ws), nws,
+                        ctypes.c_void_p(st))
+            else:
+                import torch.distributed as dist
+                cnt = torch.tensor([N, n_iters], dtype=torch.int64, device=dev)
+                mx = cnt.clone()
+                dist.all_reduce(cnt, op=dist.ReduceOp.SUM, group=self.group)
+                dist.all_reduce(mx, op=dist.ReduceOp.MAX, group=self.group)
+                if int(mx[1]) * self._small_ar.world != int(cnt[1]):
+                    raise NFError('train(): every rank must run the same number of iterations')
+                ar = self._small_ar
+                status = torch.zeros(1, dtype=torch.float32, device=dev)
+                rc = lib.nf_script_train_sharded_f32(vp(eps_dev), n_iters, N, int(cnt[0]), D, K, vp(p_dev), ops.TARGET_IDS[self.target_name],
+                                                     vp(self.tparams), 0 if self.tparams is None else self.tparams.numel(),
+                                                     ctypes.c_float(self.log_eps), code, ctypes.c_float(step_size), ctypes.c_float(h1),
+                                                     ctypes.c_float(h2), ctypes.c_float(h3), first_iter, resume, stride, vp(opt), vp(trace),
+                                                     vp(ws), nws, ar._ptrs, ar.world, ar.rank, ctypes.c_uint64(ar.seq + 1), vp(status),
+                                                     ctypes.c_void_p(st))
+                ar.seq += max(n_iters, 0)
+                if rc == 0 and float(status.item()) != 0.0:
+                    raise NFError('train(): a rank did not arrive at an exchange within the time limit; the parameters are not valid')
         _lib.check(rc)
         self.launches += 3 * n_iters + 1
         self.train_state = {'opt': opt, 'iters': first_iter + n_iters, 'optimizer': optimizer}
