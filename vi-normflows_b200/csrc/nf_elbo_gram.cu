@@ -24,6 +24,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include "nf_common.cuh"
+#include "nf_elbo_pair.cuh"
 
 namespace nf {
 
@@ -391,6 +392,189 @@ rec_bwd_kernel(const float* __restrict__ PT, const float* __restrict__ TT, long 
 }
 
 // ------------------------------------------------------------------------------------------------
+// Packed-pair recurrences: a thread owns TWO samples (columns tid and tid + 128 of a 256-sample block) and keeps their
+// running values as one 64-bit register pair per layer, so that the K^2/2 updates per sample are FFMA2 instructions
+// (fma.rn.f32x2: both samples per issue slot, the M value as the scalar-broadcast operand).  The same values as the
+// scalar kernels above, operation for operation (fma.rn.f32x2 rounds each half like fmaf); what differs is the block
+// size of the partial sums.  These have half the instructions per sample of the one-sample kernels, at 8 warps per SM
+// instead of 16: the updates of one layer are independent of each other, which is what the FMA pipe needs.
+using pr::u64; using pr::pk; using pr::upk; using pr::fma2; using pr::mul2; using pr::add2;
+constexpr int kRecPkW = 2 * kRecThreads;         // samples per block of the packed kernels
+
+template <int KP, int j>
+struct FwdLayerP {
+    static __device__ __forceinline__ void run(const FwdCtx<KP, 2>& x_, u64 (&a)[KP], u64& prod, u64& ld) {
+        using M_ = Mth<float>;
+        constexpr int NG = KP / 16, W = kRecPkW;
+        if (j > 0 && (j & 15) == 0) { cp_async_wait_le(NG - 1 - j / 16); if (kRecThreads > 128) __syncthreads(); }
+        const u64 one2 = pk(1.f, 1.f);
+        const u64 arg = fma2(pk(x_.stage[j * W], x_.stage[j * W + kRecThreads]), pk(M_::kArgScale, M_::kArgScale), a[j]);
+        float a0, a1;
+        upk(arg, a0, a1);
+        const u64 den = add2(pk(M_::ex2(a0), M_::ex2(a1)), one2);
+        float d0, d1;
+        upk(den, d0, d1);
+        const u64 r = pk(M_::rcp(d0), M_::rcp(d1));
+        const u64 t = fma2(pk(-2.f, -2.f), r, one2);                 // tanh_pre
+        const u64 nt = fma2(pk(2.f, 2.f), r, pk(-1.f, -1.f));        // -t, exactly
+        const u64 hp = fma2(nt, t, one2);
+        const float cj = x_.sc[j], ej = x_.se[j];
+        float x0, x1;
+        upk(fma2(hp, pk(cj, cj), one2), x0, x1);
+        prod = mul2(prod, add2(pk(fabsf(x0), fabsf(x1)), pk(ej, ej)));
+        if ((j & 3) == 3) {
+            float p0, p1;
+            upk(prod, p0, p1);
+            ld = fma2(pk(M_::lg2(p0), M_::lg2(p1)), pk(0.6931471805599453f, 0.6931471805599453f), ld);
+            prod = one2;
+        }
+        float t0, t1;
+        upk(t, t0, t1);
+        x_.dst[(size_t)j * x_.ldn] = t0;
+        x_.dst[(size_t)j * x_.ldn + kRecThreads] = t1;
+#pragma unroll
+        for (int k4 = (j + 1) / 4; k4 < KP / 4; ++k4) {
+            const float4 m = *reinterpret_cast<const float4*>(&x_.sM[j * KP + 4 * k4]);
+            if (4 * k4 + 0 > j) a[4 * k4 + 0] = fma2(pk(m.x, m.x), t, a[4 * k4 + 0]);
+            if (4 * k4 + 1 > j) a[4 * k4 + 1] = fma2(pk(m.y, m.y), t, a[4 * k4 + 1]);
+            if (4 * k4 + 2 > j) a[4 * k4 + 2] = fma2(pk(m.z, m.z), t, a[4 * k4 + 2]);
+            if (4 * k4 + 3 > j) a[4 * k4 + 3] = fma2(pk(m.w, m.w), t, a[4 * k4 + 3]);
+        }
+        if constexpr (j + 1 < KP) FwdLayerP<KP, j + 1>::run(x_, a, prod, ld);
+    }
+};
+
+template <int KP>
+__global__ void __launch_bounds__(kRecThreads, 2)
+rec_fwd_pk_kernel(const float* __restrict__ AT, long long ldn, int n_act, int K, const float* __restrict__ Mt,
+                  const float* __restrict__ c, float epsv, float* __restrict__ TT, float* __restrict__ part_ld) {
+    constexpr int W = kRecPkW;
+    extern __shared__ __align__(16) float dyn[];
+    float* sM = dyn;                              // [KP][KP]
+    float* stage = dyn + KP * KP;                 // [KP][W]
+    __shared__ float sc[KP], se[KP];
+    __shared__ float red[kRecThreads / 32];
+    constexpr int NG = KP / 16;
+    const int n = blockIdx.x * W + threadIdx.x;
+    const float* src = AT + n;
+    for (int i = threadIdx.x; i < KP * KP / 4; i += kRecThreads) cp_async16(sM + 4 * i, Mt + 4 * i);
+#pragma unroll
+    for (int g = 0; g < NG; ++g) {
+#pragma unroll
+        for (int k = 16 * g; k < 16 * g + 16; ++k) {
+            cp_async4(stage + k * W + threadIdx.x, src + (size_t)k * ldn);
+            cp_async4(stage + k * W + kRecThreads + threadIdx.x, src + (size_t)k * ldn + kRecThreads);
+        }
+        cp_async_commit();
+    }
+    for (int i = threadIdx.x; i < KP; i += kRecThreads) { sc[i] = i < K ? c[i] : 0.f; se[i] = i < K ? epsv : 0.f; }
+    cp_async_wait_le(NG - 1);
+    __syncthreads();
+    FwdCtx<KP, 2> x_;
+    x_.stage = stage + threadIdx.x; x_.sM = sM; x_.sc = sc; x_.se = se; x_.dst = TT + n; x_.ldn = ldn;
+    u64 a[KP];
+#pragma unroll
+    for (int k = 0; k < KP; ++k) a[k] = pk(0.f, 0.f);
+    u64 prod = pk(1.f, 1.f), ld = pk(0.f, 0.f);
+    FwdLayerP<KP, 0>::run(x_, a, prod, ld);
+    float l0, l1;
+    upk(ld, l0, l1);
+    const float mine = (n < n_act ? l0 : 0.f) + (n + kRecThreads < n_act ? l1 : 0.f);
+    const float tot = block_sum<kRecThreads>(mine, red);
+    if (threadIdx.x == 0) part_ld[blockIdx.x] = tot;
+}
+
+template <int KP, int k>
+struct BwdLayerP {
+    static __device__ __forceinline__ void run(const BwdCtx<KP, 2>& x_, u64 (&p)[KP], float (&gbv)[16], float (&gcv)[16]) {
+        using M_ = Mth<float>;
+        constexpr int NQ = KP / 16, q = k / 16, W = kRecPkW;
+        if ((k & 15) == 15) {
+            if (q < NQ - 1 && q >= 1) bwd_issue_quarter<KP, 2>(x_, q - 1);
+            cp_async_wait_le(q >= 1 ? 1 : 0);
+            if (kRecThreads > 128 && q < NQ - 1) __syncthreads();
+        }
+        const float* slot = x_.stage + (q & 1) * 16 * 2 * W + 2 * (k & 15) * W;
+        const float ck = x_.sc[k], ek = x_.se[k], mk = x_.smask[k];
+        const u64 one2 = pk(1.f, 1.f);
+        const u64 pin = pk(slot[0], slot[kRecThreads]);
+        const u64 t = pk(slot[W], slot[W + kRecThreads]);
+        const u64 hp = fma2(mul2(t, pk(-1.f, -1.f)), t, one2);
+        float x0, x1;
+        upk(fma2(hp, pk(ck, ck), one2), x0, x1);
+        float y0, y1;
+        upk(add2(pk(fabsf(x0), fabsf(x1)), pk(ek, ek)), y0, y1);
+        const u64 gx = mul2(pk(M_::neg_copysign(M_::rcp(y0), x0), M_::neg_copysign(M_::rcp(y1), x1)), pk(mk, mk));
+        const float m2ck = -2.f * ck;
+        const u64 gt = fma2(mul2(pk(m2ck, m2ck), gx), t, add2(p[k], pin));
+        const u64 ga = mul2(gt, hp);
+        float c0, c1, b0, b1;
+        upk(mul2(gx, hp), c0, c1);
+        upk(ga, b0, b1);
+        gcv[k & 15] = (x_.ok[0] ? c0 : 0.f) + (x_.ok[1] ? c1 : 0.f);
+        gbv[k & 15] = (x_.ok[0] ? b0 : 0.f) + (x_.ok[1] ? b1 : 0.f);
+        x_.dst[(size_t)k * x_.ldn] = b0;
+        x_.dst[(size_t)k * x_.ldn + kRecThreads] = b1;
+#pragma unroll
+        for (int i4 = 0; i4 < (k + 3) / 4; ++i4) {
+            const float4 m = *reinterpret_cast<const float4*>(&x_.sM[k * KP + 4 * i4]);
+            if (4 * i4 + 0 < k) p[4 * i4 + 0] = fma2(pk(m.x, m.x), ga, p[4 * i4 + 0]);
+            if (4 * i4 + 1 < k) p[4 * i4 + 1] = fma2(pk(m.y, m.y), ga, p[4 * i4 + 1]);
+            if (4 * i4 + 2 < k) p[4 * i4 + 2] = fma2(pk(m.z, m.z), ga, p[4 * i4 + 2]);
+            if (4 * i4 + 3 < k) p[4 * i4 + 3] = fma2(pk(m.w, m.w), ga, p[4 * i4 + 3]);
+        }
+        if ((k & 15) == 0) {
+            warp_reduce_multi<float, 16>(gbv, x_.lane);
+            warp_reduce_multi<float, 16>(gcv, x_.lane);
+            if (warp_slot_owner<16>(x_.lane)) {
+                x_.sg[k + warp_slot<16>(x_.lane)] = gbv[0];
+                x_.sg[KP + k + warp_slot<16>(x_.lane)] = gcv[0];
+            }
+        }
+        if constexpr (k > 0) BwdLayerP<KP, k - 1>::run(x_, p, gbv, gcv);
+    }
+};
+
+template <int KP>
+__global__ void __launch_bounds__(kRecThreads, 2)
+rec_bwd_pk_kernel(const float* __restrict__ PT, const float* __restrict__ TT, long long ldn, int n_act, int K,
+                  const float* __restrict__ Mrow, const float* __restrict__ c, float epsv, float* __restrict__ DT,
+                  float* __restrict__ part_g /* [gridDim][2][KP] : g_b | g_c */) {
+    extern __shared__ __align__(16) float dyn[];
+    float* sM = dyn;
+    __shared__ float sc[KP], se[KP], smask[KP];
+    __shared__ float sg[kRecThreads / 32][2 * KP];
+    constexpr int NQ = KP / 16;
+    const int n = blockIdx.x * kRecPkW + threadIdx.x;
+    BwdCtx<KP, 2> x_;
+    x_.srcp = PT + n; x_.srct = TT + n; x_.dst = DT + n; x_.ldn = ldn;
+    x_.sM = sM; x_.sc = sc; x_.se = se; x_.smask = smask; x_.sg = sg[threadIdx.x >> 5];
+    x_.stage = dyn + KP * KP + threadIdx.x;
+    x_.ok[0] = n < n_act; x_.ok[1] = n + kRecThreads < n_act;
+    x_.lane = threadIdx.x & 31;
+    for (int i = threadIdx.x; i < KP * KP / 4; i += kRecThreads) cp_async16(sM + 4 * i, Mrow + 4 * i);
+    bwd_issue_quarter<KP, 2>(x_, NQ - 1);
+    if (NQ >= 2) bwd_issue_quarter<KP, 2>(x_, NQ - 2);
+    for (int i = threadIdx.x; i < KP; i += kRecThreads) {
+        sc[i] = i < K ? c[i] : 0.f; se[i] = i < K ? epsv : 0.f; smask[i] = i < K ? 1.f : 0.f;
+    }
+    cp_async_wait_le(NQ >= 2 ? 1 : 0);
+    __syncthreads();
+    u64 p[KP];
+#pragma unroll
+    for (int k = 0; k < KP; ++k) p[k] = pk(0.f, 0.f);
+    float gcv[16], gbv[16];
+    BwdLayerP<KP, KP - 1>::run(x_, p, gbv, gcv);
+    __syncthreads();
+    if (threadIdx.x < 2 * KP) {
+        float t = 0.f;
+#pragma unroll
+        for (int w = 0; w < kRecThreads / 32; ++w) t += sg[w][threadIdx.x];
+        part_g[(size_t)blockIdx.x * 2 * KP + threadIdx.x] = t;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // Target kernel: z_K = z_0 + Y, log p(z_K), log q_0(z_0) and gz_K = dF/dz_K = -d log p / dz_K, which replaces Y in
 // place (rows: operand of product 3 as it is, and -- read sample-major by the product kernel -- of product 4).
 // Eight lanes share a sample (four samples per warp, 32 per block); a lane keeps its float4 slices of z_K in
@@ -607,10 +791,17 @@ static cudaError_t launch_target(bool bwd, const float* z0, float* Y, int n_act,
     return launch_target_v<TGT, 16>(bwd, z0, Y, n_act, D, tp, ntp, epsv, part, st);
 }
 
+// samples per block of the recurrence kernels for a chunk of n_act samples: the packed-pair kernels (256) once they
+// fill the GPU twice over, the one-sample kernels (128) below that.  NF_REC_PACKED=0/1 forces one (tuning knob).
+static inline int rec_block_samples(int n_act) {
+    if (const char* e = getenv("NF_REC_PACKED")) return atoi(e) ? kRecPkW : kRecS * kRecThreads;
+    return n_act >= 2 * 148 * 2 * kRecPkW ? kRecPkW : kRecS * kRecThreads;
+}
 template <int KP>
 static cudaError_t launch_rec(bool fwd, const Layout& L, float* ws, int n_act, int K, const float* c, float epsv, cudaStream_t st) {
     constexpr int S = kRecS;
-    const int blocks = (n_act + S * kRecThreads - 1) / (S * kRecThreads);
+    const int per_block = rec_block_samples(n_act);
+    const int blocks = (n_act + per_block - 1) / per_block;
     static bool attr_done_dev[64] = {};           // the attribute is per device
     int dev_id = 0;
     cudaGetDevice(&dev_id);
@@ -618,7 +809,18 @@ static cudaError_t launch_rec(bool fwd, const Layout& L, float* ws, int n_act, i
     if (!attr_done) {
         cudaFuncSetAttribute(rec_fwd_kernel<KP, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rec_fwd_smem<KP, S>());
         cudaFuncSetAttribute(rec_bwd_kernel<KP, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rec_bwd_smem<KP, S>());
+        cudaFuncSetAttribute(rec_fwd_pk_kernel<KP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rec_fwd_smem<KP, 2>());
+        cudaFuncSetAttribute(rec_bwd_pk_kernel<KP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rec_bwd_smem<KP, 2>());
         attr_done = true;
+    }
+    if (per_block == kRecPkW) {
+        if (fwd)
+            rec_fwd_pk_kernel<KP><<<blocks, kRecThreads, rec_fwd_smem<KP, 2>(), st>>>(ws + L.AT, L.Nc, n_act, K, ws + L.Mt, c, epsv,
+                                                                                     ws + L.TT, ws + L.part_ld);
+        else
+            rec_bwd_pk_kernel<KP><<<blocks, kRecThreads, rec_bwd_smem<KP, 2>(), st>>>(ws + L.AT, ws + L.TT, L.Nc, n_act, K, ws + L.M, c,
+                                                                                     epsv, ws + L.DT, ws + L.part_g);
+        return cudaGetLastError();
     }
     if (fwd)
         rec_fwd_kernel<KP, S><<<blocks, kRecThreads, rec_fwd_smem<KP, S>(), st>>>(ws + L.AT, L.Nc, n_act, K, ws + L.Mt, c, epsv, ws + L.TT,
@@ -715,7 +917,7 @@ int gram_piece(bool bwd, bool first, const float* z0, int n_act, long long layou
                                       nullptr, 0, 0, st, L.splits, ws + L.split56, !first)) != NF_OK) return rc;
     }
     chunk_totals_kernel<<<2 * K + 1, 256, 0, st>>>(ws + L.part_g, KP, K, bwd ? 1 : 0, ws + L.part_ld,
-                                              (n_act + kRecS * kRecThreads - 1) / (kRecS * kRecThreads), ws + L.part_t,
+                                              (n_act + rec_block_samples(n_act) - 1) / rec_block_samples(n_act), ws + L.part_t,
                                               (n_act + kTgtRows - 1) / kTgtRows, ws + L.acc);
     NF_CUDA_OK(cudaGetLastError());
     return NF_OK;
