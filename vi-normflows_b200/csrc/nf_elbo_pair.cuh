@@ -516,6 +516,11 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
     // competing for the same pipe at the same time.  Which warp owns which samples does not change.
     const int nrounds = (int)nfull + (srem > 0 ? 1 : 0);
     const int rot = (nrounds > 1 && !(flags & 1)) ? (warp >> 2) % nrounds : 0;
+    // A warp's first round may be cut in two sub-rounds (`split` samples of every lane first, the rest after): the warps
+    // of a scheduler then fall out of step, so that forward sweeps (transcendental-bound) of some run beside reverse
+    // sweeps (issue-bound) of the others.  flags bits 8.. : split of warp group (warp >> 2) & 3 = 1, 2, 3 (a nibble each).
+    const int wgrp = (warp >> 2) & 3;
+    const int split = wgrp ? (flags >> (4 + 4 * wgrp)) & 15 : 0;
     for (int rr = 0; rr < nrounds; ++rr) {
         const long long r = (rr + rot) % nrounds;
         if (rr + 1 < nrounds) {
@@ -525,29 +530,26 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
                                             : nfull * T * SMAX + gw * 32 * srem + (long long)lane * srem;
             if (eps && sn < N) asm volatile("prefetch.global.L2 [%0];" ::"l"(eps + sn * D));
         }
-        if (r < nfull) {
-            const long long start = r * T * SMAX + gw * 32 * SMAX;
-            if (start >= N) continue;
-            const long long n0 = start + (long long)lane * SMAX;
-            if (start + 32 * SMAX <= N)
-                pair_tile<D, SMAX, SMAX, ST, SG, NT, TGT, false>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p, rng, gst_t);
-            else
-                pair_tile<D, SMAX, SMAX, ST, SG, NT, TGT, true>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p, rng, gst_t);
-            continue;
-        }
-        const long long start = nfull * T * SMAX + gw * 32 * srem;
-        const long long n0 = start + (long long)lane * srem;
-        if (start < N) {
-            const bool full = start + 32LL * srem <= N;
-#define NF_PR_REM(S_)                                                                                                        \
-    if (SMAX > S_ && srem == S_) {                                                                                           \
-        if (full) pair_tile<D, (S_ < SMAX ? S_ : 2), SMAX, ST, SG, NT, TGT, false>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p, rng, gst_t); \
-        else pair_tile<D, (S_ < SMAX ? S_ : 2), SMAX, ST, SG, NT, TGT, true>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p, rng, gst_t);      \
+        const int sr = r < nfull ? SMAX : srem;                   // samples per lane in this round
+        const long long start = (r < nfull ? r : nfull) * T * SMAX + gw * 32 * sr;
+        if (start >= N) continue;
+        const bool full = start + 32LL * sr <= N;
+        const long long nl = start + (long long)lane * sr;
+        const int first = (rr == 0 && split > 0 && split < sr) ? split : sr;
+        for (int off = 0; off < sr;) {
+            const int sc = off == 0 ? first : sr - off;
+            const long long n0 = nl + off;
+#define NF_PR_RUN(S_)                                                                                                        \
+    if (SMAX >= S_ && sc == S_) {                                                                                            \
+        if (full) pair_tile<D, (S_ <= SMAX ? S_ : 2), SMAX, ST, SG, NT, TGT, false>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p, rng, gst_t); \
+        else pair_tile<D, (S_ <= SMAX ? S_ : 2), SMAX, ST, SG, NT, TGT, true>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p, rng, gst_t);      \
     }
-            NF_PR_REM(2)
-            NF_PR_REM(4)
-            NF_PR_REM(6)
-#undef NF_PR_REM
+            NF_PR_RUN(2)
+            NF_PR_RUN(4)
+            NF_PR_RUN(6)
+            NF_PR_RUN(8)
+#undef NF_PR_RUN
+            off += sc;
         }
     }
 
