@@ -279,7 +279,10 @@ def run_ours(args):
                               process_group=dist.group.WORLD if world > 1 else None)
     params = sem.pack(W, U, B)
     host = [torch.randn(N_PER_GPU, DIM, dtype=torch.float32).pin_memory() for _ in range(4)]
-    for i in range(3):
+    # warm-up: the first ~100 uploads after idle run at a fraction of the PCIe rate (the link trains up under load:
+    # 540 -> 230 us per 8 MiB call over the first 100 calls, tools/e2e_stages.py with NF_SESSION_TIMING=1), so the host-API
+    # legs are warmed by call count like the device leg is by time
+    for i in range(max(3, args.warmup, 150)):
         obj.value_and_grad(params, host[i % 4])
     barrier()
     t0 = time.perf_counter()

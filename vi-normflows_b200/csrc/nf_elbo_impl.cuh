@@ -23,6 +23,7 @@
 #pragma once
 #include <cstdio>
 #include <cstdlib>
+#include <ctime>
 #include <mutex>
 #include <vector>
 #include "nf_common.cuh"
@@ -868,6 +869,10 @@ static int session_elbo_host(Session* S, const T* eps_host, int64_t N, const T* 
                              const T* tp_host, int ntp, T epsv, int backward, T* out_host) {
     if (!S || S->elem != sizeof(T) || N < 0 || N > S->cap || !lc_host || !out_host || (N > 0 && !eps_host)) return NF_ERR_INVALID;
     if (ntp < 0 || (size_t)ntp > S->tp_cap || (ntp > 0 && !tp_host)) return NF_ERR_INVALID;
+    static const bool timing = getenv("NF_SESSION_TIMING") != nullptr;      // debug aid: host-side time stamps of this call
+    double tq[8] = {0};
+    auto now = []() { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e6 + ts.tv_nsec * 1e-3; };
+    if (timing) tq[0] = now();
     NF_CUDA_OK(cudaSetDevice(S->dev));
     const int D = S->D, K = S->K;
     const int nlc = 2 * K * D + 2 * K;
@@ -939,14 +944,19 @@ static int session_elbo_host(Session* S, const T* eps_host, int64_t N, const T* 
         if (rc != NF_OK) return rc;
         rows += nb;
     }
+    if (timing) tq[1] = now();
     T* out = reinterpret_cast<T*>(S->out_dev);
     rc = elbo_finish<T>(backward != 0, partials, rows, D, K, out, out + 3, out + 3 + K * D, out + 3 + 2 * K * D,
                         out + 3 + 2 * K * D + K, S->s_comp);
     if (rc != NF_OK) return rc;
     NF_CUDA_OK(cudaMemcpyAsync(S->out_pin, out, (size_t)S->n_out * sizeof(T), cudaMemcpyDeviceToHost, S->s_comp));
+    if (timing) tq[2] = now();
     NF_CUDA_OK(cudaStreamSynchronize(S->s_comp));
+    if (timing) tq[3] = now();
     const T* op = reinterpret_cast<const T*>(S->out_pin);
     for (int i = 0; i < S->n_out; ++i) out_host[i] = op[i];
+    if (timing) fprintf(stderr, "[nf session] N=%lld enqueue chunks %.1f us | finish+D2H enqueue %.1f | wait %.1f | total %.1f\n", (long long)N,
+                        tq[1] - tq[0], tq[2] - tq[1], tq[3] - tq[2], now() - tq[0]);
     return NF_OK;
 }
 
