@@ -10,7 +10,7 @@ import numpy as np, torch
 from nfcore import ops, semantics as sem, _lib
 
 lg = int(sys.argv[1]) if len(sys.argv) > 1 else 20
-N, K = 1 << lg, 32
+N, K = (1 << lg) if lg < 64 else lg, 32       # lg >= 64: the sample count itself
 dev = torch.device('cuda:0')
 rs = np.random.RandomState(7)
 W = 0.1 + 0.01 * rs.randn(K, 2); U = 0.1 + 0.01 * rs.randn(K, 2); B = 0.1 * np.ones(K)
@@ -36,6 +36,14 @@ for rep in range(3):
         wt = (full[200 + 4 * b:200 + 4 * b + 4].reshape(-1)[:32] - st[:, 0].min()) / 1e3
         wt = wt[wt > 0]
         print('   block %d: warps finish at ' % b + ' '.join('%.1f' % x for x in wt))
+    ph = (full[216:232].reshape(16, 2, 4) - t0) / 1e3          # block 0: [warp][round][start, forward done, target done, reverse done]
+    for rr in range(2):
+        v = ph[:, rr]
+        if (v[:, 3] > 0).all():
+            print('   block 0 round %d: start %.1f..%.1f | forward %.2f..%.2f us | target %.2f..%.2f | reverse %.2f..%.2f  (per warp: fwd/tgt/rev)'
+                  % (rr, v[:, 0].min(), v[:, 0].max(), (v[:, 1] - v[:, 0]).min(), (v[:, 1] - v[:, 0]).max(), (v[:, 2] - v[:, 1]).min(),
+                     (v[:, 2] - v[:, 1]).max(), (v[:, 3] - v[:, 2]).min(), (v[:, 3] - v[:, 2]).max()))
+            print('      warps 0,1,4,5 start/fwd/rev: ' + ' '.join('%.1f/%.1f/%.1f' % (v[w, 0], v[w, 1] - v[w, 0], v[w, 3] - v[w, 2]) for w in (0, 1, 4, 5)))
     print('   last block %d: ticket %.2f | rows loaded and staged %.2f | vector built %.2f | outputs written %.2f us'
           % (last, rel[last, 3], (st[last, 6] - t0) / 1e3, (st[last, 7] - t0) / 1e3, rel[last, 4]))
     print('N=2^%d  entry %.1f..%.1f us | set-up done %.1f..%.1f | samples done %.1f..%.1f (median %.1f) | ticket %.1f..%.1f | finalize done %.1f (block %d; its ticket at %.1f)'

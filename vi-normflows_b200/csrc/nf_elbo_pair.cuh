@@ -190,7 +190,8 @@ __device__ __forceinline__ void pair_tile(const float* __restrict__ eps, long lo
                                           u64* __restrict__ hist_t, uint32_t taddr, float* __restrict__ acc_w, int lane,
                                           float* __restrict__ stg_w /* staging area of this warp */, float& sum_q, float& sum_p,
                                           const RngDesc& rng /* eps == NULL: the samples are drawn here (nf_philox.cuh) */,
-                                          u64* __restrict__ gst_t /* this thread's column of the global-memory history [K][SG/2][NT] */) {
+                                          u64* __restrict__ gst_t /* this thread's column of the global-memory history [K][SG/2][NT] */,
+                                          unsigned long long* ph = nullptr /* phase stamps (tuning aid), else NULL */) {
     using M = Mth<float>;
     constexpr int V = 2 * D + 2;
     constexpr int P = S / 2;                        // pairs this round
@@ -262,6 +263,7 @@ __device__ __forceinline__ void pair_tile(const float* __restrict__ eps, long lo
         }
         if (!MASKED) ep[0] = pk(epsv, epsv);
     }
+    if (ph) ph[0] = gtime();
     // ---- forward over the K layers (get_data.py:104-109); the log-det is left to the reverse sweep ----
     for (int k = 0; k < K; ++k) {
         u64 rf[recf_pairs<D>()];
@@ -294,6 +296,7 @@ __device__ __forceinline__ void pair_tile(const float* __restrict__ eps, long lo
         if (PT > 0) Tm<2 * (PT > 0 ? PT : 1)>::st(taddr + k * ST, tt);
     }
     if (PT > 0) tm_wait_st();
+    if (ph) ph[1] = gtime();
     // ---- target: log(eps + target(z_K)) and the reverse seed gz = -d log p / dz ----
 #pragma unroll
     for (int p = 0; p < P; ++p) {
@@ -312,6 +315,7 @@ __device__ __forceinline__ void pair_tile(const float* __restrict__ eps, long lo
             for (int d = 0; d < D; ++d) gz[p][d] = pk(ga[d], gb[d]);
         }
     }
+    if (ph) ph[2] = gtime();
     // ---- reverse sweep: restores z, accumulates log|det| and the gradient partials ----
     // Layer k+1's partials are merged (pair halves added) at the end of its iteration and reduced across the warp
     // inside iteration k, next to arithmetic they do not depend on.  History held in tensor memory is fetched one
@@ -411,6 +415,7 @@ __device__ __forceinline__ void pair_tile(const float* __restrict__ eps, long lo
         layer(k - 1, tb, ta, gb_, ga_);
     }
     if (k == 0) layer(0, ta, tb, ga_, gb_);
+    if (ph) ph[3] = gtime();
 #pragma unroll
     for (int p = 0; p < P; ++p) {
         float a, b;
@@ -536,13 +541,15 @@ elbo_pair_kernel(const float* __restrict__ eps, long long N, int K, const float*
         const bool full = start + 32LL * sr <= N;
         const long long nl = start + (long long)lane * sr;
         const int first = (rr == 0 && split > 0 && split < sr) ? split : sr;
+        // tuning: phase stamps of the warps of block 0 (rows 216.. of the stamp buffer: [warp][round < 2][start, forward, target, reverse])
+        unsigned long long* ph = (stamps && blockIdx.x == 0 && lane == 0 && rr < 2) ? stamps + (216 + warp) * 8 + 4 * rr : nullptr;
         for (int off = 0; off < sr;) {
             const int sc = off == 0 ? first : sr - off;
             const long long n0 = nl + off;
 #define NF_PR_RUN(S_)                                                                                                        \
     if (SMAX >= S_ && sc == S_) {                                                                                            \
-        if (full) pair_tile<D, (S_ <= SMAX ? S_ : 2), SMAX, ST, SG, NT, TGT, false>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p, rng, gst_t); \
-        else pair_tile<D, (S_ <= SMAX ? S_ : 2), SMAX, ST, SG, NT, TGT, true>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p, rng, gst_t);      \
+        if (full) pair_tile<D, (S_ <= SMAX ? S_ : 2), SMAX, ST, SG, NT, TGT, false>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p, rng, gst_t, ph); \
+        else pair_tile<D, (S_ <= SMAX ? S_ : 2), SMAX, ST, SG, NT, TGT, true>(eps, n0, N, K, lcf, lcb, tp, ntp, epsv, hist_t, taddr, acc_w, lane, stg_w, sum_q, sum_p, rng, gst_t, ph);      \
     }
             NF_PR_RUN(2)
             NF_PR_RUN(4)
