@@ -101,6 +101,42 @@ def test_tensor_core_gemm_is_float32_accurate(M, N, K, act):
     assert _rel(C.double().cpu().numpy(), ref.cpu().numpy()) < 1e-4
 
 
+@pytest.mark.parametrize('M,N,K,act,out', [(128 * 700, 64, 64, 0, 'CT'), (128 * 650 + 37, 64, 96, 1, 'C'), (128 * 300, 200, 64, 0, 'C'),
+                                           (128 * 600, 40, 256, 2, 'CT'), (128 * 640 + 5, 64, 64, 0, 'C'), (128 * 333 + 77, 100, 32, 0, 'CT')])
+def test_persistent_gemm_matches_per_tile_kernel(M, N, K, act, out, monkeypatch):
+    """Short contraction, thousands of tiles, one output (C or C^T): the persistent kernel (tile loop per CTA, double-buffered
+    TMEM accumulator, bulk tensor stores).  Same MMAs in the same order as the per-tile kernel, so the two must agree bit
+    for bit, and both with float64; rows / columns past M / N must stay untouched."""
+    import ctypes
+    import nfcore
+    lib = nfcore.load()
+    torch.manual_seed(M % 1000 + N + K)
+    dev = 'cuda:0'
+    A = torch.randn(M, K, device=dev)
+    B = torch.randn(N, K, device=dev) / K ** 0.5
+    bias = torch.randn(N, device=dev)
+    p = lambda t: ctypes.c_void_p(t.data_ptr()) if t is not None else None
+    pad = 8                                   # guard rows / columns around the output: must keep their fill value
+    ldo = ((N if out == 'C' else M) + pad + 3) // 4 * 4
+    outs = []
+    for persist in ('1', '0'):
+        monkeypatch.setenv('NF_GEMM_PERSIST', persist)
+        buf = torch.full(((M if out == 'C' else N) + pad, ldo), -7.0, device=dev)
+        C, CT = (buf, None) if out == 'C' else (None, buf)
+        rc = lib.nf_gemm_tn_tf32x3(p(A), K, p(B), K, M, N, K, p(C), ldo if out == 'C' else 0, p(CT), ldo if out == 'CT' else 0, p(bias), act,
+                                   ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+        assert rc == 0
+        torch.cuda.synchronize()
+        outs.append(buf)
+    assert torch.equal(outs[0], outs[1])
+    got = outs[0][:M, :N] if out == 'C' else outs[0][:N, :M].T
+    guard = torch.cat([outs[0][(M if out == 'C' else N):].reshape(-1), outs[0][:, (N if out == 'C' else M):].reshape(-1)])
+    assert bool((guard == -7.0).all())
+    ref = A.double() @ B.double().T + bias.double()
+    ref = torch.relu(ref) if act == 1 else (torch.sigmoid(ref) if act == 2 else ref)
+    assert _rel(got.double().cpu().numpy(), ref.cpu().numpy()) <= 5e-5
+
+
 def test_bernoulli_ll_matches_oracle():
     from nfcore import ops
     from oracle import planar_np as pn

@@ -43,10 +43,23 @@ def shared_case(name, K, D, N, target, tname, tparams=None, steps=50, dtype=torc
     dt = timed(lambda i: ops.planar_elbo(eps[i % nbuf], *a, tname, tp, out=out), steps)
     roof, fl, mu = roofline(K, D, target)
     v = N / dt
-    note = '  [matrix-product path; the bound shown is the CUDA-core bound of the direct algorithm]' if (D >= 32 and dtype == torch.float32) else ''
+    note, extra = '', {}
+    if D >= 32 and dtype == torch.float32:
+        # what runs is the matrix-product chain.  Its own bounds per sample: HBM traffic of the chain as it is
+        # decomposed (every [N][D] and [KP][N] intermediate written once and read by its consumers: 32 D + 44 KP bytes),
+        # and the tensor time of five products at three TF32 passes (5 * 2 K D * 3 flop at the nominal dense TF32 rate)
+        KP = 16 if K <= 16 else (32 if K <= 32 else 64)
+        hbm_bytes = 32 * D + 44 * KP
+        t_hbm = hbm_bytes / 6455.9e9
+        t_tc = 30.0 * K * D / 1.1e15
+        extra = {'chain_hbm_bytes_per_sample': hbm_bytes, 'frac_chain_hbm': t_hbm * v, 'frac_tf32x3': t_tc * v}
+        note = ('  [matrix-product path: %.2f of the HBM time of its own chain (%d B/sample), %.2f of the 3-pass TF32 tensor time; '
+                'the roofline column is the CUDA-core bound of the direct algorithm]' % (t_hbm * v, hbm_bytes, t_tc * v))
     print('%-34s K=%-3d D=%-4d N=2^%-2d %9.1f us/step %10.3e samples/s  roofline %.3e  frac %.3f%s' %
           (name, K, D, N.bit_length() - 1, dt * 1e6, v, roof, v / roof, note), flush=True)
-    return {'case': name, 'K': K, 'D': D, 'N': N, 'us_per_step': dt * 1e6, 'samples_per_s': v, 'roofline': roof, 'frac': v / roof}
+    r = {'case': name, 'K': K, 'D': D, 'N': N, 'us_per_step': dt * 1e6, 'samples_per_s': v, 'roofline': roof, 'frac': v / roof}
+    r.update(extra)
+    return r
 
 
 def main():

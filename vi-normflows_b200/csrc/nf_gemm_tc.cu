@@ -21,6 +21,7 @@
 #include <cuda.h>
 #include <cudaTypedefs.h>
 #include "nf_common.cuh"
+#include "nf_launch.cuh"
 
 namespace nf {
 namespace tc {
@@ -57,6 +58,11 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     while (!mbar_try_wait(bar, parity)) {}
+}
+// the same with a pause between probes: for roles that share an SM with working warps for a long time (a spinning warp
+// takes issue slots and shared-memory pipe slots from them)
+__device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity) {
+    while (!mbar_try_wait(bar, parity)) __nanosleep(40);
 }
 __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
@@ -317,17 +323,20 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
                   "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
                 : "r"(taddr) : "memory");
             asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            // bias and activation with the decisions outside the element loops.  Columns past N: bias slots are zero and the
+            // values are never stored; relu(0) = 0 as before, sigmoid is applied only below N
+            float v[16];
 #pragma unroll
-            for (int i = 0; i < 16; ++i) {
-                const int n = n0 + c0 + i;
-                float v = nkb > 0 ? __uint_as_float(r[i]) : 0.f;
-                if (n < p.N) {
-                    v += sbias[c0 + i];
-                    if (p.act == EPI_ACT_RELU) v = v > 0.f ? v : 0.f;
-                    else if (p.act == EPI_ACT_SIGMOID) v = 1.f / (1.f + __expf(-v));
-                }
-                slab[lane * 65 + c0 + i] = v;
+            for (int i = 0; i < 16; ++i) v[i] = (nkb > 0 ? __uint_as_float(r[i]) : 0.f) + sbias[c0 + i];
+            if (p.act == EPI_ACT_RELU) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], 0.f);
+            } else if (p.act == EPI_ACT_SIGMOID) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) v[i] = (n0 + c0 + i < p.N) ? 1.f / (1.f + __expf(-v[i])) : v[i];
             }
+#pragma unroll
+            for (int i = 0; i < 16; ++i) slab[lane * 65 + c0 + i] = v[i];
         }
         __syncwarp();
         if (dbg && t == 64) p.dbg[2] = clock64();
@@ -393,6 +402,272 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(tmem_cols) : "memory");
 }
 
+// ------------------------------------------------------------------------------------------------
+// Persistent variant for products with a short contraction and many output tiles (the [N][D] x [D][K] products of the
+// matrix-product free-energy chain: two to eight k-blocks per tile, thousands of tiles).  In the kernel above a CTA lives
+// for one tile, so its prologue (barriers, TMEM allocation), the latency of its first loads and its epilogue are paid per
+// tile and covered only by the other CTAs of the SM; such a product runs at half of HBM speed.  Here a CTA walks over
+// tiles blockIdx.x, blockIdx.x + gridDim.x, ...: the shared-memory ring keeps running across tile boundaries, the
+// accumulator is double-buffered in tensor memory, and four more warps run the epilogue of tile j while the loads,
+// splits and MMAs of tile j+1 proceed.  A operand through tensor memory only; no split-K.
+//   warp 0 TMA producer | warp 1 MMA issue | warps 2-3 split B | warps 4-7 split A into TMEM | warps 8-11 epilogue
+// TMEM columns: [0,64) accumulator 0 | [64,128) accumulator 1 | [128 + 64 s, +64) A of stage s (hi | lo)
+constexpr int P_THREADS = 384;
+constexpr int P_STAGES = 2;
+constexpr int P_ACC_COLS = 128;
+constexpr int P_SLAB_BYTES = BM * BN * 4;            // staging area of the epilogue's bulk stores
+constexpr int P_SMEM_BYTES = P_STAGES * STAGE_BYTES_TS + P_SLAB_BYTES + 1024;
+
+__global__ void __launch_bounds__(P_THREADS, 2)
+gemm_tf32x3_persist_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                           const __grid_constant__ CUtensorMap map_a2, const __grid_constant__ CUtensorMap map_a_half,
+                           const __grid_constant__ CUtensorMap map_out /* C: {32 x 128} boxes, 128-byte swizzle; else C^T: {128 x 64} boxes */, Params p) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    __shared__ uint64_t full_bar[P_STAGES], split_bar[P_STAGES], empty_bar[P_STAGES], acc_full[2], acc_empty[2];
+    __shared__ uint32_t tmem_base;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tiles_n = (p.N + BN - 1) / BN, tiles_m = (p.M + BM - 1) / BM, tiles = tiles_m * tiles_n;
+    const int nkb = (p.K + BK - 1) / BK;
+    constexpr uint32_t tmem_cols = 256;
+
+    if (threadIdx.x == 32) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a2) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_out) : "memory");
+    }
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < P_STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&split_bar[s], SPLIT_THREADS);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int b = 0; b < 2; ++b) { mbar_init(&acc_full[b], 1); mbar_init(&acc_empty[b], 128); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base)), "r"(tmem_cols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_d = tmem_base;
+    // bring-up aid (NF_GEMM_DBG): cycles CTA 0's role leaders spend waiting on barriers, and their total
+    const bool dbg = p.dbg && blockIdx.x == 0 && lane == 0;
+    long long t_wait = 0;
+    const long long t_begin = dbg ? clock64() : 0;
+#define NF_PWAIT(bar, par) do { if (dbg) { const long long c0_ = clock64(); mbar_wait_relaxed(bar, par); t_wait += clock64() - c0_; } else mbar_wait_relaxed(bar, par); } while (0)
+
+    if (warp == 0) {
+        // ---------------- TMA producer ----------------
+        if (lane == 0) {
+            int g = 0;
+            for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
+                const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * BN;
+                for (int kb = 0; kb < nkb; ++kb, ++g) {
+                    const int s = g % P_STAGES, it = g / P_STAGES;
+                    if (it > 0) NF_PWAIT(&empty_bar[s], (it - 1) & 1);
+                    uint8_t* st = smem + (size_t)s * STAGE_BYTES_TS;
+                    mbar_expect_tx(&full_bar[s], A_BYTES + B_BYTES);
+                    const int a1_rows = p.m_split - m0;
+                    if (a1_rows < BM) {
+                        if (a1_rows > 0) tma_load_2d(st, &map_a_half, kb * BK, m0, &full_bar[s]);
+                        for (int q = a1_rows > 0 ? 2 : 0; q < 4; ++q)
+                            tma_load_2d(st + q * 4096, &map_a2, m0 + 32 * q - p.m_split, kb * BK, &full_bar[s]);
+                    } else {
+                        tma_load_2d(st, &map_a, kb * BK, m0, &full_bar[s]);
+                    }
+                    tma_load_2d(st + A_BYTES, &map_b, kb * BK, n0, &full_bar[s]);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ---------------- MMA issuer ----------------
+        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+        int g = 0, j = 0;
+        for (int t = blockIdx.x; t < tiles; t += gridDim.x, ++j) {
+            const int b = j & 1, u = j >> 1;
+            if (u > 0) NF_PWAIT(&acc_empty[b], (u - 1) & 1);        // the epilogue has drained this accumulator
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t acc = tmem_d + 64u * (uint32_t)b;
+            for (int kb = 0; kb < nkb; ++kb, ++g) {
+                const int s = g % P_STAGES, it = g / P_STAGES;
+                NF_PWAIT(&split_bar[s], it & 1);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                if (lane == 0) {
+                    const uint32_t b_hi = smem_u32(smem + (size_t)s * STAGE_BYTES_TS) + A_BYTES;
+                    const uint32_t b_lo = b_hi + B_BYTES;
+                    const uint32_t ta_hi = tmem_d + P_ACC_COLS + (uint32_t)s * 64u, ta_lo = ta_hi + 32u;
+#pragma unroll
+                    for (int k = 0; k < BK / 8; ++k) {
+                        const uint32_t off = k * 32;
+                        umma_tf32_ts(acc, ta_hi + 8u * k, umma_desc(b_hi + off), idesc, (kb | k) != 0);
+                        umma_tf32_ts(acc, ta_lo + 8u * k, umma_desc(b_hi + off), idesc, true);
+                        umma_tf32_ts(acc, ta_hi + 8u * k, umma_desc(b_lo + off), idesc, true);
+                    }
+                    umma_commit(&empty_bar[s]);
+                    if (kb == nkb - 1) umma_commit(&acc_full[b]);
+                }
+                __syncwarp();
+            }
+        }
+    } else if (warp < 8) {
+        // ---------------- split hi/lo: warps 2-3 B in shared memory, warps 4-7 A into tensor memory ----------------
+        const int t64 = threadIdx.x - 64;
+        int g = 0;
+        for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
+            const int m0 = (t / tiles_n) * BM;
+            for (int kb = 0; kb < nkb; ++kb, ++g) {
+                const int s = g % P_STAGES, it = g / P_STAGES;
+                NF_PWAIT(&full_bar[s], it & 1);
+                uint8_t* st = smem + (size_t)s * STAGE_BYTES_TS;
+                if (warp < 4) {
+#pragma unroll 4
+                    for (int i = t64; i < B_BYTES / 16; i += 64) {
+                        uint8_t* hi = st + A_BYTES + (size_t)i * 16;
+                        float4 v = *reinterpret_cast<float4*>(hi);
+                        float4 h, l;
+                        h.x = __uint_as_float(__float_as_uint(v.x) & 0xFFFFE000u); l.x = v.x - h.x;
+                        h.y = __uint_as_float(__float_as_uint(v.y) & 0xFFFFE000u); l.y = v.y - h.y;
+                        h.z = __uint_as_float(__float_as_uint(v.z) & 0xFFFFE000u); l.z = v.z - h.z;
+                        h.w = __uint_as_float(__float_as_uint(v.w) & 0xFFFFE000u); l.w = v.w - h.w;
+                        *reinterpret_cast<float4*>(hi) = h;
+                        *reinterpret_cast<float4*>(hi + B_BYTES) = l;
+                    }
+                } else {
+                    const int q = warp - 4, row = 32 * q + lane;
+                    const uint8_t* rp = st + (size_t)row * 128;
+                    const float* cp = reinterpret_cast<const float*>(st + q * 4096) + lane;
+                    const bool km = m0 + 32 * q >= p.m_split;
+                    const uint32_t ta = tmem_base + ((uint32_t)(32 * q) << 16) + P_ACC_COLS + (uint32_t)s * 64u;
+#pragma unroll
+                    for (int h2 = 0; h2 < 2; ++h2) {
+                        uint32_t hi[16], lo[16];
+                        float x[16];
+                        if (km) {
+#pragma unroll
+                            for (int e = 0; e < 16; ++e) x[e] = cp[(16 * h2 + e) * 32];
+                        } else {
+#pragma unroll
+                            for (int jj = 0; jj < 4; ++jj) {
+                                const float4 v = *reinterpret_cast<const float4*>(rp + 16 * ((4 * h2 + jj) ^ (row & 7)));
+                                x[4 * jj] = v.x; x[4 * jj + 1] = v.y; x[4 * jj + 2] = v.z; x[4 * jj + 3] = v.w;
+                            }
+                        }
+#pragma unroll
+                        for (int e = 0; e < 16; ++e) {
+                            const uint32_t hb = __float_as_uint(x[e]) & 0xFFFFE000u;
+                            hi[e] = hb;
+                            lo[e] = __float_as_uint(x[e] - __uint_as_float(hb));
+                        }
+                        tmem_st16(ta + 16u * h2, hi);
+                        tmem_st16(ta + 32u + 16u * h2, lo);
+                    }
+                    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+                    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                }
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                mbar_arrive(&split_bar[s]);
+            }
+        }
+    } else {
+        // ---------------- epilogue: warp q = warp - 8 owns TMEM lanes 32q .. 32q+31 ----------------
+        // The tile goes to global memory as bulk tensor stores: the four warps lay it out in shared memory (C: two
+        // 128-byte-swizzled boxes of 32 columns; C^T: [64 n][128 m], consecutive lanes = consecutive m), one thread
+        // issues the store(s).  Rows and columns past M / N are clipped by the tensor map.
+        const int q = warp - 8;
+        uint8_t* stg = smem + (size_t)P_STAGES * STAGE_BYTES_TS;
+        const bool to_ct = p.CT != nullptr;
+        const int row = 32 * q + lane;                    // row of the tile this thread holds
+        int j = 0;
+        for (int t = blockIdx.x; t < tiles; t += gridDim.x, ++j) {
+            const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * BN;
+            const int b = j & 1, u = j >> 1;
+            NF_PWAIT(&acc_full[b], u & 1);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const long long e0_ = dbg ? clock64() : 0;
+            if (j > 0) {
+                // the previous tile's store must have read the staging area before it is overwritten
+                if (threadIdx.x == 8 * 32) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+            }
+            const long long e1_ = dbg ? clock64() : 0;
+#pragma unroll
+            for (int c0 = 0; c0 < BN; c0 += 16) {
+                uint32_t r[16];
+                const uint32_t taddr = tmem_d + ((uint32_t)(32 * q) << 16) + 64u * (uint32_t)b + (uint32_t)c0;
+                asm volatile(
+                    "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                    : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+                      "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                    : "r"(taddr) : "memory");
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                // bias and activation with the decisions outside the element loops (columns past N are clipped by the store)
+                float v[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+                if (p.bias) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) v[i] += (n0 + c0 + i < p.N) ? __ldg(p.bias + n0 + c0 + i) : 0.f;
+                }
+                if (p.act == EPI_ACT_RELU) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], 0.f);
+                } else if (p.act == EPI_ACT_SIGMOID) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) v[i] = 1.f / (1.f + __expf(-v[i]));
+                }
+                if (to_ct) {
+                    float* dst = reinterpret_cast<float*>(stg) + (size_t)c0 * BM + row;
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) dst[(size_t)i * BM] = v[i];
+                } else {
+                    // box = columns [32 h, 32 h + 32) of the tile: 128 rows of 128 bytes, 16-byte chunk c of row r at c ^ (r % 8)
+                    uint8_t* box = stg + (size_t)(c0 / 32) * (BM * 128) + (size_t)row * 128;
+#pragma unroll
+                    for (int c4 = 0; c4 < 4; ++c4) {
+                        const int chunk = (c0 % 32) / 4 + c4;
+                        *reinterpret_cast<float4*>(box + 16 * (chunk ^ (row & 7))) = make_float4(v[4 * c4], v[4 * c4 + 1], v[4 * c4 + 2], v[4 * c4 + 3]);
+                    }
+                }
+            }
+            const long long e2_ = dbg ? clock64() : 0;
+            // the accumulator has been read: hand the buffer back, publish the staged tile to the async proxy
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            mbar_arrive(&acc_empty[b]);
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (threadIdx.x == 8 * 32) {
+                if (to_ct) {
+                    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];" ::"l"(&map_out), "r"(m0), "r"(n0),
+                                 "r"(smem_u32(stg)) : "memory");
+                } else {
+                    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];" ::"l"(&map_out), "r"(n0), "r"(m0),
+                                 "r"(smem_u32(stg)) : "memory");
+                    if (n0 + 32 < p.N)
+                        asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];" ::"l"(&map_out), "r"(n0 + 32),
+                                     "r"(m0), "r"(smem_u32(stg + BM * 128)) : "memory");
+                }
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+            if (dbg && warp == 8) { const long long e3_ = clock64(); p.dbg[10] += e1_ - e0_; p.dbg[11] += e2_ - e1_; p.dbg[12] += e3_ - e2_; }
+        }
+        if (threadIdx.x == 8 * 32) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    }
+#undef NF_PWAIT
+    if (dbg && (warp == 0 || warp == 1 || warp == 2 || warp == 4 || warp == 8)) {
+        const int role = warp == 0 ? 0 : (warp == 1 ? 1 : (warp == 2 ? 2 : (warp == 4 ? 3 : 4)));
+        p.dbg[2 * role] = t_wait;
+        p.dbg[2 * role + 1] = clock64() - t_begin;
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 1)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(tmem_cols) : "memory");
+}
+
 static PFN_cuTensorMapEncodeTiled get_encoder() {
     static PFN_cuTensorMapEncodeTiled fn = nullptr;
     if (!fn) {
@@ -407,28 +682,29 @@ static PFN_cuTensorMapEncodeTiled get_encoder() {
 // row-major [rows][cols] float matrix with leading dimension ld (elements); box = box_rows x 32 columns.
 // Encoding a map costs several microseconds on the host; the MLP re-uses the same buffers step after
 // step (the framework's caching allocator hands the same addresses back), so maps are memoised.
-struct MapKey { const float* base; long long rows, cols, ld; int box_rows; bool swz; };
-static bool make_map(CUtensorMap* map, const float* base, long long rows, long long cols, long long ld, int box_rows, bool swz = true) {
+struct MapKey { const float* base; long long rows, cols, ld; int box_rows; bool swz; int box_cols; };
+static bool make_map(CUtensorMap* map, const float* base, long long rows, long long cols, long long ld, int box_rows, bool swz = true,
+                     int box_cols = BK) {
     constexpr int kCache = 128;
     static thread_local MapKey keys[kCache];
     static thread_local CUtensorMap vals[kCache];
     static thread_local int used = 0, next = 0;
     for (int i = 0; i < used; ++i) {
         const MapKey& k = keys[i];
-        if (k.base == base && k.rows == rows && k.cols == cols && k.ld == ld && k.box_rows == box_rows && k.swz == swz) { *map = vals[i]; return true; }
+        if (k.base == base && k.rows == rows && k.cols == cols && k.ld == ld && k.box_rows == box_rows && k.swz == swz && k.box_cols == box_cols) { *map = vals[i]; return true; }
     }
     PFN_cuTensorMapEncodeTiled enc = get_encoder();
     if (!enc) return false;
     cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
     cuuint64_t gstride[1] = {(cuuint64_t)ld * 4};
-    cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+    cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
     cuuint32_t estr[2] = {1, 1};
     if (enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstride, box, estr,
             CU_TENSOR_MAP_INTERLEAVE_NONE, swz ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
         return false;
     const int slot = used < kCache ? used++ : (next++ % kCache);
-    keys[slot] = MapKey{base, rows, cols, ld, box_rows, swz};
+    keys[slot] = MapKey{base, rows, cols, ld, box_rows, swz, box_cols};
     vals[slot] = *map;
     return true;
 }
@@ -513,6 +789,39 @@ int tc_gemm_stacked_f32(const float* A, long long lda, int M1, const float* A2, 
         attr_done = true;
     }
     dim3 grid((N + tc::BN - 1) / tc::BN, (M + tc::BM - 1) / tc::BM, splits);
+    // short contraction, many tiles, no split: the persistent kernel (NF_GEMM_PERSIST=0 keeps the per-tile one)
+    const char* pe = getenv("NF_GEMM_PERSIST");                  // read per call: the tests compare the two kernels in one process
+    const bool persist_on = !(pe && atoi(pe) == 0);
+    const long long n_tiles = (long long)grid.x * grid.y;
+    const DevInfo di = dev_info();
+    const bool one_out = (C != nullptr) != (CT != nullptr);      // the persistent kernel stores one of C / C^T, by bulk tensor stores
+    const float* outp = C ? C : CT;
+    const long long ldo = C ? ldc : ldct;
+    CUtensorMap mo;
+    bool persist = persist_on && atmem && !via_ws && splits == 1 && di.ok && nkb_all <= 16 && n_tiles >= 4LL * di.sms && n_tiles < (1LL << 30) &&
+                   one_out && mask == 0 && (ldo % 4) == 0 && ((uintptr_t)outp & 15) == 0 &&
+                   ((C ? N : M) % 4) == 0;       // bulk tensor stores write whole 16-byte units of a row
+    if (persist) persist = C ? tc::make_map(&mo, C, M, N, ldc, tc::BM, true, 32) : tc::make_map(&mo, CT, N, M, ldct, tc::BN, false, tc::BM);
+    if (persist) {
+        static bool pattr_done_dev[64] = {};
+        bool& pattr_done = pattr_done_dev[dev_id & 63];
+        if (!pattr_done) {
+            NF_CUDA_OK(cudaFuncSetAttribute(tc::gemm_tf32x3_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::P_SMEM_BYTES));
+            pattr_done = true;
+        }
+        tc::gemm_tf32x3_persist_kernel<<<2 * di.sms, tc::P_THREADS, tc::P_SMEM_BYTES, st>>>(ma, mb, ma2, mah, mo, p);
+        NF_CUDA_OK(cudaGetLastError());
+        if (dbg_buf) {
+            cudaStreamSynchronize(st);
+            fprintf(stderr, "[gemm persist dbg] M=%d N=%d K=%d tiles=%lld (per CTA %.1f) | waiting/total clk of CTA 0: producer %lld/%lld, mma %lld/%lld, "
+                    "split-B %lld/%lld, split-A %lld/%lld, epilogue %lld/%lld\n", M, N, K, n_tiles, (double)n_tiles / (2 * di.sms), dbg_buf[0], dbg_buf[1],
+                    dbg_buf[2], dbg_buf[3], dbg_buf[4], dbg_buf[5], dbg_buf[6], dbg_buf[7], dbg_buf[8], dbg_buf[9]);
+            fprintf(stderr, "[gemm persist dbg]   epilogue of CTA 0: staging free %lld clk, TMEM -> staging %lld, hand-over + store issue %lld\n", dbg_buf[10],
+                    dbg_buf[11], dbg_buf[12]);
+            dbg_buf[10] = dbg_buf[11] = dbg_buf[12] = 0;
+        }
+        return NF_OK;
+    }
     if (atmem) tc::gemm_tf32x3_kernel<true><<<grid, tc::THREADS, smem, st>>>(ma, mb, ma2, mah, p);
     else tc::gemm_tf32x3_kernel<false><<<grid, tc::THREADS, smem, st>>>(ma, mb, ma2, mah, p);
     NF_CUDA_OK(cudaGetLastError());
