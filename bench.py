@@ -43,7 +43,7 @@ UNIT = 'samples/s'
 FLOPS_PER_SAMPLE = K_LAYERS * (14 * DIM + 25) + 2 * DIM + 64        # 1764
 MUFU_PER_SAMPLE = 4 * K_LAYERS + 10                                 # 138
 BYTES_PER_SAMPLE = 4 * DIM                                          # 8
-NCU_TRAFFIC_BYTES = 8.673280e6
+NCU_TRAFFIC_BYTES = 8.620800e6
 NCU_TRAFFIC_SOURCE = 'ncu capture profiles/r02_ncu_elbo_pair_kernel.txt (not measured in this run)'
 
 
@@ -357,8 +357,8 @@ def run_ours(args):
             'frac_mufu_at_clock_under_load': (per_gpu * MUFU_PER_SAMPLE / (sms * 16 * f_load)) if f_load else None,
             # what the kernel issues, from the committed ncu capture (not measured by this run): the instruction-issue bound
             # sits below the MUFU bound and is the one the kernel runs into
-            'issue_model': {'lane_instructions_per_sample': 1040, 'issue_bound_samples_per_s': sms * 128 * f_max / 1040.0,
-                            'smsp_issue_active_pct': 51.9, 'source': 'profiles/r02_ncu_elbo_pair_kernel.txt'},
+            'issue_model': {'lane_instructions_per_sample': 1026, 'issue_bound_samples_per_s': sms * 128 * f_max / 1026.0,
+                            'smsp_issue_active_pct': 51.3, 'source': 'profiles/r02_ncu_elbo_pair_kernel.txt'},
             'kernel_ms': ms_per_step,
             'kernel_note': 'events bracket one launch per step: the objective kernel, whose last block adds the per-SM rows'
                            + ((' and does the NVLink peer exchange' if small_ar is not None else '; + NCCL all-reduce') if world > 1 else ''),
