@@ -445,7 +445,7 @@ struct FwdLayerP {
 };
 
 template <int KP>
-__global__ void __launch_bounds__(kRecThreads, 2)
+__global__ void __launch_bounds__(kRecThreads, kRecThreads <= 128 ? 2 : 1)
 rec_fwd_pk_kernel(const float* __restrict__ AT, long long ldn, int n_act, int K, const float* __restrict__ Mt,
                   const float* __restrict__ c, float epsv, float* __restrict__ TT, float* __restrict__ part_ld) {
     constexpr int W = kRecPkW;
@@ -536,7 +536,7 @@ struct BwdLayerP {
 };
 
 template <int KP>
-__global__ void __launch_bounds__(kRecThreads, 2)
+__global__ void __launch_bounds__(kRecThreads, kRecThreads <= 128 ? 2 : 1)
 rec_bwd_pk_kernel(const float* __restrict__ PT, const float* __restrict__ TT, long long ldn, int n_act, int K,
                   const float* __restrict__ Mrow, const float* __restrict__ c, float epsv, float* __restrict__ DT,
                   float* __restrict__ part_g /* [gridDim][2][KP] : g_b | g_c */) {
