@@ -281,19 +281,35 @@ def run_ours(args):
     host = [torch.randn(N_PER_GPU, DIM, dtype=torch.float32).pin_memory() for _ in range(4)]
     # warm-up: the first ~100 uploads after idle run at a fraction of the PCIe rate (the link trains up under load:
     # 540 -> 230 us per 8 MiB call over the first 100 calls, tools/e2e_stages.py with NF_SESSION_TIMING=1), so the host-API
-    # legs are warmed by call count like the device leg is by time
-    for i in range(max(3, args.warmup, 150)):
-        obj.value_and_grad(params, host[i % 4])
-    barrier()
-    t0 = time.perf_counter()
-    for i in range(args.steps):
-        F_e2e, g_e2e = obj.value_and_grad(params, host[i % 4])
-    torch.cuda.synchronize()
-    dt = time.perf_counter() - t0
-    tdt = torch.tensor([dt], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(tdt, op=dist.ReduceOp.MAX)
-    e2e_value = N_PER_GPU * world * args.steps / float(tdt.item())
+    # legs are warmed until 50 calls take the same time as the 50 before them (within 2 %)
+    prev = None
+    for chunk in range(40):                        # at most 2000 calls (~0.6 s); every rank runs the same count
+        t0 = time.perf_counter()
+        for i in range(50):
+            obj.value_and_grad(params, host[i % 4])
+        cur = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(cur, op=dist.ReduceOp.MAX)
+        cur = float(cur.item())
+        if chunk >= 2 and prev is not None and abs(cur - prev) <= 0.02 * prev:
+            break
+        prev = cur
+    # five timed regions of exactly K steps each (barrier + synchronize on both sides, max over ranks), the median is
+    # reported: a K = 20 region lasts 5 ms, and one host hiccup of a millisecond would otherwise decide the number
+    e2e_regions = []
+    for rep in range(5):
+        barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for i in range(args.steps):
+            F_e2e, g_e2e = obj.value_and_grad(params, host[i % 4])
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        tdt = torch.tensor([dt], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tdt, op=dist.ReduceOp.MAX)
+        e2e_regions.append(float(tdt.item()))
+    e2e_value = N_PER_GPU * world * args.steps / float(np.median(e2e_regions))
     # the same call with what a drop-in caller holds: a pageable NumPy array (what np.random.multivariate_normal returns,
     # get_data.py:100), converted to float32 inside the call; the draw itself is outside the timed region
     host_np = [h.numpy().astype(np.float64) for h in host[:2]]
@@ -415,7 +431,8 @@ def run_ours(args):
             'dtype': 'f32', 'data': 'synthetic', 'config': config_dict(world),
             'roofline': roofline,
             'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
-                    'F': float(F_e2e), 'input': 'pinned host float32 samples (best case of the host API)'},
+                    'F': float(F_e2e), 'input': 'pinned host float32 samples (best case of the host API)',
+                    'regions_ms': [round(x * 1e3, 3) for x in e2e_regions], 'stat': 'median of 5 timed regions of `steps` calls each'},
             'e2e_pageable': {'value': e2e_pageable, 'unit': UNIT, 'steps': n_pg,
                              'input': 'pageable float64 NumPy array, as np.random.multivariate_normal returns it (get_data.py:100); '
                                       'the RNG draw itself is not timed'},
