@@ -151,6 +151,18 @@ int nf_session_elbo_host_f32(nf_session* s, const float* eps_host, int64_t N, co
 int nf_session_elbo_host_f64(nf_session* s, const double* eps_host, int64_t N, const double* layer_consts_host,
                              int target_id, const double* target_params_host, int n_target_params,
                              double log_eps, int backward, double* out_host);
+/* The literal objective(params, t) / gradient(params, t) of get_data.py:97-115 (`variational_objective` and
+ * `grad(variational_objective)`) in one call: `params` is the reference's float64 parameter vector [W | U | B]
+ * (get_data.py:74-78), `eps_host` the N x D draws of :100-101 in host memory.  Internally nf_script_constants_host,
+ * nf_session_elbo_host_* and nf_script_chain_host.  F_parts[3] = sums over the samples of (F, log q_K, log p)
+ * (divide by N for the means of :113 and :80-95); grad[2KD+K] = d(mean F)/d params (float64), untouched when backward = 0.
+ * semantics: 0 = script (get_data.py:106-108), 1 = package (flows.py:37-39). */
+int nf_session_objective_host_f32(nf_session* s, const float* eps_host, int64_t N, const double* params, int semantics,
+                                  int target_id, const float* target_params_host, int n_target_params, float log_eps,
+                                  int backward, double* F_parts, double* grad);
+int nf_session_objective_host_f64(nf_session* s, const double* eps_host, int64_t N, const double* params, int semantics,
+                                  int target_id, const double* target_params_host, int n_target_params, double log_eps,
+                                  int backward, double* F_parts, double* grad);
 
 /* ---------------------------------------------------------------------------
  * The whole optimisation loop of the script path on the device: get_data.py:119-142 `optimise`

@@ -18,6 +18,13 @@ int nf_session_elbo_host_f64(nf_session* s, const double* eps_host, int64_t N, c
                                          target_params_host, n_target_params, log_eps, backward, out_host);
 }
 
+int nf_session_objective_host_f64(nf_session* s, const double* eps_host, int64_t N, const double* params, int semantics, int target_id,
+                                  const double* target_params_host, int n_target_params, double log_eps, int backward, double* F_parts,
+                                  double* grad) {
+    return nf::session_objective_host<double>(reinterpret_cast<nf::Session*>(s), eps_host, N, params, semantics, target_id,
+                                              target_params_host, n_target_params, log_eps, backward, F_parts, grad);
+}
+
 int nf_script_train_f64(const double* eps_all, int64_t n_iters, int64_t N, int D, int K, double* params, int target_id,
                         const double* target_params, int n_target_params, double log_eps, int optimizer, double step_size, double h1,
                         double h2, double h3, int64_t first_iter, int resume, int64_t eps_stride, double* opt_state, double* trace_F,

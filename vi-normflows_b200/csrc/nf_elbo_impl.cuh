@@ -960,6 +960,31 @@ static int session_elbo_host(Session* S, const T* eps_host, int64_t N, const T* 
     return NF_OK;
 }
 
+// objective(params, t) / gradient(params, t) of get_data.py:97-115 in ONE call with host buffers in and out: the reference's
+// parameter vector [W | U | B] (float64) -> kernel constants (nf_script_constants_host), the session evaluation above,
+// and the chain rule back to d(mean F)/d[W | U | B] (nf_script_chain_host).  What the Python face does in three calls.
+template <typename T>
+static int session_objective_host(Session* S, const T* eps_host, int64_t N, const double* params, int semantics, int target_id,
+                                  const T* tp_host, int ntp, T epsv, int backward, double* F_parts, double* grad) {
+    if (!S || !params || !F_parts || (backward && !grad) || N < 1) return NF_ERR_INVALID;
+    const int D = S->D, K = S->K;
+    const int nlc = 2 * K * D + 2 * K;
+    static thread_local std::vector<double> lc64, g64;
+    static thread_local std::vector<T> lc, out;
+    lc64.resize(nlc); g64.resize(nlc); lc.resize(nlc); out.resize(3 + nlc);
+    int rc = nf_script_constants_host(params, K, D, semantics, lc64.data());
+    if (rc != NF_OK) return rc;
+    for (int i = 0; i < nlc; ++i) lc[i] = (T)lc64[i];
+    rc = session_elbo_host<T>(S, eps_host, N, lc.data(), target_id, tp_host, ntp, epsv, backward, out.data());
+    if (rc != NF_OK) return rc;
+    for (int i = 0; i < 3; ++i) F_parts[i] = (double)out[i];
+    if (backward) {
+        for (int i = 0; i < nlc; ++i) g64[i] = (double)out[3 + i];
+        rc = nf_script_chain_host(params, g64.data(), K, D, semantics, 1.0 / (double)N, grad);
+    }
+    return rc;
+}
+
 // ---- whole optimisation loop on the device (get_data.py:119-142 `optimise`, experimentation.py:99-109) ----
 // One tiny kernel per iteration applies the previous iteration's update (chain rule from the kernel's
 // (g_w, g_s, g_b, g_c) back to (dW, dU, dB), then sgd / rmsprop / adam with autograd 1.3's update rules) and

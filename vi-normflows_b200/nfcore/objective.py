@@ -201,6 +201,42 @@ class SharedFlowObjective:
         self.launches += 2
         return out.astype(np.float64), N, p64
 
+    def _host_objective(self, params, z0, backward):
+        """nf_session_objective_host_*: parameters in, (F parts, gradient) out -- one library call per objective call."""
+        lib = _lib.load()
+        if isinstance(z0, torch.Tensor):
+            if z0.dtype != self.dtype or not z0.is_contiguous():
+                z0 = z0.to(self.dtype).contiguous()
+            ptr, shape = z0.data_ptr(), tuple(z0.shape)
+        else:
+            z0 = np.ascontiguousarray(z0, dtype=self.np_dtype)
+            ptr, shape = z0.ctypes.data, z0.shape
+        if len(shape) != 2 or shape[1] != self.D:
+            raise NFError('z0 must have shape (N, %d), got %r' % (self.D, shape))
+        N = shape[0]
+        p = np.ascontiguousarray(params, dtype=np.float64).ravel()
+        if p.size != 2 * self.K * self.D + self.K:
+            raise NFError('params must have 2*K*D + K = %d entries, got %d' % (2 * self.K * self.D + self.K, p.size))
+        if self._session is None or N > self._session_cap:
+            if self._session is not None:
+                lib.nf_session_destroy(self._session)
+                self._session = None
+            h = ctypes.c_void_p()
+            with torch.cuda.device(self.device):
+                _lib.check(lib.nf_session_create(ctypes.byref(h), max(int(N), 1), self.D, self.K, self.np_dtype.itemsize))
+            self._session, self._session_cap = h, max(int(N), 1)
+        parts = np.empty(3, dtype=np.float64)
+        grad = np.empty(p.size, dtype=np.float64) if backward else None
+        tp = self._tparams_host
+        f32 = self.np_dtype == np.float32
+        fn = lib.nf_session_objective_host_f32 if f32 else lib.nf_session_objective_host_f64
+        _lib.check(fn(self._session, ptr, N, p.ctypes.data, sem.SEMANTICS.index(self.semantics), ops.TARGET_IDS[self.target_name],
+                      tp.ctypes.data if tp is not None else None, 0 if tp is None else tp.size,
+                      (ctypes.c_float if f32 else ctypes.c_double)(self.log_eps), 1 if backward else 0, parts.ctypes.data,
+                      grad.ctypes.data if backward else None))
+        self.launches += 2
+        return parts, N, grad
+
     def _is_host(self, z0):
         return self.group is None and not (isinstance(z0, torch.Tensor) and z0.is_cuda)
 
@@ -290,6 +326,9 @@ class SharedFlowObjective:
 
     def value_and_grad(self, params, z0):
         if self._is_host(z0):
+            if np.shape(z0)[0] > 0:
+                parts, n, grad = self._host_objective(params, z0, True)
+                return parts[0] / n, grad
             res, n, p64 = self._host_eval(params, z0, True)
         else:
             eps_dev = self.stage_samples(z0)
