@@ -163,6 +163,12 @@ int nf_session_objective_host_f32(nf_session* s, const float* eps_host, int64_t 
 int nf_session_objective_host_f64(nf_session* s, const double* eps_host, int64_t N, const double* params, int semantics,
                                   int target_id, const double* target_params_host, int n_target_params, double log_eps,
                                   int backward, double* F_parts, double* grad);
+/* The same objective + gradient with the draw of get_data.py:100-101 made inside the kernel (the library's counter-based
+ * stream for (seed, step), see nf_planar_elbo_fwd_bwd_rng_f32): no sample buffer at all.  float32 session, D <= 2,
+ * N large enough for the kernel that draws (NF_ERR_UNSUPPORTED otherwise). */
+int nf_session_objective_rng_f32(nf_session* s, uint64_t seed, uint64_t step, int64_t N, const double* params, int semantics,
+                                 int target_id, const float* target_params_host, int n_target_params, float log_eps,
+                                 double* F_parts, double* grad);
 
 /* ---------------------------------------------------------------------------
  * The whole optimisation loop of the script path on the device: get_data.py:119-142 `optimise`

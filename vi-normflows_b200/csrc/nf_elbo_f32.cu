@@ -104,6 +104,13 @@ int nf_session_objective_host_f32(nf_session* s, const float* eps_host, int64_t 
                                               target_params_host, n_target_params, log_eps, backward, F_parts, grad);
 }
 
+int nf_session_objective_rng_f32(nf_session* s, uint64_t seed, uint64_t step, int64_t N, const double* params, int semantics,
+                                 int target_id, const float* target_params_host, int n_target_params, float log_eps, double* F_parts,
+                                 double* grad) {
+    return nf::session_objective_rng(reinterpret_cast<nf::Session*>(s), seed, step, N, params, semantics, target_id, target_params_host,
+                                     n_target_params, log_eps, F_parts, grad);
+}
+
 int nf_script_train_f32(const float* eps_all, int64_t n_iters, int64_t N, int D, int K, float* params, int target_id,
                         const float* target_params, int n_target_params, float log_eps, int optimizer, float step_size, float h1,
                         float h2, float h3, int64_t first_iter, int resume, int64_t eps_stride, float* opt_state, float* trace_F,

@@ -960,6 +960,44 @@ static int session_elbo_host(Session* S, const T* eps_host, int64_t N, const T* 
     return NF_OK;
 }
 
+// The same with the samples drawn inside the kernel (nf_philox.cuh): nothing but the K x D constants goes up, nothing but
+// F and the gradient comes back.  float32, D <= 2, and N large enough for the packed-pair kernel (the one that draws).
+static int session_objective_rng(Session* S, uint64_t seed, uint64_t step, int64_t N, const double* params, int semantics,
+                                 int target_id, const float* tp_host, int ntp, float epsv, double* F_parts, double* grad) {
+    if (!S || S->elem != 4 || !params || !F_parts || !grad || N < 1) return NF_ERR_INVALID;
+    if (ntp < 0 || (size_t)ntp > S->tp_cap || (ntp > 0 && !tp_host)) return NF_ERR_INVALID;
+    const int D = S->D, K = S->K;
+    if (D != 1 && D != 2) return NF_ERR_UNSUPPORTED;
+    NF_CUDA_OK(cudaSetDevice(S->dev));
+    const int nlc = 2 * K * D + 2 * K;
+    static thread_local std::vector<double> lc64, g64;
+    lc64.resize(nlc); g64.resize(nlc);
+    int rc = nf_script_constants_host(params, K, D, semantics, lc64.data());
+    if (rc != NF_OK) return rc;
+    float* lc_pin = reinterpret_cast<float*>(S->lc_pin);
+    for (int i = 0; i < nlc; ++i) lc_pin[i] = (float)lc64[i];
+    for (int i = 0; i < ntp; ++i) lc_pin[nlc + i] = tp_host[i];
+    float* lc = reinterpret_cast<float*>(S->lc_dev);
+    float* tp = reinterpret_cast<float*>(S->tp_dev);
+    NF_CUDA_OK(cudaMemcpyAsync(lc, lc_pin, (size_t)nlc * sizeof(float), cudaMemcpyHostToDevice, S->s_comp));
+    if (ntp > 0) NF_CUDA_OK(cudaMemcpyAsync(tp, lc_pin + nlc, (size_t)ntp * sizeof(float), cudaMemcpyHostToDevice, S->s_comp));
+    const float *w = lc, *s = lc + K * D, *b = lc + 2 * K * D, *c = lc + 2 * K * D + K;
+    rc = elbo_validate<float>(lc /* stands in for the absent sample pointer */, N, D, K, w, s, b, c, target_id, ntp > 0 ? tp : nullptr, ntp);
+    if (rc != NF_OK) return rc;
+    float* out = reinterpret_cast<float*>(S->out_dev);
+    const RngDesc rng = {seed, step};
+    rc = elbo_fused<float>(true, nullptr, N, D, K, w, s, b, c, target_id, ntp > 0 ? tp : nullptr, ntp, epsv, out, out + 3, out + 3 + K * D,
+                           out + 3 + 2 * K * D, out + 3 + 2 * K * D + K, reinterpret_cast<float*>(S->ws_dev), S->s_comp, nullptr, nullptr, &rng,
+                           S->ws_chunk_bytes * kSessionMaxChunks);
+    if (rc != NF_OK) return rc;
+    NF_CUDA_OK(cudaMemcpyAsync(S->out_pin, out, (size_t)S->n_out * sizeof(float), cudaMemcpyDeviceToHost, S->s_comp));
+    NF_CUDA_OK(cudaStreamSynchronize(S->s_comp));
+    const float* op = reinterpret_cast<const float*>(S->out_pin);
+    for (int i = 0; i < 3; ++i) F_parts[i] = (double)op[i];
+    for (int i = 0; i < nlc; ++i) g64[i] = (double)op[3 + i];
+    return nf_script_chain_host(params, g64.data(), K, D, semantics, 1.0 / (double)N, grad);
+}
+
 // objective(params, t) / gradient(params, t) of get_data.py:97-115 in ONE call with host buffers in and out: the reference's
 // parameter vector [W | U | B] (float64) -> kernel constants (nf_script_constants_host), the session evaluation above,
 // and the chain rule back to d(mean F)/d[W | U | B] (nf_script_chain_host).  What the Python face does in three calls.

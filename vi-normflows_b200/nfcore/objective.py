@@ -343,20 +343,26 @@ class SharedFlowObjective:
         gradient comes back.  float32, D <= 2, single process."""
         if self.group is not None or self.dtype != torch.float32:
             raise NFError('value_and_grad_rng: float32, single process')
-        K, D = self.K, self.D
-        lc64, p64 = self._constants(params)
-        self._lc_host.numpy()[:] = lc64
-        self._lc.copy_(self._lc_host, non_blocking=True)
-        lc, r = self._lc, self._res
-        out = (r[:3], r[3:3 + K * D].view(K, D), r[3 + K * D:3 + 2 * K * D].view(K, D), r[3 + 2 * K * D:3 + 2 * K * D + K],
-               r[3 + 2 * K * D + K:self.n_res])
-        ops.planar_elbo_rng(seed, step, int(num_samples), lc[:K * D].view(K, D), lc[K * D:2 * K * D].view(K, D), lc[2 * K * D:2 * K * D + K],
-                            lc[2 * K * D + K:], self.target_name, self.tparams, self.log_eps, out)
+        lib = _lib.load()
+        N = int(num_samples)
+        p = np.ascontiguousarray(params, dtype=np.float64).ravel()
+        if p.size != 2 * self.K * self.D + self.K:
+            raise NFError('params must have 2*K*D + K = %d entries, got %d' % (2 * self.K * self.D + self.K, p.size))
+        if self._session is None:
+            h = ctypes.c_void_p()
+            with torch.cuda.device(self.device):
+                _lib.check(lib.nf_session_create(ctypes.byref(h), 1, self.D, self.K, 4))
+            self._session, self._session_cap = h, 1
+        parts = np.empty(3, dtype=np.float64)
+        grad = np.empty(p.size, dtype=np.float64)
+        tp = self._tparams_host
+        # nf_session_objective_rng_f32: constants up, one launch, F and the gradient back -- one library call
+        _lib.check(lib.nf_session_objective_rng_f32(self._session, int(seed), int(step), N, p.ctypes.data,
+                                                    sem.SEMANTICS.index(self.semantics), ops.TARGET_IDS[self.target_name],
+                                                    tp.ctypes.data if tp is not None else None, 0 if tp is None else tp.size,
+                                                    ctypes.c_float(self.log_eps), parts.ctypes.data, grad.ctypes.data))
         self.launches += 1
-        self._res_host.copy_(self._res, non_blocking=True)
-        torch.cuda.current_stream(self.device).synchronize()
-        res = self._res_host.numpy().astype(np.float64)[:self.n_res]
-        return res[0] / num_samples, self._chain(p64, res, num_samples)
+        return parts[0] / N, grad
 
     def value(self, params, z0):
         if self._is_host(z0):
