@@ -33,7 +33,8 @@ typedef enum {
     NF_ERR_WORKSPACE = -3,    /* workspace_bytes smaller than nf_planar_elbo_workspace_bytes() */
     NF_ERR_CUDA = -4,         /* a CUDA runtime call failed; see nf_last_cuda_error() */
     NF_ERR_NO_DEVICE = -5,    /* no CUDA device / not an sm_100 device */
-    NF_ERR_SCRATCH_LIMIT = -6 /* nf_planar_elbo_fwd_bwd_noalloc_f32: problem needs more than NF_NOALLOC_SCRATCH_BYTES */
+    NF_ERR_SCRATCH_LIMIT = -6, /* nf_planar_elbo_fwd_bwd_noalloc_f32: problem needs more than NF_NOALLOC_SCRATCH_BYTES */
+    NF_ERR_PEER = -7          /* multi-GPU exchange: a rank did not arrive within the time limit; the sums are not valid */
 } nf_status;
 
 /* Target densities exp(-U(z)) the free energy is taken against.  The objective
@@ -166,6 +167,14 @@ int nf_session_objective_host_f64(nf_session* s, const double* eps_host, int64_t
 /* The same objective + gradient with the draw of get_data.py:100-101 made inside the kernel (the library's counter-based
  * stream for (seed, step), see nf_planar_elbo_fwd_bwd_rng_f32): no sample buffer at all.  float32 session, D <= 2,
  * N large enough for the kernel that draws (NF_ERR_UNSUPPORTED otherwise). */
+/* nf_session_objective_host_f32 over this rank's shard of the draws, summed over the `world` GPUs of one box by the
+ * peer exchange of nf_allreduce_small_counted_f32 (same buffers, same seq discipline: every rank calls with the same
+ * seq > the previous one).  F_parts are global sums, grad = d(mean over ALL samples of F)/d params, *n_global the
+ * global sample count.  NF_ERR_PEER when a rank did not arrive. */
+int nf_session_objective_host_exchange_f32(nf_session* s, const float* eps_host, int64_t N_local, const double* params,
+                                           int semantics, int target_id, const float* target_params_host, int n_target_params,
+                                           float log_eps, void* const* peer_buffers, int world, int rank, uint64_t seq,
+                                           double* F_parts, double* grad, int64_t* n_global);
 int nf_session_objective_rng_f32(nf_session* s, uint64_t seed, uint64_t step, int64_t N, const double* params, int semantics,
                                  int target_id, const float* target_params_host, int n_target_params, float log_eps,
                                  double* F_parts, double* grad);

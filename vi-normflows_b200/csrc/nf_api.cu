@@ -16,6 +16,7 @@ const char* nf_status_string(int status) {
         case NF_ERR_CUDA: return "CUDA runtime error (see nf_last_cuda_error)";
         case NF_ERR_NO_DEVICE: return "no sm_100 CUDA device is current";
         case NF_ERR_SCRATCH_LIMIT: return "problem needs more scratch than the built-in no-allocation buffer holds (NF_NOALLOC_SCRATCH_BYTES)";
+        case NF_ERR_PEER: return "multi-GPU exchange: a rank did not arrive within the time limit";
         default: return "unknown status";
     }
 }

@@ -104,6 +104,17 @@ int nf_session_objective_host_f32(nf_session* s, const float* eps_host, int64_t 
                                               target_params_host, n_target_params, log_eps, backward, F_parts, grad);
 }
 
+int nf_session_objective_host_exchange_f32(nf_session* s, const float* eps_host, int64_t N_local, const double* params, int semantics,
+                                           int target_id, const float* target_params_host, int n_target_params, float log_eps,
+                                           void* const* peer_buffers, int world, int rank, uint64_t seq, double* F_parts,
+                                           double* grad, int64_t* n_global) {
+    nf::pr::ArDesc ar;
+    const int rc = nf::make_ar_desc(&ar, peer_buffers, world, rank, seq, N_local, nullptr);
+    if (rc != NF_OK) return rc;
+    return nf::session_objective_host<float>(reinterpret_cast<nf::Session*>(s), eps_host, N_local, params, semantics, target_id,
+                                             target_params_host, n_target_params, log_eps, 1, F_parts, grad, &ar, n_global);
+}
+
 int nf_session_objective_rng_f32(nf_session* s, uint64_t seed, uint64_t step, int64_t N, const double* params, int semantics,
                                  int target_id, const float* target_params_host, int n_target_params, float log_eps, double* F_parts,
                                  double* grad) {

@@ -852,13 +852,13 @@ static inline int session_create(Session** out, int64_t max_samples, int D, int 
     ok(cudaMalloc(&S->eps_dev, (size_t)max_samples * D * S->elem));
     ok(cudaMalloc(&S->lc_dev, (size_t)(2 * K * D + 2 * K) * S->elem));
     ok(cudaMalloc(&S->tp_dev, S->tp_cap * S->elem));
-    ok(cudaMalloc(&S->out_dev, (size_t)S->n_out * S->elem));
+    ok(cudaMalloc(&S->out_dev, (size_t)(S->n_out + 4) * S->elem));      // + (n_hi, n_lo, status) of the multi-GPU exchange
     ok(cudaMalloc(&S->ws_dev, S->ws_chunk_bytes * kSessionMaxChunks));
     S->gram_layout_n = max_samples < kSessionChunkSamples ? max_samples : kSessionChunkSamples;
     if (elem_size == 4 && gram_applicable(1 << 30, D, K, -1, 0))        // shape supported (the per-call cost model decides later)
         ok(cudaMalloc(&S->gram_ws, gram_workspace_bytes(S->gram_layout_n, D, K)));
     ok(cudaMallocHost(&S->lc_pin, (size_t)(2 * K * D + 2 * K + S->tp_cap) * S->elem));
-    ok(cudaMallocHost(&S->out_pin, (size_t)S->n_out * S->elem));
+    ok(cudaMallocHost(&S->out_pin, (size_t)(S->n_out + 4) * S->elem));
     if (e != cudaSuccess) { nf_set_last_cuda_error(e); session_free(S); return NF_ERR_CUDA; }
     *out = S;
     return NF_OK;
@@ -866,7 +866,9 @@ static inline int session_create(Session** out, int64_t max_samples, int D, int 
 
 template <typename T>
 static int session_elbo_host(Session* S, const T* eps_host, int64_t N, const T* lc_host, int target_id,
-                             const T* tp_host, int ntp, T epsv, int backward, T* out_host) {
+                             const T* tp_host, int ntp, T epsv, int backward, T* out_host,
+                             const pr::ArDesc* ar = nullptr /* float32: sum the result over the ranks of one box (nf_allreduce.cu) */,
+                             T* tail_host = nullptr /* with ar: (n_hi, n_lo, status) as nf_allreduce_small_counted_f32 leaves them */) {
     if (!S || S->elem != sizeof(T) || N < 0 || N > S->cap || !lc_host || !out_host || (N > 0 && !eps_host)) return NF_ERR_INVALID;
     if (ntp < 0 || (size_t)ntp > S->tp_cap || (ntp > 0 && !tp_host)) return NF_ERR_INVALID;
     static const bool timing = getenv("NF_SESSION_TIMING") != nullptr;      // debug aid: host-side time stamps of this call
@@ -910,10 +912,17 @@ static int session_elbo_host(Session* S, const T* eps_host, int64_t N, const T* 
             rc = gram_end(backward != 0, S->gram_layout_n, D, K, w, s, out, out + 3, out + 3 + K * D, out + 3 + 2 * K * D,
                           out + 3 + 2 * K * D + K, S->gram_ws, S->s_comp);
             if (rc != NF_OK) return rc;
-            NF_CUDA_OK(cudaMemcpyAsync(S->out_pin, out, (size_t)S->n_out * sizeof(T), cudaMemcpyDeviceToHost, S->s_comp));
+            if (ar) {
+                pr::ArDesc a2 = *ar;
+                a2.xout = reinterpret_cast<float*>(out) + S->n_out;
+                rc = launch_allreduce_small(a2, reinterpret_cast<float*>(out), reinterpret_cast<float*>(out), S->n_out, nullptr, S->s_comp);
+                if (rc != NF_OK) return rc;
+            }
+            NF_CUDA_OK(cudaMemcpyAsync(S->out_pin, out, (size_t)(S->n_out + (ar ? 3 : 0)) * sizeof(T), cudaMemcpyDeviceToHost, S->s_comp));
             NF_CUDA_OK(cudaStreamSynchronize(S->s_comp));
             const T* op = reinterpret_cast<const T*>(S->out_pin);
             for (int j = 0; j < S->n_out; ++j) out_host[j] = op[j];
+            if (ar && tail_host) for (int j = 0; j < 3; ++j) tail_host[j] = op[S->n_out + j];
             return NF_OK;
         }
     }
@@ -949,12 +958,21 @@ static int session_elbo_host(Session* S, const T* eps_host, int64_t N, const T* 
     rc = elbo_finish<T>(backward != 0, partials, rows, D, K, out, out + 3, out + 3 + K * D, out + 3 + 2 * K * D,
                         out + 3 + 2 * K * D + K, S->s_comp);
     if (rc != NF_OK) return rc;
-    NF_CUDA_OK(cudaMemcpyAsync(S->out_pin, out, (size_t)S->n_out * sizeof(T), cudaMemcpyDeviceToHost, S->s_comp));
+    if constexpr (sizeof(T) == 4) {
+        if (ar) {
+            pr::ArDesc a2 = *ar;
+            a2.xout = reinterpret_cast<float*>(out) + S->n_out;
+            rc = launch_allreduce_small(a2, reinterpret_cast<float*>(out), reinterpret_cast<float*>(out), S->n_out, nullptr, S->s_comp);
+            if (rc != NF_OK) return rc;
+        }
+    }
+    NF_CUDA_OK(cudaMemcpyAsync(S->out_pin, out, (size_t)(S->n_out + (ar ? 3 : 0)) * sizeof(T), cudaMemcpyDeviceToHost, S->s_comp));
     if (timing) tq[2] = now();
     NF_CUDA_OK(cudaStreamSynchronize(S->s_comp));
     if (timing) tq[3] = now();
     const T* op = reinterpret_cast<const T*>(S->out_pin);
     for (int i = 0; i < S->n_out; ++i) out_host[i] = op[i];
+    if (ar && tail_host) for (int i = 0; i < 3; ++i) tail_host[i] = op[S->n_out + i];
     if (timing) fprintf(stderr, "[nf session] N=%lld enqueue chunks %.1f us | finish+D2H enqueue %.1f | wait %.1f | total %.1f\n", (long long)N,
                         tq[1] - tq[0], tq[2] - tq[1], tq[3] - tq[2], now() - tq[0]);
     return NF_OK;
@@ -1003,8 +1021,10 @@ static int session_objective_rng(Session* S, uint64_t seed, uint64_t step, int64
 // and the chain rule back to d(mean F)/d[W | U | B] (nf_script_chain_host).  What the Python face does in three calls.
 template <typename T>
 static int session_objective_host(Session* S, const T* eps_host, int64_t N, const double* params, int semantics, int target_id,
-                                  const T* tp_host, int ntp, T epsv, int backward, double* F_parts, double* grad) {
+                                  const T* tp_host, int ntp, T epsv, int backward, double* F_parts, double* grad,
+                                  const pr::ArDesc* ar = nullptr, int64_t* n_global = nullptr) {
     if (!S || !params || !F_parts || (backward && !grad) || N < 1) return NF_ERR_INVALID;
+    if (ar && (sizeof(T) != 4 || S->n_out > pr::kArStride - 2)) return NF_ERR_UNSUPPORTED;
     const int D = S->D, K = S->K;
     const int nlc = 2 * K * D + 2 * K;
     static thread_local std::vector<double> lc64, g64;
@@ -1013,12 +1033,19 @@ static int session_objective_host(Session* S, const T* eps_host, int64_t N, cons
     int rc = nf_script_constants_host(params, K, D, semantics, lc64.data());
     if (rc != NF_OK) return rc;
     for (int i = 0; i < nlc; ++i) lc[i] = (T)lc64[i];
-    rc = session_elbo_host<T>(S, eps_host, N, lc.data(), target_id, tp_host, ntp, epsv, backward, out.data());
+    T tail[3] = {0, 0, 0};
+    rc = session_elbo_host<T>(S, eps_host, N, lc.data(), target_id, tp_host, ntp, epsv, backward, out.data(), ar, tail);
     if (rc != NF_OK) return rc;
+    int64_t ng = N;
+    if (ar) {
+        if ((double)tail[2] != 0.0) return NF_ERR_PEER;       // a rank did not arrive: the sums are not valid
+        ng = (int64_t)llround((double)tail[0]) * (1 << 20) + (int64_t)llround((double)tail[1]);
+    }
+    if (n_global) *n_global = ng;
     for (int i = 0; i < 3; ++i) F_parts[i] = (double)out[i];
     if (backward) {
         for (int i = 0; i < nlc; ++i) g64[i] = (double)out[3 + i];
-        rc = nf_script_chain_host(params, g64.data(), K, D, semantics, 1.0 / (double)N, grad);
+        rc = nf_script_chain_host(params, g64.data(), K, D, semantics, 1.0 / (double)ng, grad);
     }
     return rc;
 }

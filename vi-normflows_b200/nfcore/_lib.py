@@ -53,6 +53,8 @@ PROTOTYPES = {
     'nf_session_elbo_host_f64': (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int, c_void_p, c_int, c_double, c_int, c_void_p]),
     'nf_session_objective_host_f32': (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int, c_int, c_void_p, c_int, c_float, c_int, c_void_p, c_void_p]),
     'nf_session_objective_host_f64': (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int, c_int, c_void_p, c_int, c_double, c_int, c_void_p, c_void_p]),
+    'nf_session_objective_host_exchange_f32': (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int, c_int, c_void_p, c_int, c_float,
+                                               ctypes.POINTER(c_void_p), c_int, c_int, ctypes.c_uint64, c_void_p, c_void_p, c_void_p]),
     'nf_session_objective_rng_f32': (c_int, [c_void_p, ctypes.c_uint64, ctypes.c_uint64, c_int64, c_void_p, c_int, c_int, c_void_p, c_int, c_float, c_void_p, c_void_p]),
     'nf_planar_flow_f32': (c_int, [c_void_p] * 4 + [c_int64, c_int, c_int, c_int, c_void_p, c_void_p]),
     'nf_planar_flow_f64': (c_int, [c_void_p] * 4 + [c_int64, c_int, c_int, c_int, c_void_p, c_void_p]),

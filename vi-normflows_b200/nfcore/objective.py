@@ -201,8 +201,10 @@ class SharedFlowObjective:
         self.launches += 2
         return out.astype(np.float64), N, p64
 
-    def _host_objective(self, params, z0, backward):
-        """nf_session_objective_host_*: parameters in, (F parts, gradient) out -- one library call per objective call."""
+    def _host_objective(self, params, z0, backward, exchange=False):
+        """nf_session_objective_host_*: parameters in, (F parts, gradient) out -- one library call per objective call.
+        exchange: this rank's shard; the sums go over the ranks of the box (nf_session_objective_host_exchange_f32) and the
+        returned count is the global one."""
         lib = _lib.load()
         if isinstance(z0, torch.Tensor):
             if z0.dtype != self.dtype or not z0.is_contiguous():
@@ -229,6 +231,15 @@ class SharedFlowObjective:
         grad = np.empty(p.size, dtype=np.float64) if backward else None
         tp = self._tparams_host
         f32 = self.np_dtype == np.float32
+        if exchange:
+            ar = self._small_ar
+            ng = ctypes.c_int64(0)
+            _lib.check(lib.nf_session_objective_host_exchange_f32(
+                self._session, ptr, N, p.ctypes.data, sem.SEMANTICS.index(self.semantics), ops.TARGET_IDS[self.target_name],
+                tp.ctypes.data if tp is not None else None, 0 if tp is None else tp.size, ctypes.c_float(self.log_eps),
+                ar._ptrs, ar.world, ar.rank, ctypes.c_uint64(ar.next_seq()), parts.ctypes.data, grad.ctypes.data, ctypes.byref(ng)))
+            self.launches += 3
+            return parts, int(ng.value), grad
         fn = lib.nf_session_objective_host_f32 if f32 else lib.nf_session_objective_host_f64
         _lib.check(fn(self._session, ptr, N, p.ctypes.data, sem.SEMANTICS.index(self.semantics), ops.TARGET_IDS[self.target_name],
                       tp.ctypes.data if tp is not None else None, 0 if tp is None else tp.size,
@@ -325,6 +336,12 @@ class SharedFlowObjective:
         return res[:self.n_res], n_global
 
     def value_and_grad(self, params, z0):
+        if (self.group is not None and self._small_ar is not None and self.np_dtype == np.float32
+                and not (isinstance(z0, torch.Tensor) and z0.is_cuda) and np.shape(z0)[0] > 0
+                and 3 + self.n_lc <= self._small_ar.max_count):
+            # sharded, host samples: chunked upload + kernels + peer exchange + chain rule in one library call
+            parts, n, grad = self._host_objective(params, z0, True, exchange=True)
+            return parts[0] / n, grad
         if self._is_host(z0):
             if np.shape(z0)[0] > 0:
                 parts, n, grad = self._host_objective(params, z0, True)
