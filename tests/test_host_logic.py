@@ -66,6 +66,11 @@ def test_library_loads_and_exports_header_symbols():
     from nfcore import _lib
     assert set(_lib.PROTOTYPES) == set(declared)
     assert lib.nf_built_for_sm() == 100
+    # every status of the header has its own explanation
+    lib.nf_status_string.restype = ctypes.c_char_p
+    texts = [lib.nf_status_string(c) for c in range(0, -8, -1)]
+    assert len(set(texts)) == 8 and b'unknown' not in b''.join(texts) and lib.nf_status_string(-99) == b'unknown status'
+    assert b'did not arrive' in lib.nf_status_string(-7)            # NF_ERR_PEER
 
 
 def test_no_cpu_fallback():
